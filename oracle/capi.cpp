@@ -1,0 +1,181 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  C entry points for ctypes (tests/,
+// smoke(), bench.py cpu_baseline / --impl reference).  Never linked into the
+// product library.
+#include "oracle.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+
+using namespace orc;
+
+extern "C" {
+
+// ---------------- ORB ----------------
+void* orc_orb_create(int nfeatures, float scale, int nlevels, int iniTh, int minTh)
+{
+    return new OrbExtractor(nfeatures, scale, nlevels, iniTh, minTh);
+}
+void orc_orb_destroy(void* h) { delete (OrbExtractor*)h; }
+
+// returns the number of keypoints (may exceed cap; only cap are written)
+int orc_orb_extract(void* h, const uint8_t* img, int w, int ht, int stride, KeyPoint* kps, uint8_t* desc, int cap)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    std::vector<KeyPoint> k;
+    std::vector<uint8_t> d;
+    e->extract(img, w, ht, stride, k, d);
+    int n = std::min((int)k.size(), cap);
+    if (n > 0) {
+        memcpy(kps, k.data(), (size_t)n * sizeof(KeyPoint));
+        memcpy(desc, d.data(), (size_t)n * 32);
+    }
+    return (int)k.size();
+}
+void orc_orb_tables(void* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* quota, int* umax)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    for (int i = 0; i < e->nlevels; i++) {
+        scale[i] = e->mvScaleFactor[i];
+        inv_scale[i] = e->mvInvScaleFactor[i];
+        sigma2[i] = e->mvLevelSigma2[i];
+        inv_sigma2[i] = e->mvInvLevelSigma2[i];
+        quota[i] = e->mnFeaturesPerLevel[i];
+    }
+    for (int i = 0; i < 16; i++)
+        umax[i] = e->umax[i];
+}
+void orc_orb_level_size(void* h, int level, int* w, int* ht)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    *w = e->levels[level].w;
+    *ht = e->levels[level].h;
+}
+// padded level image ((w+38) x (h+38)) of the last extract()
+void orc_orb_level_padded(void* h, int level, uint8_t* dst)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    memcpy(dst, e->levels[level].padded.data(), e->levels[level].padded.size());
+}
+int orc_orb_level_blurred(void* h, int level, uint8_t* dst)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    if (e->levels[level].blurred.empty())
+        return 0;
+    memcpy(dst, e->levels[level].blurred.data(), e->levels[level].blurred.size());
+    return 1;
+}
+int orc_orb_level_candidates(void* h, int level, KeyPoint* out, int cap)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    const std::vector<KeyPoint>& c = e->levels[level].candidates;
+    int n = std::min((int)c.size(), cap);
+    if (n > 0)
+        memcpy(out, c.data(), (size_t)n * sizeof(KeyPoint));
+    return (int)c.size();
+}
+int orc_orb_level_keypoints(void* h, int level, KeyPoint* out, int cap)
+{
+    OrbExtractor* e = (OrbExtractor*)h;
+    const std::vector<KeyPoint>& c = e->levels[level].keypoints;
+    int n = std::min((int)c.size(), cap);
+    if (n > 0)
+        memcpy(out, c.data(), (size_t)n * sizeof(KeyPoint));
+    return (int)c.size();
+}
+int orc_quadtree(const KeyPoint* in, int n, int minX, int maxX, int minY, int maxY, int N, KeyPoint* out, int cap)
+{
+    std::vector<KeyPoint> k(in, in + n);
+    std::vector<KeyPoint> r = OrbExtractor::distribute_quadtree(k, minX, maxX, minY, maxY, N);
+    int m = std::min((int)r.size(), cap);
+    if (m > 0)
+        memcpy(out, r.data(), (size_t)m * sizeof(KeyPoint));
+    return (int)r.size();
+}
+
+// ---------------- Matcher ----------------
+int orc_match(const uint8_t* qdesc, int nq, const uint8_t* tdesc, int nt, const uint8_t* q_outlier, const Point3f* q3d,
+    const Point3f* t3d, float ratio, int discard_outliers, DMatch* out, int cap)
+{
+    std::vector<DMatch> m;
+    matcher_match(qdesc, nq, tdesc, nt, q_outlier, q3d, t3d, ratio, discard_outliers, m);
+    int n = std::min((int)m.size(), cap);
+    if (n > 0)
+        memcpy(out, m.data(), (size_t)n * sizeof(DMatch));
+    return (int)m.size();
+}
+
+// ---------------- RansacSE3 ----------------
+struct OrcSe3Out {
+    int ok;
+    float rmse;
+    float T[16];
+    int n_inliers;
+    int iters_executed;
+    long es, ef, adds, svds, rounds;
+};
+// rng: GlibcRand state (in/out). latch: {latched, cov} (in/out).
+void orc_ransac_se3(const Point3f* p1, const Point3f* p2, const DMatch* m, int nm, int iters, unsigned min_inl, float max_mahal,
+    unsigned sample, GlibcRand* rng, int* latched, double* latch_cov, OrcSe3Out* out, DMatch* inliers, int cap)
+{
+    std::vector<DMatch> mv(m, m + nm);
+    Se3Params prm = { iters, min_inl, max_mahal, sample };
+    DepthCovLatch latch = { *latched, *latch_cov };
+    Se3Result r;
+    Se3Stats st = { 0, 0, 0, 0, 0, 0 };
+    ransac_se3(p1, p2, mv, prm, *rng, latch, r, &st);
+    *latched = latch.latched;
+    *latch_cov = latch.cov;
+    out->ok = r.ok;
+    out->rmse = r.rmse;
+    memcpy(out->T, r.T, sizeof(r.T));
+    out->n_inliers = (int)r.inliers.size();
+    out->iters_executed = r.iters_executed;
+    out->es = st.es, out->ef = st.ef, out->adds = st.adds, out->svds = st.svds, out->rounds = st.rounds;
+    int n = std::min((int)r.inliers.size(), cap);
+    if (n > 0)
+        memcpy(inliers, r.inliers.data(), (size_t)n * sizeof(DMatch));
+}
+void orc_tfc_fit(const Point3f* p1, const Point3f* p2, const DMatch* m, int n, float* T) { tfc_fit(p1, p2, m, n, T); }
+double orc_mahal2(const Point3f* a, const Point3f* b, const float* T4f, int* latched, double* cov)
+{
+    double T[16];
+    for (int i = 0; i < 16; i++)
+        T[i] = T4f[i];
+    DepthCovLatch l = { *latched, *cov };
+    double r = mahal2(*a, *b, T, l, nullptr);
+    *latched = l.latched;
+    *cov = l.cov;
+    return r;
+}
+void orc_jacobi_svd3(const float* A, float* U, float* S, float* V) { jacobi_svd3(A, U, S, V); }
+// std::sort with DMatch::operator< (distance only), as SolverSE3.cpp:52
+void orc_sort_matches(DMatch* m, int n)
+{
+    std::sort(m, m + n, [](const DMatch& a, const DMatch& b) { return a.distance < b.distance; });
+}
+
+// ---------------- Ransac (Umeyama) ----------------
+struct OrcUmeOut {
+    int ok;
+    float T[16];
+    int n_inliers;
+    int iters_executed;
+};
+void orc_ransac_umeyama(const Point3f* p1, const Point3f* p2, const DMatch* m, int nm, int errorVersion, double thEuclid,
+    double minRatio, int minMatches, int usedPairs, GlibcRand* rng, OrcUmeOut* out, DMatch* inliers, int cap)
+{
+    std::vector<DMatch> mv(m, m + nm);
+    UmeyamaParams prm = { errorVersion, thEuclid, minRatio, minMatches, usedPairs };
+    UmeyamaResult r;
+    ransac_umeyama(p1, p2, mv, prm, *rng, r);
+    out->ok = r.ok;
+    memcpy(out->T, r.T, sizeof(r.T));
+    out->n_inliers = (int)r.inliers.size();
+    out->iters_executed = r.iters_executed;
+    int n = std::min((int)r.inliers.size(), cap);
+    if (n > 0)
+        memcpy(inliers, r.inliers.data(), (size_t)n * sizeof(DMatch));
+}
+void orc_umeyama3(const float* src, const float* dst, int n, float* T) { umeyama3(src, dst, n, T); }
+}
