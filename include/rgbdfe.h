@@ -1,0 +1,185 @@
+/*
+ * rgbdfe.h — C ABI of the B200-native RGB-D tracking front end.
+ *
+ * Drop-in boundary for the frame-to-frame tracking hot path of
+ * toniortiz/rgbd-slam: ORB extraction -> Hamming kNN + ratio test -> 3D-3D SE3
+ * RANSAC, plus batched loop-pair verification.  The reference has no FFI; its
+ * boundary is four C++ classes.  The host shims under rgbd-slam_b200/host/
+ * re-create those classes on top of exactly these entry points (INTEGRATION.md
+ * shows the binding).  Every function returns 0 on success and a negative
+ * RGBDFE_E_* code on error; rgbdfe_last_error() returns the message.  No CPU
+ * fallback exists: without a CUDA device rgbdfe_create() fails.
+ *
+ * Plain pointers and sizes only; the caller owns every host buffer, the
+ * context owns all device memory, streams, the RNG stream and the
+ * depth-covariance latch.
+ *
+ * Layout-compatible PODs: rgbdfe_keypoint == cv::KeyPoint (28 B),
+ * rgbdfe_dmatch == cv::DMatch (16 B), rgbdfe_point3f == cv::Point3f (12 B).
+ */
+#ifndef RGBDFE_H
+#define RGBDFE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RGBDFE_OK 0
+#define RGBDFE_E_ARG (-1)      /* bad argument */
+#define RGBDFE_E_CAPACITY (-2) /* output / context capacity too small */
+#define RGBDFE_E_CUDA (-3)     /* CUDA runtime error, see rgbdfe_last_error */
+#define RGBDFE_E_STATE (-4)    /* call order / configuration error */
+
+typedef struct rgbdfe_ctx rgbdfe_ctx;
+typedef struct rgbdfe_frame rgbdfe_frame; /* device-resident Frame data (Core/Frame.h:141-155,195) */
+typedef struct rgbdfe_kfdb rgbdfe_kfdb;   /* device-resident keyframe shard for batched verification */
+
+typedef struct {
+    float x, y, size, angle, response;
+    int octave, class_id;
+} rgbdfe_keypoint;
+
+typedef struct {
+    int queryIdx, trainIdx, imgIdx;
+    float distance;
+} rgbdfe_dmatch;
+
+typedef struct {
+    float x, y, z;
+} rgbdfe_point3f;
+
+/* Public results of RansacSE3 (Solver/SolverSE3.h:54-56) + bookkeeping. */
+typedef struct {
+    int ok;             /* return value of RansacSE3::compute */
+    float rmse;         /* RansacSE3::rmse */
+    float T21[16];      /* RansacSE3::mT21, row-major 4x4 */
+    int n_inliers;      /* mvInliers.size() */
+    int iters_executed; /* RANSAC iterations the sequential reference would have run */
+    int n_matches;      /* size of the match list the solver saw */
+} rgbdfe_se3_result;
+
+/* Ransac::parameters subset that is executable in the reference (Solver/Ransac.h:21-29). */
+typedef struct {
+    int errorVersion; /* 0 EUCLIDEAN_ERROR, 4 ADAPTIVE_ERROR */
+    double inlierThresholdEuclidean;
+    double minimalInlierRatioThreshold;
+    int minimalNumberOfMatches;
+    int usedPairs;
+} rgbdfe_umeyama_params;
+
+typedef struct {
+    int ok; /* return value of Ransac::compute (= !T.isIdentity()) */
+    float T[16];
+    int n_inliers;
+    int iters_executed;
+} rgbdfe_umeyama_result;
+
+/* ---- context ---------------------------------------------------------- */
+/* max_w/max_h: largest gray image; max_feats: nfeatures upper bound;
+ * max_batch: frames processed per batched call (>= 1). */
+int rgbdfe_create(rgbdfe_ctx** ctx, int device, int max_w, int max_h, int max_feats, int max_batch);
+void rgbdfe_destroy(rgbdfe_ctx* ctx);
+const char* rgbdfe_last_error(const rgbdfe_ctx* ctx);
+/* cudaStream_t the context launches on (for callers that time with events). */
+void* rgbdfe_stream(rgbdfe_ctx* ctx);
+/* number of kernels launched by the context so far (bench gpu_launches). */
+long long rgbdfe_launch_count(const rgbdfe_ctx* ctx);
+int rgbdfe_sync(rgbdfe_ctx* ctx);
+
+/* ---- Extractor / ORBextractor ---------------------------------------- */
+/* Extractor::setParameters (Features/Extractor.cpp:24-48) -> ORBextractor ctor
+ * (Features/ORBextractor.cpp:348-406). */
+int rgbdfe_orb_configure(rgbdfe_ctx* ctx, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+/* Extractor::getScaleFactors / getInverseScaleFactors / getScaleSigmaSquares /
+ * getInverseScaleSigmaSquares (Features/Extractor.cpp:111-158) + per-level quotas.
+ * Each array has nlevels entries; any pointer may be NULL. */
+int rgbdfe_orb_tables(rgbdfe_ctx* ctx, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* quota);
+/* ORBextractor::operator() (Features/ORBextractor.cpp:706-766): gray u8 image in,
+ * keypoints + 32-byte descriptors out.  *n receives the keypoint count. */
+int rgbdfe_orb_extract(rgbdfe_ctx* ctx, const uint8_t* gray, int w, int h, int stride, rgbdfe_keypoint* kps, uint8_t* desc, int cap, int* n);
+/* ORBextractor::mvImagePyramid[level] of the last extract, including the 19 px
+ * border ring (Features/ORBextractor.cpp:773-797).  dst is (w+38) x (h+38). */
+int rgbdfe_orb_pyramid_level(rgbdfe_ctx* ctx, int level, uint8_t* dst, int dst_stride, int* w, int* h);
+/* Stage outputs of the last extract, for stage-by-stage parity tests:
+ * per-cell FAST candidates before the quadtree (coordinates relative to the
+ * detection window, as at ORBextractor.cpp:666-668) and the blurred level. */
+int rgbdfe_orb_stage_candidates(rgbdfe_ctx* ctx, int level, rgbdfe_keypoint* out, int cap, int* n);
+int rgbdfe_orb_stage_blurred(rgbdfe_ctx* ctx, int level, uint8_t* dst, int dst_stride);
+
+/* ---- Matcher ---------------------------------------------------------- */
+/* Matcher::match (Features/Matcher.cpp:106-139): kNN k=2 Hamming + ratio test +
+ * unique-train + outlier / valid-depth filters.  q_outlier may be NULL. */
+int rgbdfe_match_knn2(rgbdfe_ctx* ctx, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt, const uint8_t* q_outlier,
+    const rgbdfe_point3f* q_xyz, const rgbdfe_point3f* t_xyz, float ratio, int discard_outliers, rgbdfe_dmatch* out, int cap, int* n);
+
+/* ---- Random (System/Random.cpp) --------------------------------------- */
+/* The context owns one glibc-rand()-compatible stream (TYPE_3).  state is 35
+ * int32: 34 ring words + the linear output index. */
+int rgbdfe_rng_seed(rgbdfe_ctx* ctx, unsigned seed);
+int rgbdfe_rng_get_state(rgbdfe_ctx* ctx, int32_t* state35);
+int rgbdfe_rng_set_state(rgbdfe_ctx* ctx, const int32_t* state35);
+
+/* ---- RansacSE3 -------------------------------------------------------- */
+/* depthCovariance latch (Solver/SolverSE3.cpp:282-287): function-local statics
+ * latched from the first depth seen in the process. */
+int rgbdfe_depth_cov_get(rgbdfe_ctx* ctx, int* latched, double* cov);
+int rgbdfe_depth_cov_set(rgbdfe_ctx* ctx, int latched, double cov);
+/* RansacSE3::compute (Solver/SolverSE3.cpp:23-133) on host arrays.  p1/p2 are
+ * Frame::mvKeys3Dc of F1/F2.  inliers (may be NULL) receives mvInliers. The
+ * Frame side effects (setOutlier / setInlier / setPose) stay with the shim. */
+int rgbdfe_ransac_se3(rgbdfe_ctx* ctx, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches,
+    int nm, int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result,
+    rgbdfe_dmatch* inliers, int cap);
+
+/* ---- Ransac (Umeyama) ------------------------------------------------- */
+/* Ransac::estimateTransformation (Solver/Ransac.cpp:61-181). */
+int rgbdfe_ransac_umeyama(rgbdfe_ctx* ctx, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2,
+    const rgbdfe_dmatch* matches, int nm, const rgbdfe_umeyama_params* params, rgbdfe_umeyama_result* result,
+    rgbdfe_dmatch* inliers, int cap);
+
+/* ---- device-resident frames (tracking pipeline) ----------------------- */
+int rgbdfe_frame_create(rgbdfe_ctx* ctx, rgbdfe_frame** frame);
+void rgbdfe_frame_destroy(rgbdfe_ctx* ctx, rgbdfe_frame* frame);
+/* Frame ctor hot part (Core/Frame.cpp:51,91-117): extract ORB from gray, then
+ * back-project every keypoint with the metric depth map (float32, 0 = invalid)
+ * and pinhole intrinsics; outlier flags reset to false.  Asynchronous on the
+ * context stream; host buffers must stay valid until rgbdfe_sync().
+ * count frames are processed as one batch (count <= max_batch). */
+int rgbdfe_frames_extract(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
+    const float* const* depth, int depth_stride_elems, float fx, float fy, float cx, float cy);
+/* Copy a frame's data back (any pointer may be NULL). */
+int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
+    uint8_t* outlier, int cap, int* n);
+/* Tracking::visualOdometry core (System/Tracking.cpp:125-130): Matcher(ratio)
+ * .match(ref, cur, discardOutliers) then RansacSE3(...).compute(ref, cur,
+ * matches, updateF2) entirely on the device; cur's outlier flags are updated as
+ * SolverSE3.cpp:38-42,119-123 do.  Asynchronous: result_slot indexes a
+ * context-owned result ring read back with rgbdfe_track_results(). */
+int rgbdfe_track(rgbdfe_ctx* ctx, rgbdfe_frame* ref, rgbdfe_frame* cur, float ratio, int discard_outliers, int iterations,
+    unsigned min_inlier_th, float max_mahal, unsigned sample_size, int update_f2, int result_slot);
+/* Synchronise and copy results [first, first+count) of the ring to the host.
+ * inlier_trainidx (may be NULL) is count x cap ints. */
+int rgbdfe_track_results(rgbdfe_ctx* ctx, int first, int count, rgbdfe_se3_result* results);
+
+/* ---- batched loop-pair verification (PoseGraph.cpp:135-154,260-284) ---- */
+/* A keyframe shard: n_kf keyframes x n_feat features each, resident on the
+ * device.  desc: n_kf*n_feat*32 B, xyz: n_kf*n_feat*12 B (host pointers). */
+int rgbdfe_kfdb_create(rgbdfe_ctx* ctx, rgbdfe_kfdb** db, int n_kf, int n_feat, const uint8_t* desc, const rgbdfe_point3f* xyz);
+void rgbdfe_kfdb_destroy(rgbdfe_ctx* ctx, rgbdfe_kfdb* db);
+/* For every keyframe k of the shard: Matcher(ratio).match(KF_k, query) then
+ * RansacSE3(iterations, min_inlier_th, max_mahal, sample).compute(KF_k, query,
+ * m, false) with the per-pair stream srand(seed + first_pair_index + k)
+ * (SURVEY 8e).  Pairs with fewer than min_matches matches report ok = 0 without
+ * running RANSAC (PoseGraph.cpp:142-144).  results: n_kf entries (host).  If
+ * results_dev != NULL the same structs are also left at that device address
+ * (for an NCCL gather without a host hop). */
+int rgbdfe_verify_batch(rgbdfe_ctx* ctx, rgbdfe_kfdb* db, const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, float ratio,
+    int min_matches, int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, unsigned seed, int first_pair_index,
+    rgbdfe_se3_result* results, void* results_dev);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RGBDFE_H */

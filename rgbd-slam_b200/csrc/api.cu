@@ -1,0 +1,905 @@
+// C ABI of librgbdfe.so (include/rgbdfe.h): context, configuration, host-buffer entry
+// points that mirror the reference classes, device-resident frame pipeline, batched
+// verification.  No CPU fallback: every entry point runs CUDA kernels on the context's
+// stream and reports CUDA errors as RGBDFE_E_CUDA.
+#include "common.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+
+using namespace rgbdfe;
+
+namespace {
+
+int cv_round_f(float v) { return (int)lrintf(v); }
+int cv_floor_f(float v)
+{
+    int i = (int)v;
+    return i - (i > v);
+}
+
+template <class T>
+cudaError_t dmalloc(T** p, size_t n)
+{
+    return cudaMalloc((void**)p, n * sizeof(T) > 0 ? n * sizeof(T) : 1);
+}
+
+// cv::resize(INTER_LINEAR) coefficient tables for one level (OpenCV resize.cpp: 11-bit
+// fixed point, coordinates (dx+0.5)*scale-0.5 computed in double, narrowed to float).
+void resize_tables(int sw, int sh, int dw, int dh, int* xofs, short* xa, int* yofs, short* yb)
+{
+    const double scale_x = 1. / ((double)dw / sw), scale_y = 1. / ((double)dh / sh);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = cv_floor_f(fx);
+        fx -= sx;
+        if (sx < 0) {
+            fx = 0;
+            sx = 0;
+        }
+        if (sx >= sw - 1) {
+            fx = 0;
+            sx = sw - 1;
+        }
+        xofs[dx] = sx;
+        xa[dx * 2] = (short)cv_round_f((1.f - fx) * 2048);
+        xa[dx * 2 + 1] = (short)cv_round_f(fx * 2048);
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = cv_floor_f(fy);
+        fy -= sy;
+        yofs[dy] = sy;
+        yb[dy * 2] = (short)cv_round_f((1.f - fy) * 2048);
+        yb[dy * 2 + 1] = (short)cv_round_f(fy * 2048);
+    }
+}
+
+// Build the per-level geometry for a w x h image (ORBextractor.cpp:773-782, 613-634) and
+// upload it with the resize tables.
+int build_level_config(rgbdfe_ctx* c, int w, int h)
+{
+    if (c->cfg.w == w && c->cfg.h == h && c->cfg.nlevels == c->nlevels && c->cfg.nfeatures == c->nfeatures)
+        return RGBDFE_OK;
+    if (w > c->max_w || h > c->max_h || w < 64 || h < 64) {
+        c->set_error("image size outside [64, max_w] x [64, max_h]");
+        return RGBDFE_E_ARG;
+    }
+    OrbConfig& g = c->cfg;
+    memset(&g, 0, sizeof(g));
+    g.nlevels = c->nlevels;
+    g.nfeatures = c->nfeatures;
+    g.iniTh = c->iniTh;
+    g.minTh = c->minTh;
+    g.w = w;
+    g.h = h;
+    static const int umax[16] = { 15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3 }; // ORBextractor.cpp:391-405
+    memcpy(g.umax, umax, sizeof(umax));
+    unsigned pyr = 0, blur = 0;
+    int cells = 0, cand = 0, sel = 0, tx = 0, ty = 0, tiles = 0;
+    std::vector<int> xofs, yofs;
+    std::vector<short> xa, yb;
+    for (int l = 0; l < g.nlevels; l++) {
+        LevelDesc& L = g.lv[l];
+        const float s = c->inv_scale[l];
+        L.w = cv_round_f((float)w * s);
+        L.h = cv_round_f((float)h * s);
+        if (L.w < 40 || L.h < 40) {
+            c->set_error("pyramid level smaller than 40 px; reduce nlevels");
+            return RGBDFE_E_ARG;
+        }
+        L.pstride = align_up(L.w + 2 * EDGE_THRESHOLD, 64);
+        L.bstride = align_up(L.w, 64);
+        L.pyr_off = pyr;
+        pyr += (unsigned)L.pstride * (L.h + 2 * EDGE_THRESHOLD);
+        L.blur_off = blur;
+        blur += (unsigned)L.bstride * L.h;
+        L.maxBorderX = L.w - EDGE_THRESHOLD + 3;
+        L.maxBorderY = L.h - EDGE_THRESHOLD + 3;
+        const float width = (float)(L.maxBorderX - 16), height = (float)(L.maxBorderY - 16);
+        L.nCols = (int)(width / 30.f);
+        L.nRows = (int)(height / 30.f);
+        if (L.nCols < 1 || L.nRows < 1) {
+            c->set_error("pyramid level too small for a FAST cell");
+            return RGBDFE_E_ARG;
+        }
+        L.wCell = (int)ceilf(width / L.nCols);
+        L.hCell = (int)ceilf(height / L.nRows);
+        if (L.wCell + 6 > CELL_MAX_DIM || L.hCell + 6 > CELL_MAX_DIM) {
+            c->set_error("FAST cell exceeds CELL_MAX_DIM");
+            return RGBDFE_E_CAPACITY;
+        }
+        L.cell_off = cells;
+        cells += L.nCols * L.nRows;
+        L.cand_off = cand;
+        L.cand_cap = L.nCols * L.nRows * CELL_CAP;
+        cand += L.cand_cap;
+        L.quota = c->quota[l];
+        L.sel_off = sel;
+        L.sel_cap = L.quota + 16;
+        sel += L.sel_cap;
+        L.scale = c->scale[l];
+        L.patch_size = (int)(31 * c->scale[l]);
+        g.max_quota = std::max(g.max_quota, L.quota);
+        L.tab_x_off = tx;
+        L.tab_y_off = ty;
+        g.blur_tile_start[l] = tiles;
+        tiles += ((L.w + 63) / 64) * ((L.h + 31) / 32);
+        if (l > 0) {
+            xofs.resize(tx + L.w);
+            xa.resize(2 * (tx + L.w));
+            yofs.resize(ty + L.h);
+            yb.resize(2 * (ty + L.h));
+            resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xofs.data() + tx, xa.data() + 2 * tx, yofs.data() + ty, yb.data() + 2 * ty);
+            tx += L.w;
+            ty += L.h;
+        }
+    }
+    g.blur_tile_start[g.nlevels] = tiles;
+    g.total_cells = cells;
+    g.total_cand = cand;
+    g.total_sel = sel;
+    g.pyr_bytes = pyr;
+    g.blur_bytes = blur;
+    if ((size_t)pyr > c->pyr_slot || (size_t)blur > c->blur_slot || cells > c->cell_slot || cand > c->cand_slot || sel > c->sel_slot
+        || tx > c->tab_x_cap || ty > c->tab_y_cap) {
+        c->set_error("internal: workspace too small for this configuration");
+        return RGBDFE_E_CAPACITY;
+    }
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(c->d_cfg, &g, sizeof(g), cudaMemcpyHostToDevice));
+    if (tx > 0) {
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_xofs, xofs.data(), tx * sizeof(int), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_xa, xa.data(), 2 * tx * sizeof(short), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_yofs, yofs.data(), ty * sizeof(int), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_yb, yb.data(), 2 * ty * sizeof(short), cudaMemcpyHostToDevice));
+    }
+    return RGBDFE_OK;
+}
+
+int alloc_frame(rgbdfe_ctx* c, rgbdfe_frame** out)
+{
+    rgbdfe_frame* f = new (std::nothrow) rgbdfe_frame();
+    if (!f)
+        return RGBDFE_E_ARG;
+    memset(f, 0, sizeof(*f));
+    f->cap = c->kp_cap;
+    CUDA_TRY(c, dmalloc(&f->kps, f->cap));
+    CUDA_TRY(c, dmalloc(&f->desc, (size_t)f->cap * 32));
+    CUDA_TRY(c, dmalloc(&f->xyz, f->cap));
+    CUDA_TRY(c, dmalloc(&f->outlier, f->cap));
+    CUDA_TRY(c, dmalloc(&f->n, 1));
+    CUDA_TRY(c, cudaMemset(f->n, 0, sizeof(int)));
+    CUDA_TRY(c, cudaMemset(f->outlier, 0, f->cap));
+    CUDA_TRY(c, cudaMemset(f->xyz, 0, sizeof(rgbdfe_point3f) * f->cap));
+    *out = f;
+    return RGBDFE_OK;
+}
+
+void free_frame(rgbdfe_frame* f)
+{
+    if (!f)
+        return;
+    cudaFree(f->kps);
+    cudaFree(f->desc);
+    cudaFree(f->xyz);
+    cudaFree(f->outlier);
+    cudaFree(f->n);
+    delete f;
+}
+
+} // namespace
+
+namespace {
+
+__global__ void k_set_pair(MatchPair* dst, MatchPair v) { *dst = v; }
+__global__ void k_set_int(int* dst, int v) { *dst = v; }
+
+void free_orb_workspaces(rgbdfe_ctx* c)
+{
+    cudaFree(c->d_img), cudaFree(c->d_depth), cudaFree(c->d_pyr), cudaFree(c->d_blur);
+    cudaFree(c->d_cell_count), cudaFree(c->d_cell_list), cudaFree(c->d_cand), cudaFree(c->d_label);
+    cudaFree(c->d_cand_count), cudaFree(c->d_sel), cudaFree(c->d_sel_count);
+    cudaFree(c->d_tab_xofs), cudaFree(c->d_tab_xa), cudaFree(c->d_tab_yofs), cudaFree(c->d_tab_yb);
+    c->d_img = nullptr, c->d_depth = nullptr, c->d_pyr = nullptr, c->d_blur = nullptr;
+    c->d_cell_count = nullptr, c->d_cell_list = nullptr, c->d_cand = nullptr, c->d_label = nullptr;
+    c->d_cand_count = nullptr, c->d_sel = nullptr, c->d_sel_count = nullptr;
+    c->d_tab_xofs = nullptr, c->d_tab_xa = nullptr, c->d_tab_yofs = nullptr, c->d_tab_yb = nullptr;
+}
+
+void free_pair_workspaces(rgbdfe_ctx* c)
+{
+    cudaFree(c->d_pairs), cudaFree(c->d_partial), cudaFree(c->d_matches), cudaFree(c->d_nmatch), cudaFree(c->d_samples);
+    cudaFree(c->d_rng_used), cudaFree(c->d_hyp), cudaFree(c->d_hyp_mask), cudaFree(c->d_replay), cudaFree(c->d_inl_pos), cudaFree(c->d_pair_rng);
+    c->d_pairs = nullptr, c->d_partial = nullptr, c->d_matches = nullptr, c->d_nmatch = nullptr, c->d_samples = nullptr;
+    c->d_rng_used = nullptr, c->d_hyp = nullptr, c->d_hyp_mask = nullptr, c->d_replay = nullptr, c->d_inl_pos = nullptr, c->d_pair_rng = nullptr;
+    c->pair_cap = 0;
+}
+
+int ensure_pairs(rgbdfe_ctx* c, int npairs)
+{
+    if (npairs <= c->pair_cap)
+        return RGBDFE_OK;
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    free_pair_workspaces(c);
+    const size_t P = (size_t)npairs, K = (size_t)c->kp_cap;
+    c->mask_words = (c->kp_cap + 31) / 32;
+    const size_t partial_rows = std::max(P, (size_t)64 * c->knn_splits);
+    CUDA_TRY(c, dmalloc(&c->d_pairs, P));
+    CUDA_TRY(c, dmalloc(&c->d_partial, partial_rows * K));
+    CUDA_TRY(c, dmalloc(&c->d_matches, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_nmatch, P));
+    CUDA_TRY(c, dmalloc(&c->d_samples, P * MAX_ITERS * 8));
+    CUDA_TRY(c, dmalloc(&c->d_rng_used, P * MAX_ITERS));
+    CUDA_TRY(c, dmalloc(&c->d_hyp, P * MAX_ITERS));
+    CUDA_TRY(c, dmalloc(&c->d_hyp_mask, P * MAX_ITERS * c->mask_words));
+    CUDA_TRY(c, dmalloc(&c->d_replay, P));
+    CUDA_TRY(c, dmalloc(&c->d_inl_pos, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_pair_rng, P));
+    c->pair_cap = npairs;
+    return RGBDFE_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rgbdfe_create(rgbdfe_ctx** out, int device, int max_w, int max_h, int max_feats, int max_batch)
+{
+    if (!out || max_w < 64 || max_h < 64 || max_w > 4095 || max_h > 4095 || max_feats < 1 || max_batch < 1 || max_batch > 64)
+        return RGBDFE_E_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return RGBDFE_E_CUDA; // no CUDA device: there is no CPU fallback
+    rgbdfe_ctx* c = new (std::nothrow) rgbdfe_ctx();
+    if (!c)
+        return RGBDFE_E_ARG;
+    c->device = device;
+    c->max_w = max_w, c->max_h = max_h, c->max_feats = max_feats, c->max_batch = max_batch;
+    c->kp_cap = align_up(max_feats + 64, 32);
+    memset(&c->cfg, 0, sizeof(c->cfg));
+    auto fail = [&](const char* what) {
+        fprintf(stderr, "rgbdfe_create: %s: %s\n", what, cudaGetErrorString(cudaGetLastError()));
+        delete c;
+        return RGBDFE_E_CUDA;
+    };
+    if (cudaSetDevice(device) != cudaSuccess)
+        return fail("cudaSetDevice");
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess)
+        return fail("cudaStreamCreate");
+    if (dmalloc(&c->d_cfg, 1) != cudaSuccess || dmalloc(&c->d_rng, 1) != cudaSuccess || dmalloc(&c->d_latch, 1) != cudaSuccess
+        || dmalloc(&c->d_const_n, 16) != cudaSuccess)
+        return fail("cudaMalloc");
+    c->result_cap = 4096;
+    if (dmalloc(&c->d_results, c->result_cap) != cudaSuccess || cudaMallocHost((void**)&c->h_results, sizeof(rgbdfe_se3_result) * c->result_cap) != cudaSuccess)
+        return fail("cudaMalloc results");
+    cudaMemset(c->d_latch, 0, sizeof(DepthLatch));
+    // raster covariances of errorFunction2 (SolverSE3.cpp:218-225)
+    const double cam_angle_x = 58.0 / 180.0 * M_PI, cam_angle_y = 45.0 / 180.0 * M_PI;
+    const double sx = 3 * tan(cam_angle_x / 640), sy = 3 * tan(cam_angle_y / 480);
+    c->rcx = sx * sx;
+    c->rcy = sy * sy;
+    if (alloc_frame(c, &c->scratch) != RGBDFE_OK || alloc_frame(c, &c->scratch2) != RGBDFE_OK)
+        return fail("frame alloc");
+    *out = c;
+    rgbdfe_rng_seed(c, 1); // srand() default state; the reference seeds with time(NULL) (System/Random.cpp:7-13)
+    int rc = rgbdfe_orb_configure(c, std::min(1000, max_feats), 1.2f, 8, 20, 7); // Extractor ctor defaults (Extractor.cpp:21)
+    if (rc != RGBDFE_OK) {
+        fprintf(stderr, "rgbdfe_create: %s\n", c->err.c_str());
+        rgbdfe_destroy(c);
+        *out = nullptr;
+        return rc;
+    }
+    return RGBDFE_OK;
+}
+
+void rgbdfe_destroy(rgbdfe_ctx* c)
+{
+    if (!c)
+        return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_orb_workspaces(c);
+    free_pair_workspaces(c);
+    free_frame(c->scratch);
+    free_frame(c->scratch2);
+    cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
+    cudaFreeHost(c->h_results);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* rgbdfe_last_error(const rgbdfe_ctx* c) { return c ? c->err.c_str() : "null context"; }
+void* rgbdfe_stream(rgbdfe_ctx* c) { return c ? (void*)c->stream : nullptr; }
+long long rgbdfe_launch_count(const rgbdfe_ctx* c) { return c ? c->launches : 0; }
+int rgbdfe_sync(rgbdfe_ctx* c)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    if (nfeatures < 1 || nfeatures > c->max_feats || nlevels < 1 || nlevels > RGBDFE_MAX_LEVELS || !(scaleFactor > 1.0f) || iniThFAST < 0
+        || iniThFAST > 255 || minThFAST < 0 || minThFAST > 255) {
+        c->set_error("orb_configure: parameter out of range");
+        return RGBDFE_E_ARG;
+    }
+    cudaSetDevice(c->device);
+    c->nfeatures = nfeatures, c->scaleFactorF = scaleFactor, c->nlevels = nlevels, c->iniTh = iniThFAST, c->minTh = minThFAST;
+    // ORBextractor constructor tables (ORBextractor.cpp:348-383); scaleFactor is a double member
+    const double sf = (double)scaleFactor;
+    c->scale.assign(nlevels, 1.0f), c->sigma2.assign(nlevels, 1.0f), c->inv_scale.assign(nlevels, 1.0f), c->inv_sigma2.assign(nlevels, 1.0f);
+    for (int i = 1; i < nlevels; i++) {
+        c->scale[i] = (float)(c->scale[i - 1] * sf);
+        c->sigma2[i] = c->scale[i] * c->scale[i];
+    }
+    for (int i = 0; i < nlevels; i++) {
+        c->inv_scale[i] = 1.0f / c->scale[i];
+        c->inv_sigma2[i] = 1.0f / c->sigma2[i];
+    }
+    c->quota.assign(nlevels, 0);
+    float factor = (float)(1.0f / sf);
+    float nDesired = nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nlevels));
+    int sum = 0;
+    for (int l = 0; l < nlevels - 1; l++) {
+        c->quota[l] = cv_round_f(nDesired);
+        sum += c->quota[l];
+        nDesired *= factor;
+    }
+    c->quota[nlevels - 1] = std::max(nfeatures - sum, 0);
+
+    // size the extraction workspaces for the largest image
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    free_orb_workspaces(c);
+    size_t pyr = 0, blur = 0;
+    int cells = 0, cand = 0, sel = 0, tx = 0, ty = 0;
+    for (int l = 0; l < nlevels; l++) {
+        const int w = cv_round_f((float)c->max_w * c->inv_scale[l]), h = cv_round_f((float)c->max_h * c->inv_scale[l]);
+        pyr += (size_t)align_up(w + 38, 64) * (h + 38);
+        blur += (size_t)align_up(w, 64) * h;
+        const int nc = std::max((w - 32) / 30, 1), nr = std::max((h - 32) / 30, 1);
+        cells += nc * nr;
+        cand += nc * nr * CELL_CAP;
+        sel += c->quota[l] + 16;
+        tx += w, ty += h;
+    }
+    const size_t B = (size_t)c->max_batch;
+    c->img_slot = (size_t)align_up(c->max_w, 64) * c->max_h;
+    c->depth_slot = (size_t)c->max_w * c->max_h;
+    c->pyr_slot = align_up((int)pyr, 256), c->blur_slot = align_up((int)blur, 256);
+    c->cell_slot = cells, c->cand_slot = cand, c->sel_slot = sel, c->tab_x_cap = tx, c->tab_y_cap = ty;
+    CUDA_TRY(c, dmalloc(&c->d_img, B * c->img_slot));
+    CUDA_TRY(c, dmalloc(&c->d_depth, B * c->depth_slot));
+    CUDA_TRY(c, dmalloc(&c->d_pyr, B * c->pyr_slot + 256));
+    CUDA_TRY(c, dmalloc(&c->d_blur, B * c->blur_slot + 256));
+    CUDA_TRY(c, dmalloc(&c->d_cell_count, B * cells));
+    CUDA_TRY(c, dmalloc(&c->d_cell_list, B * cells * CELL_CAP));
+    CUDA_TRY(c, dmalloc(&c->d_cand, B * cand));
+    CUDA_TRY(c, dmalloc(&c->d_label, B * cand));
+    CUDA_TRY(c, dmalloc(&c->d_cand_count, B * RGBDFE_MAX_LEVELS));
+    CUDA_TRY(c, dmalloc(&c->d_sel, B * sel));
+    CUDA_TRY(c, dmalloc(&c->d_sel_count, B * RGBDFE_MAX_LEVELS));
+    CUDA_TRY(c, dmalloc(&c->d_tab_xofs, (size_t)tx));
+    CUDA_TRY(c, dmalloc(&c->d_tab_xa, (size_t)2 * tx));
+    CUDA_TRY(c, dmalloc(&c->d_tab_yofs, (size_t)ty));
+    CUDA_TRY(c, dmalloc(&c->d_tab_yb, (size_t)2 * ty));
+    CUDA_TRY(c, cudaMemset(c->d_sel_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
+    CUDA_TRY(c, cudaMemset(c->d_cand_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
+    memset(&c->cfg, 0, sizeof(c->cfg)); // geometry is rebuilt on the next extract
+    c->configured = true;
+    return RGBDFE_OK;
+}
+
+int rgbdfe_orb_tables(rgbdfe_ctx* c, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* quota)
+{
+    if (!c || !c->configured)
+        return RGBDFE_E_STATE;
+    for (int i = 0; i < c->nlevels; i++) {
+        if (scale)
+            scale[i] = c->scale[i];
+        if (inv_scale)
+            inv_scale[i] = c->inv_scale[i];
+        if (sigma2)
+            sigma2[i] = c->sigma2[i];
+        if (inv_sigma2)
+            inv_sigma2[i] = c->inv_sigma2[i];
+        if (quota)
+            quota[i] = c->quota[i];
+    }
+    return RGBDFE_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// Upload `count` gray (+ optional depth) images and run K1..K6 on them as one batch.
+int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
+    const float* const* depth, int depth_stride, float fx, float fy, float cx, float cy)
+{
+    if (!c->configured)
+        return RGBDFE_E_STATE;
+    if (count < 1 || count > c->max_batch || !gray || !frames) {
+        c->set_error("extract: count outside [1, max_batch]");
+        return RGBDFE_E_ARG;
+    }
+    cudaSetDevice(c->device);
+    int rc = build_level_config(c, w, h);
+    if (rc != RGBDFE_OK)
+        return rc;
+    FrameBatch fb;
+    memset(&fb, 0, sizeof(fb));
+    for (int i = 0; i < count; i++) {
+        if (!gray[i] || !frames[i])
+            return RGBDFE_E_ARG;
+        fb.f[i] = *frames[i];
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_img + i * c->img_slot, w, gray[i], stride, w, h, cudaMemcpyHostToDevice, c->stream));
+        if (depth)
+            CUDA_TRY(c, cudaMemcpy2DAsync(c->d_depth + i * c->depth_slot, (size_t)w * 4, depth[i], (size_t)depth_stride * 4, (size_t)w * 4, h,
+                            cudaMemcpyHostToDevice, c->stream));
+    }
+    if ((rc = launch_pyramid(c, count)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_fast(c, count)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_blur(c, count)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_describe(c, count, fb, depth != nullptr, w, fx, fy, cx, cy)) != RGBDFE_OK)
+        return rc;
+    return RGBDFE_OK;
+}
+
+int set_pair(rgbdfe_ctx* c, int slot, const MatchPair& p)
+{
+    k_set_pair<<<1, 1, 0, c->stream>>>(c->d_pairs + slot, p);
+    c->launches++;
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+Se3Params make_params(rgbdfe_ctx* c, int iterations, unsigned min_inl, float max_mahal, unsigned sample)
+{
+    Se3Params p;
+    p.iterations = iterations;
+    p.min_inlier_th = min_inl;
+    p.max_mahal = max_mahal;
+    p.sample_size = sample;
+    p.rcx = c->rcx;
+    p.rcy = c->rcy;
+    return p;
+}
+
+} // namespace
+
+extern "C" {
+
+int rgbdfe_orb_extract(rgbdfe_ctx* c, const uint8_t* gray, int w, int h, int stride, rgbdfe_keypoint* kps, uint8_t* desc, int cap, int* n)
+{
+    if (!c || !n)
+        return RGBDFE_E_ARG;
+    *n = 0;
+    if (!gray || w <= 0 || h <= 0)
+        return RGBDFE_OK; // ORBextractor::operator() returns silently on an empty image (ORBextractor.cpp:708-709)
+    rgbdfe_frame* f = c->scratch;
+    int rc = run_extract(c, &f, 1, &gray, w, h, stride, nullptr, 0, 0, 0, 0, 0);
+    if (rc != RGBDFE_OK)
+        return rc;
+    return rgbdfe_frame_download(c, f, kps, desc, nullptr, nullptr, cap, n);
+}
+
+int rgbdfe_orb_pyramid_level(rgbdfe_ctx* c, int level, uint8_t* dst, int dst_stride, int* w, int* h)
+{
+    if (!c || level < 0 || level >= c->cfg.nlevels || c->cfg.w == 0)
+        return RGBDFE_E_STATE;
+    const LevelDesc& L = c->cfg.lv[level];
+    if (w)
+        *w = L.w;
+    if (h)
+        *h = L.h;
+    if (dst) {
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        CUDA_TRY(c, cudaMemcpy2D(dst, dst_stride, c->d_pyr + L.pyr_off, L.pstride, L.w + 38, L.h + 38, cudaMemcpyDeviceToHost));
+    }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_orb_stage_blurred(rgbdfe_ctx* c, int level, uint8_t* dst, int dst_stride)
+{
+    if (!c || level < 0 || level >= c->cfg.nlevels || c->cfg.w == 0 || !dst)
+        return RGBDFE_E_STATE;
+    const LevelDesc& L = c->cfg.lv[level];
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy2D(dst, dst_stride, c->d_blur + L.blur_off, L.bstride, L.w, L.h, cudaMemcpyDeviceToHost));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_orb_stage_candidates(rgbdfe_ctx* c, int level, rgbdfe_keypoint* out, int cap, int* n)
+{
+    if (!c || level < 0 || level >= c->cfg.nlevels || c->cfg.w == 0 || !n)
+        return RGBDFE_E_STATE;
+    const LevelDesc& L = c->cfg.lv[level];
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int cnt = 0;
+    CUDA_TRY(c, cudaMemcpy(&cnt, c->d_cand_count + level, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = cnt;
+    const int m = std::min(cnt, cap);
+    if (m > 0 && out) {
+        std::vector<unsigned> tmp(m);
+        CUDA_TRY(c, cudaMemcpy(tmp.data(), c->d_cand + L.cand_off, (size_t)m * 4, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < m; i++) {
+            out[i].x = (float)cand_x(tmp[i]);
+            out[i].y = (float)cand_y(tmp[i]);
+            out[i].size = 7.f;
+            out[i].angle = -1.f;
+            out[i].response = (float)cand_s(tmp[i]);
+            out[i].octave = 0;
+            out[i].class_id = -1;
+        }
+    }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_frame_create(rgbdfe_ctx* c, rgbdfe_frame** frame)
+{
+    if (!c || !frame)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    return alloc_frame(c, frame);
+}
+
+void rgbdfe_frame_destroy(rgbdfe_ctx* c, rgbdfe_frame* frame)
+{
+    if (c) {
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+    }
+    free_frame(frame);
+}
+
+int rgbdfe_frames_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
+    const float* const* depth, int depth_stride_elems, float fx, float fy, float cx, float cy)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    return run_extract(c, frames, count, gray, w, h, stride, depth, depth_stride_elems, fx, fy, cx, cy);
+}
+
+int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz, uint8_t* outlier, int cap,
+    int* n)
+{
+    if (!c || !f || !n)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int cnt = 0;
+    CUDA_TRY(c, cudaMemcpy(&cnt, f->n, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = cnt;
+    if (cnt < 0) {
+        c->set_error("quadtree node capacity overflow");
+        return RGBDFE_E_CAPACITY;
+    }
+    const int m = std::min(cnt, cap);
+    if (m > 0) {
+        if (kps)
+            CUDA_TRY(c, cudaMemcpy(kps, f->kps, (size_t)m * sizeof(rgbdfe_keypoint), cudaMemcpyDeviceToHost));
+        if (desc)
+            CUDA_TRY(c, cudaMemcpy(desc, f->desc, (size_t)m * 32, cudaMemcpyDeviceToHost));
+        if (xyz)
+            CUDA_TRY(c, cudaMemcpy(xyz, f->xyz, (size_t)m * sizeof(rgbdfe_point3f), cudaMemcpyDeviceToHost));
+        if (outlier)
+            CUDA_TRY(c, cudaMemcpy(outlier, f->outlier, (size_t)m, cudaMemcpyDeviceToHost));
+    }
+    return cnt > cap ? RGBDFE_E_CAPACITY : RGBDFE_OK;
+}
+
+int rgbdfe_match_knn2(rgbdfe_ctx* c, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt, const uint8_t* q_outlier,
+    const rgbdfe_point3f* q_xyz, const rgbdfe_point3f* t_xyz, float ratio, int discard_outliers, rgbdfe_dmatch* out, int cap, int* n)
+{
+    if (!c || !n || nq < 0 || nt < 0)
+        return RGBDFE_E_ARG;
+    *n = 0;
+    if (nq > c->kp_cap || nt > c->kp_cap) {
+        c->set_error("match: descriptor count exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    if (nq == 0 || nt == 0)
+        return RGBDFE_OK;
+    if (!q_desc || !t_desc || !q_xyz || !t_xyz)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, 1);
+    if (rc != RGBDFE_OK)
+        return rc;
+    rgbdfe_frame *Q = c->scratch, *T = c->scratch2;
+    cudaStream_t s = c->stream;
+    CUDA_TRY(c, cudaMemcpyAsync(Q->desc, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(T->desc, t_desc, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, q_xyz, (size_t)nq * 12, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(T->xyz, t_xyz, (size_t)nt * 12, cudaMemcpyHostToDevice, s));
+    if (q_outlier)
+        CUDA_TRY(c, cudaMemcpyAsync(Q->outlier, q_outlier, (size_t)nq, cudaMemcpyHostToDevice, s));
+    k_set_int<<<1, 1, 0, s>>>(Q->n, nq);
+    k_set_int<<<1, 1, 0, s>>>(T->n, nt);
+    c->launches += 2;
+    MatchPair p = { Q->desc, T->desc, Q->n, T->n, q_outlier ? Q->outlier : nullptr, Q->xyz, T->xyz, nullptr };
+    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_match(c, c->d_pairs, 1, nq, nt, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
+        return rc;
+    CUDA_TRY(c, cudaStreamSynchronize(s));
+    int cnt = 0;
+    CUDA_TRY(c, cudaMemcpy(&cnt, c->d_nmatch, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = cnt;
+    const int m = std::min(cnt, cap);
+    if (m > 0 && out)
+        CUDA_TRY(c, cudaMemcpy(out, c->d_matches, (size_t)m * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
+    return cnt > cap ? RGBDFE_E_CAPACITY : RGBDFE_OK;
+}
+
+int rgbdfe_rng_seed(rgbdfe_ctx* c, unsigned seed)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    // glibc srandom_r (TYPE_3): 31-word LCG fill, then 310 discarded outputs
+    RngState s;
+    unsigned lin[344];
+    if (seed == 0)
+        seed = 1;
+    lin[0] = seed;
+    for (int i = 1; i < 31; i++) {
+        long long w = (16807LL * (int)lin[i - 1]) % 2147483647;
+        if (w < 0)
+            w += 2147483647;
+        lin[i] = (unsigned)w;
+    }
+    for (int i = 31; i < 34; i++)
+        lin[i] = lin[i - 31];
+    for (int i = 34; i < 344; i++)
+        lin[i] = lin[i - 31] + lin[i - 3];
+    for (int i = 344 - 34; i < 344; i++)
+        s.r[i % 34] = (int)lin[i];
+    s.idx = 344;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(c->d_rng, &s, sizeof(s), cudaMemcpyHostToDevice));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_rng_get_state(rgbdfe_ctx* c, int32_t* state35)
+{
+    if (!c || !state35)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(state35, c->d_rng, sizeof(RngState), cudaMemcpyDeviceToHost));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_rng_set_state(rgbdfe_ctx* c, const int32_t* state35)
+{
+    if (!c || !state35)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(c->d_rng, state35, sizeof(RngState), cudaMemcpyHostToDevice));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_depth_cov_get(rgbdfe_ctx* c, int* latched, double* cov)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    DepthLatch l;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(&l, c->d_latch, sizeof(l), cudaMemcpyDeviceToHost));
+    if (latched)
+        *latched = l.latched;
+    if (cov)
+        *cov = l.cov;
+    return RGBDFE_OK;
+}
+
+int rgbdfe_depth_cov_set(rgbdfe_ctx* c, int latched, double cov)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    DepthLatch l = { latched, 0, cov };
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemcpy(c->d_latch, &l, sizeof(l), cudaMemcpyHostToDevice));
+    return RGBDFE_OK;
+}
+
+} // extern "C"
+
+extern "C" {
+
+int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches, int nm,
+    int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result, rgbdfe_dmatch* inliers, int cap)
+{
+    if (!c || !result || nm < 0 || n1 < 0 || n2 < 0 || (nm > 0 && (!p1 || !p2 || !matches)))
+        return RGBDFE_E_ARG;
+    if (n1 > c->kp_cap || n2 > c->kp_cap || nm > c->kp_cap) {
+        c->set_error("ransac_se3: input exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    for (int i = 0; i < nm; i++)
+        if (matches[i].queryIdx < 0 || matches[i].queryIdx >= n1 || matches[i].trainIdx < 0 || matches[i].trainIdx >= n2) {
+            c->set_error("ransac_se3: match index out of range");
+            return RGBDFE_E_ARG;
+        }
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, 1);
+    if (rc != RGBDFE_OK)
+        return rc;
+    rgbdfe_frame *Q = c->scratch, *T = c->scratch2;
+    cudaStream_t s = c->stream;
+    if (n1 > 0)
+        CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, p1, (size_t)n1 * 12, cudaMemcpyHostToDevice, s));
+    if (n2 > 0)
+        CUDA_TRY(c, cudaMemcpyAsync(T->xyz, p2, (size_t)n2 * 12, cudaMemcpyHostToDevice, s));
+    if (nm > 0)
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_matches, matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyHostToDevice, s));
+    k_set_int<<<1, 1, 0, s>>>(c->d_nmatch, nm);
+    c->launches++;
+    MatchPair p = { nullptr, nullptr, Q->n, T->n, nullptr, Q->xyz, T->xyz, nullptr };
+    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
+        return rc;
+    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    if ((rc = launch_ransac_se3(c, c->d_pairs, 1, prm, 0, 0, 0, 0, 0, c->d_results)) != RGBDFE_OK)
+        return rc;
+    CUDA_TRY(c, cudaStreamSynchronize(s));
+    CUDA_TRY(c, cudaMemcpy(result, c->d_results, sizeof(*result), cudaMemcpyDeviceToHost));
+    if (inliers && result->n_inliers > 0) {
+        std::vector<rgbdfe_dmatch> sorted(nm);
+        std::vector<int> pos(result->n_inliers);
+        CUDA_TRY(c, cudaMemcpy(sorted.data(), c->d_matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
+        CUDA_TRY(c, cudaMemcpy(pos.data(), c->d_inl_pos, (size_t)result->n_inliers * sizeof(int), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < result->n_inliers && i < cap; i++)
+            inliers[i] = sorted[pos[i]];
+        if (result->n_inliers > cap)
+            return RGBDFE_E_CAPACITY;
+    }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_ransac_umeyama(rgbdfe_ctx* c, const rgbdfe_point3f*, int, const rgbdfe_point3f*, int, const rgbdfe_dmatch*, int,
+    const rgbdfe_umeyama_params*, rgbdfe_umeyama_result*, rgbdfe_dmatch*, int)
+{
+    if (c)
+        c->set_error("rgbdfe_ransac_umeyama: kernel K12 not built yet");
+    return RGBDFE_E_STATE;
+}
+
+int rgbdfe_track(rgbdfe_ctx* c, rgbdfe_frame* ref, rgbdfe_frame* cur, float ratio, int discard_outliers, int iterations, unsigned min_inlier_th,
+    float max_mahal, unsigned sample_size, int update_f2, int result_slot)
+{
+    if (!c || !ref || !cur || result_slot < 0 || result_slot >= c->result_cap)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, 1);
+    if (rc != RGBDFE_OK)
+        return rc;
+    // Matcher::match(ref, cur): query = ref, train = cur (Tracking.cpp:127)
+    MatchPair p = { ref->desc, cur->desc, ref->n, cur->n, ref->outlier, ref->xyz, cur->xyz, cur->outlier };
+    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_match(c, c->d_pairs, 1, c->kp_cap, c->kp_cap, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
+        return rc;
+    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    return launch_ransac_se3(c, c->d_pairs, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + result_slot);
+}
+
+int rgbdfe_track_results(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result* results)
+{
+    if (!c || first < 0 || count < 0 || first + count > c->result_cap || (count > 0 && !results))
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    if (count > 0)
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_results + first, c->d_results + first, (size_t)count * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost,
+                        c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    if (count > 0)
+        memcpy(results, c->h_results + first, (size_t)count * sizeof(rgbdfe_se3_result));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_kfdb_create(rgbdfe_ctx* c, rgbdfe_kfdb** out, int n_kf, int n_feat, const uint8_t* desc, const rgbdfe_point3f* xyz)
+{
+    if (!c || !out || n_kf < 1 || n_feat < 1 || !desc || !xyz)
+        return RGBDFE_E_ARG;
+    if (n_feat > c->kp_cap) {
+        c->set_error("kfdb: n_feat exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    cudaSetDevice(c->device);
+    rgbdfe_kfdb* db = new (std::nothrow) rgbdfe_kfdb();
+    if (!db)
+        return RGBDFE_E_ARG;
+    db->n_kf = n_kf, db->n_feat = n_feat, db->desc = nullptr, db->xyz = nullptr;
+    const size_t N = (size_t)n_kf * n_feat;
+    CUDA_TRY(c, dmalloc(&db->desc, N * 32));
+    CUDA_TRY(c, dmalloc(&db->xyz, N));
+    CUDA_TRY(c, cudaMemcpy(db->desc, desc, N * 32, cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(db->xyz, xyz, N * sizeof(rgbdfe_point3f), cudaMemcpyHostToDevice));
+    *out = db;
+    return RGBDFE_OK;
+}
+
+void rgbdfe_kfdb_destroy(rgbdfe_ctx* c, rgbdfe_kfdb* db)
+{
+    if (!db)
+        return;
+    if (c) {
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+    }
+    cudaFree(db->desc);
+    cudaFree(db->xyz);
+    delete db;
+}
+
+int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, float ratio, int min_matches,
+    int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, unsigned seed, int first_pair_index,
+    rgbdfe_se3_result* results, void* results_dev)
+{
+    if (!c || !db || !q_desc || !q_xyz || nq < 1 || (!results && !results_dev))
+        return RGBDFE_E_ARG;
+    if (nq > c->kp_cap)
+        return RGBDFE_E_CAPACITY;
+    cudaSetDevice(c->device);
+    const int np = db->n_kf;
+    int rc = ensure_pairs(c, np);
+    if (rc != RGBDFE_OK)
+        return rc;
+    cudaStream_t s = c->stream;
+    rgbdfe_frame* Q = c->scratch; // the current frame = train side of every pair
+    CUDA_TRY(c, cudaMemcpyAsync(Q->desc, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, q_xyz, (size_t)nq * 12, cudaMemcpyHostToDevice, s));
+    k_set_int<<<1, 1, 0, s>>>(c->d_const_n + 0, db->n_feat);
+    k_set_int<<<1, 1, 0, s>>>(c->d_const_n + 1, nq);
+    c->launches += 2;
+    // Matcher(0.9).match(KF_k, cur): query = keyframe k, train = current frame (PoseGraph.cpp:139-141)
+    std::vector<MatchPair> hp(np);
+    for (int k = 0; k < np; k++)
+        hp[k] = MatchPair { db->desc + (size_t)k * db->n_feat * 32, Q->desc, c->d_const_n + 0, c->d_const_n + 1, nullptr,
+            db->xyz + (size_t)k * db->n_feat, Q->xyz, nullptr };
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_pairs, hp.data(), (size_t)np * sizeof(MatchPair), cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaStreamSynchronize(s)); // hp is pageable
+    if ((rc = launch_match(c, c->d_pairs, np, db->n_feat, nq, ratio, 1, nullptr)) != RGBDFE_OK)
+        return rc;
+    rgbdfe_se3_result* d_res = results_dev ? (rgbdfe_se3_result*)results_dev : nullptr;
+    rgbdfe_se3_result* tmp = nullptr;
+    if (!d_res) {
+        CUDA_TRY(c, dmalloc(&tmp, (size_t)np));
+        d_res = tmp;
+    }
+    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    rc = launch_ransac_se3(c, c->d_pairs, np, prm, 0, 1, seed, first_pair_index, min_matches, d_res);
+    if (rc == RGBDFE_OK && results) {
+        cudaError_t e = cudaMemcpyAsync(results, d_res, (size_t)np * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) {
+            c->set_error(std::string("verify_batch copy: ") + cudaGetErrorString(e));
+            rc = RGBDFE_E_CUDA;
+        }
+    }
+    if (tmp) {
+        cudaStreamSynchronize(s);
+        cudaFree(tmp);
+    }
+    return rc;
+}
+
+} // extern "C"

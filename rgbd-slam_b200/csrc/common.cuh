@@ -1,0 +1,217 @@
+// Shared declarations of the rgbdfe CUDA library (sm_100a only).
+#pragma once
+#include "../../include/rgbdfe.h"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#define RGBDFE_MAX_LEVELS 12
+#define EDGE_THRESHOLD 19
+#define CELL_CAP 256     // max NMS survivors kept per ~30 px FAST cell
+#define CELL_MAX_DIM 72  // max cell ROI side (wCell + 6)
+#define MAX_ITERS 512    // max RANSAC iterations per pair
+#define QT_THREADS 256
+
+// One pyramid level.  Offsets are relative to a frame slot's base pointer.
+struct LevelDesc {
+    int w, h;            // un-padded size
+    int pstride;         // padded row stride in bytes (>= w + 38, multiple of 64)
+    int bstride;         // blurred row stride (multiple of 64)
+    unsigned pyr_off;    // byte offset of the padded buffer (row -19, col -19)
+    unsigned blur_off;
+    int nCols, nRows, wCell, hCell; // FAST cell grid (ORBextractor.cpp:628-634)
+    int maxBorderX, maxBorderY;     // w-16, h-16
+    int cell_off;        // index of this level's first cell in the per-frame cell arrays
+    int cand_off;        // first candidate slot of this level
+    int cand_cap;
+    int quota;           // mnFeaturesPerLevel
+    int sel_off, sel_cap;
+    int tab_x_off, tab_y_off; // resize coefficient tables (level > 0)
+    float scale;         // mvScaleFactor[level]
+    int patch_size;      // int(31 * scale)
+};
+
+struct OrbConfig {
+    int nlevels;
+    int nfeatures, iniTh, minTh;
+    int w, h;            // image size the tables were built for
+    int total_cells, total_cand, total_sel, max_quota;
+    unsigned pyr_bytes, blur_bytes; // per frame slot
+    int umax[16];
+    int blur_tile_start[RGBDFE_MAX_LEVELS + 1]; // first k_gauss7 tile of each level; [nlevels] = total
+    LevelDesc lv[RGBDFE_MAX_LEVELS];
+};
+
+// glibc TYPE_3 generator state, device-resident.
+struct RngState {
+    int32_t r[34];
+    int32_t idx; // linear index of the next output
+};
+
+struct DepthLatch {
+    int latched;
+    int pad;
+    double cov;
+};
+
+struct Se3Params {
+    int iterations;
+    unsigned min_inlier_th;
+    float max_mahal;
+    unsigned sample_size;
+    double rcx, rcy; // raster covariances (SolverSE3.cpp:218-225), host tan()
+};
+
+struct SelKp { // keypoint selected by the quadtree, level coordinates
+    short x, y;
+    int score;
+    float angle;
+};
+
+struct rgbdfe_frame {
+    int cap;
+    rgbdfe_keypoint* kps; // device
+    uint8_t* desc;
+    rgbdfe_point3f* xyz;
+    uint8_t* outlier;
+    int* n; // device count
+};
+
+// Frames of one batched call, passed to kernels by value (<= 4 KB of kernel parameters).
+struct FrameBatch {
+    rgbdfe_frame f[64];
+};
+
+struct rgbdfe_kfdb {
+    int n_kf, n_feat;
+    uint8_t* desc;
+    rgbdfe_point3f* xyz;
+};
+
+// packed FAST candidate: x (12 bits) | y (12 bits) << 12 | score << 24
+__host__ __device__ inline unsigned pack_cand(int x, int y, int s) { return (unsigned)x | ((unsigned)y << 12) | ((unsigned)s << 24); }
+__host__ __device__ inline int cand_x(unsigned c) { return c & 0xfff; }
+__host__ __device__ inline int cand_y(unsigned c) { return (c >> 12) & 0xfff; }
+__host__ __device__ inline int cand_s(unsigned c) { return c >> 24; }
+
+// One (query frame, train frame) pair handed to the match / RANSAC kernels.
+struct MatchPair {
+    const uint8_t* q_desc;
+    const uint8_t* t_desc;
+    const int* nq; // device counts
+    const int* nt;
+    const uint8_t* q_outlier; // may be null
+    const rgbdfe_point3f* q_xyz;
+    const rgbdfe_point3f* t_xyz;
+    uint8_t* t_outlier;       // F2 flags updated when update_f2 (may be null)
+};
+
+// Result of one RANSAC hypothesis (one executed iteration of SolverSE3.cpp:54-103).
+struct HypOut {
+    int count;  // vRefinedMatches.size()
+    int pad;
+    double err; // refinedError
+    float T[16];
+};
+
+// Sequential accept / skip / break state of the RANSAC loop, replayed on the device.
+struct ReplayState {
+    int n;          // the reference's loop variable (with its += 10 skips)
+    int k;          // executed iterations so far (= hypotheses consumed)
+    int done;
+    int validIters;
+    int bestHyp;    // -1 none
+    int bestCount;
+    float rmse;
+    int run;        // RANSAC loop runs for this pair
+    int nm;         // matches seen
+    int rng_calls;  // rand() calls consumed by the executed iterations
+};
+
+struct rgbdfe_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    long long launches = 0;
+    int max_w = 0, max_h = 0, max_feats = 0, max_batch = 1;
+    int kp_cap = 0; // per-frame keypoint capacity (max_feats + slack)
+
+    // ORB configuration
+    bool configured = false;
+    int nfeatures = 1000, nlevels = 8, iniTh = 20, minTh = 7;
+    float scaleFactorF = 1.2f;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> quota;
+    OrbConfig cfg;          // host copy (valid for cfg.w x cfg.h)
+    OrbConfig* d_cfg = nullptr;
+
+    // extraction workspaces, max_batch frame slots each
+    uint8_t* d_img = nullptr;   size_t img_slot = 0;
+    float* d_depth = nullptr;   size_t depth_slot = 0;
+    uint8_t* d_pyr = nullptr;   size_t pyr_slot = 0;
+    uint8_t* d_blur = nullptr;  size_t blur_slot = 0;
+    int* d_cell_count = nullptr; unsigned* d_cell_list = nullptr; int cell_slot = 0;
+    unsigned* d_cand = nullptr; int* d_label = nullptr; int cand_slot = 0;
+    int* d_cand_count = nullptr; // [slot][level]
+    SelKp* d_sel = nullptr; int sel_slot = 0;
+    int* d_sel_count = nullptr;  // [slot][level]
+    int* d_tab_xofs = nullptr; short* d_tab_xa = nullptr; int* d_tab_yofs = nullptr; short* d_tab_yb = nullptr;
+    int tab_x_cap = 0, tab_y_cap = 0;
+    uint8_t* h_img = nullptr;   // pinned staging
+    float* h_depth = nullptr;
+    rgbdfe_frame* scratch = nullptr; // frame used by the host-buffer extract API
+    rgbdfe_frame* scratch2 = nullptr;
+    int last_extract_slot = 0;
+
+    // match / RANSAC workspaces for pair_cap pairs
+    int pair_cap = 0;
+    int knn_splits = 8;
+    MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
+    int4* d_partial = nullptr;      // [pairs][splits][kp_cap]
+    rgbdfe_dmatch* d_matches = nullptr; // [pairs][kp_cap]  (sorted in place by RANSAC)
+    int* d_nmatch = nullptr;        // [pairs]
+    int* d_samples = nullptr;       // [pairs][MAX_ITERS][8]
+    int* d_rng_used = nullptr;      // [pairs][MAX_ITERS] rand() calls consumed after iteration k
+    HypOut* d_hyp = nullptr;        // [pairs][MAX_ITERS]
+    unsigned* d_hyp_mask = nullptr; // [pairs][MAX_ITERS][mask_words]
+    int mask_words = 0;
+    ReplayState* d_replay = nullptr; // [pairs]
+    rgbdfe_se3_result* d_results = nullptr; int result_cap = 0;
+    rgbdfe_se3_result* h_results = nullptr; // pinned
+    int* d_inl_pos = nullptr;       // [pairs][kp_cap] positions (in the sorted match list) of the winning inliers
+    int* d_const_n = nullptr;       // small device ints for host-API counts
+    RngState* d_rng = nullptr;      // context stream
+    RngState* d_pair_rng = nullptr; // [pairs] per-pair streams (batched)
+    DepthLatch* d_latch = nullptr;
+    double rcx = 0, rcy = 0;
+
+    void set_error(const std::string& s) { err = s; }
+};
+
+#define CUDA_TRY(ctx, expr)                                                       \
+    do {                                                                          \
+        cudaError_t _e = (expr);                                                  \
+        if (_e != cudaSuccess) {                                                  \
+            (ctx)->set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+            return RGBDFE_E_CUDA;                                                 \
+        }                                                                         \
+    } while (0)
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+namespace rgbdfe {
+// orb_image.cu
+int launch_pyramid(rgbdfe_ctx* c, int count);
+int launch_blur(rgbdfe_ctx* c, int count);
+int launch_fast(rgbdfe_ctx* c, int count);
+// orb_keypoints.cu
+int launch_quadtree(rgbdfe_ctx* c, int count);
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, int depth_stride, float fx, float fy, float cx, float cy);
+// match.cu
+int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
+// ransac.cu
+int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng, unsigned seed,
+    int first_pair_index, int min_matches, rgbdfe_se3_result* d_results);
+}

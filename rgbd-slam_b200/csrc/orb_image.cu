@@ -1,0 +1,331 @@
+// Image-side ORB kernels (integer, HBM/L2-bound):
+//   K1 k_pyramid_level  — ORBextractor::ComputePyramid (Features/ORBextractor.cpp:773-797):
+//        level 0 = copy + REFLECT_101 ring; level l = cv::resize(INTER_LINEAR) of
+//        level l-1 (8-bit fixed point, 11-bit coefficients) + ring, in one pass.
+//   K5 k_gauss7         — cv::GaussianBlur(7x7, sigma 2, REFLECT_101) call site :745-746,
+//        fixed-point kernel {18,34,48,56,48,34,18}/256, one rounding (>>16).
+//   K2 k_fast_cells     — per-30px-cell cv::FAST(th=ini, nonmax) with fallback to th=min
+//        (:636-672): FAST-9/16 corner strength, cell-local 3x3 NMS, row-major output.
+// blockIdx.z (or .y) is the frame slot: every kernel processes a batch of frames.
+#include "common.cuh"
+
+namespace rgbdfe {
+
+__device__ __forceinline__ int reflect101(int p, int len)
+{
+    // |p| < 2*len always holds here (border 19 / kernel radius 3 vs len >= 20)
+    if (p < 0)
+        p = -p;
+    if (p >= len)
+        p = 2 * (len - 1) - p;
+    if (p < 0)
+        p = -p;
+    return p;
+}
+
+// ------------------------------------------------------------------ K1 ----
+// One thread per 4 horizontally adjacent padded pixels (one 32-bit store).
+__global__ void __launch_bounds__(256) k_pyramid_level(const OrbConfig* __restrict__ cfg, int level, const uint8_t* __restrict__ img,
+    size_t img_slot, int img_stride, uint8_t* __restrict__ pyr, size_t pyr_slot, const int* __restrict__ xofs,
+    const short* __restrict__ xa, const int* __restrict__ yofs, const short* __restrict__ yb)
+{
+    const LevelDesc L = cfg->lv[level];
+    const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
+    const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int py = blockIdx.y * blockDim.y + threadIdx.y;
+    if (px0 >= pw || py >= ph)
+        return;
+    const int slot = blockIdx.z;
+    uint8_t* dst = pyr + slot * pyr_slot + L.pyr_off + (size_t)py * L.pstride;
+    const int y = reflect101(py - EDGE_THRESHOLD, L.h);
+    unsigned packed = 0;
+    if (level == 0) {
+        const uint8_t* src = img + slot * img_slot + (size_t)y * img_stride;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            int px = px0 + k;
+            int x = reflect101(min(px, pw - 1) - EDGE_THRESHOLD, L.w);
+            packed |= (unsigned)src[x] << (8 * k);
+        }
+    } else {
+        const LevelDesc P = cfg->lv[level - 1];
+        const uint8_t* prev = pyr + slot * pyr_slot + P.pyr_off + (size_t)EDGE_THRESHOLD * P.pstride + EDGE_THRESHOLD;
+        const int* xo = xofs + L.tab_x_off;
+        const short* al = xa + 2 * L.tab_x_off;
+        int sy0 = yofs[L.tab_y_off + y];
+        const int b0 = yb[2 * (L.tab_y_off + y)], b1 = yb[2 * (L.tab_y_off + y) + 1];
+        int sy1 = min(max(sy0 + 1, 0), P.h - 1);
+        sy0 = min(max(sy0, 0), P.h - 1);
+        const uint8_t* r0 = prev + (size_t)sy0 * P.pstride;
+        const uint8_t* r1 = prev + (size_t)sy1 * P.pstride;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            int px = px0 + k;
+            int x = reflect101(min(px, pw - 1) - EDGE_THRESHOLD, L.w);
+            int sx = xo[x];
+            int a0 = al[2 * x], a1 = al[2 * x + 1];
+            int h0 = r0[sx] * a0 + r0[sx + 1] * a1; // sx+1 may touch the ring only when a1 == 0
+            int h1 = r1[sx] * a0 + r1[sx + 1] * a1;
+            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+            v = min(max(v, 0), 255);
+            packed |= (unsigned)v << (8 * k);
+        }
+    }
+    *reinterpret_cast<unsigned*>(dst + px0) = packed; // pstride is a multiple of 64: never crosses the row
+}
+
+// ------------------------------------------------------------------ K5 ----
+#define BLUR_TW 64
+#define BLUR_TH 32
+__global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    uint8_t* __restrict__ blur, size_t blur_slot)
+{
+    // blockIdx.x enumerates tiles of all levels
+    int level = 0;
+    while (level + 1 < cfg->nlevels && (int)blockIdx.x >= cfg->blur_tile_start[level + 1])
+        level++;
+    const LevelDesc L = cfg->lv[level];
+    const int t = blockIdx.x - cfg->blur_tile_start[level];
+    const int tiles_x = (L.w + BLUR_TW - 1) / BLUR_TW;
+    const int tx0 = (t % tiles_x) * BLUR_TW, ty0 = (t / tiles_x) * BLUR_TH;
+    const int slot = blockIdx.y;
+    const uint8_t* src = pyr + slot * pyr_slot + L.pyr_off + (size_t)EDGE_THRESHOLD * L.pstride + EDGE_THRESHOLD;
+
+    __shared__ uint8_t s_src[BLUR_TH + 6][BLUR_TW + 8];
+    __shared__ unsigned short s_h[BLUR_TH + 6][BLUR_TW];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
+        int r = i / (BLUR_TW + 6), c = i % (BLUR_TW + 6);
+        int y = reflect101(min(ty0 + r - 3, L.h + 2), L.h);
+        int x = reflect101(min(tx0 + c - 3, L.w + 2), L.w);
+        s_src[r][c] = src[(size_t)y * L.pstride + x];
+    }
+    __syncthreads();
+    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
+        int r = i / BLUR_TW, c = i % BLUR_TW;
+        const uint8_t* p = &s_src[r][c];
+        int a = 18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3];
+        s_h[r][c] = (unsigned short)a;
+    }
+    __syncthreads();
+    uint8_t* dst = blur + slot * blur_slot + L.blur_off;
+    for (int i = tid; i < BLUR_TH * BLUR_TW / 4; i += 256) {
+        int r = i / (BLUR_TW / 4), c = (i % (BLUR_TW / 4)) * 4;
+        int y = ty0 + r, x = tx0 + c;
+        if (y >= L.h || x >= L.w)
+            continue;
+        unsigned packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            int a = 18 * (s_h[r][c + k] + s_h[r + 6][c + k]) + 34 * (s_h[r + 1][c + k] + s_h[r + 5][c + k])
+                + 48 * (s_h[r + 2][c + k] + s_h[r + 4][c + k]) + 56 * s_h[r + 3][c + k];
+            int v = min((a + 32768) >> 16, 255);
+            packed |= (unsigned)v << (8 * k);
+        }
+        *reinterpret_cast<unsigned*>(dst + (size_t)y * L.bstride + x) = packed; // bstride multiple of 64, x multiple of 4
+    }
+}
+
+// ------------------------------------------------------------------ K2 ----
+__device__ __forceinline__ bool has9(unsigned m)
+{
+    m |= m << 16;
+    unsigned r = m & (m >> 1);
+    r &= r >> 2;
+    r &= r >> 4;
+    r &= m >> 8;
+    return (r & 0xffffu) != 0;
+}
+
+// FAST-9/16 corner strength S: the pixel is a corner at threshold t iff S > t,
+// and OpenCV's response (cornerScore<16>) is S - 1.  Returns 0 when S <= th_lo.
+__device__ __forceinline__ int fast_strength(const uint8_t* __restrict__ p, int pitch, int th_lo)
+{
+    const int v = p[0];
+    int d[16];
+    d[0] = v - p[3 * pitch];
+    d[1] = v - p[3 * pitch + 1];
+    d[2] = v - p[2 * pitch + 2];
+    d[3] = v - p[pitch + 3];
+    d[4] = v - p[3];
+    d[5] = v - p[-pitch + 3];
+    d[6] = v - p[-2 * pitch + 2];
+    d[7] = v - p[-3 * pitch + 1];
+    d[8] = v - p[-3 * pitch];
+    d[9] = v - p[-3 * pitch - 1];
+    d[10] = v - p[-2 * pitch - 2];
+    d[11] = v - p[-pitch - 3];
+    d[12] = v - p[-3];
+    d[13] = v - p[pitch - 3];
+    d[14] = v - p[2 * pitch - 2];
+    d[15] = v - p[3 * pitch - 1];
+    unsigned md = 0, mb = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        md |= (unsigned)(d[k] > th_lo) << k;
+        mb |= (unsigned)(-d[k] > th_lo) << k;
+    }
+    const bool dark = has9(md), bright = has9(mb);
+    if (!dark && !bright)
+        return 0;
+    int best = 0;
+    if (dark) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            int a = d[k];
+#pragma unroll
+            for (int j = 1; j < 9; j++)
+                a = min(a, d[(k + j) & 15]);
+            best = max(best, a);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            int a = -d[k];
+#pragma unroll
+            for (int j = 1; j < 9; j++)
+                a = min(a, -d[(k + j) & 15]);
+            best = max(best, a);
+        }
+    }
+    return best;
+}
+
+__global__ void __launch_bounds__(256) k_fast_cells(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    int* __restrict__ cell_count, unsigned* __restrict__ cell_list, int cell_slot)
+{
+    int level = 0;
+    while (level + 1 < cfg->nlevels && (int)blockIdx.x >= cfg->lv[level + 1].cell_off)
+        level++;
+    const LevelDesc L = cfg->lv[level];
+    const int cell = blockIdx.x - L.cell_off;
+    const int ci = cell / L.nCols, cj = cell % L.nCols;
+    const int slot = blockIdx.y;
+    const int tid = threadIdx.x;
+    int* out_count = cell_count + (size_t)slot * cell_slot + blockIdx.x;
+    unsigned* out_list = cell_list + ((size_t)slot * cell_slot + blockIdx.x) * CELL_CAP;
+
+    const int iniY = 16 + ci * L.hCell, iniX = 16 + cj * L.wCell;
+    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+    bool skip = (iniY >= L.maxBorderY - 3) || (iniX >= L.maxBorderX - 6);
+    if (maxY > L.maxBorderY)
+        maxY = L.maxBorderY;
+    if (maxX > L.maxBorderX)
+        maxX = L.maxBorderX;
+    const int cw = maxX - iniX, ch = maxY - iniY;
+    if (skip || cw < 7 || ch < 7) {
+        if (tid == 0)
+            *out_count = 0;
+        return;
+    }
+    __shared__ uint8_t s_img[CELL_MAX_DIM][CELL_MAX_DIM + 8];
+    __shared__ uint8_t s_S[CELL_MAX_DIM][CELL_MAX_DIM + 8];
+    __shared__ uint8_t s_keep[CELL_MAX_DIM * CELL_MAX_DIM];
+    __shared__ int s_n;
+    const uint8_t* src = pyr + slot * pyr_slot + L.pyr_off + (size_t)(EDGE_THRESHOLD + iniY) * L.pstride + EDGE_THRESHOLD + iniX;
+    for (int i = tid; i < cw * ch; i += 256) {
+        int r = i / cw, c = i % cw;
+        s_img[r][c] = src[(size_t)r * L.pstride + c];
+        s_S[r][c] = 0;
+    }
+    if (tid == 0)
+        s_n = 0;
+    __syncthreads();
+    const int dw = cw - 6, dh = ch - 6;
+    const int th_lo = min(cfg->iniTh, cfg->minTh);
+    for (int i = tid; i < dw * dh; i += 256) {
+        int r = 3 + i / dw, c = 3 + i % dw;
+        int S = fast_strength(&s_img[r][c], CELL_MAX_DIM + 8, th_lo);
+        s_S[r][c] = (uint8_t)min(S, 255);
+    }
+    __syncthreads();
+    int th = cfg->iniTh;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        int local = 0;
+        for (int i = tid; i < dw * dh; i += 256) {
+            int r = 3 + i / dw, c = 3 + i % dw;
+            int S = s_S[r][c];
+            bool keep = false;
+            if (S > th) {
+                const int sc = S - 1;
+                keep = true;
+#pragma unroll
+                for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+                    for (int dx = -1; dx <= 1; dx++) {
+                        if (dx == 0 && dy == 0)
+                            continue;
+                        int Sn = s_S[r + dy][c + dx];
+                        int sn = Sn > th ? Sn - 1 : 0;
+                        keep = keep && (sc > sn);
+                    }
+            }
+            s_keep[i] = keep;
+            local += keep;
+        }
+        if (local)
+            atomicAdd(&s_n, local);
+        __syncthreads();
+        if (s_n > 0 || th == cfg->minTh)
+            break;
+        th = cfg->minTh; // cv::FAST returned nothing at iniThFAST: retry at minThFAST (:658-661)
+        __syncthreads();
+    }
+    // ordered (row-major) compaction by warp 0
+    if (tid < 32) {
+        int base = 0;
+        const int total = dw * dh;
+        for (int i0 = 0; i0 < total; i0 += 32) {
+            int i = i0 + tid;
+            bool k = i < total && s_keep[i];
+            unsigned bal = __ballot_sync(0xffffffffu, k);
+            if (k) {
+                int pos = base + __popc(bal & ((1u << tid) - 1));
+                if (pos < CELL_CAP) {
+                    int r = 3 + i / dw, c = 3 + i % dw;
+                    out_list[pos] = pack_cand(c + cj * L.wCell, r + ci * L.hCell, s_S[r][c] - 1);
+                }
+            }
+            base += __popc(bal);
+        }
+        if (tid == 0)
+            *out_count = min(base, CELL_CAP);
+    }
+}
+
+// ---------------------------------------------------------------- launchers
+int launch_pyramid(rgbdfe_ctx* c, int count)
+{
+    const OrbConfig& cfg = c->cfg;
+    for (int l = 0; l < cfg.nlevels; l++) {
+        const LevelDesc& L = cfg.lv[l];
+        int pw = L.w + 38, ph = L.h + 38;
+        dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
+        k_pyramid_level<<<grd, blk, 0, c->stream>>>(c->d_cfg, l, c->d_img, c->img_slot, cfg.w, c->d_pyr, c->pyr_slot, c->d_tab_xofs,
+            c->d_tab_xa, c->d_tab_yofs, c->d_tab_yb);
+        c->launches++;
+    }
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+int launch_blur(rgbdfe_ctx* c, int count)
+{
+    const OrbConfig& cfg = c->cfg;
+    const int total = cfg.blur_tile_start[cfg.nlevels];
+    k_gauss7<<<dim3(total, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot);
+    c->launches++;
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+int launch_fast(rgbdfe_ctx* c, int count)
+{
+    k_fast_cells<<<dim3(c->cfg.total_cells, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list,
+        c->cell_slot);
+    c->launches++;
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+} // namespace rgbdfe

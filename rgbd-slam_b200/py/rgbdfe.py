@@ -1,0 +1,269 @@
+"""ctypes binding of librgbdfe.so (include/rgbdfe.h) for the tests and bench.py.
+
+Plumbing only: every call goes straight through the C ABI; there is no Python or
+CPU implementation behind it.  Importing works without a GPU (the library loads
+and its symbols can be inspected); creating a Context without a CUDA device
+raises RgbdfeError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "librgbdfe.so")
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")]
+)
+DM_DTYPE = np.dtype([("queryIdx", "<i4"), ("trainIdx", "<i4"), ("imgIdx", "<i4"), ("distance", "<f4")])
+SE3_DTYPE = np.dtype(
+    [("ok", "<i4"), ("rmse", "<f4"), ("T21", "<f4", (16,)), ("n_inliers", "<i4"), ("iters_executed", "<i4"), ("n_matches", "<i4")]
+)
+assert KP_DTYPE.itemsize == 28 and DM_DTYPE.itemsize == 16 and SE3_DTYPE.itemsize == 84
+
+
+class RgbdfeError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RgbdfeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)"
+            )
+        _lib = C.CDLL(LIB_PATH)
+        _lib.rgbdfe_last_error.restype = C.c_char_p
+        _lib.rgbdfe_stream.restype = C.c_void_p
+        _lib.rgbdfe_launch_count.restype = C.c_longlong
+        for name in ("rgbdfe_last_error", "rgbdfe_stream", "rgbdfe_launch_count", "rgbdfe_destroy", "rgbdfe_sync"):
+            getattr(_lib, name).argtypes = [C.c_void_p]
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Frame:
+    def __init__(self, ctx):
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx._chk(lib().rgbdfe_frame_create(ctx.h, C.byref(h)))
+        self.h = h
+
+    def download(self):
+        cap = self.ctx.kp_cap
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        xyz = np.zeros((cap, 3), np.float32)
+        outl = np.zeros(cap, np.uint8)
+        n = C.c_int()
+        self.ctx._chk(lib().rgbdfe_frame_download(self.ctx.h, self.h, _p(kps), _p(desc), _p(xyz), _p(outl), cap, C.byref(n)))
+        n = n.value
+        return kps[:n].copy(), desc[:n].copy(), xyz[:n].copy(), outl[:n].copy()
+
+    def close(self):
+        if self.h:
+            lib().rgbdfe_frame_destroy(self.ctx.h, self.h)
+            self.h = None
+
+
+class Context:
+    def __init__(self, device=0, max_w=640, max_h=480, max_feats=1000, max_batch=1):
+        self.h = C.c_void_p()
+        rc = lib().rgbdfe_create(C.byref(self.h), device, max_w, max_h, max_feats, max_batch)
+        if rc != 0:
+            self.h = None
+            raise RgbdfeError(f"rgbdfe_create failed ({rc}): no usable CUDA device or bad arguments; there is no CPU fallback")
+        self.max_feats = max_feats
+        self.kp_cap = (max_feats + 64 + 31) // 32 * 32
+        self.max_batch = max_batch
+        self.nlevels = 8
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise RgbdfeError(f"rgbdfe error {rc}: {lib().rgbdfe_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            lib().rgbdfe_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return lib().rgbdfe_stream(self.h)
+
+    @property
+    def launches(self):
+        return lib().rgbdfe_launch_count(self.h)
+
+    def sync(self):
+        self._chk(lib().rgbdfe_sync(self.h))
+
+    # ---- Extractor / ORBextractor ----
+    def orb_configure(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        self._chk(lib().rgbdfe_orb_configure(self.h, nfeatures, C.c_float(scale), nlevels, ini_th, min_th))
+        self.nlevels = nlevels
+
+    def orb_tables(self):
+        n = self.nlevels
+        f = [np.zeros(n, np.float32) for _ in range(4)]
+        q = np.zeros(n, np.int32)
+        self._chk(lib().rgbdfe_orb_tables(self.h, _p(f[0]), _p(f[1]), _p(f[2]), _p(f[3]), _p(q)))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3], quota=q)
+
+    def orb_extract(self, gray):
+        gray = np.ascontiguousarray(gray, np.uint8)
+        cap = self.kp_cap
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int()
+        self._chk(lib().rgbdfe_orb_extract(self.h, _p(gray), gray.shape[1], gray.shape[0], gray.strides[0], _p(kps), _p(desc), cap, C.byref(n)))
+        return kps[: n.value].copy(), desc[: n.value].copy()
+
+    def pyramid_level(self, level):
+        w, h = C.c_int(), C.c_int()
+        self._chk(lib().rgbdfe_orb_pyramid_level(self.h, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value + 38, w.value + 38), np.uint8)
+        self._chk(lib().rgbdfe_orb_pyramid_level(self.h, level, _p(out), out.strides[0], C.byref(w), C.byref(h)))
+        return out
+
+    def stage_blurred(self, level):
+        w, h = C.c_int(), C.c_int()
+        self._chk(lib().rgbdfe_orb_pyramid_level(self.h, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        self._chk(lib().rgbdfe_orb_stage_blurred(self.h, level, _p(out), out.strides[0]))
+        return out
+
+    def stage_candidates(self, level):
+        cap = 1 << 17
+        out = np.zeros(cap, KP_DTYPE)
+        n = C.c_int()
+        self._chk(lib().rgbdfe_orb_stage_candidates(self.h, level, _p(out), cap, C.byref(n)))
+        return out[: n.value].copy()
+
+    # ---- Matcher ----
+    def match(self, qdesc, tdesc, q_outlier, q_xyz, t_xyz, ratio=0.9, discard_outliers=True):
+        qdesc = np.ascontiguousarray(qdesc, np.uint8)
+        tdesc = np.ascontiguousarray(tdesc, np.uint8)
+        q_xyz = np.ascontiguousarray(q_xyz, np.float32)
+        t_xyz = np.ascontiguousarray(t_xyz, np.float32)
+        if q_outlier is not None:
+            q_outlier = np.ascontiguousarray(q_outlier, np.uint8)
+        out = np.zeros(max(len(qdesc), 1), DM_DTYPE)
+        n = C.c_int()
+        self._chk(
+            lib().rgbdfe_match_knn2(
+                self.h, _p(qdesc), len(qdesc), _p(tdesc), len(tdesc), _p(q_outlier), _p(q_xyz), _p(t_xyz), C.c_float(ratio),
+                int(discard_outliers), _p(out), len(out), C.byref(n),
+            )
+        )
+        return out[: n.value].copy()
+
+    # ---- Random ----
+    def rng_seed(self, seed):
+        self._chk(lib().rgbdfe_rng_seed(self.h, C.c_uint(seed)))
+
+    def rng_get_state(self):
+        st = np.zeros(35, np.int32)
+        self._chk(lib().rgbdfe_rng_get_state(self.h, _p(st)))
+        return st
+
+    def rng_set_state(self, st):
+        st = np.ascontiguousarray(st, np.int32)
+        self._chk(lib().rgbdfe_rng_set_state(self.h, _p(st)))
+
+    def depth_cov_get(self):
+        l, cov = C.c_int(), C.c_double()
+        self._chk(lib().rgbdfe_depth_cov_get(self.h, C.byref(l), C.byref(cov)))
+        return l.value, cov.value
+
+    def depth_cov_set(self, latched, cov):
+        self._chk(lib().rgbdfe_depth_cov_set(self.h, int(latched), C.c_double(cov)))
+
+    # ---- RansacSE3 ----
+    def ransac_se3(self, p1, p2, matches, iters=200, min_inl=10, max_mahal=3.0, sample=4):
+        p1 = np.ascontiguousarray(p1, np.float32)
+        p2 = np.ascontiguousarray(p2, np.float32)
+        matches = np.ascontiguousarray(matches, DM_DTYPE)
+        res = np.zeros(1, SE3_DTYPE)
+        inl = np.zeros(max(len(matches), 1), DM_DTYPE)
+        self._chk(
+            lib().rgbdfe_ransac_se3(
+                self.h, _p(p1), len(p1), _p(p2), len(p2), _p(matches), len(matches), iters, C.c_uint(min_inl), C.c_float(max_mahal),
+                C.c_uint(sample), _p(res), _p(inl), len(inl),
+            )
+        )
+        r = res[0]
+        return dict(
+            ok=bool(r["ok"]), rmse=np.float32(r["rmse"]), T=r["T21"].reshape(4, 4).copy(), inliers=inl[: r["n_inliers"]].copy(),
+            iters_executed=int(r["iters_executed"]), n_matches=int(r["n_matches"]),
+        )
+
+    # ---- device-resident pipeline ----
+    def frames_extract(self, frames, grays, depths, cam):
+        n = len(frames)
+        fr = (C.c_void_p * n)(*[f.h for f in frames])
+        gp = (C.c_void_p * n)(*[g.ctypes.data for g in grays])
+        h, w = grays[0].shape
+        if depths is not None:
+            dp = (C.c_void_p * n)(*[d.ctypes.data for d in depths])
+            dstride = depths[0].strides[0] // 4
+        else:
+            dp, dstride = None, 0
+        self._chk(
+            lib().rgbdfe_frames_extract(
+                self.h, fr, n, gp, w, h, grays[0].strides[0], dp, dstride, C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]),
+                C.c_float(cam["cy"]),
+            )
+        )
+
+    def track(self, ref, cur, slot, ratio=0.9, discard=True, iters=200, min_inl=10, max_mahal=3.0, sample=4, update_f2=True):
+        self._chk(
+            lib().rgbdfe_track(
+                self.h, ref.h, cur.h, C.c_float(ratio), int(discard), iters, C.c_uint(min_inl), C.c_float(max_mahal), C.c_uint(sample),
+                int(update_f2), slot,
+            )
+        )
+
+    def track_results(self, first, count):
+        res = np.zeros(count, SE3_DTYPE)
+        self._chk(lib().rgbdfe_track_results(self.h, first, count, _p(res)))
+        return res
+
+    # ---- batched verification ----
+    def kfdb_create(self, desc, xyz):
+        desc = np.ascontiguousarray(desc, np.uint8)
+        xyz = np.ascontiguousarray(xyz, np.float32)
+        h = C.c_void_p()
+        self._chk(lib().rgbdfe_kfdb_create(self.h, C.byref(h), desc.shape[0], desc.shape[1], _p(desc), _p(xyz)))
+        return h
+
+    def kfdb_destroy(self, db):
+        lib().rgbdfe_kfdb_destroy(self.h, db)
+
+    def verify_batch(self, db, n_kf, q_desc, q_xyz, ratio=0.9, min_matches=30, iters=200, min_inl=30, max_mahal=3.0, sample=4, seed=42,
+                     first_pair_index=0, results_dev=None, want_host=True):
+        q_desc = np.ascontiguousarray(q_desc, np.uint8)
+        q_xyz = np.ascontiguousarray(q_xyz, np.float32)
+        res = np.zeros(n_kf, SE3_DTYPE) if want_host else None
+        self._chk(
+            lib().rgbdfe_verify_batch(
+                self.h, db, _p(q_desc), _p(q_xyz), len(q_desc), C.c_float(ratio), min_matches, iters, C.c_uint(min_inl), C.c_float(max_mahal),
+                C.c_uint(sample), C.c_uint(seed), first_pair_index, _p(res), C.c_void_p(results_dev) if results_dev else None,
+            )
+        )
+        return res

@@ -1,0 +1,255 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle, stage by stage.
+
+Bar (north_star): keypoints, descriptors, match indices and RANSAC inlier sets bit-exact;
+poses within 1e-5 (rotation entries and translation, FP32).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+POSE_TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import rgbdfe
+
+    c = rgbdfe.Context(0, 640, 480, 2000, 4)
+    yield c
+    c.close()
+
+
+def _unproject(cam, kps, depth):
+    import synth
+
+    return synth.unproject(cam, np.stack([kps["x"], kps["y"]], 1), depth)
+
+
+@pytest.mark.parametrize("nfeat", [1000, 2000, 300])
+def test_orb_stages_bit_exact(ctx, oracle, seq_vga, nfeat):
+    cam, frames = seq_vga
+    ctx.orb_configure(nfeat, 1.2, 8, 20, 7)
+    orb = oracle.Orb(nfeat)
+    t_o, t_g = orb.tables(), ctx.orb_tables()
+    for k in ("scale", "inv_scale", "sigma2", "inv_sigma2", "quota"):
+        assert (t_o[k] == t_g[k]).all(), k
+    for gray, _ in frames[:2]:
+        kps_o, desc_o = orb.extract(gray)
+        kps_g, desc_g = ctx.orb_extract(gray)
+        for l in range(8):
+            assert (ctx.pyramid_level(l) == orb.level_padded(l)).all(), f"pyramid level {l}"
+            c_o, c_g = orb.level_candidates(l), ctx.stage_candidates(l)
+            assert len(c_o) == len(c_g), f"FAST candidate count level {l}: {len(c_o)} vs {len(c_g)}"
+            for f in ("x", "y", "response"):
+                assert (c_o[f] == c_g[f]).all(), f"FAST candidates level {l} field {f}"
+            b = orb.level_blurred(l)
+            if b is not None:
+                assert (ctx.stage_blurred(l) == b).all(), f"blur level {l}"
+        assert len(kps_o) == len(kps_g)
+        for f in ("x", "y", "size", "response", "octave", "class_id"):
+            assert (kps_o[f] == kps_g[f]).all(), f"keypoint field {f}"
+        assert (kps_o["angle"].view(np.uint32) == kps_g["angle"].view(np.uint32)).all(), "angle bit pattern"
+        assert (desc_o == desc_g).all(), "descriptors"
+
+
+def test_orb_fast_threshold_fallback(ctx, oracle):
+    """Low-contrast image: cells with no FAST corner at 20 but some at 7 (ORBextractor.cpp:658-661)."""
+    rng = np.random.default_rng(11)
+    img = (128 + rng.integers(-9, 10, (480, 640))).astype(np.uint8)
+    img[100:300, 200:400] = rng.integers(0, 256, (200, 200), dtype=np.uint8)
+    ctx.orb_configure(1000, 1.2, 8, 20, 7)
+    orb = oracle.Orb(1000)
+    k_o, d_o = orb.extract(img)
+    k_g, d_g = ctx.orb_extract(img)
+    assert len(k_o) == len(k_g) and (k_o == k_g).all() and (d_o == d_g).all()
+
+
+def test_orb_flat_image_has_no_keypoints(ctx, oracle):
+    img = np.full((480, 640), 77, np.uint8)
+    ctx.orb_configure(1000, 1.2, 8, 20, 7)
+    k_g, d_g = ctx.orb_extract(img)
+    k_o, _ = oracle.Orb(1000).extract(img)
+    assert len(k_g) == 0 and len(k_o) == 0
+
+
+def test_match_bit_exact(ctx, oracle, seq_vga):
+    cam, frames = seq_vga
+    ctx.orb_configure(1000, 1.2, 8, 20, 7)
+    orb = oracle.Orb(1000)
+    data = []
+    for g, d in frames[:2]:
+        k, de = orb.extract(g)
+        data.append((k, de, _unproject(cam, k, d)))
+    rng = np.random.default_rng(5)
+    outl = (rng.random(len(data[0][0])) < 0.2).astype(np.uint8)
+    for discard in (True, False):
+        for ratio in (0.9, 0.6):
+            m_o = oracle.match(data[0][1], data[1][1], outl, data[0][2], data[1][2], ratio, discard)
+            m_g = ctx.match(data[0][1], data[1][1], outl, data[0][2], data[1][2], ratio, discard)
+            assert len(m_o) == len(m_g) and (m_o == m_g).all()
+
+
+def test_match_ties_and_degenerate(ctx, oracle):
+    rng = np.random.default_rng(6)
+    q = rng.integers(0, 256, (257, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    t[100:140] = t[100]  # exact ties: lower train index must win
+    q[:50] = t[100]
+    t[200] = q[60]
+    xyz_q = np.ones((257, 3), np.float32)
+    xyz_t = np.ones((300, 3), np.float32)
+    xyz_t[::7, 2] = 0  # invalid depth
+    z = np.zeros(257, np.uint8)
+    for ratio in (0.9, 1.5):
+        m_o = oracle.match(q, t, z, xyz_q, xyz_t, ratio, True)
+        m_g = ctx.match(q, t, z, xyz_q, xyz_t, ratio, True)
+        assert len(m_o) == len(m_g) and (m_o == m_g).all()
+    # < 2 train descriptors: no match (guarded UB of Matcher.cpp:117); empty inputs
+    assert len(ctx.match(q, t[:1], z, xyz_q, xyz_t[:1], 0.9, True)) == 0
+    assert len(ctx.match(q[:0], t, z[:0], xyz_q[:0], xyz_t, 0.9, True)) == 0
+
+
+def _pair(oracle, cam, frames, i, j, nfeat=1000):
+    orb = oracle.Orb(nfeat)
+    out = []
+    for g, d in (frames[i], frames[j]):
+        k, de = orb.extract(g)
+        out.append((k, de, _unproject(cam, k, d)))
+    m = oracle.match(out[0][1], out[1][1], np.zeros(len(out[0][0]), np.uint8), out[0][2], out[1][2], 0.9, True)
+    return out[0][2], out[1][2], m
+
+
+def _check_se3(r_o, r_g):
+    assert r_o["ok"] == r_g["ok"]
+    assert r_o["iters_executed"] == r_g["iters_executed"]
+    assert len(r_o["inliers"]) == len(r_g["inliers"])
+    assert (r_o["inliers"] == r_g["inliers"]).all(), "inlier set / order"
+    assert np.abs(r_o["T"] - r_g["T"]).max() <= POSE_TOL
+    assert (r_o["T"] == r_g["T"]).all(), "pose bits"
+    assert r_o["rmse"] == r_g["rmse"]
+
+
+def test_ransac_se3_parity_and_rng_stream(ctx, oracle, seq_vga):
+    cam, frames = seq_vga
+    p1, p2, m = _pair(oracle, cam, frames, 0, 1)
+    rng = oracle.Rng(42)
+    latch = oracle.Latch()
+    ctx.rng_seed(42)
+    ctx.depth_cov_set(0, 0.0)
+    for it in range(3):  # consecutive calls share the rand() stream and the latch
+        r_o = oracle.ransac_se3(p1, p2, m, rng, latch, 200, 10, 3.0, 4)
+        r_g = ctx.ransac_se3(p1, p2, m, 200, 10, 3.0, 4)
+        _check_se3(r_o, r_g)
+        st = ctx.rng_get_state()
+        probe = oracle.Rng(1)
+        probe.buf[:] = rng.buf
+        ctx_next = _next_from_state(st)
+        assert ctx_next == probe.next(), "rand() stream position after compute()"
+    l, cov = ctx.depth_cov_get()
+    assert l == latch.latched.value == 1 and cov == latch.cov.value
+
+
+def _next_from_state(st):
+    r, idx = st[:34].astype(np.uint32), int(st[34])
+    return int((int(r[(idx - 31) % 34]) + int(r[(idx - 3) % 34])) & 0xFFFFFFFF) >> 1
+
+
+def test_ransac_se3_hard_cases(ctx, oracle, seq_vga):
+    """Outlier-heavy matches (many iterations, n += 10 skips), too few matches, identity fallback."""
+    cam, frames = seq_vga
+    p1, p2, m = _pair(oracle, cam, frames, 0, 3)
+    rs = np.random.default_rng(9)
+    for frac, seed in ((0.5, 1), (0.7, 2), (0.9, 3)):
+        mm = m.copy()
+        bad = rs.random(len(mm)) < frac
+        mm["trainIdx"][bad] = rs.integers(0, len(p2), bad.sum())
+        for iters, min_inl in ((200, 10), (500, 30)):
+            rng, latch = oracle.Rng(seed), oracle.Latch()
+            ctx.rng_seed(seed)
+            ctx.depth_cov_set(0, 0.0)
+            r_o = oracle.ransac_se3(p1, p2, mm, rng, latch, iters, min_inl, 3.0, 4)
+            r_g = ctx.ransac_se3(p1, p2, mm, iters, min_inl, 3.0, 4)
+            _check_se3(r_o, r_g)
+    # fewer matches than the inlier threshold -> false, identity, stream untouched
+    ctx.rng_seed(5)
+    before = ctx.rng_get_state()
+    r_g = ctx.ransac_se3(p1, p2, m[:5], 200, 10, 3.0, 4)
+    assert not r_g["ok"] and len(r_g["inliers"]) == 0 and (r_g["T"] == np.eye(4, dtype=np.float32)).all()
+    assert (before == ctx.rng_get_state()).all()
+    # identical frames: every hypothesis is perfect; all-equal-distance ties exercise the sort
+    mm = m.copy()
+    mm["distance"] = 3.0
+    rng, latch = oracle.Rng(7), oracle.Latch()
+    ctx.rng_seed(7)
+    ctx.depth_cov_set(0, 0.0)
+    _check_se3(oracle.ransac_se3(p1, p2, mm, rng, latch), ctx.ransac_se3(p1, p2, mm))
+
+
+def test_tracking_pipeline_device_resident(oracle, seq_vga):
+    """T2: extract (batched) -> match -> RansacSE3 with outlier-flag carry-over, frame to frame."""
+    import rgbdfe
+
+    cam, frames = seq_vga
+    ctx = rgbdfe.Context(0, 640, 480, 1000, 4)
+    try:
+        ctx.rng_seed(42)
+        fr = [rgbdfe.Frame(ctx) for _ in frames]
+        ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)
+        for i in range(1, len(frames)):
+            ctx.track(fr[i - 1], fr[i], i - 1)
+        res = ctx.track_results(0, len(frames) - 1)
+        orb = oracle.Orb(1000)
+        rng, latch = oracle.Rng(42), oracle.Latch()
+        prev = None
+        for i, (g, d) in enumerate(frames):
+            k, de = orb.extract(g)
+            p3 = _unproject(cam, k, d)
+            outl = np.zeros(len(k), np.uint8)
+            if prev is not None:
+                m = oracle.match(prev[1], de, prev[3], prev[2], p3, 0.9, True)
+                r = oracle.ransac_se3(prev[2], p3, m, rng, latch, 200, 10, 3.0, 4)
+                if len(m) >= 10:
+                    outl[m["trainIdx"]] = 1
+                if r["ok"]:
+                    outl[r["inliers"]["trainIdx"]] = 0
+                g_r = res[i - 1]
+                assert g_r["n_matches"] == len(m)
+                assert bool(g_r["ok"]) == r["ok"] and g_r["n_inliers"] == len(r["inliers"])
+                assert g_r["iters_executed"] == r["iters_executed"]
+                assert np.abs(g_r["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
+            gk, gd, gp, go = fr[i].download()
+            assert (gk == k).all() and (gd == de).all() and (gp == p3).all()
+            assert (go == outl).all(), f"outlier flags of frame {i}"
+            prev = (k, de, p3, outl)
+    finally:
+        ctx.close()
+
+
+def test_verify_batch_matches_per_pair_oracle(oracle):
+    """Config-4-shaped (small): one query vs keyframes, per-pair srand(seed + index)."""
+    import rgbdfe
+    import synth
+
+    n_kf, n_feat = 24, 500
+    qd, qp, kd, kp, _ = synth.synth_pair_sets(n_kf, n_feat, seed=77, overlap_frac=0.6)
+    ctx = rgbdfe.Context(0, 640, 480, n_feat, 1)
+    try:
+        db = ctx.kfdb_create(kd, kp)
+        ctx.depth_cov_set(1, (0.01 * 2.0 * 2.0) ** 2)  # latch pinned so pairs are order independent
+        res = ctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=1000, first_pair_index=5)
+        for k in range(n_kf):
+            m = oracle.match(kd[k], qd, np.zeros(n_feat, np.uint8), kp[k], qp, 0.9, True)
+            rng, latch = oracle.Rng(1000 + 5 + k), oracle.Latch()
+            latch.latched.value, latch.cov.value = 1, (0.01 * 2.0 * 2.0) ** 2
+            assert res[k]["n_matches"] == len(m)
+            if len(m) < 30:
+                assert res[k]["ok"] == 0
+                continue
+            r = oracle.ransac_se3(kp[k], qp, m, rng, latch, 200, 30, 3.0, 4)
+            assert bool(res[k]["ok"]) == r["ok"] and res[k]["n_inliers"] == len(r["inliers"]), k
+            assert res[k]["iters_executed"] == r["iters_executed"]
+            assert np.abs(res[k]["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
+        ctx.kfdb_destroy(db)
+    finally:
+        ctx.close()
