@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py — tracked frames/s of the RGB-D front end (ORB + match + SE3 RANSAC, 640x480).
+
+Workload (BASELINE.json configs[1]): ICL-NUIM-shaped synthetic 640x480 sequence, 2000 ORB
+features, kNN k=2 + ratio 0.9, RansacSE3 with 500 iterations.  One "step" = one batch of
+BATCH consecutive frames: batched extraction (K1-K6) + per-frame match and RANSAC (K7-K11)
+chained through the previous frame's outlier flags and the shared rand() stream.
+
+  value : frames/s with the frames already resident in HBM (device pointers handed to the C ABI)
+  e2e   : frames/s through the same C-ABI calls with pinned HOST buffers (H2D + result D2H timed)
+Multi-GPU (--gpus N under torchrun): single-frame tracking does not shard (every frame needs the
+previous frame's state), so ranks run independent replicas ("replicas only", weak scaling) and
+additionally time the sharded loop-pair verification, reported under "verify".
+
+--impl reference: the CPU oracle port (oracle/, the reference's algorithm restated; the reference
+itself cannot be compiled here) on all host cores, same config / metric / unit.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools"), os.path.join(ROOT, "rgbd-slam_b200", "py")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np
+
+W, H, NFEAT, ITERS, MIN_INL, RATIO = 640, 480, 2000, 500, 10, 0.9
+LEVEL_PX = [640 * 480, 533 * 400, 444 * 333, 370 * 278, 309 * 231, 257 * 193, 214 * 161, 179 * 134]
+SUM_P = sum(LEVEL_PX)
+# algorithmic bytes per frame of each extraction kernel (SURVEY 8d / DESIGN.md)
+ALG_BYTES = {
+    "k_pyramid_level(x levels)": LEVEL_PX[0] + sum(LEVEL_PX[1:]) + sum(LEVEL_PX[:-1]),
+    "k_fast_cells": SUM_P,
+    "k_gauss7": 2 * SUM_P,
+    "k_orient_describe": 60 * NFEAT,
+}
+METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
+
+
+def make_sequence(n_frames):
+    import synth
+
+    cam = synth.CAMS["icl"]
+    room = synth.Room(2345)
+    poses = synth.xyz_trajectory(1000, 2347)[:n_frames]
+    frames = [room.render(cam, R, t, 0.0, 0.0) for R, t in poses]
+    return cam, frames
+
+
+def pingpong(n):
+    order = list(range(n)) + list(range(n - 2, 0, -1))
+    i = 0
+    while True:
+        yield order[i % len(order)]
+        i += 1
+
+
+def sample_clocks_start():
+    f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+    q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    try:
+        p = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200"], stdout=f, stderr=subprocess.DEVNULL)
+    except Exception:
+        return None, f.name
+    return p, f.name
+
+
+def sample_clocks_stop(p, path, gpu_index):
+    if p is not None:
+        time.sleep(0.25)
+        p.terminate()
+        try:
+            p.wait(timeout=5)
+        except Exception:
+            p.kill()
+    sm, mx, reasons = [], 0, set()
+    try:
+        for line in open(path):
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9 or c[0] != str(gpu_index):
+                continue
+            sm.append(float(c[1]))
+            mx = max(mx, float(c[2]))
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(path)
+    except Exception:
+        pass
+    return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons)}
+
+
+def cpu_track(frames, cam, idx, threads=1):
+    """Time the oracle port over len(idx) frames per thread; returns (frames/s, seconds)."""
+    import orclib
+
+    L = orclib.lib()
+    n = len(idx)
+    g = (C.c_void_p * n)(*[frames[i][0].ctypes.data for i in idx])
+    d = (C.c_void_p * n)(*[frames[i][1].ctypes.data for i in idx])
+    done = [0] * threads
+
+    def work(t):
+        done[t] = L.orc_track_sequence(
+            n, g, d, W, H, C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"]), NFEAT, C.c_float(RATIO), ITERS,
+            C.c_uint(MIN_INL), C.c_float(3.0), C.c_uint(4), C.c_uint(42 + t), None,
+        )
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    dt = time.perf_counter() - t0
+    return sum(done) / dt, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    per_thread = 5  # frames per thread per step (4 tracked pairs + the first extraction)
+    cam, frames = make_sequence(per_thread)
+    idx = list(range(per_thread))
+    for _ in range(args.warmup):
+        cpu_track(frames, cam, idx[:2], cores)
+    t0 = time.perf_counter()
+    tracked = 0
+    for _ in range(args.steps):
+        fps, dt = cpu_track(frames, cam, idx, cores)
+        tracked += fps * dt
+    total = time.perf_counter() - t0
+    v = tracked / total
+    sample = f"{per_thread} frames x {cores} threads per step (oracle port, -O2, one tracking stream per thread)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32/f64",
+        "data": "synthetic", "config": {"workload": "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters", "path": "cpu"},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--frames", type=int, default=96)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--verify-kf", type=int, default=512, help="keyframes per GPU for the verification leg (N>1)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+
+    import rgbdfe
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    B, F = args.batch, args.frames
+    cam, frames = make_sequence(F)
+    gray_h = torch.from_numpy(np.stack([f[0] for f in frames])).pin_memory()
+    depth_h = torch.from_numpy(np.stack([f[1] for f in frames])).pin_memory()
+    gray_d, depth_d = gray_h.cuda(), depth_h.cuda()
+    ctx = rgbdfe.Context(local_rank, W, H, NFEAT, B)
+    ctx.orb_configure(NFEAT, 1.2, 8, 20, 7)
+    ctx.rng_seed(42)
+    ring = [rgbdfe.Frame(ctx) for _ in range(B + 1)]
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+    gp_h, dp_h = gray_h.numpy(), depth_h.numpy()
+    order = pingpong(F)
+    state = {"ring": ring, "have_ref": False, "inliers": [], "ok": 0, "n": 0}
+
+    def step(dev):
+        idx = [next(order) for _ in range(B)]
+        r = state["ring"]
+        cur = r[1:]
+        if dev:
+            g = [gray_d[i] for i in idx]
+            d = [depth_d[i] for i in idx]
+            fr = (C.c_void_p * B)(*[f.h for f in cur])
+            gp = (C.c_void_p * B)(*[t.data_ptr() for t in g])
+            dp = (C.c_void_p * B)(*[t.data_ptr() for t in d])
+            ctx._chk(rgbdfe.lib().rgbdfe_frames_extract(ctx.h, fr, B, gp, W, H, W, dp, W, C.c_float(cam["fx"]), C.c_float(cam["fy"]),
+                                                         C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+        else:
+            ctx.frames_extract(cur, [gp_h[i] for i in idx], [dp_h[i] for i in idx], cam)
+        first = 0 if state["have_ref"] else 1
+        for j in range(first, B):
+            ctx.track(r[j], r[j + 1], j, RATIO, True, ITERS, MIN_INL, 3.0, 4, True)
+        res = ctx.track_results(first, B - first)
+        state["ok"] += int(res["ok"].sum())
+        state["n"] += len(res)
+        state["inliers"].append(float(res["n_inliers"].mean()))
+        state["ring"] = [r[B]] + r[:B]
+        state["have_ref"] = True
+        return B
+
+    def timed(dev, steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = ctx.launches
+        e0.record(stream)
+        n = 0
+        for _ in range(steps):
+            n += step(dev)
+        e1.record(stream)
+        e1.synchronize()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return n, ms, ctx.launches - l0
+
+    for _ in range(args.warmup):
+        step(True)
+        step(False)
+    proc, path = sample_clocks_start() if rank == 0 else (None, None)
+    n_dev, ms_dev, launches = timed(True, args.steps)
+    n_e2e, ms_e2e, _ = timed(False, args.steps)
+    clocks = sample_clocks_stop(proc, path, local_rank) if rank == 0 else None
+    value = n_dev * world / (ms_dev * 1e-3)
+    e2e = n_e2e * world / (ms_e2e * 1e-3)
+
+    # ---- per-kernel timing pass (CUDA events around every kernel, separate from the headline timing) ----
+    lib = rgbdfe.lib()
+    lib.rgbdfe_profile_name.restype = C.c_char_p
+    ctx._chk(lib.rgbdfe_profile_enable(ctx.h, 1))
+    prof_steps = 2
+    for _ in range(prof_steps):
+        step(True)
+    ms_k = (C.c_double * 16)()
+    cnt_k = (C.c_longlong * 16)()
+    ctx._chk(lib.rgbdfe_profile_read(ctx.h, ms_k, cnt_k, 16))
+    ctx._chk(lib.rgbdfe_profile_enable(ctx.h, 0))
+    kernels = {lib.rgbdfe_profile_name(i).decode(): (ms_k[i], cnt_k[i]) for i in range(10)}
+    tot_ms = sum(v[0] for v in kernels.values()) or 1.0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    # dominant HBM-bound kernel of the extraction stage
+    ext = {k: v for k, v in kernels.items() if k in ALG_BYTES and v[1] > 0}
+    dom = max(ext, key=lambda k: ext[k][0])
+    dom_ms, dom_cnt = ext[dom]
+    per_launch_bytes = ALG_BYTES[dom] * B
+    achieved = per_launch_bytes / (dom_ms / dom_cnt * 1e-3) / 1e9
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
+        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+        "share_of_step": {k: round(v[0] / tot_ms, 4) for k, v in kernels.items()},
+        "ms_per_launch": {k: (v[0] / v[1] if v[1] else None) for k, v in kernels.items()},
+    }
+
+    # ---- sharded loop-pair verification (the part of the path that shards), N >= 1 ----
+    verify = None
+    try:
+        import synth
+
+        n_kf = args.verify_kf
+        qd, qp, kd, kp, _ = synth.synth_pair_sets(n_kf, 1000, seed=5678 + rank, overlap_frac=0.05)
+        qd, qp = np.ascontiguousarray(qd), np.ascontiguousarray(qp)
+        vctx = rgbdfe.Context(local_rank, W, H, 1000, 1)
+        vctx.depth_cov_set(1, (0.01 * 2.0 * 2.0) ** 2)
+        db = vctx.kfdb_create(kd, kp)
+        res_dev = torch.empty(n_kf * 84, dtype=torch.uint8, device="cuda")
+        gathered = torch.empty(world * n_kf * 84, dtype=torch.uint8, device="cuda") if world > 1 else None
+        vstream = torch.cuda.ExternalStream(vctx.stream, device=local_rank)
+
+        def vstep():
+            vctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rank * n_kf, results_dev=res_dev.data_ptr(), want_host=False)
+            if world > 1:
+                torch.cuda.current_stream().wait_stream(vstream)
+                dist.all_gather_into_tensor(gathered, res_dev)
+                vstream.wait_stream(torch.cuda.current_stream())
+
+        for _ in range(2):
+            vstep()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(vstream)
+        vs = 4
+        for _ in range(vs):
+            vstep()
+        e1.record(vstream)
+        torch.cuda.synchronize()
+        vms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([vms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            vms = float(t.item())
+        verify = {"value": vs * n_kf * world / (vms * 1e-3), "unit": "pairs/s", "pairs_per_gpu": n_kf, "features": 1000, "sharding": "keyframes block-sharded, NCCL all_gather of 84 B/pair" if world > 1 else "single GPU"}
+        vctx.kfdb_destroy(db)
+        vctx.close()
+    except Exception as ex:  # the headline metric does not depend on this leg
+        verify = {"error": str(ex)[:200]}
+
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        cores = 1
+        sample_n = 41
+        fps, dt = cpu_track(frames, cam, [i % F for i in range(sample_n)], 1)
+        cpu = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": f"{sample_n - 1} tracked frames of the same sequence, oracle port single thread, {dt:.1f} s"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32/f64",
+            "data": "synthetic",
+            "config": {"workload": "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])",
+                       "batch_frames_per_step": B, "distinct_frames": F, "l2": f"inputs larger than L2: rotating {F}-frame set, {F * (W * H * 5) / 1e6:.0f} MB",
+                       "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
+                       "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H * 5, "d2h_bytes_per_step": B * 84},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify,
+        }))
+    for f in state["ring"]:
+        f.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

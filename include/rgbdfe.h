@@ -87,6 +87,13 @@ void* rgbdfe_stream(rgbdfe_ctx* ctx);
 /* number of kernels launched by the context so far (bench gpu_launches). */
 long long rgbdfe_launch_count(const rgbdfe_ctx* ctx);
 int rgbdfe_sync(rgbdfe_ctx* ctx);
+/* Per-kernel timing with CUDA events on the context stream (bench.py roofline).
+ * enable(1) starts collecting, read() synchronises and returns the summed
+ * milliseconds and launch-group counts per kernel id (n >= 10 entries);
+ * profile_name(id) names the kernel.  Off by default: no events are recorded. */
+int rgbdfe_profile_enable(rgbdfe_ctx* ctx, int on);
+int rgbdfe_profile_read(rgbdfe_ctx* ctx, double* ms_per_kernel, long long* launches_per_kernel, int n);
+const char* rgbdfe_profile_name(int id);
 
 /* ---- Extractor / ORBextractor ---------------------------------------- */
 /* Extractor::setParameters (Features/Extractor.cpp:24-48) -> ORBextractor ctor
@@ -145,7 +152,8 @@ void rgbdfe_frame_destroy(rgbdfe_ctx* ctx, rgbdfe_frame* frame);
 /* Frame ctor hot part (Core/Frame.cpp:51,91-117): extract ORB from gray, then
  * back-project every keypoint with the metric depth map (float32, 0 = invalid)
  * and pinhole intrinsics; outlier flags reset to false.  Asynchronous on the
- * context stream; host buffers must stay valid until rgbdfe_sync().
+ * context stream; host buffers must stay valid until rgbdfe_sync().  gray/depth
+ * may be host (ideally pinned) or device pointers (cudaMemcpyDefault).
  * count frames are processed as one batch (count <= max_batch). */
 int rgbdfe_frames_extract(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
     const float* const* depth, int depth_stride_elems, float fx, float fy, float cx, float cy);

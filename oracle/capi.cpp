@@ -179,3 +179,49 @@ void orc_ransac_umeyama(const Point3f* p1, const Point3f* p2, const DMatch* m, i
 }
 void orc_umeyama3(const float* src, const float* dst, int n, float* T) { umeyama3(src, dst, n, T); }
 }
+
+// ---------------- timed CPU baseline: the whole tracked-frame path ----------------
+// Frame ctor hot part (Core/Frame.cpp:51,91-117, no lens distortion) + Tracking::visualOdometry
+// core (System/Tracking.cpp:125-130) over a sequence, single thread.  Returns frames tracked.
+extern "C" int orc_track_sequence(int nframes, const uint8_t* const* gray, const float* const* depth, int w, int h, float fx, float fy, float cx,
+    float cy, int nfeatures, float ratio, int iters, unsigned min_inl, float max_mahal, unsigned sample, unsigned seed, int* inliers_out)
+{
+    OrbExtractor orb(nfeatures, 1.2f, 8, 20, 7);
+    GlibcRand rng;
+    rng.seed(seed);
+    DepthCovLatch latch = { 0, 0.0 };
+    std::vector<KeyPoint> pk, ck;
+    std::vector<uint8_t> pd, cd, po, co;
+    std::vector<Point3f> pp, cp;
+    const float invfx = 1.0f / fx, invfy = 1.0f / fy;
+    int tracked = 0;
+    for (int f = 0; f < nframes; f++) {
+        orb.extract(gray[f], w, h, w, ck, cd);
+        cp.assign(ck.size(), Point3f { 0, 0, 0 });
+        co.assign(ck.size(), 0);
+        for (size_t i = 0; i < ck.size(); i++) {
+            const float u = ck[i].x, v = ck[i].y;
+            const float z = depth[f][(size_t)(int)v * w + (int)u];
+            if (z > 0)
+                cp[i] = Point3f { (u - cx) * z * invfx, (v - cy) * z * invfy, z };
+        }
+        if (f > 0) {
+            std::vector<DMatch> m;
+            matcher_match(pd.data(), (int)pk.size(), cd.data(), (int)ck.size(), po.data(), pp.data(), cp.data(), ratio, 1, m);
+            Se3Params prm = { iters, min_inl, max_mahal, sample };
+            Se3Result r;
+            if (m.size() >= min_inl)
+                for (const DMatch& mm : m)
+                    co[mm.trainIdx] = 1;
+            ransac_se3(pp.data(), cp.data(), m, prm, rng, latch, r, nullptr);
+            if (r.ok)
+                for (const DMatch& mm : r.inliers)
+                    co[mm.trainIdx] = 0;
+            if (inliers_out)
+                inliers_out[f - 1] = (int)r.inliers.size();
+            tracked++;
+        }
+        pk.swap(ck), pd.swap(cd), pp.swap(cp), po.swap(co);
+    }
+    return tracked;
+}

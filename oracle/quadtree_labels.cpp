@@ -16,12 +16,18 @@
 // one CTA per (frame, level) on the device (quadtree.cu).
 // Tie rule for the size sort: creation order, later-created = greater
 // (the reference compares node addresses there).
-#include "common.cuh"
+#include <vector>
+// ORACLE — TEST INFRASTRUCTURE ONLY: CPU form of the label-based quadtree formulation that
+// k_quadtree implements, kept to cross-check the formulation against the std::list restatement
+// (oracle/orb.cpp) without a GPU.  Packed candidate: x | y << 12 | score << 24.
+static inline int cand_x(unsigned c) { return c & 0xfff; }
+static inline int cand_y(unsigned c) { return (c >> 12) & 0xfff; }
+static inline int cand_s(unsigned c) { return c >> 24; }
 
 #include <algorithm>
 #include <cmath>
 
-namespace rgbdfe {
+namespace orc {
 
 namespace {
     struct QNode {
@@ -211,4 +217,13 @@ void host_quadtree(const unsigned* cand, int n, int minX, int maxX, int minY, in
         out.push_back(cand[best[id]]);
 }
 
-} // namespace rgbdfe
+} // namespace orc
+
+extern "C" int orc_quadtree_labels(const unsigned* cand, int n, int minX, int maxX, int minY, int maxY, int N, unsigned* out)
+{
+    std::vector<unsigned> o;
+    orc::host_quadtree(cand, n, minX, maxX, minY, maxY, N, o);
+    for (size_t i = 0; i < o.size(); i++)
+        out[i] = o[i];
+    return (int)o.size();
+}

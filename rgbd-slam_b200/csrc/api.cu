@@ -440,10 +440,10 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
         if (!gray[i] || !frames[i])
             return RGBDFE_E_ARG;
         fb.f[i] = *frames[i];
-        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_img + i * c->img_slot, w, gray[i], stride, w, h, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_img + i * c->img_slot, w, gray[i], stride, w, h, cudaMemcpyDefault, c->stream));
         if (depth)
             CUDA_TRY(c, cudaMemcpy2DAsync(c->d_depth + i * c->depth_slot, (size_t)w * 4, depth[i], (size_t)depth_stride * 4, (size_t)w * 4, h,
-                            cudaMemcpyHostToDevice, c->stream));
+                            cudaMemcpyDefault, c->stream));
     }
     if ((rc = launch_pyramid(c, count)) != RGBDFE_OK)
         return rc;
@@ -900,6 +900,49 @@ int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, c
         cudaFree(tmp);
     }
     return rc;
+}
+
+} // extern "C"
+
+extern "C" {
+
+int rgbdfe_profile_enable(rgbdfe_ctx* c, int on)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    for (auto& e : c->prof_events) {
+        c->prof_pool.push_back(e.a);
+        c->prof_pool.push_back(e.b);
+    }
+    c->prof_events.clear();
+    c->profiling = on != 0;
+    return RGBDFE_OK;
+}
+
+int rgbdfe_profile_read(rgbdfe_ctx* c, double* ms_per_kernel, long long* launches_per_kernel, int n)
+{
+    if (!c || !ms_per_kernel || !launches_per_kernel || n < KID_COUNT)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < n; i++)
+        ms_per_kernel[i] = 0, launches_per_kernel[i] = 0;
+    for (auto& e : c->prof_events) {
+        float ms = 0;
+        CUDA_TRY(c, cudaEventElapsedTime(&ms, e.a, e.b));
+        ms_per_kernel[e.id] += ms;
+        launches_per_kernel[e.id]++;
+    }
+    return RGBDFE_OK;
+}
+
+const char* rgbdfe_profile_name(int id)
+{
+    static const char* names[KID_COUNT] = { "k_pyramid_level(x levels)", "k_fast_cells", "k_gauss7", "k_quadtree", "k_orient_describe", "k_knn2_hamming",
+        "k_ratio_filter", "k_se3_prepare", "k_se3_hypotheses", "k_se3_replay" };
+    return (id >= 0 && id < KID_COUNT) ? names[id] : "";
 }
 
 } // extern "C"

@@ -187,6 +187,12 @@ struct rgbdfe_ctx {
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
 
+    // optional per-kernel timing (CUDA events on `stream`), see rgbdfe_profile_*
+    bool profiling = false;
+    struct ProfEvt { int id; cudaEvent_t a, b; };
+    std::vector<ProfEvt> prof_events;
+    std::vector<cudaEvent_t> prof_pool;
+
     void set_error(const std::string& s) { err = s; }
 };
 
@@ -200,6 +206,42 @@ struct rgbdfe_ctx {
     } while (0)
 
 static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+// kernel ids for rgbdfe_profile_read
+enum { KID_PYRAMID = 0, KID_FAST, KID_BLUR, KID_QUADTREE, KID_DESCRIBE, KID_KNN, KID_FILTER, KID_SE3_PREPARE, KID_SE3_HYP, KID_SE3_REPLAY, KID_COUNT };
+
+// RAII helper: times one kernel (or launch group) when ctx->profiling is on.
+struct ProfScope {
+    rgbdfe_ctx* c;
+    cudaEvent_t a = nullptr, b = nullptr;
+    int id;
+    static cudaEvent_t get(rgbdfe_ctx* c)
+    {
+        if (!c->prof_pool.empty()) {
+            cudaEvent_t e = c->prof_pool.back();
+            c->prof_pool.pop_back();
+            return e;
+        }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    ProfScope(rgbdfe_ctx* ctx, int kid) : c(ctx), id(kid)
+    {
+        if (c->profiling) {
+            a = get(c);
+            b = get(c);
+            cudaEventRecord(a, c->stream);
+        }
+    }
+    ~ProfScope()
+    {
+        if (a) {
+            cudaEventRecord(b, c->stream);
+            c->prof_events.push_back({ id, a, b });
+        }
+    }
+};
 
 namespace rgbdfe {
 // orb_image.cu

@@ -160,8 +160,12 @@ int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq
     // few pairs: split the train range over several CTAs for latency; many pairs: one split
     const int splits = npairs >= 64 ? 1 : c->knn_splits;
     dim3 grd((max_nq + KNN_THREADS - 1) / KNN_THREADS, splits, npairs);
-    k_knn2_hamming<<<grd, KNN_THREADS, 0, c->stream>>>(d_pairs, c->d_partial, c->kp_cap, splits);
-    c->launches++;
+    {
+        ProfScope prof(c, KID_KNN);
+        k_knn2_hamming<<<grd, KNN_THREADS, 0, c->stream>>>(d_pairs, c->d_partial, c->kp_cap, splits);
+        c->launches++;
+    }
+    ProfScope prof(c, KID_FILTER);
     size_t smem = (size_t)max_nt * sizeof(int);
     k_ratio_filter<<<npairs, 256, smem, c->stream>>>(d_pairs, c->d_partial, c->kp_cap, splits, ratio, discard, c->d_matches, c->kp_cap, c->d_nmatch,
         d_knn_out);

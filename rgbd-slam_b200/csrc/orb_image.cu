@@ -297,6 +297,7 @@ __global__ void __launch_bounds__(256) k_fast_cells(const OrbConfig* __restrict_
 int launch_pyramid(rgbdfe_ctx* c, int count)
 {
     const OrbConfig& cfg = c->cfg;
+    ProfScope prof(c, KID_PYRAMID);
     for (int l = 0; l < cfg.nlevels; l++) {
         const LevelDesc& L = cfg.lv[l];
         int pw = L.w + 38, ph = L.h + 38;
@@ -313,6 +314,7 @@ int launch_blur(rgbdfe_ctx* c, int count)
 {
     const OrbConfig& cfg = c->cfg;
     const int total = cfg.blur_tile_start[cfg.nlevels];
+    ProfScope prof(c, KID_BLUR);
     k_gauss7<<<dim3(total, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
@@ -321,6 +323,7 @@ int launch_blur(rgbdfe_ctx* c, int count)
 
 int launch_fast(rgbdfe_ctx* c, int count)
 {
+    ProfScope prof(c, KID_FAST);
     k_fast_cells<<<dim3(c->cfg.total_cells, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list,
         c->cell_slot);
     c->launches++;

@@ -559,6 +559,7 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
         CUDA_TRY(c, cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
+    ProfScope prof(c, KID_QUADTREE);
     k_quadtree<<<dim3(c->cfg.nlevels, count), QT_THREADS, smem, c->stream>>>(c->d_cfg, c->d_cell_count, c->d_cell_list, c->cell_slot, c->d_cand,
         c->d_label, c->cand_slot, c->d_cand_count, c->d_sel, c->sel_slot, c->d_sel_count, NC, SC);
     c->launches++;
@@ -573,6 +574,7 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
         g_pattern_uploaded[c->device] = true;
     }
     const int warps = c->kp_cap + 1; // one extra warp publishes the count
+    ProfScope prof(c, KID_DESCRIBE);
     k_orient_describe<<<dim3((warps + 7) / 8, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot, c->d_sel,
         c->sel_slot, c->d_sel_count, frames, c->d_depth, c->depth_slot, depth_stride, unproject ? 1 : 0, fx, fy, cx, cy);
     c->launches++;

@@ -477,9 +477,12 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const
         return RGBDFE_E_ARG;
     }
     const int iters = prm.iterations < MAX_ITERS ? prm.iterations : MAX_ITERS;
+    {
+    ProfScope prof(c, KID_SE3_PREPARE);
     k_se3_prepare<<<npairs, 64, 0, c->stream>>>(d_pairs, c->d_matches, c->kp_cap, c->d_nmatch, prm, update_f2, per_pair_rng, seed, first_pair_index,
         min_matches, c->d_rng, c->d_pair_rng, c->d_latch, c->d_samples, c->d_rng_used, c->d_replay, MAX_ITERS);
     c->launches++;
+    }
     const size_t hyp_smem = (size_t)c->kp_cap * 24 + (size_t)HYP_WARPS * 2 * c->mask_words * 4;
     static size_t configured = 0;
     if (hyp_smem > configured) {
@@ -496,10 +499,12 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const
             continue;
         const bool last = e >= iters;
         if (e > b) {
+            ProfScope prof(c, KID_SE3_HYP);
             k_se3_hypotheses<<<dim3((e - b + HYP_WARPS - 1) / HYP_WARPS, npairs), HYP_WARPS * 32, hyp_smem, c->stream>>>(d_pairs, c->d_matches,
                 c->kp_cap, c->d_nmatch, prm, c->d_latch, c->d_samples, c->d_hyp, c->d_hyp_mask, c->mask_words, c->d_replay, b, e);
             c->launches++;
         }
+        ProfScope prof2(c, KID_SE3_REPLAY);
         k_se3_replay<<<npairs, 32, (size_t)c->mask_words * 4, c->stream>>>(d_pairs, c->d_matches, c->kp_cap, c->d_nmatch, prm, update_f2, per_pair_rng,
             c->d_rng, c->d_latch, c->d_rng_used, c->d_hyp, c->d_hyp_mask, c->mask_words, c->d_replay, e, last ? 1 : 0, d_results, c->d_inl_pos);
         c->launches++;

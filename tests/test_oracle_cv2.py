@@ -108,3 +108,23 @@ def test_orb_pyramid_vs_cv2(oracle, seq_vga):
         assert (cv2.copyMakeBorder(cur, 19, 19, 19, 19, cv2.BORDER_REFLECT_101) == orb.level_padded(l)).all()
         assert (cv2.GaussianBlur(cur, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101) == orb.level_blurred(l)).all()
         prev = cur
+
+
+def test_label_quadtree_formulation_matches_list_restatement(oracle, seq_vga):
+    """The pass-synchronous label formulation (what k_quadtree runs) == the std::list restatement."""
+    cam, frames = seq_vga
+    L = oracle.lib()
+    for nf in (1000, 300):
+        orb = oracle.Orb(nf)
+        q = orb.tables()["quota"]
+        orb.extract(frames[0][0])
+        for l in range(8):
+            c = orb.level_candidates(l)
+            w, h = orb.level_size(l)
+            packed = (c["x"].astype(np.uint32) | (c["y"].astype(np.uint32) << 12) | (c["response"].astype(np.uint32) << 24)).astype(np.uint32)
+            for N in (int(q[l]), 5, 37, len(c) + 10):
+                ref = oracle.quadtree(c, 16, w - 16, 16, h - 16, N)
+                out = np.zeros(len(c) + 8, np.uint32)
+                n = L.orc_quadtree_labels(packed.ctypes.data_as(C.c_void_p), len(c), 16, w - 16, 16, h - 16, N, out.ctypes.data_as(C.c_void_p))
+                rp = ref["x"].astype(np.uint32) | (ref["y"].astype(np.uint32) << 12) | (ref["response"].astype(np.uint32) << 24)
+                assert n == len(ref) and (out[:n] == rp).all()
