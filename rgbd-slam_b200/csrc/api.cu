@@ -211,8 +211,9 @@ void free_orb_workspaces(rgbdfe_ctx* c)
 
 void free_pair_workspaces(rgbdfe_ctx* c)
 {
-    cudaFree(c->d_pairs), cudaFree(c->d_partial), cudaFree(c->d_matches), cudaFree(c->d_nmatch), cudaFree(c->d_samples);
+    cudaFree(c->d_pairs), cudaFree(c->d_partial), cudaFree(c->d_matches), cudaFree(c->d_sorted), cudaFree(c->d_P1), cudaFree(c->d_P2), cudaFree(c->d_w), cudaFree(c->d_nmatch), cudaFree(c->d_samples);
     cudaFree(c->d_rng_used), cudaFree(c->d_hyp), cudaFree(c->d_hyp_mask), cudaFree(c->d_replay), cudaFree(c->d_inl_pos), cudaFree(c->d_pair_rng);
+    c->d_sorted = nullptr, c->d_P1 = nullptr, c->d_P2 = nullptr, c->d_w = nullptr;
     c->d_pairs = nullptr, c->d_partial = nullptr, c->d_matches = nullptr, c->d_nmatch = nullptr, c->d_samples = nullptr;
     c->d_rng_used = nullptr, c->d_hyp = nullptr, c->d_hyp_mask = nullptr, c->d_replay = nullptr, c->d_inl_pos = nullptr, c->d_pair_rng = nullptr;
     c->pair_cap = 0;
@@ -230,6 +231,10 @@ int ensure_pairs(rgbdfe_ctx* c, int npairs)
     CUDA_TRY(c, dmalloc(&c->d_pairs, P));
     CUDA_TRY(c, dmalloc(&c->d_partial, partial_rows * K));
     CUDA_TRY(c, dmalloc(&c->d_matches, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_sorted, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_P1, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_P2, P * K));
+    CUDA_TRY(c, dmalloc(&c->d_w, P * K));
     CUDA_TRY(c, dmalloc(&c->d_nmatch, P));
     CUDA_TRY(c, dmalloc(&c->d_samples, P * MAX_ITERS * 8));
     CUDA_TRY(c, dmalloc(&c->d_rng_used, P * MAX_ITERS));
@@ -763,7 +768,7 @@ int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgb
     if (inliers && result->n_inliers > 0) {
         std::vector<rgbdfe_dmatch> sorted(nm);
         std::vector<int> pos(result->n_inliers);
-        CUDA_TRY(c, cudaMemcpy(sorted.data(), c->d_matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
+        CUDA_TRY(c, cudaMemcpy(sorted.data(), c->d_sorted, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
         CUDA_TRY(c, cudaMemcpy(pos.data(), c->d_inl_pos, (size_t)result->n_inliers * sizeof(int), cudaMemcpyDeviceToHost));
         for (int i = 0; i < result->n_inliers && i < cap; i++)
             inliers[i] = sorted[pos[i]];

@@ -128,6 +128,8 @@ struct ReplayState {
     int run;        // RANSAC loop runs for this pair
     int nm;         // matches seen
     int rng_calls;  // rand() calls consumed by the executed iterations
+    int sampled_k;     // iterations whose samples have been drawn so far
+    int sampled_calls; // rand() calls those samples consumed
 };
 
 struct rgbdfe_ctx {
@@ -170,7 +172,9 @@ struct rgbdfe_ctx {
     int knn_splits = 8;
     MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
     int4* d_partial = nullptr;      // [pairs][splits][kp_cap]
-    rgbdfe_dmatch* d_matches = nullptr; // [pairs][kp_cap]  (sorted in place by RANSAC)
+    rgbdfe_dmatch* d_matches = nullptr; // [pairs][kp_cap]  Matcher::match output (query order)
+    rgbdfe_dmatch* d_sorted = nullptr;  // [pairs][kp_cap]  std::sort'ed copy used by RANSAC
+    rgbdfe_point3f* d_P1 = nullptr; rgbdfe_point3f* d_P2 = nullptr; float* d_w = nullptr; // matched points / TFC weights, sorted order
     int* d_nmatch = nullptr;        // [pairs]
     int* d_samples = nullptr;       // [pairs][MAX_ITERS][8]
     int* d_rng_used = nullptr;      // [pairs][MAX_ITERS] rand() calls consumed after iteration k

@@ -124,17 +124,20 @@ __global__ void __launch_bounds__(256) k_ratio_filter(const MatchPair* __restric
             v = partial[((size_t)blockIdx.x * splits) * q_cap + q];
             win = v.z && s_claim[v.y] == q;
         }
-        s_scan[tid] = win;
+        const unsigned bal = __ballot_sync(0xffffffffu, win);
+        if ((tid & 31) == 0)
+            s_scan[tid >> 5] = __popc(bal);
         __syncthreads();
-        for (int off = 1; off < 256; off <<= 1) {
-            int t = tid >= off ? s_scan[tid - off] : 0;
-            __syncthreads();
-            s_scan[tid] += t;
-            __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int wv = 0; wv < 8; wv++) {
+            const int cw = s_scan[wv];
+            before += wv < (tid >> 5) ? cw : 0;
+            total += cw;
         }
         const int base = s_carry;
         if (win) {
-            const int pos = base + s_scan[tid] - 1;
+            const int pos = base + before + __popc(bal & ((1u << (tid & 31)) - 1));
             if (pos < match_cap) {
                 rgbdfe_dmatch m;
                 m.queryIdx = q;
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(256) k_ratio_filter(const MatchPair* __restric
         }
         __syncthreads();
         if (tid == 0)
-            s_carry = base + s_scan[255];
+            s_carry = base + total;
         __syncthreads();
     }
     if (tid == 0)
