@@ -778,12 +778,103 @@ int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgb
     return RGBDFE_OK;
 }
 
-int rgbdfe_ransac_umeyama(rgbdfe_ctx* c, const rgbdfe_point3f*, int, const rgbdfe_point3f*, int, const rgbdfe_dmatch*, int,
-    const rgbdfe_umeyama_params*, rgbdfe_umeyama_result*, rgbdfe_dmatch*, int)
+int rgbdfe_ransac_umeyama(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches, int nm,
+    const rgbdfe_umeyama_params* params, rgbdfe_umeyama_result* result, rgbdfe_dmatch* inliers, int cap)
 {
-    if (c)
-        c->set_error("rgbdfe_ransac_umeyama: kernel K12 not built yet");
-    return RGBDFE_E_STATE;
+    if (!c || !result || !params || nm < 0 || n1 < 0 || n2 < 0 || (nm > 0 && (!p1 || !p2 || !matches)))
+        return RGBDFE_E_ARG;
+    if (params->errorVersion != 0 && params->errorVersion != 4) {
+        // REPROJECTION / MAHALANOBIS versions dereference a null camera or read an uninitialised covariance
+        // in the reference (Ransac.cpp:15,282-321,350); they are not executable there and are refused here
+        c->set_error("ransac_umeyama: only EUCLIDEAN_ERROR (0) and ADAPTIVE_ERROR (4) are executable in the reference");
+        return RGBDFE_E_ARG;
+    }
+    if (params->usedPairs < 1 || params->usedPairs > 8) {
+        c->set_error("ransac_umeyama: usedPairs must be in [1, 8]");
+        return RGBDFE_E_ARG;
+    }
+    if (n1 > c->kp_cap || n2 > c->kp_cap || nm > c->kp_cap) {
+        c->set_error("ransac_umeyama: input exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    int M = 0; // matches that pass the depth gate (Ransac.cpp:72-83); only the count is needed on the host
+    for (int i = 0; i < nm; i++) {
+        const rgbdfe_dmatch& m = matches[i];
+        if (m.queryIdx < 0 || m.queryIdx >= n1 || m.trainIdx < 0 || m.trainIdx >= n2) {
+            c->set_error("ransac_umeyama: match index out of range");
+            return RGBDFE_E_ARG;
+        }
+        const float z1 = p1[m.queryIdx].z, z2 = p2[m.trainIdx].z;
+        if (!(z1 < 0.1f || z1 > 6.0f || z2 < 0.1f || z2 > 6.0f))
+            M++;
+    }
+    result->ok = 0;
+    for (int i = 0; i < 16; i++)
+        result->T[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    result->n_inliers = 0;
+    result->iters_executed = 0;
+    if (M < params->minimalNumberOfMatches) // Ransac.cpp:86-89
+        return RGBDFE_OK;
+    if (M < params->usedPairs) {
+        c->set_error("ransac_umeyama: fewer matches than usedPairs (the reference's getRandomMatches would never return)");
+        return RGBDFE_E_ARG;
+    }
+    // computeRANSACIteration (Ransac.cpp:449-454) for every reachable inlier ratio count / M, with the C library
+    auto ransac_iters = [](double inlierRatio) {
+        const double q = log(1 - 0.98) / log(1 - pow(inlierRatio, 3));
+        if (!(q > -2147483649.0 && q < 2147483648.0))
+            return (int)0x80000000; // what cvttsd2si yields for NaN / out-of-range, i.e. the reference binary's value
+        return int(q);
+    };
+    const int iters0 = ransac_iters(0.20); // the ctor ignores params.iterationCount (Ransac.cpp:26)
+    const int iters_min = ransac_iters(params->minimalInlierRatioThreshold);
+    std::vector<int> tab((size_t)M + 1, 0);
+    for (int k = 1; k <= M; k++)
+        tab[k] = ransac_iters((double)(float(k) / float(M)));
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, 1);
+    if (rc != RGBDFE_OK)
+        return rc;
+    rgbdfe_frame *Q = c->scratch, *T = c->scratch2;
+    cudaStream_t s = c->stream;
+    int* d_tab = nullptr;
+    UmeState* d_state = nullptr;
+    rgbdfe_umeyama_result* d_res = nullptr;
+    CUDA_TRY(c, dmalloc(&d_tab, (size_t)M + 1));
+    CUDA_TRY(c, dmalloc(&d_state, 1));
+    CUDA_TRY(c, dmalloc(&d_res, 1));
+    cudaError_t e = cudaMemcpyAsync(Q->xyz, p1, (size_t)n1 * 12, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(T->xyz, p2, (size_t)n2 * 12, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(c->d_matches, matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d_tab, tab.data(), ((size_t)M + 1) * sizeof(int), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) {
+        rc = rgbdfe::launch_ransac_umeyama(c, nm, Q->xyz, T->xyz, params->usedPairs, iters0, d_tab, iters_min, params->inlierThresholdEuclidean,
+            params->errorVersion == 4, params->minimalInlierRatioThreshold, d_state, d_res);
+        if (rc == RGBDFE_OK)
+            e = cudaStreamSynchronize(s);
+    }
+    if (e == cudaSuccess && rc == RGBDFE_OK)
+        e = cudaMemcpy(result, d_res, sizeof(*result), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rc == RGBDFE_OK && inliers && result->n_inliers > 0) {
+        std::vector<rgbdfe_dmatch> kept(M);
+        std::vector<int> pos(result->n_inliers);
+        e = cudaMemcpy(kept.data(), c->d_sorted, (size_t)M * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess)
+            e = cudaMemcpy(pos.data(), c->d_inl_pos, pos.size() * sizeof(int), cudaMemcpyDeviceToHost);
+        for (int i = 0; e == cudaSuccess && i < result->n_inliers && i < cap; i++)
+            inliers[i] = kept[pos[i]];
+        if (result->n_inliers > cap)
+            rc = RGBDFE_E_CAPACITY;
+    }
+    cudaFree(d_tab), cudaFree(d_state), cudaFree(d_res);
+    if (e != cudaSuccess) {
+        c->set_error(std::string("ransac_umeyama: ") + cudaGetErrorString(e));
+        return RGBDFE_E_CUDA;
+    }
+    return rc;
 }
 
 int rgbdfe_track(rgbdfe_ctx* c, rgbdfe_frame* ref, rgbdfe_frame* cur, float ratio, int discard_outliers, int iterations, unsigned min_inlier_th,

@@ -132,6 +132,12 @@ struct ReplayState {
     int sampled_calls; // rand() calls those samples consumed
 };
 
+// State handed from k_ume_prepare to the later K12 kernels.
+struct UmeState {
+    int M;           // matches after the depth gate (Ransac.cpp:72-83)
+    int total_calls; // rand() calls made while drawing all initial iterations
+};
+
 struct rgbdfe_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -260,4 +266,7 @@ int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq
 // ransac.cu
 int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng, unsigned seed,
     int first_pair_index, int min_matches, rgbdfe_se3_result* d_results);
+// ransac_umeyama.cu
+int launch_ransac_umeyama(rgbdfe_ctx* c, int nm, const rgbdfe_point3f* d_xyz1, const rgbdfe_point3f* d_xyz2, int used_pairs, int iters0,
+    const int* d_iters_tab, int iters_min, double th0, int adaptive, double min_ratio, UmeState* d_state, rgbdfe_umeyama_result* d_res);
 }

@@ -30,6 +30,15 @@ class RgbdfeError(RuntimeError):
 _lib = None
 
 
+class UmeParams(C.Structure):  # rgbdfe_umeyama_params
+    _fields_ = [("errorVersion", C.c_int), ("inlierThresholdEuclidean", C.c_double), ("minimalInlierRatioThreshold", C.c_double),
+                ("minimalNumberOfMatches", C.c_int), ("usedPairs", C.c_int)]
+
+
+class UmeResult(C.Structure):  # rgbdfe_umeyama_result
+    _fields_ = [("ok", C.c_int), ("T", C.c_float * 16), ("n_inliers", C.c_int), ("iters_executed", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -212,6 +221,22 @@ class Context:
             ok=bool(r["ok"]), rmse=np.float32(r["rmse"]), T=r["T21"].reshape(4, 4).copy(), inliers=inl[: r["n_inliers"]].copy(),
             iters_executed=int(r["iters_executed"]), n_matches=int(r["n_matches"]),
         )
+
+    # ---- Ransac (Umeyama) ----
+    def ransac_umeyama(self, p1, p2, matches, error_version=0, th=0.02, min_ratio=0.2, min_matches=10, used_pairs=3):
+        p1 = np.ascontiguousarray(p1, np.float32)
+        p2 = np.ascontiguousarray(p2, np.float32)
+        matches = np.ascontiguousarray(matches, DM_DTYPE)
+        prm = UmeParams(error_version, th, min_ratio, min_matches, used_pairs)
+        res = UmeResult()
+        inl = np.zeros(max(len(matches), 1), DM_DTYPE)
+        self._chk(
+            lib().rgbdfe_ransac_umeyama(
+                self.h, _p(p1), len(p1), _p(p2), len(p2), _p(matches), len(matches), C.byref(prm), C.byref(res), _p(inl), len(inl)
+            )
+        )
+        return dict(ok=bool(res.ok), T=np.array(res.T, np.float32).reshape(4, 4), inliers=inl[: res.n_inliers].copy(),
+                    iters_executed=int(res.iters_executed))
 
     # ---- device-resident pipeline ----
     def frames_extract(self, frames, grays, depths, cam):

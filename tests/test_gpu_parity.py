@@ -186,6 +186,55 @@ def test_ransac_se3_hard_cases(ctx, oracle, seq_vga):
     _check_se3(oracle.ransac_se3(p1, p2, mm, rng, latch), ctx.ransac_se3(p1, p2, mm))
 
 
+def test_ransac_umeyama_parity(ctx, oracle, seq_vga):
+    """K12 — class Ransac (Solver/Ransac.cpp): inlier list (order), pose bits, executed iterations, rand() position."""
+    cam, frames = seq_vga
+    p1, p2, m = _pair(oracle, cam, frames, 0, 2)
+    rs = np.random.default_rng(11)
+    cases = []
+    for frac in (0.0, 0.4, 0.8):
+        mm = m.copy()
+        bad = rs.random(len(mm)) < frac
+        mm["trainIdx"][bad] = rs.integers(0, len(p2), bad.sum())
+        cases.append(mm)
+    seed = 100
+    for mm in cases:
+        for ev, th, used in ((0, 0.02, 3), (4, 0.01, 3), (0, 0.05, 4)):
+            seed += 1
+            rng = oracle.Rng(seed)
+            ctx.rng_seed(seed)
+            r_o = oracle.ransac_umeyama(p1, p2, mm, rng, ev, th, 0.2, 10, used)
+            r_g = ctx.ransac_umeyama(p1, p2, mm, ev, th, 0.2, 10, used)
+            assert r_o["ok"] == r_g["ok"]
+            assert r_o["iters_executed"] == r_g["iters_executed"]
+            assert len(r_o["inliers"]) == len(r_g["inliers"]) and (r_o["inliers"] == r_g["inliers"]).all()
+            assert np.abs(r_o["T"] - r_g["T"]).max() <= POSE_TOL
+            assert (r_o["T"] == r_g["T"]).all(), "pose bits"
+            probe = oracle.Rng(1)
+            probe.buf[:] = rng.buf
+            assert _next_from_state(ctx.rng_get_state()) == probe.next(), "rand() stream position after compute()"
+    # too few matches after the depth gate -> identity, no inliers, stream untouched (Ransac.cpp:86-89)
+    ctx.rng_seed(3)
+    before = ctx.rng_get_state()
+    r_g = ctx.ransac_umeyama(p1, p2, m[:5], 0, 0.02, 0.2, 10, 3)
+    assert not r_g["ok"] and len(r_g["inliers"]) == 0 and (r_g["T"] == np.eye(4, dtype=np.float32)).all()
+    assert (before == ctx.rng_get_state()).all()
+    # inlier ratio below the gate -> identity (Ransac.cpp:168-171)
+    mm = m.copy()
+    mm["trainIdx"] = rs.integers(0, len(p2), len(mm))
+    rng = oracle.Rng(9)
+    ctx.rng_seed(9)
+    r_o = oracle.ransac_umeyama(p1, p2, mm, rng, 0, 0.02, 0.5, 10, 3)
+    r_g = ctx.ransac_umeyama(p1, p2, mm, 0, 0.02, 0.5, 10, 3)
+    assert r_o["ok"] == r_g["ok"] and r_o["iters_executed"] == r_g["iters_executed"] and len(r_g["inliers"]) == len(r_o["inliers"])
+    assert (r_o["T"] == r_g["T"]).all()
+    # the error versions that crash in the reference are refused, not emulated
+    import rgbdfe
+
+    with pytest.raises(rgbdfe.RgbdfeError):
+        ctx.ransac_umeyama(p1, p2, m, 1, 0.02, 0.2, 10, 3)
+
+
 def test_tracking_pipeline_device_resident(oracle, seq_vga):
     """T2: extract (batched) -> match -> RansacSE3 with outlier-flag carry-over, frame to frame."""
     import rgbdfe
