@@ -212,10 +212,10 @@ void free_orb_workspaces(rgbdfe_ctx* c)
 void free_pair_workspaces(rgbdfe_ctx* c)
 {
     cudaFree(c->d_pairs), cudaFree(c->d_partial), cudaFree(c->d_matches), cudaFree(c->d_sorted), cudaFree(c->d_P1), cudaFree(c->d_P2), cudaFree(c->d_w), cudaFree(c->d_nmatch), cudaFree(c->d_samples);
-    cudaFree(c->d_rng_used), cudaFree(c->d_hyp), cudaFree(c->d_hyp_mask), cudaFree(c->d_replay), cudaFree(c->d_inl_pos), cudaFree(c->d_pair_rng);
+    cudaFree(c->d_rng_used), cudaFree(c->d_hyp), cudaFree(c->d_hyp_mask), cudaFree(c->d_replay), cudaFree(c->d_inl_pos), cudaFree(c->d_pair_rng), cudaFree(c->d_hyp_ready), cudaFree(c->d_pair_lock);
     c->d_sorted = nullptr, c->d_P1 = nullptr, c->d_P2 = nullptr, c->d_w = nullptr;
     c->d_pairs = nullptr, c->d_partial = nullptr, c->d_matches = nullptr, c->d_nmatch = nullptr, c->d_samples = nullptr;
-    c->d_rng_used = nullptr, c->d_hyp = nullptr, c->d_hyp_mask = nullptr, c->d_replay = nullptr, c->d_inl_pos = nullptr, c->d_pair_rng = nullptr;
+    c->d_rng_used = nullptr, c->d_hyp = nullptr, c->d_hyp_mask = nullptr, c->d_replay = nullptr, c->d_inl_pos = nullptr, c->d_pair_rng = nullptr, c->d_hyp_ready = nullptr, c->d_pair_lock = nullptr;
     c->pair_cap = 0;
 }
 
@@ -243,6 +243,8 @@ int ensure_pairs(rgbdfe_ctx* c, int npairs)
     CUDA_TRY(c, dmalloc(&c->d_replay, P));
     CUDA_TRY(c, dmalloc(&c->d_inl_pos, P * K));
     CUDA_TRY(c, dmalloc(&c->d_pair_rng, P));
+    CUDA_TRY(c, dmalloc(&c->d_hyp_ready, P * MAX_ITERS));
+    CUDA_TRY(c, dmalloc(&c->d_pair_lock, P));
     c->pair_cap = npairs;
     return RGBDFE_OK;
 }

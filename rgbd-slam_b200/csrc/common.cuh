@@ -188,6 +188,8 @@ struct rgbdfe_ctx {
     unsigned* d_hyp_mask = nullptr; // [pairs][MAX_ITERS][mask_words]
     int mask_words = 0;
     ReplayState* d_replay = nullptr; // [pairs]
+    int* d_hyp_ready = nullptr;     // [pairs][MAX_ITERS] hypothesis published (reset by k_se3_prepare)
+    int* d_pair_lock = nullptr;     // [pairs] replay lock
     rgbdfe_se3_result* d_results = nullptr; int result_cap = 0;
     rgbdfe_se3_result* h_results = nullptr; // pinned
     int* d_inl_pos = nullptr;       // [pairs][kp_cap] positions (in the sorted match list) of the winning inliers

@@ -4,255 +4,104 @@
 // "n += 10" / break control; each iteration's refinement result depends on nothing but
 // its sample.  So:
 //   k_se3_prepare    1 CTA / pair: sorts the matches into exactly the permutation libstdc++'s
-//                    std::sort produces (parallel introsort, see cta_std_sort), gathers the
-//                    matched 3D points and TFC weights in sorted order, latches the depth
-//                    covariance, marks F2 outliers, and draws the biased 4-samples of the first
-//                    chunk of iterations from the glibc-compatible stream (samples depend only
-//                    on M, never on the data).
+//                    std::sort produces (std_sort.cuh), gathers the matched 3D points and TFC
+//                    weights in sorted order, latches the depth covariance, marks F2 outliers,
+//                    and (one warp, concurrently with the sort) draws the biased 4-samples of
+//                    the first chunk of iterations from the glibc-compatible stream — samples
+//                    depend only on the match count, never on the data.
 //   k_se3_hypotheses 1 CTA / (pair, iteration): up to 19 refinement rounds of
-//                    {TFC fit (FP32, 9 covariance lanes) -> Mahalanobis scoring of all matches
-//                    (FP64, all threads) -> ordered inlier list -> ordered FP64 error sum}.
-//   k_se3_replay     1 warp / pair: replays SolverSE3.cpp:86-101 over the hypothesis results
-//                    to find which iterations the reference would have executed, the best
-//                    model, the identity fallback (:105-117), the Frame flag updates
-//                    (:119-123), rewinds the RNG stream to the right position, and samples
-//                    the next chunk when the loop has not ended yet.
-// Hypotheses are evaluated in growing chunks; pairs whose loop already terminated skip later
-// chunks, so the common early exit costs one chunk.
-#include "introsort.cuh"
+//                    {TFC fit (FP32) -> Mahalanobis scoring of all matches (FP64, all threads)
+//                    -> ordered inlier list -> ordered FP64 error sum}.  A finished hypothesis
+//                    publishes its result and then replays SolverSE3.cpp:86-101 in iteration
+//                    order over everything published so far (one CTA at a time, under a
+//                    per-pair lock).  Once the replay sees the loop end (break / iterations
+//                    used up) the pair is finalised right there — best model, identity
+//                    fallback (:105-117), Frame flags (:119-123), rand() stream advanced by
+//                    exactly the calls of the executed iterations — and hypotheses still
+//                    running for that pair stop at their next round: the chunk costs the
+//                    latency of the iterations the reference would have run, not of its
+//                    slowest member.  If the chunk is used up the same CTA draws the next
+//                    chunk's samples.
+// Hypotheses are issued in growing chunks; chunks of a finished pair exit immediately.
+#include "rng.cuh"
 #include "se3_math.cuh"
+#include "std_sort.cuh"
 
 namespace rgbdfe {
 
 #define SE3_MAX_SAMPLE 8
 #define PREP_THREADS 256
-#define HYP_THREADS 128
+#define RNG_BLOCK 512 // rand() outputs generated per refill of the sampler's window
 
-__device__ __forceinline__ int rng_next(RngState& s)
+// smem scratch of the sampler / stream roll: unsigned lin[34 + RNG_BLOCK]; int ids[RNG_BLOCK]
+#define RNG_SCRATCH_WORDS (RNG_HIST + 2 * RNG_BLOCK)
+
+__device__ __forceinline__ int ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+
+// sampleMatches (SolverSE3.cpp:135-159) for iterations [k0, k1) of one pair; one warp.
+// Lane 0 extends the rand() window and walks the set-insert logic; all lanes convert the raw
+// words to Random::randomInt(0, M-1) values.  `st` is read and left at the position after the
+// last consumed rand() call.
+__device__ void warp_sample_chunk(unsigned* lin, int* ids, RngState* st, int M, int ss, int k0, int k1, int* __restrict__ samples,
+    int* __restrict__ used, int& calls, int lane)
 {
-    unsigned v = (unsigned)s.r[(s.idx - 31) % 34] + (unsigned)s.r[(s.idx - 3) % 34];
-    s.r[s.idx % 34] = (int)v;
-    s.idx++;
-    if (s.idx >= 34 * 1000000)
-        s.idx -= 34 * 999990;
-    return (int)(v >> 1);
-}
-
-__device__ void rng_seed(RngState& s, unsigned seed)
-{
-    // glibc srandom_r, TYPE_3: r[i] = 16807 * r[i-1] % 2147483647, then 310 discarded outputs
-    unsigned lin[34];
-    if (seed == 0)
-        seed = 1;
-    lin[0] = seed;
-    for (int i = 1; i < 31; i++) {
-        long long w = (16807LL * (int)lin[i - 1]) % 2147483647;
-        if (w < 0)
-            w += 2147483647;
-        lin[i] = (unsigned)w;
-    }
-    for (int i = 31; i < 34; i++)
-        lin[i] = lin[i - 31];
-    for (int i = 0; i < 34; i++)
-        s.r[i] = (int)lin[i];
-    s.idx = 34;
-    for (int i = 34; i < 344; i++)
-        rng_next(s);
-}
-
-// Random::randomInt (System/Random.cpp:15-20)
-__device__ __forceinline__ int random_int(RngState& s, int mn, int mx)
-{
-    int d = mx - mn + 1;
-    return int(((double)rng_next(s) / ((double)2147483647 + 1.0)) * d) + mn;
-}
-
-// sampleMatches (SolverSE3.cpp:135-159) for iterations [k0, k1); one thread.
-__device__ void sample_chunk(RngState& s, int M, int ss, int k0, int k1, int* __restrict__ samples, int* __restrict__ used, int& calls)
-{
-    for (int k = k0; k < k1; k++) {
-        int ids[SE3_MAX_SAMPLE];
-        int cnt = 0, safetyNet = 0;
-        while (cnt < ss) {
-            int id1 = random_int(s, 0, M - 1);
-            int id2 = random_int(s, 0, M - 1);
-            calls += 2;
-            if (id1 > id2)
-                id1 = id2;
-            int pos = 0; // std::set insert: ascending, duplicates ignored
-            while (pos < cnt && ids[pos] < id1)
-                pos++;
-            if (!(pos < cnt && ids[pos] == id1)) {
-                for (int j = cnt; j > pos; j--)
-                    ids[j] = ids[j - 1];
-                ids[pos] = id1;
-                cnt++;
-            }
-            if (++safetyNet > 10000)
-                break;
-        }
-        for (int j = 0; j < SE3_MAX_SAMPLE; j++)
-            samples[k * SE3_MAX_SAMPLE + j] = j < cnt ? ids[j] : -1;
-        used[k] = calls;
-    }
-}
-
-// ---------------------------------------------------------------------------------------
-// Parallel std::sort.  libstdc++'s introsort is reproduced range by range: a warp partitions
-// one range with the parallel form of __unguarded_partition — L-stoppers (a >= pivot) in
-// ascending position and R-stoppers (a <= pivot) in descending position are compacted with
-// ballots; the k-th swap of the sequential loop exchanges the k-th of each list while
-// L[k] < R[k]; the returned cut is min(L[K], R[K-1]) — which yields the same array as the
-// sequential scan (checked on the CPU against std::sort, tests/cpp/test_introsort.cpp).
-// Ranges of one recursion level are independent, so levels are processed breadth-first by
-// all warps.  Ranges <= 16 are finished by the final insertion sort, which never moves an
-// element across a range boundary, so each leaf is insertion-sorted by one thread.
-// ---------------------------------------------------------------------------------------
-struct SKey {
-    float d;
-    int i;
-};
-struct KeyLess {
-    __device__ bool operator()(const SKey& a, const SKey& b) const { return a.d < b.d; }
-};
-
-__device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos, int lane, int* cut_out)
-{
-    if (lane == 0) {
-        int mid = f + (l - f) / 2;
-        move_median_to_first_(a + f, a + f + 1, a + mid, a + l - 1, KeyLess());
-    }
-    __syncwarp();
-    const float p = a[f].d;
-    int nL = 0, nR = 0;
-    const int first = f + 1;
-    const unsigned lt = (1u << lane) - 1;
-    for (int x0 = first; x0 < l; x0 += 32) {
-        const int x = x0 + lane;
-        const bool isL = x < l && !(a[x].d < p);
-        const unsigned bal = __ballot_sync(0xffffffffu, isL);
-        if (isL)
-            Lpos[f + nL + __popc(bal & lt)] = x;
-        nL += __popc(bal);
-    }
-    for (int x0 = l - 1; x0 >= first; x0 -= 32) {
-        const int x = x0 - lane;
-        const bool isR = x >= first && !(p < a[x].d);
-        const unsigned bal = __ballot_sync(0xffffffffu, isR);
-        if (isR)
-            Rpos[f + nR + __popc(bal & lt)] = x;
-        nR += __popc(bal);
-    }
-    __syncwarp();
-    const int nmin = min(nL, nR);
-    int K = nmin;
-    for (int k0 = 0; k0 < nmin; k0 += 32) {
-        const int k = k0 + lane;
-        const bool stop = k < nmin && !(Lpos[f + k] < Rpos[f + k]);
-        const unsigned bal = __ballot_sync(0xffffffffu, stop);
-        if (bal) {
-            K = k0 + __ffs(bal) - 1;
-            break;
-        }
-    }
-    const int Lk = K < nL ? Lpos[f + K] : l;
-    const int Rprev = K > 0 ? Rpos[f + K - 1] : l;
-    const int cut = min(Lk, Rprev);
-    __syncwarp();
-    for (int k = lane; k < K; k += 32) {
-        const int x = Lpos[f + k], y = Rpos[f + k];
-        const SKey t = a[x];
-        a[x] = a[y];
-        a[y] = t;
-    }
-    __syncwarp();
-    *cut_out = cut;
-}
-
-// All PREP_THREADS threads call this.  a: smem keys; scratch: Lpos[n], Rpos[n], leaves[n],
-// lists: 2 x QCAP ranges (f, l, depth packed in int3).
-#define SORT_QCAP 512
-// Called by the first `nthr` threads of the CTA (a multiple of 32); synchronises on named barrier 1.
-#define SORT_BAR() asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory")
-__device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, int3* qa, int3* qb, int* counters /* [3] */, int nthr)
-{
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
-    if (n <= 1)
-        return;
-    if (tid == 0) {
-        int lg = 0;
-        for (int t = n; t > 1; t >>= 1)
-            lg++;
-        counters[0] = 0; // next-list size
-        counters[1] = 0; // leaf count
-        if (n > 16) {
-            qa[0] = make_int3(0, n, 2 * lg);
-            counters[2] = 1; // current-list size
-        } else {
-            leaves[0] = 0 | (n << 16);
-            counters[1] = 1;
-            counters[2] = 0;
-        }
-    }
-    SORT_BAR();
-    int3* cur = qa;
-    int3* nxt = qb;
-    while (true) {
-        const int ncur = counters[2];
-        if (ncur == 0)
-            break;
-        for (int r = warp; r < ncur; r += nwarps) {
-            const int3 rg = cur[r];
-            const int f = rg.x, l = rg.y, depth = rg.z;
-            if (depth == 0) { // heapsort fallback of __introsort_loop; the range is then fully sorted
-                if (lane == 0)
-                    heap_sort_(a + f, a + l, KeyLess());
-                __syncwarp();
-                continue;
-            }
-            int cut;
-            warp_partition_range(a, f, l, Lpos, Rpos, lane, &cut);
-            if (lane == 0) {
-                // right part [cut, l) and left part [f, cut), both with depth - 1
-                const int parts[2][2] = { { cut, l }, { f, cut } };
-                for (int s = 0; s < 2; s++) {
-                    const int pf = parts[s][0], pl = parts[s][1];
-                    if (pl - pf > 16) {
-                        const int slot = atomicAdd(&counters[0], 1);
-                        if (slot < SORT_QCAP)
-                            nxt[slot] = make_int3(pf, pl, depth - 1);
-                    } else if (pl - pf > 1) {
-                        const int slot = atomicAdd(&counters[1], 1);
-                        leaves[slot] = pf | (pl << 16);
-                    }
+    int idx0 = 0;
+    if (lane == 0)
+        idx0 = rng_window_load(st, lin);
+    int k = k0, cnt = 0, safetyNet = 0;
+    int cur[SE3_MAX_SAMPLE];
+    int total = 0; // outputs consumed since *st was read
+    while (k < k1) {
+        // expected 2 * ss draws per iteration; 25 % head room, whole pairs
+        int nb = 2 * ss * (k1 - k);
+        nb = min(RNG_BLOCK, (nb + (nb >> 2) + 8) & ~1);
+        if (lane == 0)
+            rng_extend(lin, nb);
+        __syncwarp();
+        for (int t = lane; t < nb; t += 32)
+            ids[t] = rng_random_int0(lin[RNG_HIST + t], M);
+        __syncwarp();
+        int pos = 0;
+        if (lane == 0) {
+            while (k < k1 && pos + 2 <= nb) {
+                int id1 = ids[pos];
+                const int id2 = ids[pos + 1];
+                pos += 2;
+                calls += 2;
+                if (id1 > id2)
+                    id1 = id2;
+                int p = 0; // std::set insert: ascending, duplicates ignored
+                while (p < cnt && cur[p] < id1)
+                    p++;
+                if (!(p < cnt && cur[p] == id1)) {
+                    for (int j = cnt; j > p; j--)
+                        cur[j] = cur[j - 1];
+                    cur[p] = id1;
+                    cnt++;
+                }
+                ++safetyNet;
+                if (cnt >= ss || safetyNet > 10000) {
+                    for (int j = 0; j < SE3_MAX_SAMPLE; j++)
+                        samples[k * SE3_MAX_SAMPLE + j] = j < cnt ? cur[j] : -1;
+                    used[k] = calls;
+                    k++;
+                    cnt = 0;
+                    safetyNet = 0;
                 }
             }
+            // slide the window: the state after `pos` outputs is lin[pos .. pos+34)
+            for (int t = 0; t < RNG_HIST; t++)
+                lin[t] = lin[pos + t];
         }
-        SORT_BAR();
-        if (tid == 0) {
-            counters[2] = min(counters[0], SORT_QCAP);
-            counters[0] = 0;
-        }
-        int3* t = cur;
-        cur = nxt;
-        nxt = t;
-        SORT_BAR();
+        k = __shfl_sync(0xffffffffu, k, 0);
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+        total += pos;
+        __syncwarp();
     }
-    // final insertion sort, leaf by leaf (stable insertion == __final_insertion_sort restricted to the leaf)
-    const int nleaves = counters[1];
-    for (int r = tid; r < nleaves; r += nthr) {
-        const int f = leaves[r] & 0xffff, l = leaves[r] >> 16;
-        for (int i = f + 1; i < l; i++) {
-            const SKey v = a[i];
-            int j = i - 1;
-            while (j >= f && v.d < a[j].d) {
-                a[j + 1] = a[j];
-                j--;
-            }
-            a[j + 1] = v;
-        }
-    }
-    SORT_BAR();
+    if (lane == 0)
+        rng_window_store(st, lin, idx0 + total);
+    calls = __shfl_sync(0xffffffffu, calls, 0);
+    __syncwarp();
 }
 
 // dynamic smem: SKey keys[cap]; int Lpos[cap], Rpos[cap], leaves[cap]; int3 qa[QCAP], qb[QCAP]
@@ -260,7 +109,8 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     rgbdfe_dmatch* __restrict__ sorted_all, rgbdfe_point3f* __restrict__ P1_all, rgbdfe_point3f* __restrict__ P2_all, float* __restrict__ w_all,
     int match_cap, const int* __restrict__ nmatch, Se3Params prm, int update_f2, int per_pair_rng, unsigned seed, int first_pair_index,
     int min_matches, const RngState* __restrict__ ctx_rng, RngState* __restrict__ pair_rng, DepthLatch* __restrict__ latch,
-    int* __restrict__ samples_all, int* __restrict__ rng_used_all, ReplayState* __restrict__ replay, int first_chunk)
+    int* __restrict__ samples_all, int* __restrict__ rng_used_all, ReplayState* __restrict__ replay, int* __restrict__ ready_all,
+    int* __restrict__ lock_all, int first_chunk)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SKey* keys = reinterpret_cast<SKey*>(smem_raw);
@@ -270,6 +120,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     int3* qa = reinterpret_cast<int3*>(leaves + match_cap);
     int3* qb = qa + SORT_QCAP;
     __shared__ int s_counters[4];
+    __shared__ unsigned s_rng[RNG_SCRATCH_WORDS];
 
     const int pair = blockIdx.x;
     const MatchPair P = pairs[pair];
@@ -280,11 +131,14 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     const bool run = M >= (int)prm.min_inlier_th && M >= min_matches; // SolverSE3.cpp:29 / PoseGraph.cpp:142-144
     const int ss = (int)prm.sample_size;
     const int n_first = (M >= ss) ? min(min(prm.iterations, MAX_ITERS), first_chunk) : 0;
+    for (int i = tid; i < MAX_ITERS; i += PREP_THREADS)
+        ready_all[(size_t)pair * MAX_ITERS + i] = 0;
     if (tid == 0) {
+        lock_all[pair] = 0;
         ReplayState st;
         st.n = 0;
         st.k = 0;
-        st.done = run ? 0 : 1;
+        st.done = 0;
         st.validIters = 0;
         st.bestHyp = -1;
         st.bestCount = 0;
@@ -293,7 +147,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
         st.nm = M;
         st.rng_calls = 0;
         st.sampled_k = run ? n_first : 0;
-        st.sampled_calls = 0; // filled by the sampler thread below
+        st.sampled_calls = 0; // filled by the sampler warp below
         replay[pair] = st;
     }
     if (!run)
@@ -307,19 +161,22 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
             P.t_outlier[mm.trainIdx] = 1;
     }
     __syncthreads();
-    // the sampler needs only M: one thread draws the first chunk while the others sort
+    // the sampler needs only M: the last warp draws the first chunk while the others sort
     if (tid >= PREP_THREADS - 32) {
-      if (tid == PREP_THREADS - 1) {
-        RngState s;
-        if (per_pair_rng)
-            rng_seed(s, seed + (unsigned)(first_pair_index + pair));
-        else
-            s = *ctx_rng;
+        const int lane = tid & 31;
+        RngState* s = pair_rng + pair; // working copy, continued by the replay when more chunks are needed
+        if (lane == 0) {
+            if (per_pair_rng)
+                rng_seed_state(*s, seed + (unsigned)(first_pair_index + pair), s_rng);
+            else
+                *s = *ctx_rng;
+        }
+        __syncwarp();
         int calls = 0;
-        sample_chunk(s, M, ss, 0, n_first, samples_all + (size_t)pair * MAX_ITERS * SE3_MAX_SAMPLE, rng_used_all + (size_t)pair * MAX_ITERS, calls);
-        pair_rng[pair] = s; // working copy, continued by k_se3_replay when more chunks are needed
-        replay[pair].sampled_calls = calls;
-      }
+        warp_sample_chunk(s_rng, reinterpret_cast<int*>(s_rng + RNG_HIST + RNG_BLOCK), s, M, ss, 0, n_first,
+            samples_all + (size_t)pair * MAX_ITERS * SE3_MAX_SAMPLE, rng_used_all + (size_t)pair * MAX_ITERS, calls, lane);
+        if (lane == 0)
+            replay[pair].sampled_calls = calls;
     } else
         cta_std_sort(keys, M, Lpos, Rpos, leaves, qa, qb, s_counters, PREP_THREADS - 32); // :52
     __syncthreads();
@@ -340,287 +197,90 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     }
     __syncthreads();
     // depthCovariance latch (:282-287): the first source depth that reaches errorFunction2
-    if (tid == 0 && !latch->latched) {
-        for (int j = 0; j < M; j++) {
-            const rgbdfe_point3f o = P1[j], t = P2[j];
-            if (o.z == 0.0f || t.x == 0.0f)
-                continue;
-            if (isnan(o.z) || isnan(t.z))
-                continue;
-            const double z = (double)o.z;
-            const double sd = 0.01 * z * z;
-            latch->cov = sd * sd;
-            __threadfence();
-            latch->latched = 1;
-            break;
-        }
-    }
-}
-
-// pcl::TransformationFromCorrespondences over the inlier list, one warp.  The 9 covariance
-// entries are independent recurrences given (alpha, d1, d2): lane c < 9 owns cov(i = c/3, j = c%3)
-// and tracks mean2_i and mean1_j itself, so every value goes through exactly the operations of
-// the sequential `add` (same order of points) while the dependent chain per point shrinks to
-// one component.  Lanes >= 9 mirror lane % 9.
-__device__ __forceinline__ void warp_tfc_fit(const float* __restrict__ P1f, const float* __restrict__ P2f, const float* __restrict__ w,
-    const int* __restrict__ idx, int cnt, int lane, float* T)
-{
-    const int c = lane % 9, ci = c / 3, cj = c % 3;
-    float accW = 0.0f, m1 = 0.0f, m2 = 0.0f, cv = 0.0f;
-    for (int k = 0; k < cnt; k++) {
-        const int jj = idx[k];
-        const float wt = w[jj];
-        if (wt == 0.0f)
-            continue; // NaN depth (SolverSE3.cpp:169-170) or weight == 0 (tfc.add early return)
-        const float from = P1f[jj * 3 + cj], to = P2f[jj * 3 + ci];
-        accW += wt;
-        const float alpha = wt / accW;
-        const float d1 = from - m1, d2 = to - m2;
-        const float oma = 1.0f - alpha;
-        const float ad2 = alpha * d2;
-        cv = oma * (cv + ad2 * d1);
-        m1 += alpha * d1;
-        m2 += alpha * d2;
-    }
-    Tfc tfc;
-    tfc.accW = accW;
-#pragma unroll
-    for (int e = 0; e < 9; e++)
-        tfc.cov[e] = __shfl_sync(0xffffffffu, cv, e);
-#pragma unroll
-    for (int e = 0; e < 3; e++) {
-        tfc.mean1[e] = __shfl_sync(0xffffffffu, m1, e);     // lanes (0, j)
-        tfc.mean2[e] = __shfl_sync(0xffffffffu, m2, 3 * e); // lanes (i, 0)
-    }
-    tfc.transform(T);
-}
-
-// dynamic smem: double d2[cap]; int idx[cap]; unsigned char flag[cap]; unsigned cur_mask[mw], ref_mask[mw]
-__global__ void __launch_bounds__(HYP_THREADS) k_se3_hypotheses(const rgbdfe_point3f* __restrict__ P1_all, const rgbdfe_point3f* __restrict__ P2_all,
-    const float* __restrict__ w_all, int match_cap, const int* __restrict__ nmatch, Se3Params prm, const DepthLatch* __restrict__ latch,
-    const int* __restrict__ samples_all, HypOut* __restrict__ hyp_all, unsigned* __restrict__ mask_all, int mask_words,
-    const ReplayState* __restrict__ replay, int hyp_begin, int hyp_end)
-{
-    const int pair = blockIdx.y;
-    const ReplayState st = replay[pair];
-    const int h = hyp_begin + blockIdx.x;
-    if (st.done || !st.run || h >= hyp_end || h >= st.sampled_k)
-        return;
-    const int M = nmatch[pair];
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* sd2 = reinterpret_cast<double*>(smem_raw);
-    int* idx = reinterpret_cast<int*>(sd2 + match_cap);
-    unsigned* cur_mask = reinterpret_cast<unsigned*>(idx + match_cap);
-    unsigned* ref_mask = cur_mask + mask_words;
-    unsigned char* flag = reinterpret_cast<unsigned char*>(ref_mask + mask_words);
-    __shared__ float sT[16], sRefT[16];
-    __shared__ int s_cnt, s_stop, s_refCount;
-    __shared__ double s_refErr;
-
-    const rgbdfe_point3f* P1 = P1_all + (size_t)pair * match_cap;
-    const rgbdfe_point3f* P2 = P2_all + (size_t)pair * match_cap;
-    const float* P1f = reinterpret_cast<const float*>(P1);
-    const float* P2f = reinterpret_cast<const float*>(P2);
-    const float* w = w_all + (size_t)pair * match_cap;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int words = (M + 31) >> 5;
-    if (tid == 0) {
-        const int* s = samples_all + ((size_t)pair * MAX_ITERS + h) * SE3_MAX_SAMPLE;
-        int c = 0;
-        for (int j = 0; j < SE3_MAX_SAMPLE; j++)
-            if (s[j] >= 0)
-                idx[c++] = s[j];
-        s_cnt = c;
-        s_stop = 0;
-        s_refCount = 0;
-        s_refErr = 1e6;
-        for (int i = 0; i < 16; i++)
-            sRefT[i] = (i % 5 == 0) ? 1.0f : 0.0f;
-    }
-    for (int i = tid; i < words; i += HYP_THREADS)
-        ref_mask[i] = 0;
-    __syncthreads();
-    const double C = latch->cov;
-    const double th = (double)(prm.max_mahal * prm.max_mahal);
-
-    for (int refinements = 1; refinements < 20; refinements++) {
-        if (warp == 0) { // getTransformFromMatches (:161-179)
-            float T[16];
-            warp_tfc_fit(P1f, P2f, w, idx, s_cnt, lane, T);
-            if (lane < 16)
-                sT[lane] = T[lane];
-        }
-        __syncthreads();
-        // computeInliersAndError (:181-214): score all matches
-        double Td[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++)
-            Td[i] = (double)sT[i];
-        for (int j = tid; j < M; j += HYP_THREADS) {
-            const rgbdfe_point3f o = P1[j], t = P2[j];
-            bool in = false;
-            double md = 0.0;
-            if (!(o.z == 0.0f || t.x == 0.0f)) {
-                md = mahal2(o, t, Td, C, prm.rcx, prm.rcy);
-                in = !(md > th) && (md >= 0.0);
+    if (tid < 32 && !latch->latched) {
+        for (int j0 = 0; j0 < M; j0 += 32) {
+            const int j = j0 + tid;
+            bool hit = false;
+            rgbdfe_point3f o = { 0.f, 0.f, 0.f };
+            if (j < M) {
+                o = P1[j];
+                const rgbdfe_point3f t = P2[j];
+                hit = !(o.z == 0.0f || t.x == 0.0f) && !(isnan(o.z) || isnan(t.z));
             }
-            flag[j] = in;
-            sd2[j] = md;
-        }
-        __syncthreads();
-        if (warp == 0) {
-            // ordered inlier list + bitmask, then the FP64 error sum in match order
-            int base = 0;
-            for (int wd = 0; wd < words; wd++) {
-                const int j = wd * 32 + lane;
-                const bool in = j < M && flag[j];
-                const unsigned bal = __ballot_sync(0xffffffffu, in);
-                if (in)
-                    idx[base + __popc(bal & ((1u << lane) - 1))] = j;
-                if (lane == 0)
-                    cur_mask[wd] = bal;
-                base += __popc(bal);
-            }
-            __syncwarp();
-            if (lane == 0) {
-                const int cnt = base;
-                double sum = 0.0;
-                for (int k = 0; k < cnt; k++)
-                    sum += sd2[idx[k]];
-                double err = 1e9;
-                if (cnt >= 3)
-                    err = sqrt(sum / (double)cnt);
-                s_cnt = cnt;
-                int stop = 0, accept = 0;
-                if (cnt < (int)prm.min_inlier_th || err > (double)prm.max_mahal)
-                    stop = 1;
-                else if (cnt >= s_refCount && err <= s_refErr) {
-                    accept = 1;
-                    if (cnt == s_refCount)
-                        stop = 1;
-                    s_refErr = err;
-                    s_refCount = cnt;
-                } else
-                    stop = 1;
-                s_stop = stop | (accept << 1);
-            }
-        }
-        __syncthreads();
-        const int ctl = s_stop;
-        if (ctl & 2) { // vRefinedMatches = vInlierMatches; refinedTransformation = transformation
-            for (int i = tid; i < words; i += HYP_THREADS)
-                ref_mask[i] = cur_mask[i];
-            if (tid < 16)
-                sRefT[tid] = sT[tid];
-        }
-        __syncthreads();
-        if (ctl & 1)
-            break;
-    }
-    HypOut* out = hyp_all + (size_t)pair * MAX_ITERS + h;
-    if (tid == 0) {
-        out->count = s_refCount;
-        out->err = s_refErr;
-    }
-    if (tid < 16)
-        out->T[tid] = sRefT[tid];
-    unsigned* om = mask_all + ((size_t)pair * MAX_ITERS + h) * mask_words;
-    for (int i = tid; i < words; i += HYP_THREADS)
-        om[i] = ref_mask[i];
-}
-
-// One warp per pair.  dynamic smem: unsigned mask[mask_words] (identity fallback)
-__global__ void __launch_bounds__(32) k_se3_replay(const MatchPair* __restrict__ pairs, const rgbdfe_dmatch* __restrict__ sorted_all,
-    const rgbdfe_point3f* __restrict__ P1_all, const rgbdfe_point3f* __restrict__ P2_all, int match_cap, Se3Params prm, int update_f2,
-    int per_pair_rng, RngState* __restrict__ ctx_rng, RngState* __restrict__ pair_rng, const DepthLatch* __restrict__ latch,
-    int* __restrict__ samples_all, int* __restrict__ rng_used_all, const HypOut* __restrict__ hyp_all, const unsigned* __restrict__ mask_all,
-    int mask_words, ReplayState* __restrict__ replay, int hyp_end, int next_end, rgbdfe_se3_result* __restrict__ results,
-    int* __restrict__ inl_pos_all)
-{
-    extern __shared__ unsigned s_mask[];
-    const int pair = blockIdx.x, lane = threadIdx.x;
-    ReplayState st = replay[pair];
-    if (st.done == 2)
-        return; // already finalised in an earlier stage
-    const int M = st.nm;
-    const MatchPair P = pairs[pair];
-    const rgbdfe_dmatch* m = sorted_all + (size_t)pair * match_cap;
-    const rgbdfe_point3f* P1 = P1_all + (size_t)pair * match_cap;
-    const rgbdfe_point3f* P2 = P2_all + (size_t)pair * match_cap;
-    rgbdfe_se3_result* res = results + pair;
-    int* inl_pos = inl_pos_all + (size_t)pair * match_cap;
-
-    if (!st.run) {
-        if (lane == 0) {
-            res->ok = 0;
-            res->rmse = 1e6f;
-            for (int i = 0; i < 16; i++)
-                res->T21[i] = (i % 5 == 0) ? 1.0f : 0.0f;
-            res->n_inliers = 0;
-            res->iters_executed = 0;
-            res->n_matches = M;
-            st.done = 2;
-            replay[pair] = st;
-        }
-        return;
-    }
-    const bool Mok = M >= (int)prm.sample_size;
-    const int max_iters = min(prm.iterations, MAX_ITERS);
-    if (!st.done) {
-        // every lane replays redundantly (uniform control flow)
-        bool broke = false;
-        const HypOut* hyp = hyp_all + (size_t)pair * MAX_ITERS;
-        while (st.n < max_iters && Mok && st.k < hyp_end && st.k < st.sampled_k) {
-            const int cnt = hyp[st.k].count;
-            const double err = hyp[st.k].err;
-            const int k = st.k;
-            st.k++;
-            if (cnt > 0) {
-                st.validIters++;
-                if (err <= (double)st.rmse && cnt >= st.bestCount && cnt >= (int)prm.min_inlier_th) {
-                    st.rmse = (float)err;
-                    st.bestHyp = k;
-                    st.bestCount = cnt;
-                    if ((double)cnt > M * 0.5)
-                        st.n += 10;
-                    if ((double)cnt > M * 0.75)
-                        st.n += 10;
-                    if ((double)cnt > M * 0.8) {
-                        broke = true;
-                        break;
-                    }
+            const unsigned bal = __ballot_sync(0xffffffffu, hit);
+            if (bal) {
+                if (tid == __ffs(bal) - 1) {
+                    const double z = (double)o.z;
+                    const double sd = 0.01 * z * z;
+                    latch->cov = sd * sd;
+                    __threadfence();
+                    latch->latched = 1;
                 }
+                break;
             }
-            st.n++;
         }
-        if (broke || st.n >= max_iters || !Mok)
-            st.done = 1;
     }
-    if (!st.done) {
-        // the loop goes on: draw the samples of the next chunk, continuing the pair's stream
-        if (lane == 0) {
-            const int k1 = min(next_end, max_iters);
-            if (k1 > st.sampled_k) {
-                RngState s = pair_rng[pair];
-                int calls = st.sampled_calls;
-                sample_chunk(s, M, (int)prm.sample_size, st.sampled_k, k1, samples_all + (size_t)pair * MAX_ITERS * SE3_MAX_SAMPLE,
-                    rng_used_all + (size_t)pair * MAX_ITERS, calls);
-                pair_rng[pair] = s;
-                st.sampled_calls = calls;
-                st.sampled_k = k1;
-            }
-            replay[pair] = st;
-        }
-        return;
-    }
-    // ---- finalise ----
-    st.rng_calls = st.k > 0 ? rng_used_all[(size_t)pair * MAX_ITERS + st.k - 1] : 0;
-    if (!per_pair_rng && lane == 0) {
-        RngState s = *ctx_rng;
-        for (int i = 0; i < st.rng_calls; i++)
-            rng_next(s);
-        *ctx_rng = s;
-    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Sequential control of the RANSAC loop, replayed over published hypotheses (one warp,
+// uniform control flow; lane 0 owns the stores).
+// ---------------------------------------------------------------------------------------
+struct ReplayCtx {
+    const MatchPair* pairs;
+    const rgbdfe_dmatch* sorted_all;
+    const rgbdfe_point3f *P1_all, *P2_all;
+    int match_cap;
+    Se3Params prm;
+    int update_f2, per_pair_rng;
+    RngState *ctx_rng, *pair_rng;
+    const DepthLatch* latch;
+    int *samples_all, *rng_used_all;
+    const HypOut* hyp_all;
+    const unsigned* mask_all;
+    int mask_words;
+    ReplayState* replay;
+    int *ready_all, *lock_all;
+    rgbdfe_se3_result* results;
+    int* inl_pos_all;
+};
+
+__device__ __forceinline__ ReplayState load_state(const ReplayState* p)
+{
+    const volatile int* v = reinterpret_cast<const volatile int*>(p);
+    ReplayState st;
+    int* d = reinterpret_cast<int*>(&st);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(ReplayState) / sizeof(int)); i++)
+        d[i] = v[i];
+    return st;
+}
+__device__ __forceinline__ void store_state(ReplayState* p, const ReplayState& st)
+{
+    volatile int* v = reinterpret_cast<volatile int*>(p);
+    const int* s = reinterpret_cast<const int*>(&st);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(ReplayState) / sizeof(int)); i++)
+        v[i] = s[i];
+}
+
+// Loop ended: pick the model, identity fallback, Frame flags, result, stream position.
+// scratch: unsigned[RNG_SCRATCH_WORDS + mask_words] of shared memory.
+__device__ void warp_finalize(const ReplayCtx& R, int pair, ReplayState& st, unsigned* scratch, int lane)
+{
+    const Se3Params& prm = R.prm;
+    const int M = st.nm, match_cap = R.match_cap;
+    const MatchPair P = R.pairs[pair];
+    const rgbdfe_dmatch* m = R.sorted_all + (size_t)pair * match_cap;
+    const rgbdfe_point3f* P1 = R.P1_all + (size_t)pair * match_cap;
+    const rgbdfe_point3f* P2 = R.P2_all + (size_t)pair * match_cap;
+    rgbdfe_se3_result* res = R.results + pair;
+    int* inl_pos = R.inl_pos_all + (size_t)pair * match_cap;
+    unsigned* s_mask = scratch + RNG_SCRATCH_WORDS;
+
+    st.rng_calls = st.k > 0 ? R.rng_used_all[(size_t)pair * MAX_ITERS + st.k - 1] : 0;
+    if (!R.per_pair_rng && lane == 0)
+        rng_advance(scratch, R.ctx_rng, st.rng_calls, 2 * RNG_BLOCK); // the process stream moves by what the executed iterations drew
     float T[16];
 #pragma unroll
     for (int i = 0; i < 16; i++)
@@ -628,6 +288,8 @@ __global__ void __launch_bounds__(32) k_se3_replay(const MatchPair* __restrict__
     int n_inl = 0;
     float rmse = st.rmse;
     const unsigned* mask = nullptr;
+    bool mask_global = false;
+    const int words = (M + 31) >> 5;
     if (st.validIters == 0) {
         // identity fallback (SolverSE3.cpp:105-117)
         const double th = (double)(prm.max_mahal * prm.max_mahal);
@@ -637,8 +299,7 @@ __global__ void __launch_bounds__(32) k_se3_replay(const MatchPair* __restrict__
 #pragma unroll
         for (int i = 0; i < 16; i++)
             Td[i] = (double)T[i];
-        const int words = (M + 31) >> 5;
-        const double C = latch->cov;
+        const double C = R.latch->cov;
         for (int w = 0; w < words; w++) {
             const int j = w * 32 + lane;
             double d2 = 0.0;
@@ -673,24 +334,24 @@ __global__ void __launch_bounds__(32) k_se3_replay(const MatchPair* __restrict__
             mask = s_mask;
         }
     } else if (st.bestHyp >= 0) {
-        const HypOut* h = hyp_all + (size_t)pair * MAX_ITERS + st.bestHyp;
+        const HypOut* h = R.hyp_all + (size_t)pair * MAX_ITERS + st.bestHyp;
 #pragma unroll
         for (int i = 0; i < 16; i++)
-            T[i] = h->T[i];
+            T[i] = __ldcg(&h->T[i]);
         n_inl = st.bestCount;
-        mask = mask_all + ((size_t)pair * MAX_ITERS + st.bestHyp) * mask_words;
+        mask = R.mask_all + ((size_t)pair * MAX_ITERS + st.bestHyp) * R.mask_words;
+        mask_global = true;
     }
     const int ok = n_inl >= (int)prm.min_inlier_th ? 1 : 0;
     // inlier positions (sorted-match order) + Frame::setInlier (:119-123)
     if (mask && n_inl > 0) {
         int base = 0;
-        const int words = (M + 31) >> 5;
         for (int w = 0; w < words; w++) {
-            const unsigned bits = mask[w];
+            const unsigned bits = mask_global ? __ldcg(&mask[w]) : mask[w];
             if (bits & (1u << lane)) {
                 const int j = w * 32 + lane;
                 inl_pos[base + __popc(bits & ((1u << lane) - 1))] = j;
-                if (ok && update_f2 && P.t_outlier)
+                if (ok && R.update_f2 && P.t_outlier)
                     P.t_outlier[m[j].trainIdx] = 0;
             }
             base += __popc(bits);
@@ -704,9 +365,465 @@ __global__ void __launch_bounds__(32) k_se3_replay(const MatchPair* __restrict__
         res->n_inliers = n_inl;
         res->iters_executed = st.k;
         res->n_matches = M;
-        st.done = 2;
-        replay[pair] = st;
     }
+}
+
+// Called by warp 0 of a CTA (all 32 lanes).  chunk_end: hypotheses [.., chunk_end) belong to this
+// launch; next_end: where the next chunk will end (samples are drawn up to there when the loop
+// goes on).
+__device__ void warp_try_replay(const ReplayCtx& R, int pair, int chunk_end, int next_end, unsigned* scratch, int lane)
+{
+    ReplayState* rp = R.replay + pair;
+    const int* ready = R.ready_all + (size_t)pair * MAX_ITERS;
+    int* lock = R.lock_all + pair;
+    const Se3Params& prm = R.prm;
+    for (;;) {
+        int got = 0;
+        if (lane == 0)
+            got = atomicCAS(lock, 0, 1) == 0;
+        got = __shfl_sync(0xffffffffu, got, 0);
+        if (!got)
+            return; // the holder re-checks the ready flags after it releases
+        __threadfence();
+        ReplayState st = load_state(rp);
+        if (st.done == 2) {
+            if (lane == 0)
+                atomicExch(lock, 0);
+            return;
+        }
+        const int M = st.nm;
+        if (!st.run) {
+            if (lane == 0) {
+                rgbdfe_se3_result* res = R.results + pair;
+                res->ok = 0;
+                res->rmse = 1e6f;
+                for (int i = 0; i < 16; i++)
+                    res->T21[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+                res->n_inliers = 0;
+                res->iters_executed = 0;
+                res->n_matches = M;
+                st.done = 2;
+                store_state(rp, st);
+                __threadfence();
+                atomicExch(lock, 0);
+            }
+            return;
+        }
+        const bool Mok = M >= (int)prm.sample_size;
+        const int max_iters = min(prm.iterations, MAX_ITERS);
+        if (!st.done) {
+            bool broke = false;
+            const HypOut* hyp = R.hyp_all + (size_t)pair * MAX_ITERS;
+            while (st.n < max_iters && Mok && st.k < chunk_end && st.k < st.sampled_k) {
+                if (!ld_volatile(&ready[st.k]))
+                    break;
+                __threadfence();
+                const int cnt = __ldcg(&hyp[st.k].count);
+                const double err = __ldcg(&hyp[st.k].err);
+                const int k = st.k;
+                st.k++;
+                if (cnt > 0) {
+                    st.validIters++;
+                    if (err <= (double)st.rmse && cnt >= st.bestCount && cnt >= (int)prm.min_inlier_th) {
+                        st.rmse = (float)err;
+                        st.bestHyp = k;
+                        st.bestCount = cnt;
+                        if ((double)cnt > M * 0.5)
+                            st.n += 10;
+                        if ((double)cnt > M * 0.75)
+                            st.n += 10;
+                        if ((double)cnt > M * 0.8) {
+                            broke = true;
+                            break;
+                        }
+                    }
+                }
+                st.n++;
+            }
+            if (broke || st.n >= max_iters || !Mok)
+                st.done = 1;
+        }
+        if (st.done) {
+            if (lane == 0)
+                *reinterpret_cast<volatile int*>(&rp->done) = 1; // running hypotheses of this pair stop at their next round
+            warp_finalize(R, pair, st, scratch, lane);
+            st.done = 2;
+            if (lane == 0) {
+                store_state(rp, st);
+                __threadfence();
+                atomicExch(lock, 0);
+            }
+            return;
+        }
+        // the loop goes on; once this chunk is used up, draw the next chunk's samples (continuing the pair's stream)
+        const int k1 = min(next_end, max_iters);
+        if (st.k >= st.sampled_k && k1 > st.sampled_k) {
+            int calls = st.sampled_calls;
+            warp_sample_chunk(scratch, reinterpret_cast<int*>(scratch + RNG_HIST + RNG_BLOCK), R.pair_rng + pair, M, (int)prm.sample_size,
+                st.sampled_k, k1, R.samples_all + (size_t)pair * MAX_ITERS * SE3_MAX_SAMPLE, R.rng_used_all + (size_t)pair * MAX_ITERS, calls, lane);
+            st.sampled_calls = calls;
+            st.sampled_k = k1;
+        }
+        if (lane == 0) {
+            store_state(rp, st);
+            __threadfence();
+            atomicExch(lock, 0);
+            __threadfence();
+        }
+        __syncwarp();
+        // a hypothesis may have been published while the lock was held (its CTA then gave up): look again
+        const bool again = st.k < chunk_end && st.k < st.sampled_k && ld_volatile(&ready[st.k]);
+        if (!again)
+            return;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// One hypothesis = one CTA.  Shared memory (dynamic), capA = cap rounded up to 4:
+//   double g_d2[capA]                 d^2 of the current inliers, list order
+//   float  g_w[capA], g_alpha[capA]   TFC weight / accumulated weight -> alpha, list order
+//   float  g_f[3][capA], g_t[3][capA] matched points of the current inliers (SoA), list order
+//   unsigned maskA[mw], maskB[mw]     inlier bitmasks (refined / current)
+//   int wbase[mw]                     per-word inlier counts -> exclusive prefix
+// The same bytes are reused as scratch by the replay (RNG window, identity-fallback mask).
+// ---------------------------------------------------------------------------------------
+template <int THREADS>
+__device__ __forceinline__ void group_bar()
+{
+    asm volatile("bar.sync 1, %0;" ::"r"(THREADS - 32) : "memory");
+}
+
+// pcl::TransformationFromCorrespondences over the gathered list (SolverSE3.cpp:161-179), run by
+// every warp except warp 1.  The reference's `add` is one sequential recurrence per point; here
+//   (1) thread 0 forms the running weight sums in list order (one dependent FADD per point),
+//   (2) all threads turn them into alpha = w / accW (the division leaves the critical chain),
+//   (3) warp 0 runs the mean / covariance recurrences: lane c < 9 owns cov(c/3, c%3) and tracks
+//       mean2[c/3], mean1[c%3] itself, so every value goes through exactly the operations of the
+//       sequential `add` while the dependent chain per point is sub-mul-add.
+// ctl: when non-null, warp 0 polls it and gives up as soon as the round's decision is "stop".
+template <int THREADS>
+__device__ void group_tfc_fit(const float* g_w, float* g_alpha, const float* g_f, const float* g_t, int capA, int cnt, float* Tout,
+    const volatile int* ctl, int tid)
+{
+    const int lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        float acc = 0.0f;
+        int k = 0;
+        for (; k + 4 <= cnt; k += 4) {
+            const float4 w4 = *reinterpret_cast<const float4*>(g_w + k);
+            float4 a4;
+            acc = (w4.x != 0.0f) ? acc + w4.x : acc; // weight == 0: tfc.add returns early / NaN depth skipped
+            a4.x = acc;
+            acc = (w4.y != 0.0f) ? acc + w4.y : acc;
+            a4.y = acc;
+            acc = (w4.z != 0.0f) ? acc + w4.z : acc;
+            a4.z = acc;
+            acc = (w4.w != 0.0f) ? acc + w4.w : acc;
+            a4.w = acc;
+            *reinterpret_cast<float4*>(g_alpha + k) = a4;
+        }
+        for (; k < cnt; k++) {
+            const float w = g_w[k];
+            acc = (w != 0.0f) ? acc + w : acc;
+            g_alpha[k] = acc;
+        }
+    }
+    group_bar<THREADS>();
+    const int gtid = warp == 0 ? lane : tid - 32;
+    for (int k = gtid; k < cnt; k += THREADS - 32) {
+        const float w = g_w[k];
+        if (w != 0.0f)
+            g_alpha[k] = w / g_alpha[k];
+    }
+    group_bar<THREADS>();
+    if (warp != 0)
+        return;
+    const int c = lane % 9, ci = c / 3, cj = c % 3;
+    const float* gf = g_f + cj * capA;
+    const float* gt = g_t + ci * capA;
+    float m1 = 0.0f, m2 = 0.0f, cv = 0.0f;
+    for (int k = 0; k < cnt; k += 4) {
+        if (ctl && (k & 63) == 0) {
+            const int v = *ctl;
+            if (v >= 0 && (v & 1))
+                return; // this round stops the refinement: the fit would be discarded
+        }
+        const float4 w4 = *reinterpret_cast<const float4*>(g_w + k);
+        const float4 a4 = *reinterpret_cast<const float4*>(g_alpha + k);
+        const float4 x4 = *reinterpret_cast<const float4*>(gf + k);
+        const float4 y4 = *reinterpret_cast<const float4*>(gt + k);
+        const float ww[4] = { w4.x, w4.y, w4.z, w4.w }, aa[4] = { a4.x, a4.y, a4.z, a4.w };
+        const float xx[4] = { x4.x, x4.y, x4.z, x4.w }, yy[4] = { y4.x, y4.y, y4.z, y4.w };
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (k + u < cnt && ww[u] != 0.0f) {
+                const float alpha = aa[u];
+                const float d1 = xx[u] - m1, d2 = yy[u] - m2;
+                const float oma = 1.0f - alpha;
+                const float ad2 = alpha * d2;
+                cv = oma * (cv + ad2 * d1);
+                m1 += alpha * d1;
+                m2 += alpha * d2;
+            }
+        }
+    }
+    Tfc tfc;
+    tfc.accW = 0.0f;
+#pragma unroll
+    for (int e = 0; e < 9; e++)
+        tfc.cov[e] = __shfl_sync(0xffffffffu, cv, e);
+#pragma unroll
+    for (int e = 0; e < 3; e++) {
+        tfc.mean1[e] = __shfl_sync(0xffffffffu, m1, e);     // lanes (0, j)
+        tfc.mean2[e] = __shfl_sync(0xffffffffu, m2, 3 * e); // lanes (i, 0)
+    }
+    float T[16];
+    tfc.transform(T);
+    if (lane < 16)
+        Tout[lane] = T[lane];
+}
+
+template <int THREADS, int NPT>
+__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
+{
+    constexpr int NW = THREADS / 32;
+    const int pair = blockIdx.y, h = hyp_begin + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int match_cap = R.match_cap, capA = (match_cap + 3) & ~3, mw = R.mask_words;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* g_d2 = reinterpret_cast<double*>(smem_raw);
+    float* g_w = reinterpret_cast<float*>(g_d2 + capA);
+    float* g_alpha = g_w + capA;
+    float* g_f = g_alpha + capA;
+    float* g_t = g_f + 3 * capA;
+    unsigned* maskA = reinterpret_cast<unsigned*>(g_t + 3 * capA);
+    unsigned* maskB = maskA + mw;
+    int* wbase = reinterpret_cast<int*>(maskB + mw);
+    unsigned* scratch = reinterpret_cast<unsigned*>(smem_raw);
+    __shared__ float sT[2][16], sRefT[16];
+    __shared__ int s_active, s_M, s_cnt, s_ctl, s_abort, s_refCount;
+    __shared__ double s_refErr;
+
+    if (tid == 0) {
+        const ReplayState* rp = R.replay + pair;
+        const int done = ld_volatile(&rp->done), run = ld_volatile(&rp->run), sk = ld_volatile(&rp->sampled_k);
+        s_active = (!done && run && h < hyp_end && h < sk) ? 1 : 0;
+        s_M = ld_volatile(&rp->nm);
+        s_abort = 0;
+        s_refCount = 0;
+        s_refErr = 1e6;
+    }
+    __syncthreads();
+    if (!s_active) {
+        // nothing to evaluate; the first CTA of the launch still drives the replay (pairs without a loop, exhausted iterations)
+        if (blockIdx.x == 0 && warp == 0)
+            warp_try_replay(R, pair, hyp_end, next_end, scratch, lane);
+        return;
+    }
+    const int M = s_M, words = (M + 31) >> 5;
+    const rgbdfe_point3f* P1 = R.P1_all + (size_t)pair * match_cap;
+    const rgbdfe_point3f* P2 = R.P2_all + (size_t)pair * match_cap;
+    const float* P1f = reinterpret_cast<const float*>(P1);
+    const float* P2f = reinterpret_cast<const float*>(P2);
+    const float* w = w_all + (size_t)pair * match_cap;
+    const Se3Params prm = R.prm;
+    const double C = R.latch->cov;
+    const double th = (double)(prm.max_mahal * prm.max_mahal);
+
+    auto gather = [&](int k, int j) {
+        g_w[k] = w[j];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            g_f[c * capA + k] = P1f[j * 3 + c];
+            g_t[c * capA + k] = P2f[j * 3 + c];
+        }
+    };
+
+    unsigned* ref_m = maskA;
+    unsigned* cur_m = maskB;
+    for (int i = tid; i < words; i += THREADS)
+        maskA[i] = 0;
+    if (tid < 16)
+        sRefT[tid] = (tid % 5 == 0) ? 1.0f : 0.0f;
+    {
+        const int* s = R.samples_all + ((size_t)pair * MAX_ITERS + h) * SE3_MAX_SAMPLE;
+        if (tid < SE3_MAX_SAMPLE) {
+            const int j = s[tid]; // ascending ids first, then -1 padding
+            if (j >= 0)
+                gather(tid, j);
+        }
+        if (tid == 0) {
+            int c = 0;
+            for (int j = 0; j < SE3_MAX_SAMPLE; j++)
+                c += s[j] >= 0 ? 1 : 0;
+            s_cnt = c;
+        }
+    }
+    __syncthreads();
+    int cur = 0;
+    if (warp != 1)
+        group_tfc_fit<THREADS>(g_w, g_alpha, g_f, g_t, capA, s_cnt, sT[0], nullptr, tid); // getTransformFromMatches (:161-179)
+    __syncthreads();
+
+    bool aborted = false;
+    for (int refinements = 1; refinements < 20; refinements++) {
+        // computeInliersAndError (:181-214): score all matches under sT[cur]
+        double Td[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            Td[i] = (double)sT[cur][i];
+        double md_r[NPT];
+        unsigned inbits = 0;
+#pragma unroll
+        for (int it = 0; it < NPT; it++) {
+            const int word = it * NW + warp;
+            md_r[it] = 0.0;
+            if (word < words) {
+                const int j = word * 32 + lane;
+                bool in = false;
+                if (j < M) {
+                    const rgbdfe_point3f o = P1[j], t = P2[j];
+                    if (!(o.z == 0.0f || t.x == 0.0f)) {
+                        const double md = mahal2(o, t, Td, C, prm.rcx, prm.rcy);
+                        in = !(md > th) && (md >= 0.0);
+                        md_r[it] = md;
+                    }
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, in);
+                if (lane == 0) {
+                    cur_m[word] = bal;
+                    wbase[word] = __popc(bal);
+                }
+                inbits |= in ? (1u << it) : 0u;
+            }
+        }
+        if (tid == THREADS - 1)
+            s_abort = ld_volatile(&R.replay[pair].done);
+        __syncthreads();
+        const int abort_now = s_abort;
+        if (warp == 0) { // exclusive prefix of the per-word counts
+            int carry = 0;
+            for (int b = 0; b < words; b += 32) {
+                const int v = (b + lane < words) ? wbase[b + lane] : 0;
+                int inc = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int n = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o)
+                        inc += n;
+                }
+                if (b + lane < words)
+                    wbase[b + lane] = carry + inc - v;
+                carry += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) {
+                s_cnt = carry;
+                s_ctl = -1;
+            }
+        }
+        __syncthreads();
+        if (abort_now) { // the pair's loop already ended on an earlier iteration: this hypothesis is never looked at
+            aborted = true;
+            break;
+        }
+        const int cnt = s_cnt;
+        // ordered inlier list: gather the inliers' data for the next fit and their d^2 for the error
+#pragma unroll
+        for (int it = 0; it < NPT; it++) {
+            const int word = it * NW + warp;
+            if (word < words && ((inbits >> it) & 1u)) {
+                const int k = wbase[word] + __popc(cur_m[word] & ((1u << lane) - 1));
+                g_d2[k] = md_r[it];
+                gather(k, word * 32 + lane);
+            }
+        }
+        __syncthreads();
+        const bool more = refinements < 19 && cnt >= (int)prm.min_inlier_th;
+        if (warp == 1) {
+            if (lane == 0) {
+                int stop = 0, accept = 0;
+                if (cnt < (int)prm.min_inlier_th)
+                    stop = 1;
+                else {
+                    double sum = 0.0; // FP64 sum in match order
+                    int k = 0;
+                    for (; k + 4 <= cnt; k += 4) {
+                        const double a = g_d2[k], b = g_d2[k + 1], c = g_d2[k + 2], d = g_d2[k + 3];
+                        sum += a;
+                        sum += b;
+                        sum += c;
+                        sum += d;
+                    }
+                    for (; k < cnt; k++)
+                        sum += g_d2[k];
+                    double err = 1e9;
+                    if (cnt >= 3)
+                        err = sqrt(sum / (double)cnt);
+                    if (err > (double)prm.max_mahal)
+                        stop = 1;
+                    else if (cnt >= s_refCount && err <= s_refErr) {
+                        accept = 1;
+                        if (cnt == s_refCount)
+                            stop = 1;
+                        s_refErr = err;
+                        s_refCount = cnt;
+                    } else
+                        stop = 1;
+                }
+                *reinterpret_cast<volatile int*>(&s_ctl) = stop | (accept << 1);
+            }
+        } else if (more)
+            group_tfc_fit<THREADS>(g_w, g_alpha, g_f, g_t, capA, cnt, sT[cur ^ 1], &s_ctl, tid); // next round's transform, speculatively
+        __syncthreads();
+        const int ctl = s_ctl;
+        if (ctl & 2) { // vRefinedMatches = vInlierMatches; refinedTransformation = transformation
+            unsigned* t = ref_m;
+            ref_m = cur_m;
+            cur_m = t;
+            if (tid < 16)
+                sRefT[tid] = sT[cur][tid];
+        }
+        if (ctl & 1)
+            break;
+        cur ^= 1;
+    }
+    if (aborted)
+        return;
+    __syncthreads();
+    HypOut* out = const_cast<HypOut*>(R.hyp_all) + (size_t)pair * MAX_ITERS + h;
+    if (tid == 0) {
+        out->count = s_refCount;
+        out->err = s_refErr;
+    }
+    if (tid < 16)
+        out->T[tid] = sRefT[tid];
+    unsigned* om = const_cast<unsigned*>(R.mask_all) + ((size_t)pair * MAX_ITERS + h) * mw;
+    for (int i = tid; i < words; i += THREADS)
+        om[i] = ref_m[i];
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        *reinterpret_cast<volatile int*>(&R.ready_all[(size_t)pair * MAX_ITERS + h]) = 1;
+        __threadfence();
+    }
+    if (warp == 0) {
+        __syncwarp();
+        warp_try_replay(R, pair, hyp_end, next_end, scratch, lane);
+    }
+}
+
+template <int THREADS, int NPT>
+static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end)
+{
+    static size_t configured = 0;
+    if (smem > configured) {
+        CUDA_TRY(c, cudaFuncSetAttribute(k_se3_hypotheses<THREADS, NPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    const int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
+    k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, npairs), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end);
+    c->launches++;
+    return RGBDFE_OK;
 }
 
 int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng, unsigned seed,
@@ -718,44 +835,77 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const
         c->set_error("sample_size must be in [1, 8]");
         return RGBDFE_E_ARG;
     }
-    const int iters = prm.iterations < MAX_ITERS ? prm.iterations : MAX_ITERS;
-    // chunk boundaries: a single pair fills the GPU with hypotheses; many pairs start small
-    const int b1 = npairs == 1 ? 32 : 8, b2 = npairs == 1 ? 160 : 64;
     const int cap = c->kp_cap;
+    if (cap > 4096) {
+        c->set_error("RANSAC: more than 4096 matches per pair are not supported");
+        return RGBDFE_E_CAPACITY;
+    }
+    const int iters = prm.iterations < MAX_ITERS ? (prm.iterations > 0 ? prm.iterations : 0) : MAX_ITERS;
+    // chunk boundaries: a single pair fills the GPU with hypotheses; many pairs start small
+    const bool few = npairs < 16;
+    const int b1 = few ? 32 : 8, b2 = few ? 160 : 64;
     const size_t prep_smem = (size_t)cap * (sizeof(SKey) + 3 * sizeof(int)) + 2 * SORT_QCAP * sizeof(int3);
-    const size_t hyp_smem = (size_t)cap * (8 + 4 + 1) + (size_t)2 * c->mask_words * 4 + 16;
-    static size_t conf_prep = 0, conf_hyp = 0;
+    const int capA = (cap + 3) & ~3;
+    size_t hyp_smem = (size_t)capA * 40 + (size_t)c->mask_words * 12;
+    const size_t min_smem = ((size_t)RNG_SCRATCH_WORDS + c->mask_words) * 4;
+    if (hyp_smem < min_smem)
+        hyp_smem = min_smem;
+    static size_t conf_prep = 0;
     if (prep_smem > conf_prep) {
         CUDA_TRY(c, cudaFuncSetAttribute(k_se3_prepare, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prep_smem));
         conf_prep = prep_smem;
-    }
-    if (hyp_smem > conf_hyp) {
-        CUDA_TRY(c, cudaFuncSetAttribute(k_se3_hypotheses, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hyp_smem));
-        conf_hyp = hyp_smem;
     }
     {
         ProfScope prof(c, KID_SE3_PREPARE);
         k_se3_prepare<<<npairs, PREP_THREADS, prep_smem, c->stream>>>(d_pairs, c->d_matches, c->d_sorted, c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch,
             prm, update_f2, per_pair_rng, seed, first_pair_index, min_matches, c->d_rng, c->d_pair_rng, c->d_latch, c->d_samples, c->d_rng_used,
-            c->d_replay, b1);
+            c->d_replay, c->d_hyp_ready, c->d_pair_lock, b1);
         c->launches++;
     }
+    ReplayCtx R;
+    R.pairs = d_pairs;
+    R.sorted_all = c->d_sorted;
+    R.P1_all = c->d_P1;
+    R.P2_all = c->d_P2;
+    R.match_cap = cap;
+    R.prm = prm;
+    R.update_f2 = update_f2;
+    R.per_pair_rng = per_pair_rng;
+    R.ctx_rng = c->d_rng;
+    R.pair_rng = c->d_pair_rng;
+    R.latch = c->d_latch;
+    R.samples_all = c->d_samples;
+    R.rng_used_all = c->d_rng_used;
+    R.hyp_all = c->d_hyp;
+    R.mask_all = c->d_hyp_mask;
+    R.mask_words = c->mask_words;
+    R.replay = c->d_replay;
+    R.ready_all = c->d_hyp_ready;
+    R.lock_all = c->d_pair_lock;
+    R.results = d_results;
+    R.inl_pos_all = c->d_inl_pos;
     const int bounds[4] = { 0, b1, b2, iters };
     for (int s = 0; s < 3; s++) {
         const int b = bounds[s] < iters ? bounds[s] : iters;
         const int e = (s == 2 || bounds[s + 1] > iters) ? iters : bounds[s + 1];
         const int next_end = s == 0 ? (b2 < iters ? b2 : iters) : iters;
-        if (e > b) {
-            ProfScope prof(c, KID_SE3_HYP);
-            k_se3_hypotheses<<<dim3(e - b, npairs), HYP_THREADS, hyp_smem, c->stream>>>(c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch, prm, c->d_latch,
-                c->d_samples, c->d_hyp, c->d_hyp_mask, c->mask_words, c->d_replay, b, e);
-            c->launches++;
-        }
-        ProfScope prof2(c, KID_SE3_REPLAY);
-        k_se3_replay<<<npairs, 32, (size_t)c->mask_words * 4, c->stream>>>(d_pairs, c->d_sorted, c->d_P1, c->d_P2, cap, prm, update_f2, per_pair_rng,
-            c->d_rng, c->d_pair_rng, c->d_latch, c->d_samples, c->d_rng_used, c->d_hyp, c->d_hyp_mask, c->mask_words, c->d_replay, e, next_end,
-            d_results, c->d_inl_pos);
-        c->launches++;
+        if (s > 0 && e <= b)
+            break;
+        ProfScope prof(c, KID_SE3_HYP);
+        int rc;
+        if (few || cap > 2304) {
+            if (cap <= 1536)
+                rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end);
+            else if (cap <= 2560)
+                rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end);
+            else
+                rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end);
+        } else if (cap <= 1152)
+            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end);
+        else
+            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end);
+        if (rc != RGBDFE_OK)
+            return rc;
         if (e >= iters)
             break;
     }

@@ -17,22 +17,15 @@
 // count / M, so the host evaluates it with the C library for every count and uploads the table
 // (bit-equal to the reference's libm, which a device log/pow is not guaranteed to be).
 // FP contract as in se3_math.cuh (FP32, no FMA); sums over correspondences run in list order.
+#include "rng.cuh"
+#include <algorithm>
 #include "se3_math.cuh"
 
 namespace rgbdfe {
 
 #define UME_THREADS 128
 #define UME_MAX_PAIRS 8
-
-__device__ __forceinline__ int ume_rng_next(RngState& s)
-{
-    unsigned v = (unsigned)s.r[(s.idx - 31) % 34] + (unsigned)s.r[(s.idx - 3) % 34];
-    s.r[s.idx % 34] = (int)v;
-    s.idx++;
-    if (s.idx >= 34 * 1000000)
-        s.idx -= 34 * 999990;
-    return (int)(v >> 1);
-}
+#define UME_RNG_BLOCK 1024
 
 // Eigen::umeyama(src, dst, with_scaling = false) over `n` correspondences given by idx (or
 // 0..n-1 when idx == nullptr); src = current-frame points (P2), dst = previous-frame points (P1).
@@ -113,6 +106,7 @@ __global__ void __launch_bounds__(256) k_ume_prepare(const rgbdfe_dmatch* __rest
 {
     __shared__ int s_warp[8];
     __shared__ int s_base;
+    __shared__ unsigned s_lin[RNG_HIST + UME_RNG_BLOCK];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0)
         s_base = 0;
@@ -157,14 +151,22 @@ __global__ void __launch_bounds__(256) k_ume_prepare(const rgbdfe_dmatch* __rest
     state->total_calls = 0;
     if (M < used_pairs)
         return; // the host refuses this case (the reference would never leave getRandomMatches)
-    RngState s = *ctx_rng;
-    int calls = 0;
+    // getRandomMatches (:183-208): one rand() per draw, already chosen indices are redrawn
+    rng_window_load(ctx_rng, s_lin);
+    int calls = 0, pos = UME_RNG_BLOCK;
     for (int k = 0; k < iters0; k++) {
         int ids[UME_MAX_PAIRS];
         int cnt = 0;
         while (cnt < used_pairs) {
-            const int d = M;
-            const int id = int(((double)ume_rng_next(s) / ((double)2147483647 + 1.0)) * d);
+            if (pos == UME_RNG_BLOCK) { // refill: slide the window over the consumed block, extend it by another one
+                if (calls > 0)
+                    for (int t = 0; t < RNG_HIST; t++)
+                        s_lin[t] = s_lin[UME_RNG_BLOCK + t];
+                rng_extend(s_lin, UME_RNG_BLOCK);
+                pos = 0;
+            }
+            const int id = rng_random_int0(s_lin[RNG_HIST + pos], M);
+            pos++;
             calls++;
             bool fresh = true;
             for (int j = 0; j < cnt; j++)
@@ -360,10 +362,7 @@ __global__ void __launch_bounds__(256) k_ume_finish(const rgbdfe_point3f* __rest
         res->iters_executed = K;
         // the executed iterations consumed rng_used[K-1] rand() calls of the process stream
         const int calls = K > 0 ? rng_used[K - 1] : 0;
-        RngState s = *ctx_rng;
-        for (int i = 0; i < calls; i++)
-            ume_rng_next(s);
-        *ctx_rng = s;
+        rng_advance(reinterpret_cast<unsigned*>(s_idx), ctx_rng, calls, UME_RNG_BLOCK); // s_idx is free by now
     }
 }
 
@@ -375,7 +374,7 @@ int launch_ransac_umeyama(rgbdfe_ctx* c, int nm, const rgbdfe_point3f* d_xyz1, c
         c->d_rng_used, d_state);
     k_ume_hypotheses<<<iters0, UME_THREADS, 0, s>>>(c->d_P1, c->d_P2, d_state, c->d_samples, used_pairs, th0, adaptive, c->d_hyp, c->d_hyp_mask,
         c->mask_words);
-    k_ume_finish<<<1, 256, (size_t)c->kp_cap * sizeof(int), s>>>(c->d_P1, c->d_P2, d_state, c->d_hyp, c->d_hyp_mask, c->mask_words, d_iters_tab,
+    k_ume_finish<<<1, 256, std::max((size_t)c->kp_cap, (size_t)(RNG_HIST + UME_RNG_BLOCK)) * sizeof(int), s>>>(c->d_P1, c->d_P2, d_state, c->d_hyp, c->d_hyp_mask, c->mask_words, d_iters_tab,
         iters_min, iters0, th0, adaptive, min_ratio, c->d_rng_used, c->d_rng, d_res, c->d_inl_pos);
     c->launches += 3;
     CUDA_TRY(c, cudaGetLastError());

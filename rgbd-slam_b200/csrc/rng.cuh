@@ -77,4 +77,38 @@ __device__ inline void rng_seed_state(RngState& s, unsigned seed, unsigned* lin 
     s.idx = 344;
 }
 
+// Window <-> ring helpers on a stream that lives in global memory (one thread).
+__device__ __forceinline__ int rng_window_load(const RngState* st, unsigned* lin)
+{
+    const int idx = st->idx, base = idx % RNG_HIST;
+    for (int t = 0; t < RNG_HIST; t++)
+        lin[t] = (unsigned)st->r[(base + t) % RNG_HIST];
+    return idx;
+}
+__device__ __forceinline__ void rng_window_store(RngState* st, const unsigned* lin, int idx)
+{
+    while (idx >= RNG_HIST * 1000000)
+        idx -= RNG_HIST * 999990; // glibc never wraps; this only keeps idx % 34 and the int range
+    const int base = idx % RNG_HIST;
+    for (int t = 0; t < RNG_HIST; t++)
+        st->r[(base + t) % RNG_HIST] = (int)lin[t];
+    st->idx = idx;
+}
+
+// Advance a stream by `n` rand() calls without using their values; one thread.
+// lin: 34 + block words of scratch.
+__device__ inline void rng_advance(unsigned* lin, RngState* st, int n, int block)
+{
+    const int idx0 = rng_window_load(st, lin);
+    int left = n;
+    while (left > 0) {
+        const int nb = min(left, block);
+        rng_extend(lin, nb);
+        for (int t = 0; t < RNG_HIST; t++)
+            lin[t] = lin[nb + t];
+        left -= nb;
+    }
+    rng_window_store(st, lin, idx0 + n);
+}
+
 } // namespace rgbdfe
