@@ -205,8 +205,7 @@ def main():
         else:
             ctx.frames_extract(cur, [gp_h[i] for i in idx], [dp_h[i] for i in idx], cam)
         first = 0 if state["have_ref"] else 1
-        for j in range(first, B):
-            ctx.track(r[j], r[j + 1], j, RATIO, True, ITERS, MIN_INL, 3.0, 4, True)
+        ctx.track_sequence(r[first:], first, RATIO, True, ITERS, MIN_INL, 3.0, 4, True)
         res = ctx.track_results(first, B - first)
         state["ok"] += int(res["ok"].sum())
         state["n"] += len(res)

@@ -167,6 +167,13 @@ int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint*
  * context-owned result ring read back with rgbdfe_track_results(). */
 int rgbdfe_track(rgbdfe_ctx* ctx, rgbdfe_frame* ref, rgbdfe_frame* cur, float ratio, int discard_outliers, int iterations,
     unsigned min_inlier_th, float max_mahal, unsigned sample_size, int update_f2, int result_slot);
+/* The same for a tracked sequence: pair i = (frames[i], frames[i+1]), i = 0 .. count-2, each the
+ * Matcher::match + RansacSE3::compute of rgbdfe_track, executed in sequence order (pair i sees the
+ * outlier flags pair i-1 left on frames[i] and continues the context's rand() stream), results in
+ * slots first_result_slot + i.  The Hamming kNN of all pairs runs as one launch ahead of the
+ * sequential part.  count <= 65.  Asynchronous. */
+int rgbdfe_track_sequence(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, float ratio, int discard_outliers, int iterations,
+    unsigned min_inlier_th, float max_mahal, unsigned sample_size, int update_f2, int first_result_slot);
 /* Synchronise and copy results [first, first+count) of the ring to the host.
  * inlier_trainidx (may be NULL) is count x cap ints. */
 int rgbdfe_track_results(rgbdfe_ctx* ctx, int first, int count, rgbdfe_se3_result* results);

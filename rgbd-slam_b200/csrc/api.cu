@@ -195,6 +195,15 @@ void free_frame(rgbdfe_frame* f)
 namespace {
 
 __global__ void k_set_pair(MatchPair* dst, MatchPair v) { *dst = v; }
+// consecutive frames of a tracked sequence -> one MatchPair per (previous, current)
+__global__ void k_build_chain_pairs(FrameChain fc, int np, MatchPair* dst)
+{
+    const int p = threadIdx.x;
+    if (p >= np)
+        return;
+    const rgbdfe_frame &ref = fc.f[p], &cur = fc.f[p + 1];
+    dst[p] = MatchPair { ref.desc, cur.desc, ref.n, cur.n, ref.outlier, ref.xyz, cur.xyz, cur.outlier };
+}
 __global__ void k_set_int(int* dst, int v) { *dst = v; }
 
 void free_orb_workspaces(rgbdfe_ctx* c)
@@ -763,7 +772,7 @@ int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgb
     if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
         return rc;
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
-    if ((rc = launch_ransac_se3(c, c->d_pairs, 1, prm, 0, 0, 0, 0, 0, c->d_results)) != RGBDFE_OK)
+    if ((rc = launch_ransac_se3(c, c->d_pairs, 0, 1, prm, 0, 0, 0, 0, 0, c->d_results, nullptr)) != RGBDFE_OK)
         return rc;
     CUDA_TRY(c, cudaStreamSynchronize(s));
     CUDA_TRY(c, cudaMemcpy(result, c->d_results, sizeof(*result), cudaMemcpyDeviceToHost));
@@ -895,7 +904,41 @@ int rgbdfe_track(rgbdfe_ctx* c, rgbdfe_frame* ref, rgbdfe_frame* cur, float rati
     if ((rc = launch_match(c, c->d_pairs, 1, c->kp_cap, c->kp_cap, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
         return rc;
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
-    return launch_ransac_se3(c, c->d_pairs, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + result_slot);
+    return launch_ransac_se3(c, c->d_pairs, 0, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + result_slot, nullptr);
+}
+
+int rgbdfe_track_sequence(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, float ratio, int discard_outliers, int iterations,
+    unsigned min_inlier_th, float max_mahal, unsigned sample_size, int update_f2, int first_result_slot)
+{
+    if (!c || !frames || count < 1 || count > CHAIN_MAX_FRAMES || first_result_slot < 0 || first_result_slot + count - 1 > c->result_cap)
+        return RGBDFE_E_ARG;
+    const int np = count - 1;
+    if (np == 0)
+        return RGBDFE_OK;
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, np);
+    if (rc != RGBDFE_OK)
+        return rc;
+    FrameChain fc;
+    for (int i = 0; i < count; i++) {
+        if (!frames[i])
+            return RGBDFE_E_ARG;
+        fc.f[i] = *frames[i];
+    }
+    // pair p = Matcher::match(frames[p] /*ref, query*/, frames[p+1] /*cur, train*/) (Tracking.cpp:127)
+    k_build_chain_pairs<<<1, CHAIN_MAX_FRAMES, 0, c->stream>>>(fc, np, c->d_pairs);
+    c->launches++;
+    // K7 for every pair of the chain at once: descriptors do not depend on the previous pair's outcome,
+    // only the filter (outlier flags) and the RANSAC (rand() stream) do
+    const int splits = rgbdfe::knn_splits_for(c, np);
+    if ((rc = rgbdfe::launch_knn(c, c->d_pairs, 0, np, c->kp_cap, splits)) != RGBDFE_OK)
+        return rc;
+    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    rgbdfe::FusedFilter ff = { splits, ratio, discard_outliers };
+    for (int p = 0; p < np; p++)
+        if ((rc = launch_ransac_se3(c, c->d_pairs, p, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + first_result_slot + p, &ff)) != RGBDFE_OK)
+            return rc;
+    return RGBDFE_OK;
 }
 
 int rgbdfe_track_results(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result* results)
@@ -983,7 +1026,7 @@ int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, c
         d_res = tmp;
     }
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
-    rc = launch_ransac_se3(c, c->d_pairs, np, prm, 0, 1, seed, first_pair_index, min_matches, d_res);
+    rc = launch_ransac_se3(c, c->d_pairs, 0, np, prm, 0, 1, seed, first_pair_index, min_matches, d_res, nullptr);
     if (rc == RGBDFE_OK && results) {
         cudaError_t e = cudaMemcpyAsync(results, d_res, (size_t)np * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess)

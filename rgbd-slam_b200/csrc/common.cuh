@@ -84,6 +84,12 @@ struct FrameBatch {
     rgbdfe_frame f[64];
 };
 
+// Frames of one rgbdfe_track_sequence call, passed by value.
+#define CHAIN_MAX_FRAMES 65
+struct FrameChain {
+    rgbdfe_frame f[CHAIN_MAX_FRAMES];
+};
+
 struct rgbdfe_kfdb {
     int n_kf, n_feat;
     uint8_t* desc;
@@ -265,9 +271,18 @@ int launch_quadtree(rgbdfe_ctx* c, int count);
 int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, int depth_stride, float fx, float fy, float cx, float cy);
 // match.cu
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
+int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);
+int knn_splits_for(const rgbdfe_ctx* c, int npairs);
 // ransac.cu
-int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng, unsigned seed,
-    int first_pair_index, int min_matches, rgbdfe_se3_result* d_results);
+// Pairs occupy workspace slots [slot0, slot0 + npairs); results go to d_results[0 .. npairs).  With `ff` the
+// Matcher::match filter (K8) runs inside k_se3_prepare on the kNN partials of the same slots.
+struct FusedFilter {
+    int splits;
+    float ratio;
+    int discard_outliers;
+};
+int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng,
+    unsigned seed, int first_pair_index, int min_matches, rgbdfe_se3_result* d_results, const FusedFilter* ff);
 // ransac_umeyama.cu
 int launch_ransac_umeyama(rgbdfe_ctx* c, int nm, const rgbdfe_point3f* d_xyz1, const rgbdfe_point3f* d_xyz2, int used_pairs, int iters0,
     const int* d_iters_tab, int iters_min, double th0, int adaptive, double min_ratio, UmeState* d_state, rgbdfe_umeyama_result* d_res);

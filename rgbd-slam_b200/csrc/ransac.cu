@@ -23,6 +23,7 @@
 //                    slowest member.  If the chunk is used up the same CTA draws the next
 //                    chunk's samples.
 // Hypotheses are issued in growing chunks; chunks of a finished pair exit immediately.
+#include "match_filter.cuh"
 #include "rng.cuh"
 #include "se3_math.cuh"
 #include "std_sort.cuh"
@@ -105,9 +106,10 @@ __device__ void warp_sample_chunk(unsigned* lin, int* ids, RngState* st, int M, 
 }
 
 // dynamic smem: SKey keys[cap]; int Lpos[cap], Rpos[cap], leaves[cap]; int3 qa[QCAP], qb[QCAP]
-__global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* __restrict__ pairs, const rgbdfe_dmatch* __restrict__ matches_all,
+__global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* __restrict__ pairs, int slot0, FusedFilter ff,
+    int4* partial, rgbdfe_dmatch* matches_all,
     rgbdfe_dmatch* __restrict__ sorted_all, rgbdfe_point3f* __restrict__ P1_all, rgbdfe_point3f* __restrict__ P2_all, float* __restrict__ w_all,
-    int match_cap, const int* __restrict__ nmatch, Se3Params prm, int update_f2, int per_pair_rng, unsigned seed, int first_pair_index,
+    int match_cap, int* __restrict__ nmatch, Se3Params prm, int update_f2, int per_pair_rng, unsigned seed, int first_pair_index,
     int min_matches, const RngState* __restrict__ ctx_rng, RngState* __restrict__ pair_rng, DepthLatch* __restrict__ latch,
     int* __restrict__ samples_all, int* __restrict__ rng_used_all, ReplayState* __restrict__ replay, int* __restrict__ ready_all,
     int* __restrict__ lock_all, int first_chunk)
@@ -122,12 +124,21 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     __shared__ int s_counters[4];
     __shared__ unsigned s_rng[RNG_SCRATCH_WORDS];
 
-    const int pair = blockIdx.x;
+    const int pair = slot0 + blockIdx.x;
     const MatchPair P = pairs[pair];
     const rgbdfe_dmatch* m = matches_all + (size_t)pair * match_cap;
     rgbdfe_dmatch* sorted = sorted_all + (size_t)pair * match_cap;
-    const int M = nmatch[pair];
     const int tid = threadIdx.x;
+    int M;
+    if (ff.splits > 0) {
+        // Matcher::match's filter half (K8) on this pair's kNN partials, fused into the chain
+        M = cta_ratio_filter(P, pair, reinterpret_cast<int*>(smem_raw), partial, match_cap, ff.splits, ff.ratio, ff.discard_outliers,
+            matches_all, match_cap, nullptr);
+        if (tid == 0)
+            nmatch[pair] = M;
+        __syncthreads();
+    } else
+        M = nmatch[pair];
     const bool run = M >= (int)prm.min_inlier_th && M >= min_matches; // SolverSE3.cpp:29 / PoseGraph.cpp:142-144
     const int ss = (int)prm.sample_size;
     const int n_first = (M >= ss) ? min(min(prm.iterations, MAX_ITERS), first_chunk) : 0;
@@ -167,7 +178,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
         RngState* s = pair_rng + pair; // working copy, continued by the replay when more chunks are needed
         if (lane == 0) {
             if (per_pair_rng)
-                rng_seed_state(*s, seed + (unsigned)(first_pair_index + pair), s_rng);
+                rng_seed_state(*s, seed + (unsigned)(first_pair_index + (int)blockIdx.x), s_rng);
             else
                 *s = *ctx_rng;
         }
@@ -241,7 +252,8 @@ struct ReplayCtx {
     int mask_words;
     ReplayState* replay;
     int *ready_all, *lock_all;
-    rgbdfe_se3_result* results;
+    rgbdfe_se3_result* results; // results[pair - slot0]
+    int slot0;
     int* inl_pos_all;
 };
 
@@ -274,7 +286,7 @@ __device__ void warp_finalize(const ReplayCtx& R, int pair, ReplayState& st, uns
     const rgbdfe_dmatch* m = R.sorted_all + (size_t)pair * match_cap;
     const rgbdfe_point3f* P1 = R.P1_all + (size_t)pair * match_cap;
     const rgbdfe_point3f* P2 = R.P2_all + (size_t)pair * match_cap;
-    rgbdfe_se3_result* res = R.results + pair;
+    rgbdfe_se3_result* res = R.results + (pair - R.slot0);
     int* inl_pos = R.inl_pos_all + (size_t)pair * match_cap;
     unsigned* s_mask = scratch + RNG_SCRATCH_WORDS;
 
@@ -394,7 +406,7 @@ __device__ void warp_try_replay(const ReplayCtx& R, int pair, int chunk_end, int
         const int M = st.nm;
         if (!st.run) {
             if (lane == 0) {
-                rgbdfe_se3_result* res = R.results + pair;
+                rgbdfe_se3_result* res = R.results + (pair - R.slot0);
                 res->ok = 0;
                 res->rmse = 1e6f;
                 for (int i = 0; i < 16; i++)
@@ -587,7 +599,7 @@ template <int THREADS, int NPT>
 __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
 {
     constexpr int NW = THREADS / 32;
-    const int pair = blockIdx.y, h = hyp_begin + blockIdx.x;
+    const int pair = R.slot0 + blockIdx.y, h = hyp_begin + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int match_cap = R.match_cap, capA = (match_cap + 3) & ~3, mw = R.mask_words;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -826,8 +838,8 @@ static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem
     return RGBDFE_OK;
 }
 
-int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng, unsigned seed,
-    int first_pair_index, int min_matches, rgbdfe_se3_result* d_results)
+int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng,
+    unsigned seed, int first_pair_index, int min_matches, rgbdfe_se3_result* d_results, const FusedFilter* ff)
 {
     if (npairs <= 0)
         return RGBDFE_OK;
@@ -857,7 +869,10 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const
     }
     {
         ProfScope prof(c, KID_SE3_PREPARE);
-        k_se3_prepare<<<npairs, PREP_THREADS, prep_smem, c->stream>>>(d_pairs, c->d_matches, c->d_sorted, c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch,
+        FusedFilter f = { 0, 0.0f, 0 };
+        if (ff)
+            f = *ff;
+        k_se3_prepare<<<npairs, PREP_THREADS, prep_smem, c->stream>>>(d_pairs, slot0, f, c->d_partial, c->d_matches, c->d_sorted, c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch,
             prm, update_f2, per_pair_rng, seed, first_pair_index, min_matches, c->d_rng, c->d_pair_rng, c->d_latch, c->d_samples, c->d_rng_used,
             c->d_replay, c->d_hyp_ready, c->d_pair_lock, b1);
         c->launches++;
@@ -883,6 +898,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, const
     R.ready_all = c->d_hyp_ready;
     R.lock_all = c->d_pair_lock;
     R.results = d_results;
+    R.slot0 = slot0;
     R.inl_pos_all = c->d_inl_pos;
     const int bounds[4] = { 0, b1, b2, iters };
     for (int s = 0; s < 3; s++) {

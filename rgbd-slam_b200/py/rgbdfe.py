@@ -264,6 +264,16 @@ class Context:
             )
         )
 
+    def track_sequence(self, frames, first_slot, ratio=0.9, discard=True, iters=200, min_inl=10, max_mahal=3.0, sample=4, update_f2=True):
+        n = len(frames)
+        fr = (C.c_void_p * n)(*[f.h for f in frames])
+        self._chk(
+            lib().rgbdfe_track_sequence(
+                self.h, fr, n, C.c_float(ratio), int(discard), iters, C.c_uint(min_inl), C.c_float(max_mahal), C.c_uint(sample), int(update_f2),
+                first_slot,
+            )
+        )
+
     def track_results(self, first, count):
         res = np.zeros(count, SE3_DTYPE)
         self._chk(lib().rgbdfe_track_results(self.h, first, count, _p(res)))

@@ -235,8 +235,10 @@ def test_ransac_umeyama_parity(ctx, oracle, seq_vga):
         ctx.ransac_umeyama(p1, p2, m, 1, 0.02, 0.2, 10, 3)
 
 
-def test_tracking_pipeline_device_resident(oracle, seq_vga):
-    """T2: extract (batched) -> match -> RansacSE3 with outlier-flag carry-over, frame to frame."""
+@pytest.mark.parametrize("chain", [False, True])
+def test_tracking_pipeline_device_resident(oracle, seq_vga, chain):
+    """T2: extract (batched) -> match -> RansacSE3 with outlier-flag carry-over, frame to frame;
+    pair by pair (rgbdfe_track) and as one rgbdfe_track_sequence call (batched kNN + fused filter)."""
     import rgbdfe
 
     cam, frames = seq_vga
@@ -245,8 +247,11 @@ def test_tracking_pipeline_device_resident(oracle, seq_vga):
         ctx.rng_seed(42)
         fr = [rgbdfe.Frame(ctx) for _ in frames]
         ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)
-        for i in range(1, len(frames)):
-            ctx.track(fr[i - 1], fr[i], i - 1)
+        if chain:
+            ctx.track_sequence(fr, 0)
+        else:
+            for i in range(1, len(frames)):
+                ctx.track(fr[i - 1], fr[i], i - 1)
         res = ctx.track_results(0, len(frames) - 1)
         orb = oracle.Orb(1000)
         rng, latch = oracle.Rng(42), oracle.Latch()
