@@ -95,6 +95,10 @@ int rgbdfe_profile_enable(rgbdfe_ctx* ctx, int on);
 int rgbdfe_profile_read(rgbdfe_ctx* ctx, double* ms_per_kernel, long long* launches_per_kernel, int n);
 const char* rgbdfe_profile_name(int id);
 
+/* Developer aid: device-side phase time stamps (ns) of the match/RANSAC chain kernels for the first pair
+ * of the last launch; on = 1 starts recording, out (may be NULL) receives up to n of 512 slots. */
+int rgbdfe_debug_timeline(rgbdfe_ctx* ctx, int on, long long* out, int n);
+
 /* ---- Extractor / ORBextractor ---------------------------------------- */
 /* Extractor::setParameters (Features/Extractor.cpp:24-48) -> ORBextractor ctor
  * (Features/ORBextractor.cpp:348-406). */

@@ -321,7 +321,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_pair_workspaces(c);
     free_frame(c->scratch);
     free_frame(c->scratch2);
-    cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
+    cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -1046,6 +1046,25 @@ int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, c
 } // extern "C"
 
 extern "C" {
+
+/* Developer aid (not part of the reference-facing surface): %globaltimer stamps of the chain kernels'
+ * phases for pair slot 0 (see DBG_STAMP in ransac.cu).  on: 1/0; out: DBG_SLOTS values. */
+int rgbdfe_debug_timeline(rgbdfe_ctx* c, int on, long long* out, int n)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    if (!c->d_dbg) {
+        CUDA_TRY(c, dmalloc(&c->d_dbg, (size_t)DBG_SLOTS));
+        CUDA_TRY(c, cudaMemset(c->d_dbg, 0, DBG_SLOTS * sizeof(long long)));
+    }
+    if (out && n > 0)
+        CUDA_TRY(c, cudaMemcpy(out, c->d_dbg, (size_t)std::min(n, DBG_SLOTS) * sizeof(long long), cudaMemcpyDeviceToHost));
+    CUDA_TRY(c, cudaMemset(c->d_dbg, 0, DBG_SLOTS * sizeof(long long)));
+    c->dbg_on = on;
+    return RGBDFE_OK;
+}
 
 int rgbdfe_profile_enable(rgbdfe_ctx* c, int on)
 {

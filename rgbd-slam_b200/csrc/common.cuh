@@ -204,6 +204,8 @@ struct rgbdfe_ctx {
     RngState* d_pair_rng = nullptr; // [pairs] per-pair streams (batched)
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
+    long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
+    int dbg_on = 0;
 
     // optional per-kernel timing (CUDA events on `stream`), see rgbdfe_profile_*
     bool profiling = false;
@@ -222,6 +224,21 @@ struct rgbdfe_ctx {
             return RGBDFE_E_CUDA;                                                 \
         }                                                                         \
     } while (0)
+
+#define DBG_SLOTS 512
+#ifdef __CUDACC__
+__device__ __forceinline__ long long dbg_now()
+{
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define DBG_STAMP(ptr, slot)                 \
+    do {                                     \
+        if ((ptr) && (slot) < DBG_SLOTS)     \
+            (ptr)[(slot)] = dbg_now();       \
+    } while (0)
+#endif
 
 static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
 

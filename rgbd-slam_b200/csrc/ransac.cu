@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     int match_cap, int* __restrict__ nmatch, Se3Params prm, int update_f2, int per_pair_rng, unsigned seed, int first_pair_index,
     int min_matches, const RngState* __restrict__ ctx_rng, RngState* __restrict__ pair_rng, DepthLatch* __restrict__ latch,
     int* __restrict__ samples_all, int* __restrict__ rng_used_all, ReplayState* __restrict__ replay, int* __restrict__ ready_all,
-    int* __restrict__ lock_all, int first_chunk)
+    int* __restrict__ lock_all, int first_chunk, long long* dbg)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SKey* keys = reinterpret_cast<SKey*>(smem_raw);
@@ -129,6 +129,9 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
     const rgbdfe_dmatch* m = matches_all + (size_t)pair * match_cap;
     rgbdfe_dmatch* sorted = sorted_all + (size_t)pair * match_cap;
     const int tid = threadIdx.x;
+    if (blockIdx.x != 0 || tid != 0)
+        dbg = nullptr;
+    DBG_STAMP(dbg, 0);
     int M;
     if (ff.splits > 0) {
         // Matcher::match's filter half (K8) on this pair's kNN partials, fused into the chain
@@ -139,6 +142,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
         __syncthreads();
     } else
         M = nmatch[pair];
+    DBG_STAMP(dbg, 1);
     const bool run = M >= (int)prm.min_inlier_th && M >= min_matches; // SolverSE3.cpp:29 / PoseGraph.cpp:142-144
     const int ss = (int)prm.sample_size;
     const int n_first = (M >= ss) ? min(min(prm.iterations, MAX_ITERS), first_chunk) : 0;
@@ -190,7 +194,9 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
             replay[pair].sampled_calls = calls;
     } else
         cta_std_sort(keys, M, Lpos, Rpos, leaves, qa, qb, s_counters, PREP_THREADS - 32); // :52
+    DBG_STAMP(dbg, 2);
     __syncthreads();
+    DBG_STAMP(dbg, 3);
     rgbdfe_point3f* P1 = P1_all + (size_t)pair * match_cap;
     rgbdfe_point3f* P2 = P2_all + (size_t)pair * match_cap;
     float* w = w_all + (size_t)pair * match_cap;
@@ -202,11 +208,12 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
         P2[j] = to;
         // TFC weight (SolverSE3.cpp:172-176); 0 encodes "skipped" (NaN depth, or tfc.add's weight == 0 early return)
         float wt = 1.0f / (from.z * to.z);
-        if (isnan(from.z) || isnan(to.z))
-            wt = 0.0f;
+        if (isnan(from.z) || isnan(to.z) || wt == 0.0f)
+            wt = 0.0f; // canonical +0
         w[j] = wt;
     }
     __syncthreads();
+    DBG_STAMP(dbg, 4);
     // depthCovariance latch (:282-287): the first source depth that reaches errorFunction2
     if (tid < 32 && !latch->latched) {
         for (int j0 = 0; j0 < M; j0 += 32) {
@@ -255,6 +262,7 @@ struct ReplayCtx {
     rgbdfe_se3_result* results; // results[pair - slot0]
     int slot0;
     int* inl_pos_all;
+    long long* dbg;
 };
 
 __device__ __forceinline__ ReplayState load_state(const ReplayState* p)
@@ -512,73 +520,84 @@ __device__ __forceinline__ void group_bar()
 //   (3) warp 0 runs the mean / covariance recurrences: lane c < 9 owns cov(c/3, c%3) and tracks
 //       mean2[c/3], mean1[c%3] itself, so every value goes through exactly the operations of the
 //       sequential `add` while the dependent chain per point is sub-mul-add.
-// ctl: when non-null, warp 0 polls it and gives up as soon as the round's decision is "stop".
+// Points the reference skips (NaN depth, weight == 0) are stored as w = +0, alpha = 0, x = y = 0:
+// accW + 0, mean + 0 * d and 1 * (cov + 0) leave every accumulator unchanged, so the loops are
+// branch-free.  The list is zero-padded to a multiple of 4 (+4 for the prefetch).
+// ctl: when non-null, the sequential loops poll it and give up as soon as the round's decision is "stop".
 template <int THREADS>
 __device__ void group_tfc_fit(const float* g_w, float* g_alpha, const float* g_f, const float* g_t, int capA, int cnt, float* Tout,
-    const volatile int* ctl, int tid)
+    const volatile int* ctl, int tid, long long* dbg = nullptr)
 {
     const int lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) {
+    if (warp == 0) {
+        // all 32 lanes run the same recurrence (same addresses, same values): a warp without a divergent
+        // sibling path issues this loop back to back, one lane alone does not
         float acc = 0.0f;
-        int k = 0;
-        for (; k + 4 <= cnt; k += 4) {
-            const float4 w4 = *reinterpret_cast<const float4*>(g_w + k);
+        float4 w4 = *reinterpret_cast<const float4*>(g_w);
+        for (int k = 0; k < cnt; k += 4) {
+            const float4 wn = *reinterpret_cast<const float4*>(g_w + k + 4);
             float4 a4;
-            acc = (w4.x != 0.0f) ? acc + w4.x : acc; // weight == 0: tfc.add returns early / NaN depth skipped
+            acc += w4.x;
             a4.x = acc;
-            acc = (w4.y != 0.0f) ? acc + w4.y : acc;
+            acc += w4.y;
             a4.y = acc;
-            acc = (w4.z != 0.0f) ? acc + w4.z : acc;
+            acc += w4.z;
             a4.z = acc;
-            acc = (w4.w != 0.0f) ? acc + w4.w : acc;
+            acc += w4.w;
             a4.w = acc;
             *reinterpret_cast<float4*>(g_alpha + k) = a4;
-        }
-        for (; k < cnt; k++) {
-            const float w = g_w[k];
-            acc = (w != 0.0f) ? acc + w : acc;
-            g_alpha[k] = acc;
+            w4 = wn;
         }
     }
+    DBG_STAMP(dbg, 0);
     group_bar<THREADS>();
     const int gtid = warp == 0 ? lane : tid - 32;
     for (int k = gtid; k < cnt; k += THREADS - 32) {
         const float w = g_w[k];
-        if (w != 0.0f)
-            g_alpha[k] = w / g_alpha[k];
+        g_alpha[k] = (w != 0.0f) ? w / g_alpha[k] : 0.0f;
     }
+    for (int k = cnt + gtid; k < ((cnt + 3) & ~3) + 4; k += THREADS - 32)
+        g_alpha[k] = 0.0f;
     group_bar<THREADS>();
+    DBG_STAMP(dbg, 1);
     if (warp != 0)
         return;
     const int c = lane % 9, ci = c / 3, cj = c % 3;
     const float* gf = g_f + cj * capA;
     const float* gt = g_t + ci * capA;
     float m1 = 0.0f, m2 = 0.0f, cv = 0.0f;
-    for (int k = 0; k < cnt; k += 4) {
-        if (ctl && (k & 63) == 0) {
+    for (int k0 = 0; k0 < cnt; k0 += 128) {
+        if (ctl) { // polled between blocks only, so that the inner loop stays a plain counted loop
             const int v = *ctl;
             if (v >= 0 && (v & 1))
                 return; // this round stops the refinement: the fit would be discarded
         }
-        const float4 w4 = *reinterpret_cast<const float4*>(g_w + k);
-        const float4 a4 = *reinterpret_cast<const float4*>(g_alpha + k);
-        const float4 x4 = *reinterpret_cast<const float4*>(gf + k);
-        const float4 y4 = *reinterpret_cast<const float4*>(gt + k);
-        const float ww[4] = { w4.x, w4.y, w4.z, w4.w }, aa[4] = { a4.x, a4.y, a4.z, a4.w };
-        const float xx[4] = { x4.x, x4.y, x4.z, x4.w }, yy[4] = { y4.x, y4.y, y4.z, y4.w };
+        const int k1 = min(cnt, k0 + 128);
+        float4 a4 = *reinterpret_cast<const float4*>(g_alpha + k0);
+        float4 x4 = *reinterpret_cast<const float4*>(gf + k0);
+        float4 y4 = *reinterpret_cast<const float4*>(gt + k0);
+        for (int k = k0; k < k1; k += 4) {
+            const float4 an = *reinterpret_cast<const float4*>(g_alpha + k + 4);
+            const float4 xn = *reinterpret_cast<const float4*>(gf + k + 4);
+            const float4 yn = *reinterpret_cast<const float4*>(gt + k + 4);
+            const float aa[4] = { a4.x, a4.y, a4.z, a4.w };
+            const float xx[4] = { x4.x, x4.y, x4.z, x4.w }, yy[4] = { y4.x, y4.y, y4.z, y4.w };
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            if (k + u < cnt && ww[u] != 0.0f) {
+            for (int u = 0; u < 4; u++) {
                 const float alpha = aa[u];
                 const float d1 = xx[u] - m1, d2 = yy[u] - m2;
                 const float oma = 1.0f - alpha;
                 const float ad2 = alpha * d2;
                 cv = oma * (cv + ad2 * d1);
                 m1 += alpha * d1;
-                m2 += alpha * d2;
+                m2 += ad2;
             }
+            a4 = an;
+            x4 = xn;
+            y4 = yn;
         }
     }
+    DBG_STAMP(dbg, 2);
     Tfc tfc;
     tfc.accW = 0.0f;
 #pragma unroll
@@ -601,7 +620,7 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     constexpr int NW = THREADS / 32;
     const int pair = R.slot0 + blockIdx.y, h = hyp_begin + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int match_cap = R.match_cap, capA = (match_cap + 3) & ~3, mw = R.mask_words;
+    const int match_cap = R.match_cap, capA = ((match_cap + 3) & ~3) + 8, mw = R.mask_words;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* g_d2 = reinterpret_cast<double*>(smem_raw);
     float* g_w = reinterpret_cast<float*>(g_d2 + capA);
@@ -633,6 +652,10 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
         return;
     }
     const int M = s_M, words = (M + 31) >> 5;
+    long long* dbg = (blockIdx.x == 0 && blockIdx.y == 0 && hyp_begin == 0 && tid == 0) ? R.dbg : nullptr;
+    DBG_STAMP(dbg, 16);
+    if (dbg)
+        dbg[300] = clock64();
     const rgbdfe_point3f* P1 = R.P1_all + (size_t)pair * match_cap;
     const rgbdfe_point3f* P2 = R.P2_all + (size_t)pair * match_cap;
     const float* P1f = reinterpret_cast<const float*>(P1);
@@ -643,11 +666,21 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     const double th = (double)(prm.max_mahal * prm.max_mahal);
 
     auto gather = [&](int k, int j) {
-        g_w[k] = w[j];
+        const float wj = w[j]; // +0 marks a correspondence the fit skips
+        g_w[k] = wj;
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            g_f[c * capA + k] = P1f[j * 3 + c];
-            g_t[c * capA + k] = P2f[j * 3 + c];
+            g_f[c * capA + k] = wj != 0.0f ? P1f[j * 3 + c] : 0.0f;
+            g_t[c * capA + k] = wj != 0.0f ? P2f[j * 3 + c] : 0.0f;
+        }
+    };
+    auto pad_list = [&](int cnt) { // zero entries [cnt, roundup4(cnt) + 4): the fit loops run in fours and prefetch one step
+        const int end = ((cnt + 3) & ~3) + 4;
+        for (int k = cnt + tid; k < end; k += THREADS) {
+            g_w[k] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                g_f[c * capA + k] = g_t[c * capA + k] = 0.0f;
         }
     };
 
@@ -670,6 +703,13 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
                 c += s[j] >= 0 ? 1 : 0;
             s_cnt = c;
         }
+        pad_list(SE3_MAX_SAMPLE); // entries [count, 8) were not written: the sample list has at most 8
+        if (tid < SE3_MAX_SAMPLE && s[tid] < 0) {
+            g_w[tid] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                g_f[c * capA + tid] = g_t[c * capA + tid] = 0.0f;
+        }
     }
     __syncthreads();
     int cur = 0;
@@ -677,8 +717,10 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
         group_tfc_fit<THREADS>(g_w, g_alpha, g_f, g_t, capA, s_cnt, sT[0], nullptr, tid); // getTransformFromMatches (:161-179)
     __syncthreads();
 
+    DBG_STAMP(dbg, 17);
     bool aborted = false;
     for (int refinements = 1; refinements < 20; refinements++) {
+        DBG_STAMP(dbg, 16 + refinements * 8);
         // computeInliersAndError (:181-214): score all matches under sT[cur]
         double Td[16];
 #pragma unroll
@@ -712,6 +754,7 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
         if (tid == THREADS - 1)
             s_abort = ld_volatile(&R.replay[pair].done);
         __syncthreads();
+        DBG_STAMP(dbg, 16 + refinements * 8 + 1);
         const int abort_now = s_abort;
         if (warp == 0) { // exclusive prefix of the per-word counts
             int carry = 0;
@@ -749,7 +792,11 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
                 gather(k, word * 32 + lane);
             }
         }
+        pad_list(cnt);
         __syncthreads();
+        DBG_STAMP(dbg, 16 + refinements * 8 + 2);
+        if (dbg)
+            dbg[16 + refinements * 8 + 7] = cnt;
         const bool more = refinements < 19 && cnt >= (int)prm.min_inlier_th;
         if (warp == 1) {
             if (lane == 0) {
@@ -785,8 +832,9 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
                 *reinterpret_cast<volatile int*>(&s_ctl) = stop | (accept << 1);
             }
         } else if (more)
-            group_tfc_fit<THREADS>(g_w, g_alpha, g_f, g_t, capA, cnt, sT[cur ^ 1], &s_ctl, tid); // next round's transform, speculatively
+            group_tfc_fit<THREADS>(g_w, g_alpha, g_f, g_t, capA, cnt, sT[cur ^ 1], &s_ctl, tid, dbg ? dbg + 16 + refinements * 8 + 4 : nullptr); // next round's transform, speculatively
         __syncthreads();
+        DBG_STAMP(dbg, 16 + refinements * 8 + 3);
         const int ctl = s_ctl;
         if (ctl & 2) { // vRefinedMatches = vInlierMatches; refinedTransformation = transformation
             unsigned* t = ref_m;
@@ -802,6 +850,9 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     if (aborted)
         return;
     __syncthreads();
+    DBG_STAMP(dbg, 200);
+    if (dbg)
+        dbg[301] = clock64();
     HypOut* out = const_cast<HypOut*>(R.hyp_all) + (size_t)pair * MAX_ITERS + h;
     if (tid == 0) {
         out->count = s_refCount;
@@ -821,6 +872,7 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     if (warp == 0) {
         __syncwarp();
         warp_try_replay(R, pair, hyp_end, next_end, scratch, lane);
+        DBG_STAMP(dbg, 201);
     }
 }
 
@@ -857,7 +909,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     const bool few = npairs < 16;
     const int b1 = few ? 32 : 8, b2 = few ? 160 : 64;
     const size_t prep_smem = (size_t)cap * (sizeof(SKey) + 3 * sizeof(int)) + 2 * SORT_QCAP * sizeof(int3);
-    const int capA = (cap + 3) & ~3;
+    const int capA = ((cap + 3) & ~3) + 8;
     size_t hyp_smem = (size_t)capA * 40 + (size_t)c->mask_words * 12;
     const size_t min_smem = ((size_t)RNG_SCRATCH_WORDS + c->mask_words) * 4;
     if (hyp_smem < min_smem)
@@ -874,7 +926,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
             f = *ff;
         k_se3_prepare<<<npairs, PREP_THREADS, prep_smem, c->stream>>>(d_pairs, slot0, f, c->d_partial, c->d_matches, c->d_sorted, c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch,
             prm, update_f2, per_pair_rng, seed, first_pair_index, min_matches, c->d_rng, c->d_pair_rng, c->d_latch, c->d_samples, c->d_rng_used,
-            c->d_replay, c->d_hyp_ready, c->d_pair_lock, b1);
+            c->d_replay, c->d_hyp_ready, c->d_pair_lock, b1, c->dbg_on ? c->d_dbg : nullptr);
         c->launches++;
     }
     ReplayCtx R;
@@ -899,6 +951,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     R.lock_all = c->d_pair_lock;
     R.results = d_results;
     R.slot0 = slot0;
+    R.dbg = c->dbg_on ? c->d_dbg : nullptr;
     R.inl_pos_all = c->d_inl_pos;
     const int bounds[4] = { 0, b1, b2, iters };
     for (int s = 0; s < 3; s++) {

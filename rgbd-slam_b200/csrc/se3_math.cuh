@@ -133,32 +133,45 @@ __device__ inline void jacobi_svd3(const float* A, float* U, float* S, float* V)
 #pragma unroll
     for (int i = 0; i < 3; i++)
         S[i] *= scale;
+    // sort the singular values in descending order (Eigen: for each i the first maximum of S[i..2] is swapped
+    // into place, stop at a zero maximum) — written out for n = 3 so that U, V, S stay in registers
+    auto swap_cols = [&](int a, int b) {
+        float t = S[a];
+        S[a] = S[b];
+        S[b] = t;
 #pragma unroll
-    for (int i = 0; i < 3; i++) {
-        int pos = i;
-        float mx = S[i];
-#pragma unroll
-        for (int k = 0; k < 3; k++)
-            if (k > i && S[k] > mx) {
-                mx = S[k];
-                pos = k;
-            }
-        if (mx == 0.0f)
-            break;
-        if (pos != i) {
-            float t = S[i];
-            S[i] = S[pos];
-            S[pos] = t;
-#pragma unroll
-            for (int r = 0; r < 3; r++) {
-                t = U[r * 3 + i];
-                U[r * 3 + i] = U[r * 3 + pos];
-                U[r * 3 + pos] = t;
-                t = V[r * 3 + i];
-                V[r * 3 + i] = V[r * 3 + pos];
-                V[r * 3 + pos] = t;
-            }
+        for (int r = 0; r < 3; r++) {
+            t = U[r * 3 + a];
+            U[r * 3 + a] = U[r * 3 + b];
+            U[r * 3 + b] = t;
+            t = V[r * 3 + a];
+            V[r * 3 + a] = V[r * 3 + b];
+            V[r * 3 + b] = t;
         }
+    };
+    {
+        int pos = 0;
+        float mx = S[0];
+        if (S[1] > mx) {
+            mx = S[1];
+            pos = 1;
+        }
+        if (S[2] > mx) {
+            mx = S[2];
+            pos = 2;
+        }
+        if (mx == 0.0f)
+            return;
+        if (pos == 1)
+            swap_cols(0, 1);
+        else if (pos == 2)
+            swap_cols(0, 2);
+    }
+    {
+        if (S[2] > S[1]) {
+            swap_cols(1, 2);
+        } else if (S[1] == 0.0f)
+            return;
     }
 }
 
