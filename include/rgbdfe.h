@@ -129,6 +129,9 @@ int rgbdfe_match_knn2(rgbdfe_ctx* ctx, const uint8_t* q_desc, int nq, const uint
 /* The context owns one glibc-rand()-compatible stream (TYPE_3).  state is 35
  * int32: 34 ring words + the linear output index. */
 int rgbdfe_rng_seed(rgbdfe_ctx* ctx, unsigned seed);
+/* One rand() draw from the context stream (what Random::randomInt / randomValue consume,
+ * System/Random.h:13-18, System/Random.cpp:15-20). */
+int rgbdfe_rng_next(rgbdfe_ctx* ctx, int* value);
 int rgbdfe_rng_get_state(rgbdfe_ctx* ctx, int32_t* state35);
 int rgbdfe_rng_set_state(rgbdfe_ctx* ctx, const int32_t* state35);
 

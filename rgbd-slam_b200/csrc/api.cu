@@ -710,6 +710,25 @@ int rgbdfe_rng_set_state(rgbdfe_ctx* c, const int32_t* state35)
     return RGBDFE_OK;
 }
 
+int rgbdfe_rng_next(rgbdfe_ctx* c, int* value)
+{
+    if (!c || !value)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    RngState s;
+    CUDA_TRY(c, cudaMemcpy(&s, c->d_rng, sizeof(s), cudaMemcpyDeviceToHost));
+    // rand(): r[i] = r[i-3] + r[i-31], output >> 1 (glibc TYPE_3)
+    const unsigned v = (unsigned)s.r[(s.idx - 31) % 34] + (unsigned)s.r[(s.idx - 3) % 34];
+    s.r[s.idx % 34] = (int)v;
+    s.idx++;
+    if (s.idx >= 34 * 1000000)
+        s.idx -= 34 * 999990;
+    *value = (int)(v >> 1);
+    CUDA_TRY(c, cudaMemcpy(c->d_rng, &s, sizeof(s), cudaMemcpyHostToDevice));
+    return RGBDFE_OK;
+}
+
 int rgbdfe_depth_cov_get(rgbdfe_ctx* c, int* latched, double* cov)
 {
     if (!c)

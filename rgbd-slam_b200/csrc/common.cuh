@@ -225,7 +225,7 @@ struct rgbdfe_ctx {
         }                                                                         \
     } while (0)
 
-#define DBG_SLOTS 512
+#define DBG_SLOTS 1024
 #ifdef __CUDACC__
 __device__ __forceinline__ long long dbg_now()
 {

@@ -23,13 +23,17 @@ struct KeyLess {
     __device__ bool operator()(const SKey& a, const SKey& b) const { return a.d < b.d; }
 };
 
-__device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos, int lane, int* cut_out)
+__device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos, int lane, int* cut_out, long long* dbg = nullptr)
 {
+    if (lane != 0)
+        dbg = nullptr;
+    if (dbg) dbg[0] = dbg_now();
     if (lane == 0) {
         int mid = f + (l - f) / 2;
         move_median_to_first_(a + f, a + f + 1, a + mid, a + l - 1, KeyLess());
     }
     __syncwarp();
+    if (dbg) dbg[1] = dbg_now();
     const float p = a[f].d;
     int nL = 0, nR = 0;
     const int first = f + 1;
@@ -51,6 +55,7 @@ __device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos
         nR += __popc(bal);
     }
     __syncwarp();
+    if (dbg) dbg[2] = dbg_now();
     const int nmin = min(nL, nR);
     int K = nmin;
     for (int k0 = 0; k0 < nmin; k0 += 32) {
@@ -66,6 +71,7 @@ __device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos
     const int Rprev = K > 0 ? Rpos[f + K - 1] : l;
     const int cut = min(Lk, Rprev);
     __syncwarp();
+    if (dbg) dbg[3] = dbg_now();
     for (int k = lane; k < K; k += 32) {
         const int x = Lpos[f + k], y = Rpos[f + k];
         const SKey t = a[x];
@@ -73,6 +79,7 @@ __device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos
         a[y] = t;
     }
     __syncwarp();
+    if (dbg) dbg[4] = dbg_now();
     *cut_out = cut;
 }
 
@@ -81,8 +88,9 @@ __device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos
 #define SORT_QCAP 512
 // Called by the first `nthr` threads of the CTA (a multiple of 32); synchronises on named barrier 1.
 #define SORT_BAR() asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory")
-__device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, int3* qa, int3* qb, int* counters /* [3] */, int nthr)
+__device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, int3* qa, int3* qb, int* counters /* [3] */, int nthr, long long* dbg = nullptr)
 {
+    int dbg_level = 0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
     if (n <= 1)
         return;
@@ -108,6 +116,11 @@ __device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, 
         const int ncur = counters[2];
         if (ncur == 0)
             break;
+        if (dbg && tid == 0 && dbg_level < 40) {
+            dbg[2 * dbg_level] = dbg_now();
+            dbg[2 * dbg_level + 1] = ncur;
+            dbg_level++;
+        }
         for (int r = warp; r < ncur; r += nwarps) {
             const int3 rg = cur[r];
             const int f = rg.x, l = rg.y, depth = rg.z;
@@ -118,7 +131,8 @@ __device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, 
                 continue;
             }
             int cut;
-            warp_partition_range(a, f, l, Lpos, Rpos, lane, &cut);
+            warp_partition_range(a, f, l, Lpos, Rpos, lane, &cut, (dbg && r == 0 && dbg_level < 12) ? dbg + 80 + 8 * dbg_level : nullptr);
+            if (dbg && r == 0 && lane == 0 && dbg_level < 12) dbg[80 + 8 * dbg_level + 6] = l - f;
             if (lane == 0) {
                 // right part [cut, l) and left part [f, cut), both with depth - 1
                 const int parts[2][2] = { { cut, l }, { f, cut } };
@@ -135,6 +149,7 @@ __device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, 
                 }
             }
         }
+        if (dbg && tid == 0 && dbg_level < 12) dbg[80 + 8 * dbg_level + 5] = dbg_now();
         SORT_BAR();
         if (tid == 0) {
             counters[2] = min(counters[0], SORT_QCAP);
@@ -144,6 +159,10 @@ __device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, 
         cur = nxt;
         nxt = t;
         SORT_BAR();
+    }
+    if (dbg && tid == 0 && dbg_level < 40) {
+        dbg[2 * dbg_level] = dbg_now();
+        dbg[2 * dbg_level + 1] = -counters[1];
     }
     // final insertion sort, leaf by leaf (stable insertion == __final_insertion_sort restricted to the leaf)
     const int nleaves = counters[1];
