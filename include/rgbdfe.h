@@ -87,6 +87,13 @@ void* rgbdfe_stream(rgbdfe_ctx* ctx);
 /* number of kernels launched by the context so far (bench gpu_launches). */
 long long rgbdfe_launch_count(const rgbdfe_ctx* ctx);
 int rgbdfe_sync(rgbdfe_ctx* ctx);
+/* Pipelining across contexts of one device (e.g. one context extracts frame batch n+1 while another tracks
+ * batch n; rgbdfe_frame handles are plain device buffers and may be used by either): everything enqueued on
+ * `waiter` after this call runs after everything enqueued on `signaler` before it.  No host synchronisation. */
+int rgbdfe_stream_wait(rgbdfe_ctx* waiter, rgbdfe_ctx* signaler);
+/* high != 0: the context's stream gets the device's highest priority (for the latency-bound match/RANSAC
+ * chain next to a throughput-bound extraction context).  Synchronises the context. */
+int rgbdfe_set_stream_priority(rgbdfe_ctx* ctx, int high);
 /* Per-kernel timing with CUDA events on the context stream (bench.py roofline).
  * enable(1) starts collecting, read() synchronises and returns the summed
  * milliseconds and launch-group counts per kernel id (n >= 10 entries);

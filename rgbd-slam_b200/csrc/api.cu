@@ -321,6 +321,8 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_pair_workspaces(c);
     free_frame(c->scratch);
     free_frame(c->scratch2);
+    if (c->order_evt)
+        cudaEventDestroy(c->order_evt);
     cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     cudaStreamDestroy(c->stream);
@@ -330,6 +332,35 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
 const char* rgbdfe_last_error(const rgbdfe_ctx* c) { return c ? c->err.c_str() : "null context"; }
 void* rgbdfe_stream(rgbdfe_ctx* c) { return c ? (void*)c->stream : nullptr; }
 long long rgbdfe_launch_count(const rgbdfe_ctx* c) { return c ? c->launches : 0; }
+int rgbdfe_stream_wait(rgbdfe_ctx* waiter, rgbdfe_ctx* signaler)
+{
+    if (!waiter || !signaler || waiter->device != signaler->device)
+        return RGBDFE_E_ARG;
+    if (waiter == signaler)
+        return RGBDFE_OK;
+    cudaSetDevice(signaler->device);
+    if (!signaler->order_evt)
+        CUDA_TRY(signaler, cudaEventCreateWithFlags(&signaler->order_evt, cudaEventDisableTiming));
+    CUDA_TRY(signaler, cudaEventRecord(signaler->order_evt, signaler->stream));
+    CUDA_TRY(waiter, cudaStreamWaitEvent(waiter->stream, signaler->order_evt, 0));
+    return RGBDFE_OK;
+}
+
+int rgbdfe_set_stream_priority(rgbdfe_ctx* c, int high)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int lo = 0, hi = 0;
+    CUDA_TRY(c, cudaDeviceGetStreamPriorityRange(&lo, &hi)); // numerically lower = higher priority
+    cudaStream_t s = nullptr;
+    CUDA_TRY(c, cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, high ? hi : lo));
+    cudaStreamDestroy(c->stream);
+    c->stream = s;
+    return RGBDFE_OK;
+}
+
 int rgbdfe_sync(rgbdfe_ctx* c)
 {
     if (!c)

@@ -147,6 +147,7 @@ struct UmeState {
 struct rgbdfe_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaEvent_t order_evt = nullptr; // rgbdfe_stream_wait
     std::string err;
     long long launches = 0;
     int max_w = 0, max_h = 0, max_feats = 0, max_batch = 1;

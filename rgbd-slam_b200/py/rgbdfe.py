@@ -119,6 +119,12 @@ class Context:
     def launches(self):
         return lib().rgbdfe_launch_count(self.h)
 
+    def stream_wait(self, signaler):
+        self._chk(lib().rgbdfe_stream_wait(self.h, signaler.h))
+
+    def set_stream_priority(self, high=True):
+        self._chk(lib().rgbdfe_set_stream_priority(self.h, int(high)))
+
     def sync(self):
         self._chk(lib().rgbdfe_sync(self.h))
 

@@ -307,3 +307,35 @@ def test_verify_batch_matches_per_pair_oracle(oracle):
         ctx.kfdb_destroy(db)
     finally:
         ctx.close()
+
+
+def test_config3_full_hd_4000_features(oracle):
+    """BASELINE configs[2]: 1920x1080 colour-sized frames, 4000 ORB features — extraction bit-exact, then one tracked pair."""
+    import rgbdfe
+    import synth
+
+    cam, frames = synth.sequence("kinect2", n=2, seed=3456)
+    ctx = rgbdfe.Context(0, 1920, 1080, 4000, 2)
+    try:
+        ctx.orb_configure(4000, 1.2, 8, 20, 7)
+        ctx.rng_seed(42)
+        fr = [rgbdfe.Frame(ctx) for _ in frames]
+        ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)
+        ctx.track_sequence(fr, 0)
+        res = ctx.track_results(0, 1)[0]
+        orb = oracle.Orb(4000)
+        ref = []
+        for f, (g, d) in zip(fr, frames):
+            k, de = orb.extract(g)
+            p3 = _unproject(cam, k, d)
+            gk, gd, gp, _ = f.download()
+            assert len(gk) == len(k) >= 3900
+            assert (gk == k).all() and (gd == de).all() and (gp == p3).all()
+            ref.append((k, de, p3))
+        m = oracle.match(ref[0][1], ref[1][1], np.zeros(len(ref[0][0]), np.uint8), ref[0][2], ref[1][2], 0.9, True)
+        r = oracle.ransac_se3(ref[0][2], ref[1][2], m, oracle.Rng(42), oracle.Latch(), 200, 10, 3.0, 4)
+        assert res["n_matches"] == len(m) and bool(res["ok"]) == r["ok"] and res["n_inliers"] == len(r["inliers"])
+        assert res["iters_executed"] == r["iters_executed"]
+        assert np.abs(res["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
+    finally:
+        ctx.close()
