@@ -87,6 +87,10 @@ void* rgbdfe_stream(rgbdfe_ctx* ctx);
 /* number of kernels launched by the context so far (bench gpu_launches). */
 long long rgbdfe_launch_count(const rgbdfe_ctx* ctx);
 int rgbdfe_sync(rgbdfe_ctx* ctx);
+/* Tuning knobs that never change results.  "ransac_first_chunk" (default 32): how many RANSAC iterations the
+ * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
+ * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU. */
+int rgbdfe_set_option(rgbdfe_ctx* ctx, const char* name, int value);
 /* Pipelining across contexts of one device (e.g. one context extracts frame batch n+1 while another tracks
  * batch n; rgbdfe_frame handles are plain device buffers and may be used by either): everything enqueued on
  * `waiter` after this call runs after everything enqueued on `signaler` before it.  No host synchronisation. */

@@ -361,6 +361,20 @@ int rgbdfe_set_stream_priority(rgbdfe_ctx* c, int high)
     return RGBDFE_OK;
 }
 
+int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
+{
+    if (!c || !name)
+        return RGBDFE_E_ARG;
+    if (!strcmp(name, "ransac_first_chunk")) {
+        if (value < 1 || value > MAX_ITERS)
+            return RGBDFE_E_ARG;
+        c->ransac_first_chunk = value;
+        return RGBDFE_OK;
+    }
+    c->set_error(std::string("unknown option ") + name);
+    return RGBDFE_E_ARG;
+}
+
 int rgbdfe_sync(rgbdfe_ctx* c)
 {
     if (!c)

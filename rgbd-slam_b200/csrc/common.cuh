@@ -205,6 +205,7 @@ struct rgbdfe_ctx {
     RngState* d_pair_rng = nullptr; // [pairs] per-pair streams (batched)
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
+    int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
     int dbg_on = 0;
 

@@ -168,30 +168,47 @@ __device__ __forceinline__ int fast_strength(const uint8_t* __restrict__ p, int 
     const bool dark = has9(md), bright = has9(mb);
     if (!dark && !bright)
         return 0;
+    // a pixel cannot be both (two 9-arcs of a 16-ring overlap): one branch-free pass over e = +-d.
+    // max over the 16 arcs of the arc minimum, arc minima by doubling (2, 4, 8, then the 9th element)
+    int e[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+        e[k] = dark ? d[k] : -d[k];
+    int m2[16], m4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+        m2[k] = min(e[k], e[(k + 1) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+        m4[k] = min(m2[k], m2[(k + 2) & 15]);
     int best = 0;
-    if (dark) {
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
-            int a = d[k];
-#pragma unroll
-            for (int j = 1; j < 9; j++)
-                a = min(a, d[(k + j) & 15]);
-            best = max(best, a);
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            int a = -d[k];
-#pragma unroll
-            for (int j = 1; j < 9; j++)
-                a = min(a, -d[(k + j) & 15]);
-            best = max(best, a);
-        }
+    for (int k = 0; k < 16; k++) {
+        const int m8 = min(m4[k], m4[(k + 4) & 15]);
+        best = max(best, min(m8, e[(k + 8) & 15]));
     }
     return best;
 }
 
-__global__ void __launch_bounds__(256) k_fast_cells(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+// Necessary condition for a 9-arc at threshold t: every opposite pair (k, k+8) of the ring has a member inside
+// the arc, so for four of the pairs at least one member must be brighter than v + t (bright corner) or darker
+// than v - t (dark corner).  8 ring pixels instead of 16, no masks; rejects most pixels.
+__device__ __forceinline__ bool fast_candidate(const uint8_t* __restrict__ p, int pitch, int t)
+{
+    const int v = p[0], hi = v + t, lo = v - t;
+    const int a0 = p[3 * pitch], a8 = p[-3 * pitch], a4 = p[3], a12 = p[-3];
+    bool b = ((a0 > hi) | (a8 > hi)) & ((a4 > hi) | (a12 > hi));
+    bool d = ((a0 < lo) | (a8 < lo)) & ((a4 < lo) | (a12 < lo));
+    if (!(b | d))
+        return false;
+    const int a2 = p[2 * pitch + 2], a10 = p[-2 * pitch - 2], a6 = p[-2 * pitch + 2], a14 = p[2 * pitch - 2];
+    b = b & ((a2 > hi) | (a10 > hi)) & ((a6 > hi) | (a14 > hi));
+    d = d & ((a2 < lo) | (a10 < lo)) & ((a6 < lo) | (a14 < lo));
+    return b | d;
+}
+
+#define FAST_THREADS 256
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     int* __restrict__ cell_count, unsigned* __restrict__ cell_list, int cell_slot)
 {
     int level = 0;
@@ -201,7 +218,7 @@ __global__ void __launch_bounds__(256) k_fast_cells(const OrbConfig* __restrict_
     const int cell = blockIdx.x - L.cell_off;
     const int ci = cell / L.nCols, cj = cell % L.nCols;
     const int slot = blockIdx.y;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     int* out_count = cell_count + (size_t)slot * cell_slot + blockIdx.x;
     unsigned* out_list = cell_list + ((size_t)slot * cell_slot + blockIdx.x) * CELL_CAP;
 
@@ -218,79 +235,114 @@ __global__ void __launch_bounds__(256) k_fast_cells(const OrbConfig* __restrict_
             *out_count = 0;
         return;
     }
-    __shared__ uint8_t s_img[CELL_MAX_DIM][CELL_MAX_DIM + 8];
-    __shared__ uint8_t s_S[CELL_MAX_DIM][CELL_MAX_DIM + 8];
-    __shared__ uint8_t s_keep[CELL_MAX_DIM * CELL_MAX_DIM];
-    __shared__ int s_n;
+    constexpr int PITCH = CELL_MAX_DIM + 8;
+    __shared__ __align__(16) uint8_t s_img[CELL_MAX_DIM][PITCH];
+    __shared__ __align__(16) uint8_t s_S[CELL_MAX_DIM][PITCH];
+    __shared__ unsigned short s_cand[CELL_MAX_DIM * CELL_MAX_DIM]; // pixels that pass the pair test: r << 8 | c
+    __shared__ unsigned short s_keep[CELL_MAX_DIM * CELL_MAX_DIM]; // NMS survivors of this attempt: r << 8 | c, unordered
+    __shared__ int s_ncand, s_n;
     const uint8_t* src = pyr + slot * pyr_slot + L.pyr_off + (size_t)(EDGE_THRESHOLD + iniY) * L.pstride + EDGE_THRESHOLD + iniX;
-    for (int i = tid; i < cw * ch; i += 256) {
-        int r = i / cw, c = i % cw;
-        s_img[r][c] = src[(size_t)r * L.pstride + c];
-        s_S[r][c] = 0;
+    // rows are staged as 32-bit words from the 4-byte aligned address at or below the cell's first column
+    const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
+    const int wpr = (cw + mis + 3) >> 2; // words per row
+    for (int i = tid; i < wpr * ch; i += FAST_THREADS) {
+        const int r = i / wpr, wq = i - r * wpr;
+        const unsigned wv = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * L.pstride + 4 * wq);
+        *reinterpret_cast<unsigned*>(&s_img[r][4 * wq]) = wv;
+        *reinterpret_cast<unsigned*>(&s_S[r][4 * wq]) = 0u;
     }
-    if (tid == 0)
+    if (tid == 0) {
+        s_ncand = 0;
         s_n = 0;
+    }
     __syncthreads();
+    // image column c lives at s_img[r][c + mis]; s_S uses the same shift
     const int dw = cw - 6, dh = ch - 6;
     const int th_lo = min(cfg->iniTh, cfg->minTh);
-    for (int i = tid; i < dw * dh; i += 256) {
-        int r = 3 + i / dw, c = 3 + i % dw;
-        int S = fast_strength(&s_img[r][c], CELL_MAX_DIM + 8, th_lo);
-        s_S[r][c] = (uint8_t)min(S, 255);
+    const unsigned lt = (1u << lane) - 1;
+    for (int i0 = 0; i0 < dw * dh; i0 += FAST_THREADS) {
+        const int i = i0 + tid;
+        bool cand = false;
+        int r = 0, c = 0;
+        if (i < dw * dh) {
+            r = 3 + i / dw;
+            c = 3 + i - (r - 3) * dw;
+            cand = fast_candidate(&s_img[r][c + mis], PITCH, th_lo);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, cand);
+        if (bal) {
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&s_ncand, __popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (cand)
+                s_cand[base + __popc(bal & lt)] = (unsigned short)(r << 8 | c);
+        }
+    }
+    __syncthreads();
+    const int ncand = s_ncand;
+    for (int i = tid; i < ncand; i += FAST_THREADS) {
+        const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
+        const int S = fast_strength(&s_img[r][c + mis], PITCH, th_lo);
+        s_S[r][c + mis] = (uint8_t)min(S, 255);
     }
     __syncthreads();
     int th = cfg->iniTh;
     for (int attempt = 0; attempt < 2; attempt++) {
-        int local = 0;
-        for (int i = tid; i < dw * dh; i += 256) {
-            int r = 3 + i / dw, c = 3 + i % dw;
-            int S = s_S[r][c];
+        // 3x3 non-max suppression inside the cell's window (cv::FAST, nonmaxSuppression = true), candidates only
+        for (int i0 = 0; i0 < ncand; i0 += FAST_THREADS) {
+            const int i = i0 + tid;
             bool keep = false;
-            if (S > th) {
-                const int sc = S - 1;
-                keep = true;
+            int rc = 0;
+            if (i < ncand) {
+                rc = s_cand[i];
+                const int r = rc >> 8, c = (rc & 255) + mis;
+                const int S = s_S[r][c];
+                if (S > th) {
+                    const int sc = S - 1;
+                    keep = true;
 #pragma unroll
-                for (int dy = -1; dy <= 1; dy++)
+                    for (int dy = -1; dy <= 1; dy++)
 #pragma unroll
-                    for (int dx = -1; dx <= 1; dx++) {
-                        if (dx == 0 && dy == 0)
-                            continue;
-                        int Sn = s_S[r + dy][c + dx];
-                        int sn = Sn > th ? Sn - 1 : 0;
-                        keep = keep && (sc > sn);
-                    }
+                        for (int dx = -1; dx <= 1; dx++) {
+                            if (dx == 0 && dy == 0)
+                                continue;
+                            const int Sn = s_S[r + dy][c + dx];
+                            const int sn = Sn > th ? Sn - 1 : 0;
+                            keep = keep && (sc > sn);
+                        }
+                }
             }
-            s_keep[i] = keep;
-            local += keep;
+            const unsigned bal = __ballot_sync(0xffffffffu, keep);
+            if (bal) {
+                int base = 0;
+                if (lane == 0)
+                    base = atomicAdd(&s_n, __popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (keep)
+                    s_keep[base + __popc(bal & lt)] = (unsigned short)rc;
+            }
         }
-        if (local)
-            atomicAdd(&s_n, local);
         __syncthreads();
         if (s_n > 0 || th == cfg->minTh)
             break;
         th = cfg->minTh; // cv::FAST returned nothing at iniThFAST: retry at minThFAST (:658-661)
         __syncthreads();
     }
-    // ordered (row-major) compaction by warp 0
-    if (tid < 32) {
-        int base = 0;
-        const int total = dw * dh;
-        for (int i0 = 0; i0 < total; i0 += 32) {
-            int i = i0 + tid;
-            bool k = i < total && s_keep[i];
-            unsigned bal = __ballot_sync(0xffffffffu, k);
-            if (k) {
-                int pos = base + __popc(bal & ((1u << tid) - 1));
-                if (pos < CELL_CAP) {
-                    int r = 3 + i / dw, c = 3 + i % dw;
-                    out_list[pos] = pack_cand(c + cj * L.wCell, r + ci * L.hCell, s_S[r][c] - 1);
-                }
-            }
-            base += __popc(bal);
+    // row-major output order (cv::FAST emits keypoints row by row): rank each survivor by its (r, c) key
+    const int n = s_n;
+    for (int i = tid; i < n; i += FAST_THREADS) {
+        const int key = s_keep[i];
+        int rank = 0;
+        for (int j = 0; j < n; j++)
+            rank += s_keep[j] < key;
+        if (rank < CELL_CAP) {
+            const int r = key >> 8, c = key & 255;
+            out_list[rank] = pack_cand(c + cj * L.wCell, r + ci * L.hCell, s_S[r][c + mis] - 1);
         }
-        if (tid == 0)
-            *out_count = min(base, CELL_CAP);
     }
+    if (tid == 0)
+        *out_count = min(n, CELL_CAP);
 }
 
 // ---------------------------------------------------------------- launchers

@@ -17,7 +17,10 @@
 
 namespace rgbdfe {
 
-__constant__ signed char c_pattern[1024];
+// bit_pattern_31_ as int8 (x0, y0, x1, y1) x 256.  Lane L of a warp reads bytes [32 L, 32 L + 32): a per-lane index,
+// which constant memory would serialise (one address per cycle through the ADU), so the table lives in global
+// memory and is staged into shared memory by every CTA.
+__device__ __align__(16) signed char g_pattern[1024];
 
 struct QtNode {
     short ulx, uly, brx, bry;
@@ -451,6 +454,9 @@ __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __rest
     const FrameBatch frames /* by value: one frame struct per slot */, const float* __restrict__ depth, size_t depth_slot,
     int depth_stride, int unproject, float fx, float fy, float cx, float cy)
 {
+    __shared__ __align__(16) signed char s_pattern[1024];
+    reinterpret_cast<int*>(s_pattern)[threadIdx.x] = reinterpret_cast<const int*>(g_pattern)[threadIdx.x]; // 256 threads x 4 B
+    __syncthreads();
     const int slot = blockIdx.y;
     const int lane = threadIdx.x & 31;
     int gi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); // output keypoint index
@@ -499,7 +505,9 @@ __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __rest
     float a, b;
     sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);
     const uint8_t* bc = blur + slot * blur_slot + L.blur_off + (size_t)s.y * L.bstride + s.x;
-    const signed char* pat = c_pattern + lane * 32;
+    signed char pat[32];
+    *reinterpret_cast<uint4*>(pat) = *reinterpret_cast<const uint4*>(s_pattern + lane * 32);
+    *reinterpret_cast<uint4*>(pat + 16) = *reinterpret_cast<const uint4*>(s_pattern + lane * 32 + 16);
     unsigned val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
@@ -570,7 +578,7 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
 int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, int depth_stride, float fx, float fy, float cx, float cy)
 {
     if (!g_pattern_uploaded[c->device]) {
-        CUDA_TRY(c, cudaMemcpyToSymbolAsync(c_pattern, kBriefPattern, 1024, 0, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaMemcpyToSymbolAsync(g_pattern, kBriefPattern, 1024, 0, cudaMemcpyHostToDevice, c->stream));
         g_pattern_uploaded[c->device] = true;
     }
     const int warps = c->kp_cap + 1; // one extra warp publishes the count

@@ -907,7 +907,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     const int iters = prm.iterations < MAX_ITERS ? (prm.iterations > 0 ? prm.iterations : 0) : MAX_ITERS;
     // chunk boundaries: a single pair fills the GPU with hypotheses; many pairs start small
     const bool few = npairs < 16;
-    const int b1 = few ? 32 : 8, b2 = few ? (iters > 32 ? iters : 33) : 64; // few pairs: one follow-up launch takes the rest
+    const int b1 = few ? c->ransac_first_chunk : 8, b2 = few ? (iters > b1 ? iters : b1 + 1) : 64; // few pairs: one follow-up launch takes the rest
     const size_t prep_smem = (size_t)cap * (sizeof(SKey) + 3 * sizeof(int)) + 2 * SORT_QCAP * sizeof(int3);
     const int capA = ((cap + 3) & ~3) + 8;
     size_t hyp_smem = (size_t)capA * 40 + (size_t)c->mask_words * 12;

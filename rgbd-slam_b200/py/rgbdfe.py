@@ -125,6 +125,9 @@ class Context:
     def set_stream_priority(self, high=True):
         self._chk(lib().rgbdfe_set_stream_priority(self.h, int(high)))
 
+    def set_option(self, name, value):
+        self._chk(lib().rgbdfe_set_option(self.h, name.encode(), int(value)))
+
     def sync(self):
         self._chk(lib().rgbdfe_sync(self.h))
 

@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box pass: parity tests, smoke, bench, ncu launch list. Outputs under gpurun_out/.
+# One GPU-box pass: parity tests, smoke, bench (both arms), ncu launch list + full captures. Outputs under gpurun_out/.
 set -x
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/smi.txt 2>&1
@@ -7,5 +7,9 @@ timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 3000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 1 --no-cpu --frames 66 > gpurun_out/ncu_bench.log 2>&1
+NCU_BENCH="python bench.py --steps 1 --warmup 1 --no-cpu --frames 66 --sequences 1"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 2500 --csv --log-file gpurun_out/launches.csv $NCU_BENCH > gpurun_out/ncu_bench.log 2>&1
+for k in k_fast_cells k_orient_describe k_knn2_hamming k_se3_hypotheses k_gauss7 k_se3_prepare; do
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 2 -c 1 -f -o gpurun_out/full_$k $NCU_BENCH > gpurun_out/ncu_full_$k.log 2>&1
+done
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; cat gpurun_out/bench.json
