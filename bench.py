@@ -25,6 +25,10 @@ import tempfile
 import threading
 import time
 
+# Every sequence in flight owns two streams; with the default of 8 hardware work queues they alias and the chains
+# of different sequences serialise behind each other's extraction kernels.  Must be set before CUDA initialises.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools"), os.path.join(ROOT, "rgbd-slam_b200", "py")):
     if p not in sys.path:
@@ -156,9 +160,13 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=96)
-    ap.add_argument("--sequences", type=int, default=8, help="independent tracked sequences in flight on each GPU")
+    ap.add_argument("--sequences", type=int, default=24, help="independent tracked sequences in flight on each GPU")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--latency-sms", type=int, default=0,
+                    help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
+    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial"],
+                    help="diagnostic: time only the extraction half or only the match/RANSAC chains (not a bench value)")
     ap.add_argument("--verify-kf", type=int, default=512, help="keyframes per GPU for the verification leg (N>1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -186,6 +194,8 @@ def main():
     gp_h, dp_h = gray_h.numpy(), depth_h.numpy()
     L = rgbdfe.lib()
 
+    part = rgbdfe.device_partition(local_rank, args.latency_sms) if args.latency_sms > 0 else None
+
     class Seq:
         """One tracked sequence: two contexts of one device — ctx_x extracts frame batch n+1 (throughput-bound, big
         grids) while ctx_t runs the sequential match/RANSAC chain of batch n on a high-priority stream;
@@ -195,7 +205,11 @@ def main():
             self.ctx_x = rgbdfe.Context(local_rank, W, H, NFEAT, B)
             self.ctx_t = rgbdfe.Context(local_rank, W, H, NFEAT, 1)
             self.ctx_x.orb_configure(NFEAT, 1.2, 8, 20, 7)
-            self.ctx_t.set_stream_priority(True)
+            if part:
+                self.ctx_x.bind_partition(rgbdfe.PART_THROUGHPUT)
+                self.ctx_t.bind_partition(rgbdfe.PART_LATENCY)
+            else:
+                self.ctx_t.set_stream_priority(True)
             self.ctx_t.set_option("ransac_first_chunk", first_chunk)
             self.ctx_t.rng_seed(42 + k)
             self.sets = [[rgbdfe.Frame(self.ctx_x) for _ in range(B)] for _ in range(3)]
@@ -221,12 +235,21 @@ def main():
             i = self.i
             cur, nxt = self.sets[i % 3], self.sets[(i + 1) % 3]
             self.ctx_t.stream_wait(self.ctx_x)  # batch i was extracted by the previous step
-            self.extract(nxt, dev)              # batch i+1, concurrent with the chain below
+            if args.mode != "chain":
+                self.extract(nxt, dev)          # batch i+1, concurrent with the chain below
+            if args.mode == "serial":           # diagnostic: the chain waits for this extraction too (no overlap)
+                self.ctx_t.stream_wait(self.ctx_x)
+            if args.mode == "extract":
+                self.n_res = 0
+                return
             chain = ([self.sets[(i - 1) % 3][-1]] if self.have_ref else []) + cur
             self.ctx_t.track_sequence(chain, 0, RATIO, True, ITERS, MIN_INL, 3.0, 4, True)
             self.n_res = len(chain) - 1
 
         def collect(self):
+            if self.n_res == 0:
+                self.i += 1
+                return
             res = self.ctx_t.track_results(0, self.n_res)
             self.ok += int(res["ok"].sum())
             self.n += len(res)
@@ -330,9 +353,11 @@ def main():
     peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
     # dominant HBM-bound kernel of the extraction stage
     ext = {k: v for k, v in kernels.items() if k in ALG_BYTES and v[1] > 0}
+    if not ext:  # --mode chain (diagnostic): no extraction kernel ran
+        ext = {k: v for k, v in kernels.items() if v[1] > 0}
     dom = max(ext, key=lambda k: ext[k][0])
     dom_ms, dom_cnt = ext[dom]
-    per_launch_bytes = ALG_BYTES[dom] * B
+    per_launch_bytes = ALG_BYTES.get(dom, 0) * B
     achieved = per_launch_bytes / (dom_ms / dom_cnt * 1e-3) / 1e9
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
@@ -400,7 +425,8 @@ def main():
             "data": "synthetic",
             "config": {"workload": "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])",
                        "sequences_in_flight": S, "single_sequence_frames_per_s": single, "mean_ransac_iterations": float(np.mean(state["iters"])),
-                       "batch_frames_per_step": B, "distinct_frames": F, "pipeline": "extraction of batch n+1 (context A) overlaps the match/RANSAC chain of batch n (context B, high-priority stream)", "l2": f"inputs larger than L2: rotating {F}-frame set, {F * (W * H * 5) / 1e6:.0f} MB",
+                       "batch_frames_per_step": B, "distinct_frames": F, "pipeline": "extraction of batch n+1 (context A) overlaps the match/RANSAC chain of batch n (context B)",
+                       "sm_partition": ({"latency_sms": part[0], "throughput_sms": part[1], "how": "CUDA green contexts"} if part else "none (stream priorities)"), "l2": f"inputs larger than L2: rotating {F}-frame set, {F * (W * H * 5) / 1e6:.0f} MB",
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": S * B * W * H * 5, "d2h_bytes_per_step": S * B * 84},

@@ -98,6 +98,21 @@ int rgbdfe_stream_wait(rgbdfe_ctx* waiter, rgbdfe_ctx* signaler);
 /* high != 0: the context's stream gets the device's highest priority (for the latency-bound match/RANSAC
  * chain next to a throughput-bound extraction context).  Synchronises the context. */
 int rgbdfe_set_stream_priority(rgbdfe_ctx* ctx, int high);
+/* SM partitioning (CUDA green contexts) for the same split, stronger than priorities: the device's SMs are
+ * divided once per process into a latency partition of about `latency_sms` SMs (the driver rounds to its
+ * granularity, 8 SMs on sm_90+) and a throughput partition with the rest; the sizes actually provisioned are
+ * returned.  A second call for the same device returns the existing split.  RGBDFE_E_STATE: the driver has
+ * no green contexts (callers fall back to rgbdfe_set_stream_priority). */
+int rgbdfe_device_partition(int device, int latency_sms, int* latency_got, int* throughput_got);
+/* Moves the context's stream into a partition of its device.  RGBDFE_PART_THROUGHPUT: extraction contexts.
+ * RGBDFE_PART_LATENCY: tracking contexts — the filter/sort/RANSAC chain of rgbdfe_track_sequence runs on the
+ * latency partition at the highest stream priority while its kNN (one grid over every pair of the chain) is
+ * sent to the throughput partition.  RGBDFE_PART_NONE: back to an ordinary stream.  Synchronises the context;
+ * rgbdfe_stream() changes.  Results never depend on the binding. */
+#define RGBDFE_PART_NONE 0
+#define RGBDFE_PART_THROUGHPUT 1
+#define RGBDFE_PART_LATENCY 2
+int rgbdfe_bind_partition(rgbdfe_ctx* ctx, int role);
 /* Per-kernel timing with CUDA events on the context stream (bench.py roofline).
  * enable(1) starts collecting, read() synchronises and returns the summed
  * milliseconds and launch-group counts per kernel id (n >= 10 entries);

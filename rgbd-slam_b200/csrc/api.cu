@@ -323,6 +323,10 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_frame(c->scratch2);
     if (c->order_evt)
         cudaEventDestroy(c->order_evt);
+    if (c->bulk_evt)
+        cudaEventDestroy(c->bulk_evt);
+    if (c->bulk_stream)
+        cudaStreamDestroy(c->bulk_stream);
     cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     cudaStreamDestroy(c->stream);
@@ -989,13 +993,31 @@ int rgbdfe_track_sequence(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count,
             return RGBDFE_E_ARG;
         fc.f[i] = *frames[i];
     }
+    // A context bound to the latency partition sends the chain's throughput half (pair table + kNN, a grid
+    // that fills every SM) to its stream on the throughput partition, ordered both ways with events.
+    cudaStream_t chain_stream = c->stream;
+    if (c->bulk_stream) {
+        if (!c->bulk_evt)
+            CUDA_TRY(c, cudaEventCreateWithFlags(&c->bulk_evt, cudaEventDisableTiming));
+        CUDA_TRY(c, cudaEventRecord(c->bulk_evt, chain_stream));
+        CUDA_TRY(c, cudaStreamWaitEvent(c->bulk_stream, c->bulk_evt, 0));
+        c->stream = c->bulk_stream;
+    }
     // pair p = Matcher::match(frames[p] /*ref, query*/, frames[p+1] /*cur, train*/) (Tracking.cpp:127)
     k_build_chain_pairs<<<1, CHAIN_MAX_FRAMES, 0, c->stream>>>(fc, np, c->d_pairs);
     c->launches++;
     // K7 for every pair of the chain at once: descriptors do not depend on the previous pair's outcome,
     // only the filter (outlier flags) and the RANSAC (rand() stream) do
     const int splits = rgbdfe::knn_splits_for(c, np);
-    if ((rc = rgbdfe::launch_knn(c, c->d_pairs, 0, np, c->kp_cap, splits)) != RGBDFE_OK)
+    rc = rgbdfe::launch_knn(c, c->d_pairs, 0, np, c->kp_cap, splits);
+    if (c->bulk_stream) {
+        c->stream = chain_stream;
+        if (rc == RGBDFE_OK) {
+            CUDA_TRY(c, cudaEventRecord(c->bulk_evt, c->bulk_stream));
+            CUDA_TRY(c, cudaStreamWaitEvent(chain_stream, c->bulk_evt, 0));
+        }
+    }
+    if (rc != RGBDFE_OK)
         return rc;
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
     rgbdfe::FusedFilter ff = { splits, ratio, discard_outliers };

@@ -147,7 +147,9 @@ struct UmeState {
 struct rgbdfe_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t bulk_stream = nullptr; // RGBDFE_PART_LATENCY: stream on the throughput partition for the chain's kNN (partition.cu)
     cudaEvent_t order_evt = nullptr; // rgbdfe_stream_wait
+    cudaEvent_t bulk_evt = nullptr;  // stream <-> bulk_stream ordering
     std::string err;
     long long launches = 0;
     int max_w = 0, max_h = 0, max_feats = 0, max_batch = 1;

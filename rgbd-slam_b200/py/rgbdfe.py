@@ -84,6 +84,19 @@ class Frame:
             self.h = None
 
 
+PART_NONE, PART_THROUGHPUT, PART_LATENCY = 0, 1, 2
+
+
+def device_partition(device, latency_sms):
+    """Split the device's SMs (CUDA green contexts) into a latency and a throughput partition.
+    Returns (latency_sms, throughput_sms) as provisioned, or None when the driver has no green contexts."""
+    a, b = C.c_int(0), C.c_int(0)
+    rc = lib().rgbdfe_device_partition(int(device), int(latency_sms), C.byref(a), C.byref(b))
+    if rc != 0:
+        return None
+    return a.value, b.value
+
+
 class Context:
     def __init__(self, device=0, max_w=640, max_h=480, max_feats=1000, max_batch=1):
         self.h = C.c_void_p()
@@ -124,6 +137,10 @@ class Context:
 
     def set_stream_priority(self, high=True):
         self._chk(lib().rgbdfe_set_stream_priority(self.h, int(high)))
+
+    def bind_partition(self, role):
+        """role: PART_NONE / PART_THROUGHPUT / PART_LATENCY (after device_partition() split the device)."""
+        self._chk(lib().rgbdfe_bind_partition(self.h, int(role)))
 
     def set_option(self, name, value):
         self._chk(lib().rgbdfe_set_option(self.h, name.encode(), int(value)))

@@ -235,15 +235,22 @@ def test_ransac_umeyama_parity(ctx, oracle, seq_vga):
         ctx.ransac_umeyama(p1, p2, m, 1, 0.02, 0.2, 10, 3)
 
 
-@pytest.mark.parametrize("chain", [False, True])
+@pytest.mark.parametrize("chain", [False, True, "partitioned"])
 def test_tracking_pipeline_device_resident(oracle, seq_vga, chain):
     """T2: extract (batched) -> match -> RansacSE3 with outlier-flag carry-over, frame to frame;
-    pair by pair (rgbdfe_track) and as one rgbdfe_track_sequence call (batched kNN + fused filter)."""
+    pair by pair (rgbdfe_track), as one rgbdfe_track_sequence call (batched kNN + fused filter), and the same
+    call from a context bound to the latency SM partition (kNN on the throughput partition)."""
     import rgbdfe
 
     cam, frames = seq_vga
     ctx = rgbdfe.Context(0, 640, 480, 1000, 4)
     try:
+        if chain == "partitioned":
+            part = rgbdfe.device_partition(0, 32)
+            if part is None:
+                pytest.skip("driver without green contexts")
+            assert part[0] >= 32 and part[1] > 0
+            ctx.bind_partition(rgbdfe.PART_LATENCY)
         ctx.rng_seed(42)
         fr = [rgbdfe.Frame(ctx) for _ in frames]
         ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)

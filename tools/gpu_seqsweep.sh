@@ -1,5 +1,7 @@
 #!/bin/bash
-for cfg in "1 32" "2 8" "4 4" "8 4" "8 2" "16 4" "16 2"; do
+# sweep: sequences in flight x speculative first chunk
+mkdir -p gpurun_out
+for cfg in "$@"; do
   set -- $cfg
   timeout 300 python bench.py --steps 4 --no-cpu --sequences $1 --first-chunk $2 2>gpurun_out/sweep.err | python -c "
 import json,sys
