@@ -212,6 +212,11 @@ class Context:
     def rng_seed(self, seed):
         self._chk(lib().rgbdfe_rng_seed(self.h, C.c_uint(seed)))
 
+    def rng_next(self):
+        v = C.c_int()
+        self._chk(lib().rgbdfe_rng_next(self.h, C.byref(v)))
+        return v.value
+
     def rng_get_state(self):
         st = np.zeros(35, np.int32)
         self._chk(lib().rgbdfe_rng_get_state(self.h, _p(st)))
