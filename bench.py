@@ -45,6 +45,20 @@ ALG_BYTES = {
     "k_fast_cells": SUM_P,
     "k_gauss7": 2 * SUM_P,
     "k_orient_describe": 60 * NFEAT,
+    "k_knn2_hamming": (NFEAT + NFEAT) * 32 + NFEAT * 16,  # both descriptor sets once + one int4 per query
+}
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
+# captures summarised in profiles/r1_ncu_full_brief.txt, and the unit that actually limits each kernel there.
+NCU_TRAFFIC_64 = {
+    "k_fast_cells": 62.86e6 + 3.64e6, "k_gauss7": 71.65e6 + 31.23e6, "k_orient_describe": 140.74e6 + 8.98e6,
+    "k_knn2_hamming": 4.20e6, "k_quadtree": 8.16e6 + 0.01e6,
+}
+NCU_LIMITER = {
+    "k_fast_cells": "ALU pipe 66 % / issue slots 75 % busy (integer compare work, 1 px per thread); DRAM 2 % of peak",
+    "k_gauss7": "L1/shared 74 %, ALU; DRAM 6 % of peak",
+    "k_orient_describe": "XU 52 % / L1 74 %; DRAM 16 % of peak",
+    "k_knn2_hamming": "XU pipe (POPC, 16 lanes/clk/SM) 76-88 % busy: 8 POPC per descriptor pair; DRAM < 1 % of peak",
+    "k_pyramid_level(x levels)": "ALU 75 % / L1 76 %",
 }
 METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
 
@@ -359,8 +373,12 @@ def main():
     dom_ms, dom_cnt = ext[dom]
     per_launch_bytes = ALG_BYTES.get(dom, 0) * B
     achieved = per_launch_bytes / (dom_ms / dom_cnt * 1e-3) / 1e9
+    traffic = NCU_TRAFFIC_64.get(dom)
     roofline = {
-        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
+        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+        "traffic": (traffic * B / 64.0) if traffic else None,
+        "algorithmic_bytes_per_launch": per_launch_bytes,
+        "limiter": NCU_LIMITER.get(dom),
         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
         "share_of_step": {k: round(v[0] / tot_ms, 4) for k, v in kernels.items()},
         "ms_per_launch": {k: (v[0] / v[1] if v[1] else None) for k, v in kernels.items()},
