@@ -61,6 +61,7 @@ NCU_LIMITER = {
     "k_pyramid_level(x levels)": "ALU 75 % / L1 76 %",
 }
 METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
+WORKLOAD = "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])"
 
 
 def make_sequence(n_frames):
@@ -160,7 +161,7 @@ def run_reference(args, rank, world):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32/f64",
-        "data": "synthetic", "config": {"workload": "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters", "path": "cpu"},
+        "data": "synthetic", "config": {"workload": WORKLOAD, "path": "cpu (oracle port; the reference does not build in this image)"},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -396,14 +397,16 @@ def main():
         vctx.depth_cov_set(1, (0.01 * 2.0 * 2.0) ** 2)
         db = vctx.kfdb_create(kd, kp)
         res_dev = torch.empty(n_kf * 84, dtype=torch.uint8, device="cuda")
-        gathered = torch.empty(world * n_kf * 84, dtype=torch.uint8, device="cuda") if world > 1 else None
         vstream = torch.cuda.ExternalStream(vctx.stream, device=local_rank)
 
+        import loopverify
+
         def vstep():
+            # this rank's keyframe block through the C ABI, then the one exchange step of the path (loopverify.py)
             vctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rank * n_kf, results_dev=res_dev.data_ptr(), want_host=False)
             if world > 1:
                 torch.cuda.current_stream().wait_stream(vstream)
-                dist.all_gather_into_tensor(gathered, res_dev)
+                loopverify.gather_results(res_dev, world * n_kf, rank, world)
                 vstream.wait_stream(torch.cuda.current_stream())
 
         for _ in range(2):
@@ -441,7 +444,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev / args.steps, "frames_per_step": S * B, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32/f64",
             "data": "synthetic",
-            "config": {"workload": "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])",
+            "config": {"workload": WORKLOAD,
                        "sequences_in_flight": S, "single_sequence_frames_per_s": single, "mean_ransac_iterations": float(np.mean(state["iters"])),
                        "batch_frames_per_step": B, "distinct_frames": F, "pipeline": "extraction of batch n+1 (context A) overlaps the match/RANSAC chain of batch n (context B)",
                        "sm_partition": ({"latency_sms": part[0], "throughput_sms": part[1], "how": "CUDA green contexts"} if part else "none (stream priorities)"), "l2": f"inputs larger than L2: rotating {F}-frame set, {F * (W * H * 5) / 1e6:.0f} MB",
