@@ -12,6 +12,9 @@ namespace rgbdfe {
 
 #define KNN_THREADS 128
 #define KNN_TILE 128
+#ifndef KNN_POPC4
+#define KNN_POPC4 1
+#endif
 
 // carry-save adder on 32 bit lanes: (a, b, c) -> sum bits and carry bits (one LOP3 each)
 __device__ __forceinline__ void csa(unsigned a, unsigned b, unsigned c, unsigned& s, unsigned& cy)
@@ -25,11 +28,16 @@ __device__ __forceinline__ int hamming256(const uint4& qa, const uint4& qb, cons
 {
     const unsigned x0 = qa.x ^ ta.x, x1 = qa.y ^ ta.y, x2 = qa.z ^ ta.z, x3 = qa.w ^ ta.w;
     const unsigned x4 = qb.x ^ tb.x, x5 = qb.y ^ tb.y, x6 = qb.z ^ tb.z, x7 = qb.w ^ tb.w;
-    unsigned s1, c1, s2, c2, s3, c3;
+    unsigned s1, c1, s2, c2, s3, c3, t1, f1;
     csa(x0, x1, x2, s1, c1);
     csa(x3, x4, x5, s2, c2);
     csa(s1, s2, x6, s3, c3);
+#if KNN_POPC4
+    csa(c1, c2, c3, t1, f1);
+    return __popc(s3) + __popc(x7) + 2 * __popc(t1) + 4 * __popc(f1);
+#else
     return __popc(s3) + __popc(x7) + 2 * (__popc(c1) + __popc(c2) + __popc(c3));
+#endif
 }
 
 // partial: [pair][split][q] -> int4 (d0, i0, d1, i1)
