@@ -75,8 +75,15 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const OrbConfig* __restri
 }
 
 // ------------------------------------------------------------------ K5 ----
+// Separable 7-tap blur with the 8-bit fixed-point kernel {18,34,48,56,48,34,18}/256 on packed bytes:
+// the horizontal pass is two IDP4A per output (4 window bytes x 4 coefficient bytes each), the vertical
+// pass four IDP2A per output (two vertically adjacent 16-bit row sums x two coefficient bytes).  The
+// level's 19 px REFLECT_101 ring in the pyramid is exactly the border GaussianBlur asks for, so the
+// tile is staged straight from the padded image with 16-byte loads and no border arithmetic.
 #define BLUR_TW 64
 #define BLUR_TH 32
+#define BLUR_SROWS (BLUR_TH + 6)
+#define BLUR_SPITCH 80 // staged bytes per row: level columns tx0-3 .. tx0+76
 __global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     uint8_t* __restrict__ blur, size_t blur_slot)
 {
@@ -87,42 +94,60 @@ __global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cf
     const LevelDesc L = cfg->lv[level];
     const int t = blockIdx.x - cfg->blur_tile_start[level];
     const int tiles_x = (L.w + BLUR_TW - 1) / BLUR_TW;
-    const int tx0 = (t % tiles_x) * BLUR_TW, ty0 = (t / tiles_x) * BLUR_TH;
+    const int ty = t / tiles_x;
+    const int tx0 = (t - ty * tiles_x) * BLUR_TW, ty0 = ty * BLUR_TH;
     const int slot = blockIdx.y;
-    const uint8_t* src = pyr + slot * pyr_slot + L.pyr_off + (size_t)EDGE_THRESHOLD * L.pstride + EDGE_THRESHOLD;
+    // level pixel (x, y) sits at padded (x + 19, y + 19); `base` is level pixel (-3, -3): 16-byte aligned
+    // because pyr_off and pstride are multiples of 64 and EDGE_THRESHOLD - 3 == 16
+    const uint8_t* base = pyr + slot * pyr_slot + L.pyr_off + (size_t)(EDGE_THRESHOLD - 3) * L.pstride + (EDGE_THRESHOLD - 3);
 
-    __shared__ uint8_t s_src[BLUR_TH + 6][BLUR_TW + 8];
-    __shared__ unsigned short s_h[BLUR_TH + 6][BLUR_TW];
+    __shared__ __align__(16) uint8_t s_src[BLUR_SROWS][BLUR_SPITCH];
+    __shared__ __align__(16) unsigned short s_h[BLUR_SROWS + 2][BLUR_TW]; // rows 38, 39 only ever meet a zero coefficient
     const int tid = threadIdx.x;
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
-        int r = i / (BLUR_TW + 6), c = i % (BLUR_TW + 6);
-        int y = reflect101(min(ty0 + r - 3, L.h + 2), L.h);
-        int x = reflect101(min(tx0 + c - 3, L.w + 2), L.w);
-        s_src[r][c] = src[(size_t)y * L.pstride + x];
+    for (int i = tid; i < BLUR_SROWS * (BLUR_SPITCH / 16); i += 256) {
+        const int r = i / (BLUR_SPITCH / 16), q = i - r * (BLUR_SPITCH / 16);
+        const int y = min(ty0 + r, L.h + 5); // level row ty0 + r - 3, clamped to the last row a valid output reads
+        *reinterpret_cast<uint4*>(&s_src[r][16 * q]) = *reinterpret_cast<const uint4*>(base + (size_t)y * L.pstride + tx0 + 16 * q);
+    }
+    if (tid < BLUR_TW)
+        *reinterpret_cast<unsigned*>(&s_h[BLUR_SROWS][2 * tid]) = 0u;
+    __syncthreads();
+    // horizontal: 4 adjacent outputs per thread from 12 staged bytes
+    constexpr unsigned KH0 = 18u | 34u << 8 | 48u << 16 | 56u << 24, KH1 = 48u | 34u << 8 | 18u << 16;
+    for (int i = tid; i < BLUR_SROWS * (BLUR_TW / 4); i += 256) {
+        const int r = i >> 4, k = i & 15;
+        const unsigned* row = reinterpret_cast<const unsigned*>(&s_src[r][0]);
+        const unsigned w0 = row[k], w1 = row[k + 1], w2 = row[k + 2];
+        const unsigned a0 = __dp4a(w0, KH0, __dp4a(w1, KH1, 0u));
+        const unsigned a1 = __dp4a(__funnelshift_r(w0, w1, 8), KH0, __dp4a(__funnelshift_r(w1, w2, 8), KH1, 0u));
+        const unsigned a2 = __dp4a(__funnelshift_r(w0, w1, 16), KH0, __dp4a(__funnelshift_r(w1, w2, 16), KH1, 0u));
+        const unsigned a3 = __dp4a(__funnelshift_r(w0, w1, 24), KH0, __dp4a(__funnelshift_r(w1, w2, 24), KH1, 0u));
+        *reinterpret_cast<uint2*>(&s_h[r][4 * k]) = make_uint2(a0 | a1 << 16, a2 | a3 << 16); // sums are <= 255 * 256
     }
     __syncthreads();
-    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
-        int r = i / BLUR_TW, c = i % BLUR_TW;
-        const uint8_t* p = &s_src[r][c];
-        int a = 18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3];
-        s_h[r][c] = (unsigned short)a;
-    }
-    __syncthreads();
-    uint8_t* dst = blur + slot * blur_slot + L.blur_off;
-    for (int i = tid; i < BLUR_TH * BLUR_TW / 4; i += 256) {
-        int r = i / (BLUR_TW / 4), c = (i % (BLUR_TW / 4)) * 4;
-        int y = ty0 + r, x = tx0 + c;
-        if (y >= L.h || x >= L.w)
-            continue;
-        unsigned packed = 0;
+    // vertical: one thread = 2 adjacent columns x the 4 output rows of one parity in an 8-row band, so that the
+    // (row, row + 1) pairs it packs for IDP2A serve all four of its outputs
+    constexpr unsigned KV0 = KH0, KV1 = KH1; // lo half (18,34) / hi half (48,56); lo half (48,34) / hi half (18,0)
+    const int cp = tid & 31, par = (tid >> 5) & 1, band = tid >> 6;
+    const int r0 = band * 8 + par;
+    unsigned lo[7], hi[7];
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int a = 18 * (s_h[r][c + k] + s_h[r + 6][c + k]) + 34 * (s_h[r + 1][c + k] + s_h[r + 5][c + k])
-                + 48 * (s_h[r + 2][c + k] + s_h[r + 4][c + k]) + 56 * s_h[r + 3][c + k];
-            int v = min((a + 32768) >> 16, 255);
-            packed |= (unsigned)v << (8 * k);
-        }
-        *reinterpret_cast<unsigned*>(dst + (size_t)y * L.bstride + x) = packed; // bstride multiple of 64, x multiple of 4
+    for (int j = 0; j < 7; j++) {
+        const unsigned ra = *reinterpret_cast<const unsigned*>(&s_h[r0 + 2 * j][2 * cp]);
+        const unsigned rb = *reinterpret_cast<const unsigned*>(&s_h[r0 + 2 * j + 1][2 * cp]);
+        lo[j] = __byte_perm(ra, rb, 0x5410); // column 2cp:     (row, row + 1)
+        hi[j] = __byte_perm(ra, rb, 0x7632); // column 2cp + 1
+    }
+    uint8_t* dst = blur + slot * blur_slot + L.blur_off;
+    const int x = tx0 + 2 * cp;
+#pragma unroll
+    for (int m = 0; m < 4; m++) {
+        const int y = ty0 + r0 + 2 * m;
+        // one rounding at the end: (sum + 2^15) >> 16; the sum cannot exceed 255.5 * 2^16, no saturation needed
+        const unsigned va = __dp2a_hi(lo[m + 3], KV1, __dp2a_lo(lo[m + 2], KV1, __dp2a_hi(lo[m + 1], KV0, __dp2a_lo(lo[m], KV0, 32768u))));
+        const unsigned vb = __dp2a_hi(hi[m + 3], KV1, __dp2a_lo(hi[m + 2], KV1, __dp2a_hi(hi[m + 1], KV0, __dp2a_lo(hi[m], KV0, 32768u))));
+        if (y < L.h && x < L.w) // x + 1 == L.w only for odd widths, where the row pitch has padding
+            *reinterpret_cast<unsigned short*>(dst + (size_t)y * L.bstride + x) = (unsigned short)((va >> 16) | ((vb >> 16) << 8));
     }
 }
 
