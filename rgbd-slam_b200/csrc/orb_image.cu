@@ -217,43 +217,55 @@ __device__ __forceinline__ int fast_strength(const uint8_t* __restrict__ p, int 
 
 // Necessary condition for a 9-arc at threshold t: every opposite pair (k, k+8) of the ring has a member inside
 // the arc, so for four of the pairs at least one member must be brighter than v + t (bright corner) or darker
-// than v - t (dark corner).  8 ring pixels instead of 16, no masks; rejects most pixels.
-__device__ __forceinline__ bool fast_candidate(const uint8_t* __restrict__ p, int pitch, int t)
+// than v - t (dark corner): min over the pairs of max(a_k, a_k+8) > v + t, or max over the pairs of
+// min(a_k, a_k+8) < v - t.  Evaluated for two horizontally adjacent pixels at once in 16-bit lanes
+// (VIMNMX.U16x2); the comparisons are additions that carry into bit 15 of each lane.  c1 = 0x7fff7fff - (t, t).
+__device__ __forceinline__ unsigned fast_candidate2(unsigned v, unsigned a0, unsigned a8, unsigned a4, unsigned a12, unsigned a2, unsigned a10,
+    unsigned a6, unsigned a14, unsigned c1)
 {
-    const int v = p[0], hi = v + t, lo = v - t;
-    const int a0 = p[3 * pitch], a8 = p[-3 * pitch], a4 = p[3], a12 = p[-3];
-    bool b = ((a0 > hi) | (a8 > hi)) & ((a4 > hi) | (a12 > hi));
-    bool d = ((a0 < lo) | (a8 < lo)) & ((a4 < lo) | (a12 < lo));
-    if (!(b | d))
-        return false;
-    const int a2 = p[2 * pitch + 2], a10 = p[-2 * pitch - 2], a6 = p[-2 * pitch + 2], a14 = p[2 * pitch - 2];
-    b = b & ((a2 > hi) | (a10 > hi)) & ((a6 > hi) | (a14 > hi));
-    d = d & ((a2 < lo) | (a10 < lo)) & ((a6 < lo) | (a14 < lo));
-    return b | d;
+    const unsigned mb = __vminu2(__vminu2(__vmaxu2(a0, a8), __vmaxu2(a4, a12)), __vminu2(__vmaxu2(a2, a10), __vmaxu2(a6, a14)));
+    const unsigned md = __vmaxu2(__vmaxu2(__vminu2(a0, a8), __vminu2(a4, a12)), __vmaxu2(__vminu2(a2, a10), __vminu2(a6, a14)));
+    const unsigned tb = mb + (c1 - v); // lane >= 0x8000  <=>  mb > v + t   (no lane ever borrows or carries out)
+    const unsigned td = (v + c1) - md; // lane >= 0x8000  <=>  md < v - t
+    return (tb | td) & 0x80008000u;
 }
+// bytes (0,1) / (2,3) of u as two zero-extended 16-bit lanes
+__device__ __forceinline__ unsigned lanes_lo(unsigned u) { return __byte_perm(u, 0u, 0x4140); }
+__device__ __forceinline__ unsigned lanes_hi(unsigned u) { return __byte_perm(u, 0u, 0x4342); }
+
+// Geometry of the FAST cell grid of every level, passed by value (constant bank): the kernel's prologue has no
+// dependent global loads.
+struct FastGrid {
+    int nlevels, iniTh, minTh;
+    int cell_off[RGBDFE_MAX_LEVELS + 1];
+    int nCols[RGBDFE_MAX_LEVELS], wCell[RGBDFE_MAX_LEVELS], hCell[RGBDFE_MAX_LEVELS];
+    int maxBorderX[RGBDFE_MAX_LEVELS], maxBorderY[RGBDFE_MAX_LEVELS], pstride[RGBDFE_MAX_LEVELS];
+    unsigned pyr_off[RGBDFE_MAX_LEVELS];
+};
 
 #define FAST_THREADS 256
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FastGrid G, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     int* __restrict__ cell_count, unsigned* __restrict__ cell_list, int cell_slot)
 {
     int level = 0;
-    while (level + 1 < cfg->nlevels && (int)blockIdx.x >= cfg->lv[level + 1].cell_off)
+    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.cell_off[level + 1])
         level++;
-    const LevelDesc L = cfg->lv[level];
-    const int cell = blockIdx.x - L.cell_off;
-    const int ci = cell / L.nCols, cj = cell % L.nCols;
+    const int cell = blockIdx.x - G.cell_off[level];
+    const int nCols = G.nCols[level], wCell = G.wCell[level], hCell = G.hCell[level], pstride = G.pstride[level];
+    const int ci = cell / nCols, cj = cell - ci * nCols;
     const int slot = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31;
     int* out_count = cell_count + (size_t)slot * cell_slot + blockIdx.x;
     unsigned* out_list = cell_list + ((size_t)slot * cell_slot + blockIdx.x) * CELL_CAP;
 
-    const int iniY = 16 + ci * L.hCell, iniX = 16 + cj * L.wCell;
-    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
-    bool skip = (iniY >= L.maxBorderY - 3) || (iniX >= L.maxBorderX - 6);
-    if (maxY > L.maxBorderY)
-        maxY = L.maxBorderY;
-    if (maxX > L.maxBorderX)
-        maxX = L.maxBorderX;
+    const int iniY = 16 + ci * hCell, iniX = 16 + cj * wCell;
+    int maxY = iniY + hCell + 6, maxX = iniX + wCell + 6;
+    const int maxBorderX = G.maxBorderX[level], maxBorderY = G.maxBorderY[level];
+    bool skip = (iniY >= maxBorderY - 3) || (iniX >= maxBorderX - 6);
+    if (maxY > maxBorderY)
+        maxY = maxBorderY;
+    if (maxX > maxBorderX)
+        maxX = maxBorderX;
     const int cw = maxX - iniX, ch = maxY - iniY;
     if (skip || cw < 7 || ch < 7) {
         if (tid == 0)
@@ -266,13 +278,14 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __
     __shared__ unsigned short s_cand[CELL_MAX_DIM * CELL_MAX_DIM]; // pixels that pass the pair test: r << 8 | c
     __shared__ unsigned short s_keep[CELL_MAX_DIM * CELL_MAX_DIM]; // NMS survivors of this attempt: r << 8 | c, unordered
     __shared__ int s_ncand, s_n;
-    const uint8_t* src = pyr + slot * pyr_slot + L.pyr_off + (size_t)(EDGE_THRESHOLD + iniY) * L.pstride + EDGE_THRESHOLD + iniX;
+    const uint8_t* src = pyr + slot * pyr_slot + G.pyr_off[level] + (size_t)(EDGE_THRESHOLD + iniY) * pstride + EDGE_THRESHOLD + iniX;
     // rows are staged as 32-bit words from the 4-byte aligned address at or below the cell's first column
     const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
     const int wpr = (cw + mis + 3) >> 2; // words per row
+    const unsigned inv_wpr = 0xffffffffu / (unsigned)wpr + 1u; // i / wpr == umulhi(i, inv_wpr) for the few thousand i here
     for (int i = tid; i < wpr * ch; i += FAST_THREADS) {
-        const int r = i / wpr, wq = i - r * wpr;
-        const unsigned wv = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * L.pstride + 4 * wq);
+        const int r = (int)__umulhi((unsigned)i, inv_wpr), wq = i - r * wpr;
+        const unsigned wv = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * pstride + 4 * wq);
         *reinterpret_cast<unsigned*>(&s_img[r][4 * wq]) = wv;
         *reinterpret_cast<unsigned*>(&s_S[r][4 * wq]) = 0u;
     }
@@ -283,25 +296,59 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __
     __syncthreads();
     // image column c lives at s_img[r][c + mis]; s_S uses the same shift
     const int dw = cw - 6, dh = ch - 6;
-    const int th_lo = min(cfg->iniTh, cfg->minTh);
+    const int th_lo = min(G.iniTh, G.minTh);
     const unsigned lt = (1u << lane) - 1;
-    for (int i0 = 0; i0 < dw * dh; i0 += FAST_THREADS) {
-        const int i = i0 + tid;
-        bool cand = false;
-        int r = 0, c = 0;
-        if (i < dw * dh) {
-            r = 3 + i / dw;
-            c = 3 + i - (r - 3) * dw;
-            cand = fast_candidate(&s_img[r][c + mis], PITCH, th_lo);
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, cand);
-        if (bal) {
-            int base = 0;
-            if (lane == 0)
-                base = atomicAdd(&s_ncand, __popc(bal));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (cand)
-                s_cand[base + __popc(bal & lt)] = (unsigned short)(r << 8 | c);
+    {
+        // pair test on 4 adjacent pixels per thread: one word-aligned group of shared-memory columns [4g, 4g + 4)
+        const int s_first = 3 + mis; // shared-memory column of the first tested pixel of a row
+        const int g_lo = s_first >> 2, gpr = ((cw - 4 + mis) >> 2) - g_lo + 1;
+        const unsigned inv_gpr = 0xffffffffu / (unsigned)gpr + 1u;
+        const int ngroups = gpr * dh;
+        const unsigned c1 = 0x7fff7fffu - ((unsigned)th_lo | (unsigned)th_lo << 16);
+        for (int i0 = (tid & ~31); i0 < ngroups; i0 += FAST_THREADS) { // warp-uniform trip count
+            const int i = i0 + lane;
+            unsigned rA = 0, rB = 0;
+            int r = 0, s0 = 0;
+            if (i < ngroups) {
+                const int rr = (int)__umulhi((unsigned)i, inv_gpr);
+                const int g = g_lo + (i - rr * gpr);
+                r = 3 + rr;
+                s0 = 4 * g;
+                const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g; // PITCH is a multiple of 4
+                constexpr int RW = PITCH / 4;
+                const unsigned cm = w[-1], cc = w[0], cp = w[1];
+                const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
+                const unsigned um = w[-2 * RW - 1], uc = w[-2 * RW], upn = w[-2 * RW + 1];
+                const unsigned dm = w[2 * RW - 1], dc = w[2 * RW], dpn = w[2 * RW + 1];
+                const unsigned u4 = __funnelshift_r(cc, cp, 24), u12 = __funnelshift_r(cm, cc, 8); // columns +3 / -3 of the centre row
+                const unsigned u2 = __funnelshift_r(dc, dpn, 16), u14 = __funnelshift_r(dm, dc, 16); // row +2: columns +2 / -2
+                const unsigned u6 = __funnelshift_r(uc, upn, 16), u10 = __funnelshift_r(um, uc, 16); // row -2: columns +2 / -2
+                rA = fast_candidate2(lanes_lo(cc), lanes_lo(dn3), lanes_lo(up3), lanes_lo(u4), lanes_lo(u12), lanes_lo(u2), lanes_lo(u10),
+                    lanes_lo(u6), lanes_lo(u14), c1);
+                rB = fast_candidate2(lanes_hi(cc), lanes_hi(dn3), lanes_hi(up3), lanes_hi(u4), lanes_hi(u12), lanes_hi(u2), lanes_hi(u10),
+                    lanes_hi(u6), lanes_hi(u14), c1);
+            }
+            const int rel = s0 - s_first; // tested pixels of the row are rel + j in [0, dw)
+            const bool k0 = (rA & 0x8000u) && (unsigned)rel < (unsigned)dw, k1 = (rA >> 31) && (unsigned)(rel + 1) < (unsigned)dw;
+            const bool k2 = (rB & 0x8000u) && (unsigned)(rel + 2) < (unsigned)dw, k3 = (rB >> 31) && (unsigned)(rel + 3) < (unsigned)dw;
+            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+            const unsigned b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
+            const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
+            if (b0 | b1 | b2 | b3) {
+                int base = 0;
+                if (lane == 0)
+                    base = atomicAdd(&s_ncand, n0 + n1 + n2 + n3);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const int key = r << 8 | (s0 - mis); // window column of pixel 0 of the group
+                if (k0)
+                    s_cand[base + __popc(b0 & lt)] = (unsigned short)key;
+                if (k1)
+                    s_cand[base + n0 + __popc(b1 & lt)] = (unsigned short)(key + 1);
+                if (k2)
+                    s_cand[base + n0 + n1 + __popc(b2 & lt)] = (unsigned short)(key + 2);
+                if (k3)
+                    s_cand[base + n0 + n1 + n2 + __popc(b3 & lt)] = (unsigned short)(key + 3);
+            }
         }
     }
     __syncthreads();
@@ -312,7 +359,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __
         s_S[r][c + mis] = (uint8_t)min(S, 255);
     }
     __syncthreads();
-    int th = cfg->iniTh;
+    int th = G.iniTh;
     for (int attempt = 0; attempt < 2; attempt++) {
         // 3x3 non-max suppression inside the cell's window (cv::FAST, nonmaxSuppression = true), candidates only
         for (int i0 = 0; i0 < ncand; i0 += FAST_THREADS) {
@@ -349,9 +396,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __
             }
         }
         __syncthreads();
-        if (s_n > 0 || th == cfg->minTh)
+        if (s_n > 0 || th == G.minTh)
             break;
-        th = cfg->minTh; // cv::FAST returned nothing at iniThFAST: retry at minThFAST (:658-661)
+        th = G.minTh; // cv::FAST returned nothing at iniThFAST: retry at minThFAST (:658-661)
         __syncthreads();
     }
     // row-major output order (cv::FAST emits keypoints row by row): rank each survivor by its (r, c) key
@@ -363,7 +410,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const OrbConfig* __
             rank += s_keep[j] < key;
         if (rank < CELL_CAP) {
             const int r = key >> 8, c = key & 255;
-            out_list[rank] = pack_cand(c + cj * L.wCell, r + ci * L.hCell, s_S[r][c + mis] - 1);
+            out_list[rank] = pack_cand(c + cj * wCell, r + ci * hCell, s_S[r][c + mis] - 1);
         }
     }
     if (tid == 0)
@@ -401,8 +448,17 @@ int launch_blur(rgbdfe_ctx* c, int count)
 int launch_fast(rgbdfe_ctx* c, int count)
 {
     ProfScope prof(c, KID_FAST);
-    k_fast_cells<<<dim3(c->cfg.total_cells, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list,
-        c->cell_slot);
+    FastGrid G;
+    memset(&G, 0, sizeof(G));
+    const OrbConfig& cfg = c->cfg;
+    G.nlevels = cfg.nlevels, G.iniTh = cfg.iniTh, G.minTh = cfg.minTh;
+    for (int l = 0; l < cfg.nlevels; l++) {
+        const LevelDesc& L = cfg.lv[l];
+        G.cell_off[l] = L.cell_off, G.nCols[l] = L.nCols, G.wCell[l] = L.wCell, G.hCell[l] = L.hCell;
+        G.maxBorderX[l] = L.maxBorderX, G.maxBorderY[l] = L.maxBorderY, G.pstride[l] = L.pstride, G.pyr_off[l] = L.pyr_off;
+    }
+    G.cell_off[cfg.nlevels] = cfg.total_cells;
+    k_fast_cells<<<dim3(cfg.total_cells, count), FAST_THREADS, 0, c->stream>>>(G, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list, c->cell_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;
