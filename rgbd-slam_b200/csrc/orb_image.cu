@@ -152,67 +152,50 @@ __global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cf
 }
 
 // ------------------------------------------------------------------ K2 ----
-__device__ __forceinline__ bool has9(unsigned m)
-{
-    m |= m << 16;
-    unsigned r = m & (m >> 1);
-    r &= r >> 2;
-    r &= r >> 4;
-    r &= m >> 8;
-    return (r & 0xffffu) != 0;
-}
-
 // FAST-9/16 corner strength S: the pixel is a corner at threshold t iff S > t,
 // and OpenCV's response (cornerScore<16>) is S - 1.  Returns 0 when S <= th_lo.
+// S = max over the 16 arcs of 9 ring pixels of the arc minimum of e[k], with e[k] = a_k - v for a bright corner
+// and v - a_k for a dark one.  Both signs ride in the two signed 16-bit lanes of one register (a pixel cannot be
+// both: two 9-arcs of a 16-ring overlap), so no sign decision and no ring masks are needed: 16 three-input
+// minima give the 3-arcs, 16 more the 9-arcs, 8 three-input maxima the best arc (VIMNMX3.S16x2).
 __device__ __forceinline__ int fast_strength(const uint8_t* __restrict__ p, int pitch, int th_lo)
 {
-    const int v = p[0];
-    int d[16];
-    d[0] = v - p[3 * pitch];
-    d[1] = v - p[3 * pitch + 1];
-    d[2] = v - p[2 * pitch + 2];
-    d[3] = v - p[pitch + 3];
-    d[4] = v - p[3];
-    d[5] = v - p[-pitch + 3];
-    d[6] = v - p[-2 * pitch + 2];
-    d[7] = v - p[-3 * pitch + 1];
-    d[8] = v - p[-3 * pitch];
-    d[9] = v - p[-3 * pitch - 1];
-    d[10] = v - p[-2 * pitch - 2];
-    d[11] = v - p[-pitch - 3];
-    d[12] = v - p[-3];
-    d[13] = v - p[pitch - 3];
-    d[14] = v - p[2 * pitch - 2];
-    d[15] = v - p[3 * pitch - 1];
-    unsigned md = 0, mb = 0;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        md |= (unsigned)(d[k] > th_lo) << k;
-        mb |= (unsigned)(-d[k] > th_lo) << k;
-    }
-    const bool dark = has9(md), bright = has9(mb);
-    if (!dark && !bright)
-        return 0;
-    // a pixel cannot be both (two 9-arcs of a 16-ring overlap): one branch-free pass over e = +-d.
-    // max over the 16 arcs of the arc minimum, arc minima by doubling (2, 4, 8, then the 9th element)
-    int e[16];
+    const unsigned v = p[0];
+    const unsigned c = ((0u - v) & 0xffffu) | v << 16; // lanes (-v, +v)
+    unsigned e[16];
+    // a * 0xffff0001 = lanes (a, -a); the lane-wise add of c gives (a - v, v - a)
+#define RING(k, off) e[k] = __vadd2((unsigned)p[off] * 0xffff0001u, c)
+    RING(0, 3 * pitch);
+    RING(1, 3 * pitch + 1);
+    RING(2, 2 * pitch + 2);
+    RING(3, pitch + 3);
+    RING(4, 3);
+    RING(5, -pitch + 3);
+    RING(6, -2 * pitch + 2);
+    RING(7, -3 * pitch + 1);
+    RING(8, -3 * pitch);
+    RING(9, -3 * pitch - 1);
+    RING(10, -2 * pitch - 2);
+    RING(11, -pitch - 3);
+    RING(12, -3);
+    RING(13, pitch - 3);
+    RING(14, 2 * pitch - 2);
+    RING(15, 3 * pitch - 1);
+#undef RING
+    unsigned m3[16], m9[16];
 #pragma unroll
     for (int k = 0; k < 16; k++)
-        e[k] = dark ? d[k] : -d[k];
-    int m2[16], m4[16];
+        m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
 #pragma unroll
     for (int k = 0; k < 16; k++)
-        m2[k] = min(e[k], e[(k + 1) & 15]);
+        m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+    unsigned best = __vimax3_s16x2(m9[0], m9[1], m9[2]);
 #pragma unroll
-    for (int k = 0; k < 16; k++)
-        m4[k] = min(m2[k], m2[(k + 2) & 15]);
-    int best = 0;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int m8 = min(m4[k], m4[(k + 4) & 15]);
-        best = max(best, min(m8, e[(k + 8) & 15]));
-    }
-    return best;
+    for (int k = 3; k < 15; k += 2)
+        best = __vimax3_s16x2(best, m9[k], m9[k + 1]);
+    best = __vmaxs2(best, m9[15]);
+    const int S = max((int)(short)(best & 0xffffu), (int)best >> 16);
+    return S > th_lo ? S : 0;
 }
 
 // Necessary condition for a 9-arc at threshold t: every opposite pair (k, k+8) of the ring has a member inside
@@ -241,6 +224,8 @@ struct FastGrid {
     int nCols[RGBDFE_MAX_LEVELS], wCell[RGBDFE_MAX_LEVELS], hCell[RGBDFE_MAX_LEVELS];
     int maxBorderX[RGBDFE_MAX_LEVELS], maxBorderY[RGBDFE_MAX_LEVELS], pstride[RGBDFE_MAX_LEVELS];
     unsigned pyr_off[RGBDFE_MAX_LEVELS];
+    unsigned inv_nCols[RGBDFE_MAX_LEVELS]; // 0xffffffff / nCols + 1: cell / nCols == umulhi(cell, inv_nCols)
+    unsigned inv_small[32];                // the same reciprocal for divisors 1..31 (words / groups per cell row)
 };
 
 #define FAST_THREADS 256
@@ -252,7 +237,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         level++;
     const int cell = blockIdx.x - G.cell_off[level];
     const int nCols = G.nCols[level], wCell = G.wCell[level], hCell = G.hCell[level], pstride = G.pstride[level];
-    const int ci = cell / nCols, cj = cell - ci * nCols;
+    const int ci = (int)__umulhi((unsigned)cell, G.inv_nCols[level]), cj = cell - ci * nCols;
     const int slot = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31;
     int* out_count = cell_count + (size_t)slot * cell_slot + blockIdx.x;
@@ -282,7 +267,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     // rows are staged as 32-bit words from the 4-byte aligned address at or below the cell's first column
     const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
     const int wpr = (cw + mis + 3) >> 2; // words per row
-    const unsigned inv_wpr = 0xffffffffu / (unsigned)wpr + 1u; // i / wpr == umulhi(i, inv_wpr) for the few thousand i here
+    const unsigned inv_wpr = G.inv_small[wpr]; // wpr <= (CELL_MAX_DIM + 6) / 4
     for (int i = tid; i < wpr * ch; i += FAST_THREADS) {
         const int r = (int)__umulhi((unsigned)i, inv_wpr), wq = i - r * wpr;
         const unsigned wv = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * pstride + 4 * wq);
@@ -302,7 +287,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         // pair test on 4 adjacent pixels per thread: one word-aligned group of shared-memory columns [4g, 4g + 4)
         const int s_first = 3 + mis; // shared-memory column of the first tested pixel of a row
         const int g_lo = s_first >> 2, gpr = ((cw - 4 + mis) >> 2) - g_lo + 1;
-        const unsigned inv_gpr = 0xffffffffu / (unsigned)gpr + 1u;
+        const unsigned inv_gpr = G.inv_small[gpr];
         const int ngroups = gpr * dh;
         const unsigned c1 = 0x7fff7fffu - ((unsigned)th_lo | (unsigned)th_lo << 16);
         for (int i0 = (tid & ~31); i0 < ngroups; i0 += FAST_THREADS) { // warp-uniform trip count
@@ -458,6 +443,10 @@ int launch_fast(rgbdfe_ctx* c, int count)
         G.maxBorderX[l] = L.maxBorderX, G.maxBorderY[l] = L.maxBorderY, G.pstride[l] = L.pstride, G.pyr_off[l] = L.pyr_off;
     }
     G.cell_off[cfg.nlevels] = cfg.total_cells;
+    for (int l = 0; l < cfg.nlevels; l++)
+        G.inv_nCols[l] = 0xffffffffu / (unsigned)cfg.lv[l].nCols + 1u;
+    for (int d = 1; d < 32; d++)
+        G.inv_small[d] = 0xffffffffu / (unsigned)d + 1u;
     k_fast_cells<<<dim3(cfg.total_cells, count), FAST_THREADS, 0, c->stream>>>(G, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list, c->cell_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
