@@ -37,6 +37,7 @@ for p in (os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools"), os.path.join
 import numpy as np
 
 W, H, NFEAT, ITERS, MIN_INL, RATIO = 640, 480, 2000, 500, 10, 0.9
+DEPTH_FACTOR = 5000.0  # DepthMapFactor of the TUM-format ICL-NUIM sequences
 LEVEL_PX = [640 * 480, 533 * 400, 444 * 333, 370 * 278, 309 * 231, 257 * 193, 214 * 161, 179 * 134]
 SUM_P = sum(LEVEL_PX)
 # algorithmic bytes per frame of each extraction kernel (SURVEY 8d / DESIGN.md)
@@ -70,7 +71,13 @@ def make_sequence(n_frames):
     cam = synth.CAMS["icl"]
     room = synth.Room(2345)
     poses = synth.xyz_trajectory(1000, 2347)[:n_frames]
-    frames = [room.render(cam, R, t, 0.0, 0.0) for R, t in poses]
+    frames = []
+    for R, t in poses:
+        gray, depth = room.render(cam, R, t, 0.0, 0.0)
+        # the dataset stores depth as 16-bit PNG (metres * DepthMapFactor); Frame converts it back with
+        # convertTo(CV_32F, 1.0f / factor) (Core/Frame.cpp:48) -- both arms see exactly these values
+        d16 = np.rint(np.clip(np.nan_to_num(depth, nan=0.0) * DEPTH_FACTOR, 0, 65535)).astype(np.uint16)
+        frames.append((gray, d16.astype(np.float32) * (np.float32(1.0) / np.float32(DEPTH_FACTOR)), d16))
     return cam, frames
 
 
@@ -204,7 +211,8 @@ def main():
     B, F = args.batch, args.frames
     cam, frames = make_sequence(F)
     gray_h = torch.from_numpy(np.stack([f[0] for f in frames])).pin_memory()
-    depth_h = torch.from_numpy(np.stack([f[1] for f in frames])).pin_memory()
+    depth_h = torch.from_numpy(np.stack([f[2] for f in frames])).pin_memory()  # raw 16-bit depth, as read from the PNG
+    inv_factor = float(np.float32(1.0) / np.float32(DEPTH_FACTOR))
     gray_d, depth_d = gray_h.cuda(), depth_h.cuda()
     gp_h, dp_h = gray_h.numpy(), depth_h.numpy()
     L = rgbdfe.lib()
@@ -241,10 +249,10 @@ def main():
                 fr = (C.c_void_p * B)(*[f.h for f in batch])
                 gp = (C.c_void_p * B)(*[gray_d[i].data_ptr() for i in idx])
                 dp = (C.c_void_p * B)(*[depth_d[i].data_ptr() for i in idx])
-                cx._chk(L.rgbdfe_frames_extract(cx.h, fr, B, gp, W, H, W, dp, W, C.c_float(cam["fx"]), C.c_float(cam["fy"]),
-                                                C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+                cx._chk(L.rgbdfe_frames_extract_raw(cx.h, fr, B, gp, W, H, W, dp, W, C.c_float(inv_factor), C.c_float(cam["fx"]),
+                                                    C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"])))
             else:
-                cx.frames_extract(batch, [gp_h[i] for i in idx], [dp_h[i] for i in idx], cam)
+                cx.frames_extract_raw(batch, [gp_h[i] for i in idx], [dp_h[i] for i in idx], cam, inv_factor)
 
         def enqueue(self, dev):
             i = self.i
@@ -447,10 +455,11 @@ def main():
             "config": {"workload": WORKLOAD,
                        "sequences_in_flight": S, "single_sequence_frames_per_s": single, "mean_ransac_iterations": float(np.mean(state["iters"])),
                        "batch_frames_per_step": B, "distinct_frames": F, "pipeline": "extraction of batch n+1 (context A) overlaps the match/RANSAC chain of batch n (context B)",
-                       "sm_partition": ({"latency_sms": part[0], "throughput_sms": part[1], "how": "CUDA green contexts"} if part else "none (stream priorities)"), "l2": f"inputs larger than L2: rotating {F}-frame set, {F * (W * H * 5) / 1e6:.0f} MB",
+                       "sm_partition": ({"latency_sms": part[0], "throughput_sms": part[1], "how": "CUDA green contexts"} if part else "none (stream priorities)"), "input": "gray u8 + raw 16-bit depth per frame (Frame's convertTo(CV_32F, 1/5000) runs on the device)",
+                       "l2": f"inputs larger than L2: 24 sequences x rotating {F}-frame set ({F * (W * H * 3) / 1e6:.0f} MB) + 58 MB of pyramid per batch",
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
-            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": S * B * W * H * 5, "d2h_bytes_per_step": S * B * 84},
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": S * B * W * H * 3, "d2h_bytes_per_step": S * B * 84},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify,
         }))
     for q in seqs:

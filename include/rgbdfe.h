@@ -185,11 +185,18 @@ void rgbdfe_frame_destroy(rgbdfe_ctx* ctx, rgbdfe_frame* frame);
 /* Frame ctor hot part (Core/Frame.cpp:51,91-117): extract ORB from gray, then
  * back-project every keypoint with the metric depth map (float32, 0 = invalid)
  * and pinhole intrinsics; outlier flags reset to false.  Asynchronous on the
- * context stream; host buffers must stay valid until rgbdfe_sync().  gray/depth
- * may be host (ideally pinned) or device pointers (cudaMemcpyDefault).
- * count frames are processed as one batch (count <= max_batch). */
+ * context stream; the buffers must stay valid and unchanged until rgbdfe_sync().
+ * gray/depth may be host pointers (ideally pinned; uploaded into the context's slots)
+ * or device pointers (read in place, no staging copy); all images of one call must be
+ * of the same kind.  count frames are processed as one batch (count <= max_batch). */
 int rgbdfe_frames_extract(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
     const float* const* depth, int depth_stride_elems, float fx, float fy, float cx, float cy);
+/* The same with the RAW depth image of the dataset (16-bit, as cv::imread(..., IMREAD_UNCHANGED) returns it):
+ * Frame's `imDepth.convertTo(mImDepth, CV_32F, mDepthMapFactor)` (Core/Frame.cpp:48, mDepthMapFactor = 1.0f / DepthMapFactor,
+ * Core/RGBDcamera.cpp:21) is applied on the device where the keypoints are back-projected — z = float(d16) * depth_map_factor,
+ * OpenCV's float convert-scale — so a frame costs 2 instead of 4 bytes of depth per pixel on the way to the GPU. */
+int rgbdfe_frames_extract_raw(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
+    const uint16_t* const* depth16, int depth_stride_elems, float depth_map_factor, float fx, float fy, float cx, float cy);
 /* Copy a frame's data back (any pointer may be NULL). */
 int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
     uint8_t* outlier, int cap, int* n);

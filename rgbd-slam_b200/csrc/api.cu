@@ -133,6 +133,22 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
             yofs.resize(ty + L.h);
             yb.resize(2 * (ty + L.h));
             resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xofs.data() + tx, xa.data() + 2 * tx, yofs.data() + ty, yb.data() + 2 * ty);
+            // staged source window of the worst k_pyramid_resize tile of this level
+            const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD, srch = g.lv[l - 1].h;
+            int max_cols = 0, max_rows = 0;
+            for (int p0 = 0; p0 < pw; p0 += PYR_TW) {
+                int lo, hi;
+                ring_tile_range(p0, std::min(p0 + PYR_TW - 1, pw - 1), L.w, lo, hi);
+                max_cols = std::max(max_cols, xofs[tx + hi] + 1 - xofs[tx + lo] + 1);
+            }
+            for (int p0 = 0; p0 < ph; p0 += PYR_TH) {
+                int lo, hi;
+                ring_tile_range(p0, std::min(p0 + PYR_TH - 1, ph - 1), L.h, lo, hi);
+                const int s0 = std::min(std::max(yofs[ty + lo], 0), srch - 1), s1 = std::min(std::max(yofs[ty + hi] + 1, 0), srch - 1);
+                max_rows = std::max(max_rows, s1 - s0 + 1);
+            }
+            L.rs_cols = align_up(max_cols + 3, 16); // + up to 3 bytes of load alignment
+            L.rs_rows = max_rows;
             tx += L.w;
             ty += L.h;
         }
@@ -440,7 +456,7 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
     c->depth_slot = (size_t)c->max_w * c->max_h;
     c->pyr_slot = align_up((int)pyr, 256), c->blur_slot = align_up((int)blur, 256);
     c->cell_slot = cells, c->cand_slot = cand, c->sel_slot = sel, c->tab_x_cap = tx, c->tab_y_cap = ty;
-    CUDA_TRY(c, dmalloc(&c->d_img, B * c->img_slot));
+    CUDA_TRY(c, dmalloc(&c->d_img, B * c->img_slot + 16)); // + 16: k_pyramid_base reads whole aligned words
     CUDA_TRY(c, dmalloc(&c->d_depth, B * c->depth_slot));
     CUDA_TRY(c, dmalloc(&c->d_pyr, B * c->pyr_slot + 256));
     CUDA_TRY(c, dmalloc(&c->d_blur, B * c->blur_slot + 256));
@@ -485,9 +501,20 @@ int rgbdfe_orb_tables(rgbdfe_ctx* c, float* scale, float* inv_scale, float* sigm
 
 namespace {
 
+bool is_device_ptr(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice;
+}
+
 // Upload `count` gray (+ optional depth) images and run K1..K6 on them as one batch.
 int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
-    const float* const* depth, int depth_stride, float fx, float fy, float cx, float cy)
+    const float* const* depth, int depth_stride, float fx, float fy, float cx, float cy, const uint16_t* const* depth16 = nullptr,
+    float depth16_factor = 0.0f)
 {
     if (!c->configured)
         return RGBDFE_E_STATE;
@@ -500,17 +527,38 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
     if (rc != RGBDFE_OK)
         return rc;
     FrameBatch fb;
+    ImgPtrs gp, dp;
     memset(&fb, 0, sizeof(fb));
-    for (int i = 0; i < count; i++) {
-        if (!gray[i] || !frames[i])
+    memset(&gp, 0, sizeof(gp));
+    memset(&dp, 0, sizeof(dp));
+    const void* const* dany = depth ? (const void* const*)depth : (const void* const*)depth16;
+    const size_t delem = depth ? 4 : 2;
+    for (int i = 0; i < count; i++)
+        if (!gray[i] || !frames[i] || (dany && !dany[i]))
             return RGBDFE_E_ARG;
+    // Images that already live in device memory are read in place (all pointers of one call must be of one kind;
+    // the first and last are checked); host images are uploaded into the context's slots.
+    const bool in_place = is_device_ptr(gray[0]) && is_device_ptr(gray[count - 1])
+        && (!dany || (is_device_ptr(dany[0]) && is_device_ptr(dany[count - 1])));
+    int gstride = stride, dstride = depth_stride;
+    for (int i = 0; i < count; i++) {
         fb.f[i] = *frames[i];
+        if (in_place) {
+            gp.p[i] = gray[i];
+            dp.p[i] = dany ? dany[i] : nullptr;
+            continue;
+        }
+        gp.p[i] = c->d_img + i * c->img_slot;
         CUDA_TRY(c, cudaMemcpy2DAsync(c->d_img + i * c->img_slot, w, gray[i], stride, w, h, cudaMemcpyDefault, c->stream));
-        if (depth)
-            CUDA_TRY(c, cudaMemcpy2DAsync(c->d_depth + i * c->depth_slot, (size_t)w * 4, depth[i], (size_t)depth_stride * 4, (size_t)w * 4, h,
+        if (dany) {
+            dp.p[i] = c->d_depth + i * c->depth_slot;
+            CUDA_TRY(c, cudaMemcpy2DAsync(c->d_depth + i * c->depth_slot, (size_t)w * delem, dany[i], (size_t)depth_stride * delem, (size_t)w * delem, h,
                             cudaMemcpyDefault, c->stream));
+        }
     }
-    if ((rc = launch_pyramid(c, count)) != RGBDFE_OK)
+    if (!in_place)
+        gstride = w, dstride = w;
+    if ((rc = launch_pyramid(c, count, gp, gstride)) != RGBDFE_OK)
         return rc;
     if ((rc = launch_fast(c, count)) != RGBDFE_OK)
         return rc;
@@ -518,7 +566,7 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
         return rc;
     if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
         return rc;
-    if ((rc = launch_describe(c, count, fb, depth != nullptr, w, fx, fy, cx, cy)) != RGBDFE_OK)
+    if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, depth16 ? depth16_factor : 0.0f, fx, fy, cx, cy)) != RGBDFE_OK)
         return rc;
     return RGBDFE_OK;
 }
@@ -636,6 +684,14 @@ int rgbdfe_frames_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count,
     if (!c)
         return RGBDFE_E_ARG;
     return run_extract(c, frames, count, gray, w, h, stride, depth, depth_stride_elems, fx, fy, cx, cy);
+}
+
+int rgbdfe_frames_extract_raw(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
+    const uint16_t* const* depth16, int depth_stride_elems, float depth_map_factor, float fx, float fy, float cx, float cy)
+{
+    if (!c || !depth16 || !(depth_map_factor > 0.0f))
+        return RGBDFE_E_ARG;
+    return run_extract(c, frames, count, gray, w, h, stride, nullptr, depth_stride_elems, fx, fy, cx, cy, depth16, depth_map_factor);
 }
 
 int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz, uint8_t* outlier, int cap,

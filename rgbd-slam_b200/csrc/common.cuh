@@ -29,6 +29,7 @@ struct LevelDesc {
     int quota;           // mnFeaturesPerLevel
     int sel_off, sel_cap;
     int tab_x_off, tab_y_off; // resize coefficient tables (level > 0)
+    int rs_cols, rs_rows;     // k_pyramid_resize: staged source bytes per row (multiple of 16) / rows, worst tile of the level
     float scale;         // mvScaleFactor[level]
     int patch_size;      // int(31 * scale)
 };
@@ -84,6 +85,12 @@ struct FrameBatch {
     rgbdfe_frame f[64];
 };
 
+// Input images of one batched call (gray for K1, depth for K6), by value.  They point at the caller's buffers
+// when those are device memory (no staging copy), else at the context's upload slots.
+struct ImgPtrs {
+    const void* p[64];
+};
+
 // Frames of one rgbdfe_track_sequence call, passed by value.
 #define CHAIN_MAX_FRAMES 65
 struct FrameChain {
@@ -97,6 +104,28 @@ struct rgbdfe_kfdb {
 };
 
 // packed FAST candidate: x (12 bits) | y (12 bits) << 12 | score << 24
+// cv::BORDER_REFLECT_101 index; |p| < 2*len always holds here (border 19 / kernel radius 3 vs len >= 20)
+__host__ __device__ inline int reflect101(int p, int len)
+{
+    if (p < 0)
+        p = -p;
+    if (p >= len)
+        p = 2 * (len - 1) - p;
+    if (p < 0)
+        p = -p;
+    return p;
+}
+// k_pyramid_resize tiles the PADDED level (ring included): positions [p0, p1] of a padded row or column of a
+// level with n pixels touch level coordinates [lo, hi] (the reflection is piecewise monotone)
+#define PYR_TW 128
+#define PYR_TH 16
+__host__ __device__ inline void ring_tile_range(int p0, int p1, int n, int& lo, int& hi)
+{
+    const int a = reflect101(p0 - EDGE_THRESHOLD, n), b = reflect101(p1 - EDGE_THRESHOLD, n);
+    const int last = EDGE_THRESHOLD + n - 1;
+    lo = (p0 <= EDGE_THRESHOLD && EDGE_THRESHOLD <= p1) ? 0 : (a < b ? a : b);
+    hi = (p0 <= last && last <= p1) ? n - 1 : (a > b ? a : b);
+}
 __host__ __device__ inline unsigned pack_cand(int x, int y, int s) { return (unsigned)x | ((unsigned)y << 12) | ((unsigned)s << 24); }
 __host__ __device__ inline int cand_x(unsigned c) { return c & 0xfff; }
 __host__ __device__ inline int cand_y(unsigned c) { return (c >> 12) & 0xfff; }
@@ -284,12 +313,13 @@ struct ProfScope {
 
 namespace rgbdfe {
 // orb_image.cu
-int launch_pyramid(rgbdfe_ctx* c, int count);
+int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride);
 int launch_blur(rgbdfe_ctx* c, int count);
 int launch_fast(rgbdfe_ctx* c, int count);
 // orb_keypoints.cu
 int launch_quadtree(rgbdfe_ctx* c, int count);
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, int depth_stride, float fx, float fy, float cx, float cy);
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, float depth16_factor,
+    float fx, float fy, float cx, float cy);
 // match.cu
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);

@@ -11,67 +11,105 @@
 
 namespace rgbdfe {
 
-__device__ __forceinline__ int reflect101(int p, int len)
-{
-    // |p| < 2*len always holds here (border 19 / kernel radius 3 vs len >= 20)
-    if (p < 0)
-        p = -p;
-    if (p >= len)
-        p = 2 * (len - 1) - p;
-    if (p < 0)
-        p = -p;
-    return p;
-}
-
 // ------------------------------------------------------------------ K1 ----
-// One thread per 4 horizontally adjacent padded pixels (one 32-bit store).
-__global__ void __launch_bounds__(256) k_pyramid_level(const OrbConfig* __restrict__ cfg, int level, const uint8_t* __restrict__ img,
-    size_t img_slot, int img_stride, uint8_t* __restrict__ pyr, size_t pyr_slot, const int* __restrict__ xofs,
-    const short* __restrict__ xa, const int* __restrict__ yofs, const short* __restrict__ yb)
+// Level 0: copy + REFLECT_101 ring.  One thread per 4 horizontally adjacent padded pixels (one 32-bit store);
+// interior words are two aligned loads and a funnel shift, ring words go byte by byte.
+__global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride, unsigned pyr_off, const __grid_constant__ ImgPtrs img, int img_stride,
+    uint8_t* __restrict__ pyr, size_t pyr_slot)
 {
-    const LevelDesc L = cfg->lv[level];
-    const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
+    const int pw = w + 2 * EDGE_THRESHOLD, ph = h + 2 * EDGE_THRESHOLD;
     const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int py = blockIdx.y * blockDim.y + threadIdx.y;
     if (px0 >= pw || py >= ph)
         return;
     const int slot = blockIdx.z;
-    uint8_t* dst = pyr + slot * pyr_slot + L.pyr_off + (size_t)py * L.pstride;
-    const int y = reflect101(py - EDGE_THRESHOLD, L.h);
+    const uint8_t* src = static_cast<const uint8_t*>(img.p[slot]) + (size_t)reflect101(py - EDGE_THRESHOLD, h) * img_stride;
     unsigned packed = 0;
-    if (level == 0) {
-        const uint8_t* src = img + slot * img_slot + (size_t)y * img_stride;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int px = px0 + k;
-            int x = reflect101(min(px, pw - 1) - EDGE_THRESHOLD, L.w);
-            packed |= (unsigned)src[x] << (8 * k);
-        }
+    if (px0 >= EDGE_THRESHOLD && px0 + 3 < EDGE_THRESHOLD + w) {
+        const uint8_t* q = src + (px0 - EDGE_THRESHOLD);
+        const unsigned mis = (unsigned)(reinterpret_cast<size_t>(q) & 3);
+        const unsigned* qa = reinterpret_cast<const unsigned*>(q - mis);
+        packed = __funnelshift_r(qa[0], mis ? qa[1] : 0u, 8 * mis); // qa[1] is touched only when it holds wanted bytes
     } else {
-        const LevelDesc P = cfg->lv[level - 1];
-        const uint8_t* prev = pyr + slot * pyr_slot + P.pyr_off + (size_t)EDGE_THRESHOLD * P.pstride + EDGE_THRESHOLD;
-        const int* xo = xofs + L.tab_x_off;
-        const short* al = xa + 2 * L.tab_x_off;
-        int sy0 = yofs[L.tab_y_off + y];
-        const int b0 = yb[2 * (L.tab_y_off + y)], b1 = yb[2 * (L.tab_y_off + y) + 1];
-        int sy1 = min(max(sy0 + 1, 0), P.h - 1);
-        sy0 = min(max(sy0, 0), P.h - 1);
-        const uint8_t* r0 = prev + (size_t)sy0 * P.pstride;
-        const uint8_t* r1 = prev + (size_t)sy1 * P.pstride;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int px = px0 + k;
-            int x = reflect101(min(px, pw - 1) - EDGE_THRESHOLD, L.w);
-            int sx = xo[x];
-            int a0 = al[2 * x], a1 = al[2 * x + 1];
-            int h0 = r0[sx] * a0 + r0[sx + 1] * a1; // sx+1 may touch the ring only when a1 == 0
-            int h1 = r1[sx] * a0 + r1[sx + 1] * a1;
-            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            packed |= (unsigned)v << (8 * k);
+        for (int k = 0; k < 4; k++)
+            packed |= (unsigned)src[reflect101(min(px0 + k, pw - 1) - EDGE_THRESHOLD, w)] << (8 * k);
+    }
+    *reinterpret_cast<unsigned*>(pyr + slot * pyr_slot + pyr_off + (size_t)py * pstride + px0) = packed; // pstride is a multiple of 64
+}
+
+// Level l >= 1: cv::resize(INTER_LINEAR) of level l-1 (8-bit fixed point, 11-bit coefficients, one rounding per
+// pass as in OpenCV's resize.cpp) + ring, in one pass over 128 x 16 tiles of the PADDED level.  The source
+// window of a tile is staged in shared memory with aligned word loads, the horizontal blend is done once per
+// (source row, output column) and kept as 16-bit (h >> 4), the vertical blend packs 8 outputs per thread.
+// Ring pixels are resampled at their reflected coordinates, which is what copyMakeBorder would copy.
+struct PyrLevel {
+    int w, h, pstride;           // this level
+    unsigned pyr_off;
+    int pw_src, ph_src, pstride_src; // level l-1 (interior size, padded pitch)
+    unsigned pyr_off_src;
+    int tab_x_off, tab_y_off;
+    int rs_cols, rs_rows;
+};
+__global__ void __launch_bounds__(256) k_pyramid_resize(const __grid_constant__ PyrLevel V, uint8_t* __restrict__ pyr, size_t pyr_slot,
+    const int* __restrict__ xofs, const short* __restrict__ xa, const int* __restrict__ yofs, const short* __restrict__ yb)
+{
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    uint8_t* s_src = s_raw;                                                                   // [rs_rows][rs_cols]
+    unsigned short* s_H = reinterpret_cast<unsigned short*>(s_raw + V.rs_rows * V.rs_cols);    // [rs_rows][PYR_TW]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int pw = V.w + 2 * EDGE_THRESHOLD, ph = V.h + 2 * EDGE_THRESHOLD;
+    const int p0x = blockIdx.x * PYR_TW, p1x = min(p0x + PYR_TW - 1, pw - 1);
+    const int p0y = blockIdx.y * PYR_TH, p1y = min(p0y + PYR_TH - 1, ph - 1);
+    const int* xo = xofs + V.tab_x_off;
+    const short* al = xa + 2 * V.tab_x_off;
+    const int* yo = yofs + V.tab_y_off;
+    const short* be = yb + 2 * V.tab_y_off;
+    int xlo, xhi, ylo, yhi;
+    ring_tile_range(p0x, p1x, V.w, xlo, xhi);
+    ring_tile_range(p0y, p1y, V.h, ylo, yhi);
+    const int sx_lo = xo[xlo], ncols = xo[xhi] + 1 - sx_lo + 1; // column sx + 1 may be the source's first ring column (coefficient 0)
+    const int sy_lo = min(max(yo[ylo], 0), V.ph_src - 1), nrows = min(max(yo[yhi] + 1, 0), V.ph_src - 1) - sy_lo + 1;
+    uint8_t* slot_base = pyr + blockIdx.z * pyr_slot;
+    const uint8_t* src = slot_base + V.pyr_off_src + (size_t)(EDGE_THRESHOLD + sy_lo) * V.pstride_src + EDGE_THRESHOLD + sx_lo;
+    const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
+    const int wpr = (ncols + mis + 3) >> 2;
+    for (int r = warp; r < nrows; r += 8)
+        for (int q = lane; q < wpr; q += 32)
+            *reinterpret_cast<unsigned*>(s_src + r * V.rs_cols + 4 * q) = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * V.pstride_src + 4 * q);
+    __syncthreads();
+    {
+        // horizontal blend: thread = output column, every second staged row
+        const int cx = tid & (PYR_TW - 1);
+        const int x = reflect101(min(p0x + cx, pw - 1) - EDGE_THRESHOLD, V.w);
+        const int a0 = al[2 * x], a1 = al[2 * x + 1];
+        const uint8_t* p = s_src + (xo[x] - sx_lo + mis);
+        for (int j = tid >> 7; j < nrows; j += 2) {
+            const uint8_t* q = p + j * V.rs_cols;
+            s_H[j * PYR_TW + cx] = (unsigned short)((q[0] * a0 + q[1] * a1) >> 4);
         }
     }
-    *reinterpret_cast<unsigned*>(dst + px0) = packed; // pstride is a multiple of 64: never crosses the row
+    __syncthreads();
+    // vertical blend: thread = 8 adjacent outputs of one row
+    const int py = p0y + (tid >> 4), cg = (tid & 15) * 8;
+    if (py >= ph || p0x + cg >= pw)
+        return;
+    const int y = reflect101(py - EDGE_THRESHOLD, V.h);
+    const int s0 = yo[y];
+    const int j0 = min(max(s0, 0), V.ph_src - 1) - sy_lo, j1 = min(max(s0 + 1, 0), V.ph_src - 1) - sy_lo;
+    const int b0 = be[2 * y], b1 = be[2 * y + 1];
+    const uint4 h0 = *reinterpret_cast<const uint4*>(s_H + j0 * PYR_TW + cg), h1 = *reinterpret_cast<const uint4*>(s_H + j1 * PYR_TW + cg);
+    const unsigned hw0[4] = { h0.x, h0.y, h0.z, h0.w }, hw1[4] = { h1.x, h1.y, h1.z, h1.w };
+    unsigned out[2] = { 0u, 0u };
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int t0 = (k & 1) ? (int)(hw0[k >> 1] >> 16) : (int)(hw0[k >> 1] & 0xffffu);
+        const int t1 = (k & 1) ? (int)(hw1[k >> 1] >> 16) : (int)(hw1[k >> 1] & 0xffffu);
+        const int v = min((((b0 * t0) >> 16) + ((b1 * t1) >> 16) + 2) >> 2, 255);
+        out[k >> 2] |= (unsigned)v << (8 * (k & 3));
+    }
+    // pstride is a multiple of 64 and cg of 8: the store never leaves the row (bytes past pw are pitch padding)
+    *reinterpret_cast<uint2*>(slot_base + V.pyr_off + (size_t)py * V.pstride + p0x + cg) = make_uint2(out[0], out[1]);
 }
 
 // ------------------------------------------------------------------ K5 ----
@@ -403,16 +441,30 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
 }
 
 // ---------------------------------------------------------------- launchers
-int launch_pyramid(rgbdfe_ctx* c, int count)
+int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride)
 {
     const OrbConfig& cfg = c->cfg;
     ProfScope prof(c, KID_PYRAMID);
     for (int l = 0; l < cfg.nlevels; l++) {
         const LevelDesc& L = cfg.lv[l];
-        int pw = L.w + 38, ph = L.h + 38;
-        dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
-        k_pyramid_level<<<grd, blk, 0, c->stream>>>(c->d_cfg, l, c->d_img, c->img_slot, cfg.w, c->d_pyr, c->pyr_slot, c->d_tab_xofs,
-            c->d_tab_xa, c->d_tab_yofs, c->d_tab_yb);
+        const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
+        if (l == 0) {
+            dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
+            k_pyramid_base<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, c->d_pyr, c->pyr_slot);
+        } else {
+            const LevelDesc& P = cfg.lv[l - 1];
+            PyrLevel V;
+            V.w = L.w, V.h = L.h, V.pstride = L.pstride, V.pyr_off = L.pyr_off;
+            V.pw_src = P.w, V.ph_src = P.h, V.pstride_src = P.pstride, V.pyr_off_src = P.pyr_off;
+            V.tab_x_off = L.tab_x_off, V.tab_y_off = L.tab_y_off, V.rs_cols = L.rs_cols, V.rs_rows = L.rs_rows;
+            const size_t smem = (size_t)L.rs_rows * L.rs_cols + (size_t)L.rs_rows * PYR_TW * sizeof(unsigned short);
+            if (smem > 48 * 1024) {
+                c->set_error("pyramid scale factor too large for the resize tile");
+                return RGBDFE_E_CAPACITY;
+            }
+            dim3 grd((pw + PYR_TW - 1) / PYR_TW, (ph + PYR_TH - 1) / PYR_TH, count);
+            k_pyramid_resize<<<grd, 256, smem, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xofs, c->d_tab_xa, c->d_tab_yofs, c->d_tab_yb);
+        }
         c->launches++;
     }
     CUDA_TRY(c, cudaGetLastError());

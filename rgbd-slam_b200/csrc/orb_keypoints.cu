@@ -451,8 +451,7 @@ __device__ void sincosf_glibc(float y, float* sn, float* cs)
 
 __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     const uint8_t* __restrict__ blur, size_t blur_slot, const SelKp* __restrict__ sel_all, int sel_slot, const int* __restrict__ sel_count,
-    const FrameBatch frames /* by value: one frame struct per slot */, const float* __restrict__ depth, size_t depth_slot,
-    int depth_stride, int unproject, float fx, float fy, float cx, float cy)
+    const FrameBatch frames /* by value: one frame struct per slot */, const __grid_constant__ ImgPtrs depth, int depth_stride, int unproject, float depth16_factor /* > 0: the slots hold raw 16-bit depth */, float fx, float fy, float cx, float cy)
 {
     __shared__ __align__(16) signed char s_pattern[1024];
     reinterpret_cast<int*>(s_pattern)[threadIdx.x] = reinterpret_cast<const int*>(g_pattern)[threadIdx.x]; // 256 threads x 4 B
@@ -539,7 +538,11 @@ __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __rest
         F.outlier[gi] = 0;
         if (unproject) {
             // Frame::uprojectCamera without lens distortion (mvKeysUn == mvKeys)
-            const float z = depth[slot * depth_slot + (size_t)(int)py * depth_stride + (int)px];
+            // the depth slot holds float metres, or the raw 16-bit image: then cv::Mat::convertTo(CV_32F, factor) happens here
+            const size_t di = (size_t)(int)py * depth_stride + (int)px;
+            const float z = depth16_factor > 0.0f
+                ? __fmul_rn((float)static_cast<const unsigned short*>(depth.p[slot])[di], depth16_factor)
+                : static_cast<const float*>(depth.p[slot])[di];
             rgbdfe_point3f P = { 0.f, 0.f, 0.f };
             if (z > 0) {
                 const float invfx = __fdiv_rn(1.0f, fx), invfy = __fdiv_rn(1.0f, fy);
@@ -575,7 +578,8 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
     return RGBDFE_OK;
 }
 
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, int depth_stride, float fx, float fy, float cx, float cy)
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, float depth16_factor,
+    float fx, float fy, float cx, float cy)
 {
     if (!g_pattern_uploaded[c->device]) {
         CUDA_TRY(c, cudaMemcpyToSymbolAsync(g_pattern, kBriefPattern, 1024, 0, cudaMemcpyHostToDevice, c->stream));
@@ -584,7 +588,7 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
     const int warps = c->kp_cap + 1; // one extra warp publishes the count
     ProfScope prof(c, KID_DESCRIBE);
     k_orient_describe<<<dim3((warps + 7) / 8, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot, c->d_sel,
-        c->sel_slot, c->d_sel_count, frames, c->d_depth, c->depth_slot, depth_stride, unproject ? 1 : 0, fx, fy, cx, cy);
+        c->sel_slot, c->d_sel_count, frames, depth, depth_stride, unproject ? 1 : 0, depth16_factor, fx, fy, cx, cy);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;

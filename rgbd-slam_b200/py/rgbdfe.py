@@ -287,6 +287,21 @@ class Context:
             )
         )
 
+    def frames_extract_raw(self, frames, grays, depths16, cam, depth_map_factor):
+        """gray u8 + raw 16-bit depth; depth_map_factor = 1.0f / DepthMapFactor (Core/RGBDcamera.cpp:21)."""
+        n = len(frames)
+        fr = (C.c_void_p * n)(*[f.h for f in frames])
+        gp = (C.c_void_p * n)(*[g.ctypes.data for g in grays])
+        dp = (C.c_void_p * n)(*[d.ctypes.data for d in depths16])
+        h, w = grays[0].shape
+        assert depths16[0].dtype == np.uint16
+        self._chk(
+            lib().rgbdfe_frames_extract_raw(
+                self.h, fr, n, gp, w, h, grays[0].strides[0], dp, depths16[0].strides[0] // 2, C.c_float(depth_map_factor),
+                C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"]),
+            )
+        )
+
     def track(self, ref, cur, slot, ratio=0.9, discard=True, iters=200, min_inl=10, max_mahal=3.0, sample=4, update_f2=True):
         self._chk(
             lib().rgbdfe_track(

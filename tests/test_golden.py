@@ -135,7 +135,12 @@ def test_cuda_pyramid_blur_knn_rand_vs_cv2_golden(prim):
 
 
 @pytest.mark.gpu
-def test_cuda_pipeline_vs_golden(pipe):
+@pytest.mark.parametrize("raw_depth", [False, True, "in_place"])
+def test_cuda_pipeline_vs_golden(pipe, raw_depth):
+    """raw_depth: the 16-bit depth image goes to the device and Frame's convertTo(CV_32F, 1/factor) happens there (N1);
+    in_place: the same with images that already live in device memory (read where they are, no staging copy)."""
+    import ctypes as C
+
     import rgbdfe
 
     cam, frames = _pipe_frames(pipe)
@@ -144,7 +149,23 @@ def test_cuda_pipeline_vs_golden(pipe):
         ctx.orb_configure(int(pipe["nfeatures"]), 1.2, 8, 20, 7)
         ctx.rng_seed(42)
         fr = [rgbdfe.Frame(ctx) for _ in frames]
-        ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)
+        inv = float(np.float32(1.0) / np.float32(cam["factor"]))
+        if raw_depth == "in_place":
+            import torch
+
+            g_d = [torch.from_numpy(np.ascontiguousarray(f[0])).cuda() for f in frames]
+            d_d = [torch.from_numpy(pipe[f"depth16_{i}"].astype(np.int16)).cuda() for i in range(3)]  # same bits as uint16
+            torch.cuda.synchronize()
+            n = len(frames)
+            ctx._chk(rgbdfe.lib().rgbdfe_frames_extract_raw(
+                ctx.h, (C.c_void_p * n)(*[f.h for f in fr]), n, (C.c_void_p * n)(*[t.data_ptr() for t in g_d]), 320, 240, 320,
+                (C.c_void_p * n)(*[t.data_ptr() for t in d_d]), 320, C.c_float(inv), C.c_float(cam["fx"]), C.c_float(cam["fy"]),
+                C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+        elif raw_depth:
+            d16 = [np.ascontiguousarray(pipe[f"depth16_{i}"]) for i in range(3)]
+            ctx.frames_extract_raw(fr, [f[0] for f in frames], d16, cam, inv)
+        else:
+            ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)
         ctx.track_sequence(fr, 0)
         res = ctx.track_results(0, 2)
         for i in range(3):
