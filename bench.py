@@ -23,6 +23,7 @@ import subprocess
 import sys
 import tempfile
 import threading
+from concurrent.futures import ThreadPoolExecutor
 import time
 
 # Every sequence in flight owns two streams; with the default of 8 hardware work queues they alias and the chains
@@ -184,6 +185,8 @@ def main():
     ap.add_argument("--frames", type=int, default=96)
     ap.add_argument("--sequences", type=int, default=24, help="independent tracked sequences in flight on each GPU")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
+    ap.add_argument("--host-threads", type=int, default=1, help="host threads that enqueue the sequences' work")
+    ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
@@ -228,6 +231,8 @@ def main():
             self.ctx_x = rgbdfe.Context(local_rank, W, H, NFEAT, B)
             self.ctx_t = rgbdfe.Context(local_rank, W, H, NFEAT, 1)
             self.ctx_x.orb_configure(NFEAT, 1.2, 8, 20, 7)
+            if args.full_upload:
+                self.ctx_x.set_option("host_zero_copy", 0)
             if part:
                 self.ctx_x.bind_partition(rgbdfe.PART_THROUGHPUT)
                 self.ctx_t.bind_partition(rgbdfe.PART_LATENCY)
@@ -288,13 +293,24 @@ def main():
             self.ctx_x.close()
             self.ctx_t.close()
 
+    pool = ThreadPoolExecutor(max_workers=args.host_threads) if args.host_threads > 1 else None
+
+    def run_group(group, dev):
+        for q in group:
+            q.enqueue(dev)
+        for q in group:
+            q.collect()
+
     def run_steps(seqs, dev, steps):
+        """Every sequence enqueues one batch (extraction of the next + chain of the current) and then reads its results.
+        The C-ABI calls release the GIL, so a few host threads can feed the 2 x len(seqs) streams concurrently."""
         n = 0
+        T = args.host_threads
         for _ in range(steps):
-            for q in seqs:
-                q.enqueue(dev)
-            for q in seqs:
-                q.collect()
+            if pool and len(seqs) > 1:
+                list(pool.map(lambda k: run_group(seqs[k::T], dev), range(T)))
+            else:
+                run_group(seqs, dev)
             n += B * len(seqs)
         return n
 
@@ -330,6 +346,13 @@ def main():
     proc, path = sample_clocks_start() if rank == 0 else (None, None)
     n_dev, ms_dev, launches = timed(seqs, True, args.steps)
     n_e2e, ms_e2e, _ = timed(seqs, False, args.steps)
+    # the same with the whole 16-bit depth map uploaded per frame (option host_zero_copy = 0)
+    for q in seqs:
+        q.ctx_x.set_option("host_zero_copy", 0)
+    run_steps(seqs, False, 1)
+    n_up, ms_up, _ = timed(seqs, False, max(2, args.steps // 2))
+    for q in seqs:
+        q.ctx_x.set_option("host_zero_copy", 0 if args.full_upload else 1)
     clocks = sample_clocks_stop(proc, path, local_rank) if rank == 0 else None
     value = n_dev * world / (ms_dev * 1e-3)
     e2e = n_e2e * world / (ms_e2e * 1e-3)
@@ -459,7 +482,11 @@ def main():
                        "l2": f"inputs larger than L2: 24 sequences x rotating {F}-frame set ({F * (W * H * 3) / 1e6:.0f} MB) + 58 MB of pyramid per batch",
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
-            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": S * B * W * H * 3, "d2h_bytes_per_step": S * B * 84},
+            "e2e": {"value": e2e, "unit": "frames/s",
+                    "h2d_bytes_per_step": S * B * (W * H * (3 if args.full_upload else 1) + (0 if args.full_upload else NFEAT * 32)),
+                    "d2h_bytes_per_step": S * B * 84,
+                    "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
+                    "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify,
         }))
     for q in seqs:

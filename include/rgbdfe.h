@@ -89,7 +89,8 @@ long long rgbdfe_launch_count(const rgbdfe_ctx* ctx);
 int rgbdfe_sync(rgbdfe_ctx* ctx);
 /* Tuning knobs that never change results.  "ransac_first_chunk" (default 32): how many RANSAC iterations the
  * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
- * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU. */
+ * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU.
+ * "host_zero_copy" (default 1): see rgbdfe_frames_extract. */
 int rgbdfe_set_option(rgbdfe_ctx* ctx, const char* name, int value);
 /* Pipelining across contexts of one device (e.g. one context extracts frame batch n+1 while another tracks
  * batch n; rgbdfe_frame handles are plain device buffers and may be used by either): everything enqueued on
@@ -186,9 +187,13 @@ void rgbdfe_frame_destroy(rgbdfe_ctx* ctx, rgbdfe_frame* frame);
  * back-project every keypoint with the metric depth map (float32, 0 = invalid)
  * and pinhole intrinsics; outlier flags reset to false.  Asynchronous on the
  * context stream; the buffers must stay valid and unchanged until rgbdfe_sync().
- * gray/depth may be host pointers (ideally pinned; uploaded into the context's slots)
- * or device pointers (read in place, no staging copy); all images of one call must be
- * of the same kind.  count frames are processed as one batch (count <= max_batch). */
+ * gray/depth may be device pointers (read in place, no staging copy) or host pointers
+ * (ideally pinned; uploaded into the context's slots, images that follow each other in
+ * memory as one transfer).  A pinned host DEPTH image is not uploaded: the back-projection
+ * reads only the sectors under the keypoints over PCIe, in place (as the reference reads
+ * mImDepth only at the keypoints); rgbdfe_set_option "host_zero_copy" 0 uploads it whole.  All images of one call must be
+ * of the same kind.
+ * count frames are processed as one batch (count <= max_batch). */
 int rgbdfe_frames_extract(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
     const float* const* depth, int depth_stride_elems, float fx, float fy, float cx, float cy);
 /* The same with the RAW depth image of the dataset (16-bit, as cv::imread(..., IMREAD_UNCHANGED) returns it):

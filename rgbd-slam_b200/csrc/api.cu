@@ -385,6 +385,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
 {
     if (!c || !name)
         return RGBDFE_E_ARG;
+    if (!strcmp(name, "host_zero_copy")) {
+        c->host_zero_copy = value != 0;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "ransac_first_chunk")) {
         if (value < 1 || value > MAX_ITERS)
             return RGBDFE_E_ARG;
@@ -501,14 +505,73 @@ int rgbdfe_orb_tables(rgbdfe_ctx* c, float* scale, float* inv_scale, float* sigm
 
 namespace {
 
-bool is_device_ptr(const void* p)
+// 0: pageable / unknown host memory, 1: device (or managed) memory, 2: pinned host memory mapped into the device
+// address space.  *dev receives the pointer kernels can dereference (kinds 1 and 2).
+int pointer_kind(const void* p, const void** dev)
 {
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
         cudaGetLastError();
-        return false;
+        return 0;
     }
-    return a.type == cudaMemoryTypeDevice;
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
+        *dev = a.devicePointer ? a.devicePointer : p;
+        return 1;
+    }
+    if (a.type == cudaMemoryTypeHost && a.devicePointer) {
+        *dev = a.devicePointer;
+        return 2;
+    }
+    return 0;
+}
+
+// Kernel-visible pointers of a batch of images that are read where they are: device memory, or (depth image, option
+// "host_zero_copy") pinned host memory, of which K6 then pulls only the sectors under the keypoints over PCIe
+// instead of the whole map being uploaded.
+bool in_place_pointers(const void* const* img, int count, bool pinned_host_too, const void** out)
+{
+    const void *d0 = nullptr, *d1 = nullptr;
+    const int k0 = pointer_kind(img[0], &d0), k1 = pointer_kind(img[count - 1], &d1);
+    if (k0 == 0 || k1 != k0 || (k0 == 2 && !pinned_host_too))
+        return false;
+    if (d0 == img[0] && d1 == img[count - 1]) { // unified addressing: the pointers are usable as they are
+        for (int i = 0; i < count; i++)
+            out[i] = img[i];
+        return true;
+    }
+    for (int i = 0; i < count; i++)
+        if (pointer_kind(img[i], &out[i]) != k0)
+            return false;
+    return true;
+}
+
+// Host images -> the context's upload slots; out[i] = where image i landed.  Images with dense rows that follow
+// each other in the caller's memory (a frame ring buffer, ascending or descending) go up as ONE strided copy per
+// run: a 64-frame batch is otherwise bound by the fixed cost of its 128 separate transfers, not by PCIe.
+int upload_images(rgbdfe_ctx* c, const void* const* img, int count, size_t row_bytes, int rows, size_t src_pitch, uint8_t* slots, size_t slot_bytes,
+    const void** out)
+{
+    const size_t bytes = row_bytes * rows;
+    int i = 0;
+    while (i < count) {
+        int j = i, dir = 0;
+        while (src_pitch == row_bytes && j + 1 < count) {
+            const ptrdiff_t d = static_cast<const char*>(img[j + 1]) - static_cast<const char*>(img[j]);
+            const int nd = d == (ptrdiff_t)bytes ? 1 : (d == -(ptrdiff_t)bytes ? -1 : 0);
+            if (nd == 0 || (dir != 0 && nd != dir))
+                break;
+            dir = nd;
+            j++;
+        }
+        if (j == i)
+            CUDA_TRY(c, cudaMemcpy2DAsync(slots + i * slot_bytes, row_bytes, img[i], src_pitch, row_bytes, rows, cudaMemcpyDefault, c->stream));
+        else // one "row" per image: source pitch = image size, destination pitch = slot size
+            CUDA_TRY(c, cudaMemcpy2DAsync(slots + i * slot_bytes, slot_bytes, dir > 0 ? img[i] : img[j], bytes, bytes, j - i + 1, cudaMemcpyDefault, c->stream));
+        for (int m = i; m <= j; m++)
+            out[m] = slots + (size_t)(dir >= 0 ? m : i + (j - m)) * slot_bytes;
+        i = j + 1;
+    }
+    return RGBDFE_OK;
 }
 
 // Upload `count` gray (+ optional depth) images and run K1..K6 on them as one batch.
@@ -536,28 +599,26 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
     for (int i = 0; i < count; i++)
         if (!gray[i] || !frames[i] || (dany && !dany[i]))
             return RGBDFE_E_ARG;
-    // Images that already live in device memory are read in place (all pointers of one call must be of one kind;
-    // the first and last are checked); host images are uploaded into the context's slots.
-    const bool in_place = is_device_ptr(gray[0]) && is_device_ptr(gray[count - 1])
-        && (!dany || (is_device_ptr(dany[0]) && is_device_ptr(dany[count - 1])));
+    // Images in device memory are read in place (all pointers of one call must be of one kind; the first and last
+    // are checked); host images are uploaded into the context's slots, except a pinned depth map with "host_zero_copy".
+    const bool gray_in_place = in_place_pointers((const void* const*)gray, count, false, gp.p);
+    const bool depth_in_place = dany && in_place_pointers(dany, count, c->host_zero_copy, dp.p);
     int gstride = stride, dstride = depth_stride;
-    for (int i = 0; i < count; i++) {
+    for (int i = 0; i < count; i++)
         fb.f[i] = *frames[i];
-        if (in_place) {
-            gp.p[i] = gray[i];
-            dp.p[i] = dany ? dany[i] : nullptr;
-            continue;
-        }
-        gp.p[i] = c->d_img + i * c->img_slot;
-        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_img + i * c->img_slot, w, gray[i], stride, w, h, cudaMemcpyDefault, c->stream));
-        if (dany) {
-            dp.p[i] = c->d_depth + i * c->depth_slot;
-            CUDA_TRY(c, cudaMemcpy2DAsync(c->d_depth + i * c->depth_slot, (size_t)w * delem, dany[i], (size_t)depth_stride * delem, (size_t)w * delem, h,
-                            cudaMemcpyDefault, c->stream));
-        }
+    if (!gray_in_place) {
+        if ((rc = upload_images(c, (const void* const*)gray, count, (size_t)w, h, (size_t)stride, reinterpret_cast<uint8_t*>(c->d_img), c->img_slot, gp.p))
+            != RGBDFE_OK)
+            return rc;
+        gstride = w;
     }
-    if (!in_place)
-        gstride = w, dstride = w;
+    if (dany && !depth_in_place) {
+        if ((rc = upload_images(c, dany, count, (size_t)w * delem, h, (size_t)depth_stride * delem, reinterpret_cast<uint8_t*>(c->d_depth),
+                 c->depth_slot * sizeof(float), dp.p))
+            != RGBDFE_OK)
+            return rc;
+        dstride = w;
+    }
     if ((rc = launch_pyramid(c, count, gp, gstride)) != RGBDFE_OK)
         return rc;
     if ((rc = launch_fast(c, count)) != RGBDFE_OK)

@@ -179,6 +179,7 @@ struct rgbdfe_ctx {
     cudaStream_t bulk_stream = nullptr; // RGBDFE_PART_LATENCY: stream on the throughput partition for the chain's kNN (partition.cu)
     cudaEvent_t order_evt = nullptr; // rgbdfe_stream_wait
     cudaEvent_t bulk_evt = nullptr;  // stream <-> bulk_stream ordering
+    bool host_zero_copy = true;      // a pinned host depth map is read in place by K6 (keypoint sectors only) instead of being uploaded
     std::string err;
     long long launches = 0;
     int max_w = 0, max_h = 0, max_feats = 0, max_batch = 1;
