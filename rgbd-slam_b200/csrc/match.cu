@@ -1,43 +1,47 @@
 // K7 k_knn2_hamming + K8 k_ratio_filter — Matcher::match (Features/Matcher.cpp:106-139):
 // cv::BFMatcher(NORM_HAMMING)::knnMatch(k=2), ratio test, unique-train claim,
-// outlier / valid-depth filters.  Integer-pipe bound: the query descriptor lives in
-// 8 registers of its thread, train descriptors are staged in shared memory and read as
-// warp-wide broadcasts (2 x LDS.128 per descriptor per warp).  POPC issues on the XU pipe at a
-// quarter of the LOP3 rate, so the 256-bit count goes through carry-save adders first
-// (hamming256): 5 POPC + 14 LOP3 per descriptor pair instead of 8 POPC + 8 LOP3.
+// outlier / valid-depth filters.
+//
+// K7 is the one dense contraction of the path: hamming(q, t) = |q| + |t| - 2 * (q . t) with the descriptors as
+// 256-vectors over {0, 1}, and q . t over all (query, train) pairs is a matrix product.  It runs on the tensor
+// pipe through the warp-level u8 MMA m16n8k32 (IMMA.16832 on sm_100a: measured 0.5 per clock and SM, i.e. 8
+// descriptor pairs per clock and SM against 2.2 for the POPC/LOP3 formulation on the integer pipes).  Bits are
+// expanded to bytes once: a warp keeps 32 queries (2 m-tiles x 8 k-steps, 64 registers) stationary, the CTA
+// expands each tile of 128 train descriptors into shared memory in exactly the order the B fragments are read
+// (conflict-free 8-byte loads), and the accumulator fragment goes straight into a per-thread top-2 (strict <,
+// train index ascending), merged across the 4 lanes of a row at the end.  The k order inside the product is
+// free, so lane (g, t) simply owns bits [64t, 64t + 64) of its query rows and of its train column, 8 per k-step.
+// (The .b1 .and.popc form of the instruction would take the packed bits directly, but ptxas lowers it to a
+// subroutine of 24 MOVM transposes + 8 IMMA per call: slower than the integer pipes.)
 // Neighbour order is lexicographic (distance, trainIdx) as in OpenCV.
 #include "match_filter.cuh"
 
 namespace rgbdfe {
 
-#define KNN_THREADS 128
-#define KNN_TILE 128
-#ifndef KNN_POPC4
-#define KNN_POPC4 1
-#endif
+#define KNN_THREADS 256
+#define KNN_TILE 128      // train descriptors expanded per step (32 KB of shared memory)
+#define KNN_MT 2          // m-tiles (16 queries each) per warp
+#define KNN_QPB (KNN_THREADS / 32 * KNN_MT * 16) // queries per CTA = 256
+#define KNN_NONE 0x7fffffff
 
-// carry-save adder on 32 bit lanes: (a, b, c) -> sum bits and carry bits (one LOP3 each)
-__device__ __forceinline__ void csa(unsigned a, unsigned b, unsigned c, unsigned& s, unsigned& cy)
+__device__ __forceinline__ void mma_u8(int (&c)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1)
 {
-    s = a ^ b ^ c;
-    cy = (a & b) | (a & c) | (b & c);
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// bits [4n, 4n + 4) of w as four bytes of 0 / 1
+__device__ __forceinline__ unsigned nibble_bytes(unsigned w, int n) { return (((w >> (4 * n)) & 0xfu) * 0x00204081u) & 0x01010101u; }
 
-// popcount of the 256-bit XOR of two descriptors
-__device__ __forceinline__ int hamming256(const uint4& qa, const uint4& qb, const uint4& ta, const uint4& tb)
+// A candidate is one sortable word: (|t| - 2 q.t + 256) << 16 | train index, so that unsigned order = lexicographic
+// (distance, trainIdx) for a fixed query.  m0 <= m1 are the two smallest seen; pushing is three min/max.
+#define KNN_KEY_BIAS 256
+#define KNN_EMPTY 0x7fffffffu  // no candidate yet
+#define KNN_PAD 0x7ffe0000u    // base word of a column past the end of the train set (never beats a real one)
+__device__ __forceinline__ void top2_push(unsigned p, unsigned& m0, unsigned& m1)
 {
-    const unsigned x0 = qa.x ^ ta.x, x1 = qa.y ^ ta.y, x2 = qa.z ^ ta.z, x3 = qa.w ^ ta.w;
-    const unsigned x4 = qb.x ^ tb.x, x5 = qb.y ^ tb.y, x6 = qb.z ^ tb.z, x7 = qb.w ^ tb.w;
-    unsigned s1, c1, s2, c2, s3, c3, t1, f1;
-    csa(x0, x1, x2, s1, c1);
-    csa(x3, x4, x5, s2, c2);
-    csa(s1, s2, x6, s3, c3);
-#if KNN_POPC4
-    csa(c1, c2, c3, t1, f1);
-    return __popc(s3) + __popc(x7) + 2 * __popc(t1) + 4 * __popc(f1);
-#else
-    return __popc(s3) + __popc(x7) + 2 * (__popc(c1) + __popc(c2) + __popc(c3));
-#endif
+    m1 = min(m1, max(m0, p));
+    m0 = min(m0, p);
 }
 
 // partial: [pair][split][q] -> int4 (d0, i0, d1, i1)
@@ -47,49 +51,113 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2_hamming(const MatchPair* _
     const int pair = slot0 + blockIdx.z;
     const MatchPair P = pairs[pair];
     const int nq = *P.nq, nt = *P.nt;
-    const int q = blockIdx.x * KNN_THREADS + threadIdx.x;
-    if (blockIdx.x * KNN_THREADS >= nq)
+    const int q_base = blockIdx.x * KNN_QPB;
+    if (q_base >= nq)
         return;
-    __shared__ uint4 s_t[KNN_TILE * 2];
-    uint4 qa = make_uint4(0, 0, 0, 0), qb = qa;
-    if (q < nq) {
-        const uint4* qp = reinterpret_cast<const uint4*>(P.q_desc + (size_t)q * 32);
-        qa = qp[0];
-        qb = qp[1];
+    // expanded train tile: [n-tile of 8 columns][k-step][lane = column * 4 + quarter] -> (b0, b1)
+    __shared__ __align__(16) uint2 s_b[KNN_TILE / 8][8][32];
+    __shared__ __align__(8) unsigned s_base[KNN_TILE]; // (|t| + 256) << 16 | train index
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3; // fragment row / column and 64-bit quarter of the descriptor
+    // stationary operand: bits [64t, 64t + 64) of rows g and g + 8 of each m-tile as bytes, 8 per k-step; |q| per row
+    unsigned a[KNN_MT][8][4];
+    int qpop[KNN_MT][2];
+#pragma unroll
+    for (int m = 0; m < KNN_MT; m++) {
+        const int r0 = q_base + (warp * KNN_MT + m) * 16 + g, r1 = r0 + 8;
+        uint2 w0 = make_uint2(0u, 0u), w1 = w0;
+        if (r0 < nq)
+            w0 = reinterpret_cast<const uint2*>(P.q_desc + (size_t)r0 * 32)[t];
+        if (r1 < nq)
+            w1 = reinterpret_cast<const uint2*>(P.q_desc + (size_t)r1 * 32)[t];
+#pragma unroll
+        for (int s = 0; s < 8; s++) {
+            const unsigned v0 = s < 4 ? w0.x : w0.y, v1 = s < 4 ? w1.x : w1.y;
+            a[m][s][0] = nibble_bytes(v0, 2 * (s & 3)), a[m][s][2] = nibble_bytes(v0, 2 * (s & 3) + 1);
+            a[m][s][1] = nibble_bytes(v1, 2 * (s & 3)), a[m][s][3] = nibble_bytes(v1, 2 * (s & 3) + 1);
+        }
+        int p0 = __popc(w0.x) + __popc(w0.y), p1 = __popc(w1.x) + __popc(w1.y);
+        p0 += __shfl_xor_sync(0xffffffffu, p0, 1), p1 += __shfl_xor_sync(0xffffffffu, p1, 1);
+        p0 += __shfl_xor_sync(0xffffffffu, p0, 2), p1 += __shfl_xor_sync(0xffffffffu, p1, 2);
+        qpop[m][0] = p0, qpop[m][1] = p1;
     }
+    unsigned m0[KNN_MT][2], m1[KNN_MT][2];
+#pragma unroll
+    for (int m = 0; m < KNN_MT; m++)
+#pragma unroll
+        for (int h = 0; h < 2; h++)
+            m0[m][h] = m1[m][h] = KNN_EMPTY;
     // train range of this split, in whole tiles
     const int tiles = (nt + KNN_TILE - 1) / KNN_TILE;
     const int tps = (tiles + splits - 1) / splits;
     const int t_begin = min(blockIdx.y * tps * KNN_TILE, nt), t_end = min((blockIdx.y + 1) * tps * KNN_TILE, nt);
-    int d0 = 0x7fffffff, d1 = 0x7fffffff, i0 = -1, i1 = -1;
     for (int t0 = t_begin; t0 < t_end; t0 += KNN_TILE) {
         const int cnt = min(KNN_TILE, t_end - t0);
         __syncthreads();
-        if ((int)threadIdx.x < cnt) {
-            const uint4* tp = reinterpret_cast<const uint4*>(P.t_desc + (size_t)(t0 + threadIdx.x) * 32);
-            s_t[threadIdx.x * 2] = tp[0];
-            s_t[threadIdx.x * 2 + 1] = tp[1];
+        // expansion: work item = (column j, quarter tq), 512 per tile; consecutive lanes write consecutive 8-byte slots
+        for (int wi = tid; wi < KNN_TILE * 4; wi += KNN_THREADS) {
+            const int j = wi >> 2, tq = wi & 3;
+            uint2 w = make_uint2(0u, 0u);
+            if (j < cnt)
+                w = reinterpret_cast<const uint2*>(P.t_desc + (size_t)(t0 + j) * 32)[tq];
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                const unsigned v = s < 4 ? w.x : w.y;
+                s_b[j >> 3][s][wi & 31] = make_uint2(nibble_bytes(v, 2 * (s & 3)), nibble_bytes(v, 2 * (s & 3) + 1));
+            }
+            int pop = __popc(w.x) + __popc(w.y);
+            pop += __shfl_xor_sync(0xffffffffu, pop, 1);
+            pop += __shfl_xor_sync(0xffffffffu, pop, 2);
+            if (tq == 0)
+                s_base[j] = j < cnt ? ((unsigned)(pop + KNN_KEY_BIAS) << 16 | (unsigned)(t0 + j)) : KNN_PAD;
         }
         __syncthreads();
-#pragma unroll 4
-        for (int j = 0; j < cnt; j++) {
-            const uint4 ta = s_t[j * 2], tb = s_t[j * 2 + 1];
-            const int d = hamming256(qa, qb, ta, tb);
-            if (d < d1) { // ascending train index: strict < keeps the lower index on ties
-                if (d < d0) {
-                    d1 = d0;
-                    i1 = i0;
-                    d0 = d;
-                    i0 = t0 + j;
-                } else {
-                    d1 = d;
-                    i1 = t0 + j;
-                }
+        for (int n0 = 0; n0 < cnt; n0 += 8) {
+            int c[KNN_MT][4];
+#pragma unroll
+            for (int m = 0; m < KNN_MT; m++)
+                c[m][0] = c[m][1] = c[m][2] = c[m][3] = 0;
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                const uint2 b = s_b[n0 >> 3][s][lane];
+#pragma unroll
+                for (int m = 0; m < KNN_MT; m++)
+                    mma_u8(c[m], a[m][s][0], a[m][s][1], a[m][s][2], a[m][s][3], b.x, b.y);
+            }
+            const uint2 base = *reinterpret_cast<const uint2*>(&s_base[n0 + 2 * t]); // this thread's two columns
+#pragma unroll
+            for (int m = 0; m < KNN_MT; m++) {
+                // distance word = base - 2 (q . t) << 16  (+ |q| at the end); padded columns have q . t = 0
+                top2_push(base.x - ((unsigned)c[m][0] << 17), m0[m][0], m1[m][0]);
+                top2_push(base.y - ((unsigned)c[m][1] << 17), m0[m][0], m1[m][0]);
+                top2_push(base.x - ((unsigned)c[m][2] << 17), m0[m][1], m1[m][1]);
+                top2_push(base.y - ((unsigned)c[m][3] << 17), m0[m][1], m1[m][1]);
             }
         }
     }
-    if (q < nq)
-        partial[((size_t)pair * splits + blockIdx.y) * q_cap + q] = make_int4(d0, i0, d1, i1);
+    // the 4 lanes of a row hold disjoint column subsets: two butterfly merges, then lane t == 0 owns the result
+#pragma unroll
+    for (int m = 0; m < KNN_MT; m++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            unsigned a0 = m0[m][h], a1 = m1[m][h];
+#pragma unroll
+            for (int x = 1; x <= 2; x <<= 1) {
+                const unsigned o0 = __shfl_xor_sync(0xffffffffu, a0, x), o1 = __shfl_xor_sync(0xffffffffu, a1, x);
+                const unsigned lo = min(a0, o0);
+                a1 = min(max(a0, o0), min(a1, o1));
+                a0 = lo;
+            }
+            const int q = q_base + (warp * KNN_MT + m) * 16 + g + 8 * h;
+            if (t == 0 && q < nq) {
+                int4 r = make_int4(KNN_NONE, -1, KNN_NONE, -1);
+                if (a0 < KNN_PAD)
+                    r.x = qpop[m][h] + (int)(a0 >> 16) - KNN_KEY_BIAS, r.y = (int)(a0 & 0xffffu);
+                if (a1 < KNN_PAD)
+                    r.z = qpop[m][h] + (int)(a1 >> 16) - KNN_KEY_BIAS, r.w = (int)(a1 & 0xffffu);
+                partial[((size_t)pair * splits + blockIdx.y) * q_cap + q] = r;
+            }
+        }
 }
 
 // One CTA per pair.  dynamic smem: int claim[t_cap]
@@ -112,7 +180,11 @@ int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, i
 {
     if (npairs <= 0)
         return RGBDFE_OK;
-    dim3 grd((max_nq + KNN_THREADS - 1) / KNN_THREADS, splits, npairs);
+    if (c->kp_cap >= 65536) {
+        c->set_error("kNN: train index does not fit the 16-bit field of the candidate word");
+        return RGBDFE_E_CAPACITY;
+    }
+    dim3 grd((max_nq + KNN_QPB - 1) / KNN_QPB, splits, npairs);
     ProfScope prof(c, KID_KNN);
     k_knn2_hamming<<<grd, KNN_THREADS, 0, c->stream>>>(d_pairs, slot0, c->d_partial, c->kp_cap, splits);
     c->launches++;
