@@ -14,6 +14,8 @@
 // (The .b1 .and.popc form of the instruction would take the packed bits directly, but ptxas lowers it to a
 // subroutine of 24 MOVM transposes + 8 IMMA per call: slower than the integer pipes.)
 // Neighbour order is lexicographic (distance, trainIdx) as in OpenCV.
+#include <algorithm>
+
 #include "match_filter.cuh"
 
 namespace rgbdfe {
@@ -173,7 +175,16 @@ __global__ void __launch_bounds__(256) k_ratio_filter(const MatchPair* __restric
         nmatch[pair] = n;
 }
 
-int knn_splits_for(const rgbdfe_ctx* c, int npairs) { return npairs >= 64 ? 1 : c->knn_splits; }
+// Train-range splits per (pair, query block): enough CTAs for about six waves of the two CTAs an SM holds, so that
+// the last wave is full (a 64-pair chain alone gives 512 equal CTAs on 296 slots: 1.7 waves), within the partial
+// buffer (max(npairs, 64 * knn_splits) rows).
+int knn_splits_for(const rgbdfe_ctx* c, int npairs)
+{
+    const int qblocks = (c->kp_cap + KNN_QPB - 1) / KNN_QPB;
+    const int want = (6 * 2 * 148 + qblocks * npairs - 1) / (qblocks * npairs);
+    const int room = std::max(npairs, 64 * c->knn_splits) / npairs;
+    return std::max(1, std::min(std::min(want, c->knn_splits), room));
+}
 
 // K7 for pair slots [slot0, slot0 + npairs)
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits)
