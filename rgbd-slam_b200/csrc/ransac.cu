@@ -614,11 +614,13 @@ __device__ void group_tfc_fit(const float* g_w, float* g_alpha, const float* g_f
         Tout[lane] = T[lane];
 }
 
+// One hypothesis (iteration h of one pair) evaluated by the whole CTA; `lead` marks the CTA that drives the replay when
+// there is nothing to evaluate.
 template <int THREADS, int NPT>
-__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
+__device__ __forceinline__ void cta_se3_hypothesis(const ReplayCtx& R, const float* __restrict__ w_all, int pair, int h, int hyp_begin, int hyp_end,
+    int next_end, bool lead)
 {
     constexpr int NW = THREADS / 32;
-    const int pair = R.slot0 + blockIdx.y, h = hyp_begin + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int match_cap = R.match_cap, capA = ((match_cap + 3) & ~3) + 8, mw = R.mask_words;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -647,12 +649,12 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     __syncthreads();
     if (!s_active) {
         // nothing to evaluate; the first CTA of the launch still drives the replay (pairs without a loop, exhausted iterations)
-        if (blockIdx.x == 0 && warp == 0)
+        if (lead && warp == 0)
             warp_try_replay(R, pair, hyp_end, next_end, scratch, lane);
         return;
     }
     const int M = s_M, words = (M + 31) >> 5;
-    long long* dbg = (blockIdx.x == 0 && blockIdx.y == 0 && hyp_begin == 0 && tid == 0) ? R.dbg : nullptr;
+    long long* dbg = (h == 0 && blockIdx.y == 0 && tid == 0) ? R.dbg : nullptr;
     DBG_STAMP(dbg, 16);
     if (dbg)
         dbg[300] = clock64();
@@ -876,15 +878,39 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     }
 }
 
+// Grid: (CTAs per pair, pairs).  The first chunk of iterations gets one CTA per iteration; later chunks, which exist
+// only for the pairs whose loop has not ended (mean executed iterations on tracking data: 1.1), get a few CTAs that
+// walk the chunk's iterations in order and leave as soon as the pair is finished -- instead of one CTA per
+// iteration launched just to find that out.
 template <int THREADS, int NPT>
-static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end)
+__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
+{
+    __shared__ int s_done;
+    const int pair = R.slot0 + blockIdx.y;
+    for (int h = hyp_begin + blockIdx.x; h < hyp_end || h == hyp_begin + (int)blockIdx.x; h += gridDim.x) {
+        cta_se3_hypothesis<THREADS, NPT>(R, w_all, pair, h, hyp_begin, hyp_end, next_end, blockIdx.x == 0 && h == hyp_begin);
+        if (h + (int)gridDim.x >= hyp_end)
+            break;
+        __syncthreads(); // the replay of warp 0 used the shared scratch
+        if (threadIdx.x == 0)
+            s_done = ld_volatile(&R.replay[pair].done) | (ld_volatile(&R.replay[pair].run) ^ 1);
+        __syncthreads();
+        if (s_done)
+            break;
+    }
+}
+
+template <int THREADS, int NPT>
+static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end, int tail_ctas)
 {
     static size_t configured = 0;
     if (smem > configured) {
         CUDA_TRY(c, cudaFuncSetAttribute(k_se3_hypotheses<THREADS, NPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    const int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
+    int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
+    if (b > 0 && nblk > tail_ctas)
+        nblk = tail_ctas;
     k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, npairs), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end);
     c->launches++;
     return RGBDFE_OK;
@@ -953,6 +979,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     R.slot0 = slot0;
     R.dbg = c->dbg_on ? c->d_dbg : nullptr;
     R.inl_pos_all = c->d_inl_pos;
+    const int tail_ctas = few ? 16 : 8; // CTAs per pair for the chunks after the first
     const int bounds[4] = { 0, b1, b2, iters };
     for (int s = 0; s < 3; s++) {
         const int b = bounds[s] < iters ? bounds[s] : iters;
@@ -964,15 +991,15 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
         int rc;
         if (few || cap > 2304) {
             if (cap <= 1536)
-                rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end);
+                rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
             else if (cap <= 2560)
-                rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end);
+                rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
             else
-                rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end);
+                rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
         } else if (cap <= 1152)
-            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end);
+            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
         else
-            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end);
+            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
         if (rc != RGBDFE_OK)
             return rc;
         if (e >= iters)
