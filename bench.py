@@ -183,9 +183,9 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=96)
-    ap.add_argument("--sequences", type=int, default=24, help="independent tracked sequences in flight on each GPU")
+    ap.add_argument("--sequences", type=int, default=32, help="independent tracked sequences in flight on each GPU")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
-    ap.add_argument("--host-threads", type=int, default=1, help="host threads that enqueue the sequences' work")
+    ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--latency-sms", type=int, default=0,

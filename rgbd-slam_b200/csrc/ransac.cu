@@ -476,7 +476,7 @@ __device__ void warp_try_replay(const ReplayCtx& R, int pair, int chunk_end, int
             return;
         }
         // the loop goes on; once this chunk is used up, draw the next chunk's samples (continuing the pair's stream)
-        const int k1 = min(next_end, max_iters);
+        const int k1 = min(next_end >= 0 ? next_end : st.sampled_k - next_end, max_iters); // next_end < 0: draw -next_end more iterations
         if (st.k >= st.sampled_k && k1 > st.sampled_k) {
             int calls = st.sampled_calls;
             warp_sample_chunk(scratch, reinterpret_cast<int*>(scratch + RNG_HIST + RNG_BLOCK), R.pair_rng + pair, M, (int)prm.sample_size,
@@ -889,11 +889,19 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     const int pair = R.slot0 + blockIdx.y;
     for (int h = hyp_begin + blockIdx.x; h < hyp_end || h == hyp_begin + (int)blockIdx.x; h += gridDim.x) {
         cta_se3_hypothesis<THREADS, NPT>(R, w_all, pair, h, hyp_begin, hyp_end, next_end, blockIdx.x == 0 && h == hyp_begin);
-        if (h + (int)gridDim.x >= hyp_end)
+        const int hn = h + (int)gridDim.x;
+        if (hn >= hyp_end)
             break;
         __syncthreads(); // the replay of warp 0 used the shared scratch
-        if (threadIdx.x == 0)
-            s_done = ld_volatile(&R.replay[pair].done) | (ld_volatile(&R.replay[pair].run) ^ 1);
+        if (threadIdx.x == 0) {
+            // the next iteration of this CTA may not be drawn yet: the replay draws more once everything drawn so far has
+            // been consumed without ending the loop (every drawn iteration is owned by a CTA that publishes it)
+            const ReplayState* rp = R.replay + pair;
+            int d;
+            while (!(d = ld_volatile(&rp->done) | (ld_volatile(&rp->run) ^ 1)) && next_end < 0 && ld_volatile(&rp->sampled_k) <= hn)
+                __nanosleep(200);
+            s_done = d;
+        }
         __syncthreads();
         if (s_done)
             break;
@@ -901,7 +909,7 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
 }
 
 template <int THREADS, int NPT>
-static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end, int tail_ctas)
+static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end, int max_ctas)
 {
     static size_t configured = 0;
     if (smem > configured) {
@@ -909,8 +917,8 @@ static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem
         configured = smem;
     }
     int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
-    if (b > 0 && nblk > tail_ctas)
-        nblk = tail_ctas;
+    if (nblk > max_ctas)
+        nblk = max_ctas;
     k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, npairs), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end);
     c->launches++;
     return RGBDFE_OK;
@@ -979,27 +987,30 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     R.slot0 = slot0;
     R.dbg = c->dbg_on ? c->d_dbg : nullptr;
     R.inl_pos_all = c->d_inl_pos;
-    const int tail_ctas = few ? 16 : 8; // CTAs per pair for the chunks after the first
-    const int bounds[4] = { 0, b1, b2, iters };
+    // Few pairs (tracking chains): ONE launch of b1 CTAs per pair.  CTA k evaluates iterations k, k + b1, ... until the
+    // pair's loop has ended; iterations beyond the first b1 are drawn b1 at a time by the replay when needed.
+    // Many pairs (verification): chunks of 8, 56 and the rest, the later ones on 8 walking CTAs per pair.
+    const int bounds[4] = { 0, few ? iters : b1, few ? iters : b2, iters };
     for (int s = 0; s < 3; s++) {
         const int b = bounds[s] < iters ? bounds[s] : iters;
         const int e = (s == 2 || bounds[s + 1] > iters) ? iters : bounds[s + 1];
-        const int next_end = s == 0 ? (b2 < iters ? b2 : iters) : iters;
+        const int next_end = few ? -b1 : (s == 0 ? (b2 < iters ? b2 : iters) : iters);
+        const int max_ctas = few ? b1 : (s == 0 ? b1 : 8);
         if (s > 0 && e <= b)
             break;
         ProfScope prof(c, KID_SE3_HYP);
         int rc;
         if (few || cap > 2304) {
             if (cap <= 1536)
-                rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
+                rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
             else if (cap <= 2560)
-                rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
+                rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
             else
-                rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
+                rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         } else if (cap <= 1152)
-            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
+            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         else
-            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end, tail_ctas);
+            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         if (rc != RGBDFE_OK)
             return rc;
         if (e >= iters)
