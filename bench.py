@@ -52,15 +52,15 @@ ALG_BYTES = {
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
 # captures summarised in profiles/r1_ncu_full_brief.txt, and the unit that actually limits each kernel there.
 NCU_TRAFFIC_64 = {
-    "k_fast_cells": 62.86e6 + 3.64e6, "k_gauss7": 71.65e6 + 31.23e6, "k_orient_describe": 140.74e6 + 8.98e6,
-    "k_knn2_hamming": 4.20e6, "k_quadtree": 8.16e6 + 0.01e6,
+    "k_fast_cells": 62.85e6 + 2.91e6, "k_gauss7": 72.91e6 + 34.82e6, "k_orient_describe": 139.09e6 + 9.22e6,
+    "k_knn2_hamming": 4.20e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
 NCU_LIMITER = {
-    "k_fast_cells": "ALU pipe 66 % / issue slots 75 % busy (integer compare work, 1 px per thread); DRAM 2 % of peak",
-    "k_gauss7": "L1/shared 74 %, ALU; DRAM 6 % of peak",
-    "k_orient_describe": "XU 52 % / L1 74 %; DRAM 16 % of peak",
-    "k_knn2_hamming": "XU pipe (POPC, 16 lanes/clk/SM) 76-88 % busy: 8 POPC per descriptor pair; DRAM < 1 % of peak",
-    "k_pyramid_level(x levels)": "ALU 75 % / L1 76 %",
+    "k_fast_cells": "issue slots 79 % busy, ALU pipe 57 % (16-bit-lane min/max work): instruction-bound; DRAM traffic = 1.0x algorithmic, 3 % of peak",
+    "k_gauss7": "issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 59 %; DRAM 17 % of peak",
+    "k_orient_describe": "XU 53 % (atan2 / sin / cos), L1 74 %, issue 74 %; DRAM 16 % of peak",
+    "k_knn2_hamming": "tensor pipe (u8 IMMA m16n8k32) 65 % busy while active = 57 % of the 0.5 IMMA/clk/SM measured peak; DRAM < 1 % of peak",
+    "k_quadtree": "latency (shared-memory atomics and scans, one CTA per level and frame): issue 32 %",
 }
 METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
 WORKLOAD = "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])"
@@ -398,7 +398,8 @@ def main():
         pass
     peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
     # dominant HBM-bound kernel of the extraction stage
-    ext = {k: v for k, v in kernels.items() if k in ALG_BYTES and v[1] > 0}
+    # (the pyramid is 8 launches of two kernels per batch and is listed under per_kernel only)
+    ext = {k: v for k, v in kernels.items() if k in ALG_BYTES and v[1] > 0 and not k.startswith("k_pyramid")}
     if not ext:  # --mode chain (diagnostic): no extraction kernel ran
         ext = {k: v for k, v in kernels.items() if v[1] > 0}
     dom = max(ext, key=lambda k: ext[k][0])
@@ -412,6 +413,8 @@ def main():
         "algorithmic_bytes_per_launch": per_launch_bytes,
         "limiter": NCU_LIMITER.get(dom),
         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+        "per_kernel": {k: {"ms": v[0] / v[1], "algorithmic_GBps": ALG_BYTES[k] * B / (v[0] / v[1] * 1e-3) / 1e9} for k, v in kernels.items()
+                       if k in ALG_BYTES and v[1] > 0},
         "share_of_step": {k: round(v[0] / tot_ms, 4) for k, v in kernels.items()},
         "ms_per_launch": {k: (v[0] / v[1] if v[1] else None) for k, v in kernels.items()},
     }
@@ -479,7 +482,8 @@ def main():
                        "sequences_in_flight": S, "single_sequence_frames_per_s": single, "mean_ransac_iterations": float(np.mean(state["iters"])),
                        "batch_frames_per_step": B, "distinct_frames": F, "pipeline": "extraction of batch n+1 (context A) overlaps the match/RANSAC chain of batch n (context B)",
                        "sm_partition": ({"latency_sms": part[0], "throughput_sms": part[1], "how": "CUDA green contexts"} if part else "none (stream priorities)"), "input": "gray u8 + raw 16-bit depth per frame (Frame's convertTo(CV_32F, 1/5000) runs on the device)",
-                       "l2": f"inputs larger than L2: 24 sequences x rotating {F}-frame set ({F * (W * H * 3) / 1e6:.0f} MB) + 58 MB of pyramid per batch",
+                       "host_threads": args.host_threads,
+                       "l2": f"inputs larger than L2: {S} sequences x rotating {F}-frame set ({F * (W * H * 3) / 1e6:.0f} MB) + 58 MB of pyramid per batch",
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
             "e2e": {"value": e2e, "unit": "frames/s",
