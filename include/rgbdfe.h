@@ -202,6 +202,22 @@ int rgbdfe_frames_extract(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int coun
  * OpenCV's float convert-scale — so a frame costs 2 instead of 4 bytes of depth per pixel on the way to the GPU. */
 int rgbdfe_frames_extract_raw(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
     const uint16_t* const* depth16, int depth_stride_elems, float depth_map_factor, float fx, float fy, float cx, float cy);
+/* N1 -- the whole of Frame::Frame's image work (Core/Frame.cpp:31-73) for count frames: cvtColor(BGR2GRAY) when
+ * channels == 3 (OpenCV's 8-bit fixed point; channels == 1 takes a gray image), depth convertTo(CV_32F, factor),
+ * extractFeatures, undistortKeyPoints (cv::undistortPoints(p, K, distCoef, noArray(), K): five iterations in double;
+ * skipped when dist[0] == 0 as at Frame.cpp:256), assignFeaturesToGrid (the 64 x 48 cell of every undistorted
+ * keypoint; bounds from the undistorted image corners, Frame.cpp:283-316) and uprojectCamera (depth at the raw
+ * position, back-projection of the undistorted one). */
+typedef struct rgbdfe_camera {
+    float fx, fy, cx, cy;
+    float dist[5];          /* k1 k2 p1 p2 k3 (RGBDcamera::distCoef) */
+    float depth_map_factor; /* mDepthMapFactor = 1.0f / DepthMapFactor (Core/RGBDcamera.cpp:21) */
+} rgbdfe_camera;
+int rgbdfe_frames_from_images(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, const uint8_t* const* color, int channels, int w, int h,
+    int stride, const uint16_t* const* depth16, int depth_stride_elems, const rgbdfe_camera* cam);
+/* mvKeysUn[i].pt (2 floats per keypoint) and the grid cell x * 48 + y (-1: outside the grid) of a frame; every
+ * extraction entry point fills them (without distortion mvKeysUn == mvKeys).  Pointers may be NULL. */
+int rgbdfe_frame_download_undistorted(rgbdfe_ctx* ctx, rgbdfe_frame* frame, float* pts_un, int* grid_cell, int cap, int* n);
 /* Copy a frame's data back (any pointer may be NULL). */
 int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
     uint8_t* outlier, int cap, int* n);

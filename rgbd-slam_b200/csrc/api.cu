@@ -187,6 +187,8 @@ int alloc_frame(rgbdfe_ctx* c, rgbdfe_frame** out)
     CUDA_TRY(c, dmalloc(&f->xyz, f->cap));
     CUDA_TRY(c, dmalloc(&f->outlier, f->cap));
     CUDA_TRY(c, dmalloc(&f->n, 1));
+    CUDA_TRY(c, dmalloc(&f->pt_un, f->cap));
+    CUDA_TRY(c, dmalloc(&f->cell, f->cap));
     CUDA_TRY(c, cudaMemset(f->n, 0, sizeof(int)));
     CUDA_TRY(c, cudaMemset(f->outlier, 0, f->cap));
     CUDA_TRY(c, cudaMemset(f->xyz, 0, sizeof(rgbdfe_point3f) * f->cap));
@@ -203,6 +205,8 @@ void free_frame(rgbdfe_frame* f)
     cudaFree(f->xyz);
     cudaFree(f->outlier);
     cudaFree(f->n);
+    cudaFree(f->pt_un);
+    cudaFree(f->cell);
     delete f;
 }
 
@@ -545,6 +549,71 @@ bool in_place_pointers(const void* const* img, int count, bool pinned_host_too, 
     return true;
 }
 
+// The colour upload slots are three times the gray ones; they are allocated on first use.
+int ensure_img_slots(rgbdfe_ctx* c, int channels)
+{
+    if (channels <= c->img_channels)
+        return RGBDFE_OK;
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_img);
+    c->d_img = nullptr;
+    CUDA_TRY(c, dmalloc(&c->d_img, (size_t)c->max_batch * c->img_slot * channels + 16));
+    c->img_channels = channels;
+    return RGBDFE_OK;
+}
+
+// cv::undistortPoints(p, K, distCoef, noArray(), K) for one point, in double as OpenCV (undistort.dispatch.cpp); the
+// device runs the same recurrence for the keypoints, the host needs it for the four image corners only.
+void undistort_point(const FramePrep& P, float u, float v, float* ou, float* ov)
+{
+    double x = (u - P.cx) * P.ifx, y = (v - P.cy) * P.ify;
+    const double x0 = x, y0 = y;
+    for (int it = 0; it < 5; it++) {
+        const double r2 = x * x + y * y;
+        const double icdist = 1.0 / (1.0 + ((P.k[4] * r2 + P.k[1]) * r2 + P.k[0]) * r2);
+        if (icdist < 0) {
+            x = x0, y = y0;
+            break;
+        }
+        const double dx = 2.0 * P.k[2] * x * y + P.k[3] * (r2 + 2.0 * x * x);
+        const double dy = P.k[2] * (r2 + 2.0 * y * y) + 2.0 * P.k[3] * x * y;
+        x = (x0 - dx) * icdist;
+        y = (y0 - dy) * icdist;
+    }
+    *ou = (float)(P.fx * x + P.cx);
+    *ov = (float)(P.fy * y + P.cy);
+}
+
+// Frame preprocessing constants: intrinsics, distortion, image bounds (Frame::computeImageBounds, Core/Frame.cpp:283-316)
+// and grid cell sizes (:65-66).
+FramePrep make_frame_prep(int w, int h, float fx, float fy, float cx, float cy, const float* dist, float depth16_factor)
+{
+    FramePrep P;
+    memset(&P, 0, sizeof(P));
+    P.fx = fx, P.fy = fy, P.cx = cx, P.cy = cy;
+    P.ifx = fx != 0.0f ? 1.0 / P.fx : 0.0, P.ify = fy != 0.0f ? 1.0 / P.fy : 0.0;
+    P.cxf = cx, P.cyf = cy;
+    P.invfx = fx != 0.0f ? 1.0f / fx : 0.0f, P.invfy = fy != 0.0f ? 1.0f / fy : 0.0f;
+    P.depth16_factor = depth16_factor;
+    P.undistort = dist && dist[0] != 0.0f;
+    float minX = 0.0f, maxX = (float)w, minY = 0.0f, maxY = (float)h;
+    if (P.undistort) {
+        for (int i = 0; i < 5; i++)
+            P.k[i] = dist[i];
+        float x[4], y[4];
+        undistort_point(P, 0.0f, 0.0f, &x[0], &y[0]);
+        undistort_point(P, (float)w, 0.0f, &x[1], &y[1]);
+        undistort_point(P, 0.0f, (float)h, &x[2], &y[2]);
+        undistort_point(P, (float)w, (float)h, &x[3], &y[3]);
+        minX = std::min(x[0], x[2]), maxX = std::max(x[1], x[3]);
+        minY = std::min(y[0], y[1]), maxY = std::max(y[2], y[3]);
+    }
+    P.minX = minX, P.minY = minY;
+    P.gridWInv = 64.0f / (maxX - minX); // FRAME_GRID_COLS / (mnMaxX - mnMinX)
+    P.gridHInv = 48.0f / (maxY - minY);
+    return P;
+}
+
 // Host images -> the context's upload slots; out[i] = where image i landed.  Images with dense rows that follow
 // each other in the caller's memory (a frame ring buffer, ascending or descending) go up as ONE strided copy per
 // run: a 64-frame batch is otherwise bound by the fixed cost of its 128 separate transfers, not by PCIe.
@@ -575,9 +644,10 @@ int upload_images(rgbdfe_ctx* c, const void* const* img, int count, size_t row_b
 }
 
 // Upload `count` gray (+ optional depth) images and run K1..K6 on them as one batch.
+// channels: 1 (gray) or 3 (BGR, converted on the way into level 0); dist: k1 k2 p1 p2 k3 or nullptr.
 int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* gray, int w, int h, int stride,
     const float* const* depth, int depth_stride, float fx, float fy, float cx, float cy, const uint16_t* const* depth16 = nullptr,
-    float depth16_factor = 0.0f)
+    float depth16_factor = 0.0f, int channels = 1, const float* dist = nullptr)
 {
     if (!c->configured)
         return RGBDFE_E_STATE;
@@ -601,16 +671,21 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
             return RGBDFE_E_ARG;
     // Images in device memory are read in place (all pointers of one call must be of one kind; the first and last
     // are checked); host images are uploaded into the context's slots, except a pinned depth map with "host_zero_copy".
+    if (channels != 1 && channels != 3)
+        return RGBDFE_E_ARG;
+    if ((rc = ensure_img_slots(c, channels)) != RGBDFE_OK)
+        return rc;
     const bool gray_in_place = in_place_pointers((const void* const*)gray, count, false, gp.p);
     const bool depth_in_place = dany && in_place_pointers(dany, count, c->host_zero_copy, dp.p);
     int gstride = stride, dstride = depth_stride;
     for (int i = 0; i < count; i++)
         fb.f[i] = *frames[i];
     if (!gray_in_place) {
-        if ((rc = upload_images(c, (const void* const*)gray, count, (size_t)w, h, (size_t)stride, reinterpret_cast<uint8_t*>(c->d_img), c->img_slot, gp.p))
+        if ((rc = upload_images(c, (const void* const*)gray, count, (size_t)w * channels, h, (size_t)stride, reinterpret_cast<uint8_t*>(c->d_img),
+                 c->img_slot * c->img_channels, gp.p))
             != RGBDFE_OK)
             return rc;
-        gstride = w;
+        gstride = w * channels;
     }
     if (dany && !depth_in_place) {
         if ((rc = upload_images(c, dany, count, (size_t)w * delem, h, (size_t)depth_stride * delem, reinterpret_cast<uint8_t*>(c->d_depth),
@@ -619,7 +694,7 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
             return rc;
         dstride = w;
     }
-    if ((rc = launch_pyramid(c, count, gp, gstride)) != RGBDFE_OK)
+    if ((rc = launch_pyramid(c, count, gp, gstride, channels)) != RGBDFE_OK)
         return rc;
     if ((rc = launch_fast(c, count)) != RGBDFE_OK)
         return rc;
@@ -627,7 +702,8 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
         return rc;
     if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
         return rc;
-    if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, depth16 ? depth16_factor : 0.0f, fx, fy, cx, cy)) != RGBDFE_OK)
+    if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, make_frame_prep(w, h, fx, fy, cx, cy, dist, depth16 ? depth16_factor : 0.0f)))
+        != RGBDFE_OK)
         return rc;
     return RGBDFE_OK;
 }
@@ -753,6 +829,34 @@ int rgbdfe_frames_extract_raw(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int co
     if (!c || !depth16 || !(depth_map_factor > 0.0f))
         return RGBDFE_E_ARG;
     return run_extract(c, frames, count, gray, w, h, stride, nullptr, depth_stride_elems, fx, fy, cx, cy, depth16, depth_map_factor);
+}
+
+int rgbdfe_frames_from_images(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uint8_t* const* color, int channels, int w, int h,
+    int stride, const uint16_t* const* depth16, int depth_stride_elems, const rgbdfe_camera* cam)
+{
+    if (!c || !cam || !depth16 || !(cam->depth_map_factor > 0.0f))
+        return RGBDFE_E_ARG;
+    return run_extract(c, frames, count, color, w, h, stride, nullptr, depth_stride_elems, cam->fx, cam->fy, cam->cx, cam->cy, depth16,
+        cam->depth_map_factor, channels, cam->dist);
+}
+
+int rgbdfe_frame_download_undistorted(rgbdfe_ctx* c, rgbdfe_frame* f, float* pts_un, int* grid_cell, int cap, int* n)
+{
+    if (!c || !f || !n)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int cnt = 0;
+    CUDA_TRY(c, cudaMemcpy(&cnt, f->n, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = cnt;
+    if (cnt < 0)
+        return RGBDFE_E_CAPACITY;
+    const int m = std::min(cnt, cap);
+    if (m > 0 && pts_un)
+        CUDA_TRY(c, cudaMemcpy(pts_un, f->pt_un, (size_t)m * sizeof(float2), cudaMemcpyDeviceToHost));
+    if (m > 0 && grid_cell)
+        CUDA_TRY(c, cudaMemcpy(grid_cell, f->cell, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost));
+    return RGBDFE_OK;
 }
 
 int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz, uint8_t* outlier, int cap,

@@ -78,6 +78,19 @@ struct rgbdfe_frame {
     rgbdfe_point3f* xyz;
     uint8_t* outlier;
     int* n; // device count
+    float2* pt_un; // mvKeysUn[i].pt (Core/Frame.cpp:251-281); equals kps[i].pt without distortion
+    int* cell;     // Frame::posInGrid: x * FRAME_GRID_ROWS + y of the 64 x 48 grid, -1 outside (Core/Frame.cpp:75-89,231-241)
+};
+
+// Frame preprocessing parameters of one batched extraction, by value (N1: Core/Frame.cpp:47-48,251-316).
+struct FramePrep {
+    int undistort;            // distCoef[0] != 0 (Core/Frame.cpp:256)
+    double fx, fy, cx, cy;    // the float intrinsics widened, as cv::undistortPoints sees the CV_32F matrix
+    double ifx, ify;
+    double k[5];              // k1 k2 p1 p2 k3
+    float cxf, cyf, invfx, invfy; // uprojectCamera (float arithmetic)
+    float minX, minY, gridWInv, gridHInv; // computeImageBounds / mfGridElement*Inv
+    float depth16_factor;     // > 0: the depth images are raw 16-bit, z = float(d) * factor
 };
 
 // Frames of one batched call, passed to kernels by value (<= 4 KB of kernel parameters).
@@ -179,6 +192,7 @@ struct rgbdfe_ctx {
     cudaStream_t bulk_stream = nullptr; // RGBDFE_PART_LATENCY: stream on the throughput partition for the chain's kNN (partition.cu)
     cudaEvent_t order_evt = nullptr; // rgbdfe_stream_wait
     cudaEvent_t bulk_evt = nullptr;  // stream <-> bulk_stream ordering
+    int img_channels = 1;            // channels the image upload slots are sized for (3 after the first BGR batch)
     bool host_zero_copy = true;      // a pinned host depth map is read in place by K6 (keypoint sectors only) instead of being uploaded
     std::string err;
     long long launches = 0;
@@ -314,13 +328,12 @@ struct ProfScope {
 
 namespace rgbdfe {
 // orb_image.cu
-int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride);
+int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride, int channels);
 int launch_blur(rgbdfe_ctx* c, int count);
 int launch_fast(rgbdfe_ctx* c, int count);
 // orb_keypoints.cu
 int launch_quadtree(rgbdfe_ctx* c, int count);
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, float depth16_factor,
-    float fx, float fy, float cx, float cy);
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep);
 // match.cu
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);

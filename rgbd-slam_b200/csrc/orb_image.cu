@@ -13,9 +13,13 @@ namespace rgbdfe {
 
 // ------------------------------------------------------------------ K1 ----
 // Level 0: copy + REFLECT_101 ring.  One thread per 4 horizontally adjacent padded pixels (one 32-bit store);
-// interior words are two aligned loads and a funnel shift, ring words go byte by byte.
+// interior words are two aligned loads and a funnel shift, ring words go byte by byte.  channels == 3: the source
+// is the BGR colour image and Frame's cvtColor(BGR2GRAY) (Core/Frame.cpp:47) is applied on the way in -- OpenCV's
+// 8-bit fixed point: (B * 3735 + G * 19235 + R * 9798 + 2^14) >> 15.
+__device__ __forceinline__ unsigned bgr2gray(unsigned b, unsigned g, unsigned r) { return (b * 3735u + g * 19235u + r * 9798u + 16384u) >> 15; }
+
 __global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride, unsigned pyr_off, const __grid_constant__ ImgPtrs img, int img_stride,
-    uint8_t* __restrict__ pyr, size_t pyr_slot)
+    int channels, uint8_t* __restrict__ pyr, size_t pyr_slot)
 {
     const int pw = w + 2 * EDGE_THRESHOLD, ph = h + 2 * EDGE_THRESHOLD;
     const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -24,8 +28,23 @@ __global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride,
         return;
     const int slot = blockIdx.z;
     const uint8_t* src = static_cast<const uint8_t*>(img.p[slot]) + (size_t)reflect101(py - EDGE_THRESHOLD, h) * img_stride;
+    const bool interior = px0 >= EDGE_THRESHOLD && px0 + 3 < EDGE_THRESHOLD + w;
     unsigned packed = 0;
-    if (px0 >= EDGE_THRESHOLD && px0 + 3 < EDGE_THRESHOLD + w) {
+    if (channels == 3) {
+        const uint8_t* q = src + 3 * (px0 - EDGE_THRESHOLD);
+        if (interior && (reinterpret_cast<size_t>(q) & 3) == 0) { // 4 pixels = 3 aligned words
+            const unsigned w0 = reinterpret_cast<const unsigned*>(q)[0], w1 = reinterpret_cast<const unsigned*>(q)[1],
+                           w2 = reinterpret_cast<const unsigned*>(q)[2];
+            packed = bgr2gray(w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u) | bgr2gray(w0 >> 24, w1 & 255u, (w1 >> 8) & 255u) << 8
+                | bgr2gray((w1 >> 16) & 255u, w1 >> 24, w2 & 255u) << 16 | bgr2gray((w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24) << 24;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint8_t* p = src + 3 * reflect101(min(px0 + k, pw - 1) - EDGE_THRESHOLD, w);
+                packed |= bgr2gray(p[0], p[1], p[2]) << (8 * k);
+            }
+        }
+    } else if (interior) {
         const uint8_t* q = src + (px0 - EDGE_THRESHOLD);
         const unsigned mis = (unsigned)(reinterpret_cast<size_t>(q) & 3);
         const unsigned* qa = reinterpret_cast<const unsigned*>(q - mis);
@@ -441,7 +460,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
 }
 
 // ---------------------------------------------------------------- launchers
-int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride)
+int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride, int channels)
 {
     const OrbConfig& cfg = c->cfg;
     ProfScope prof(c, KID_PYRAMID);
@@ -450,7 +469,7 @@ int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_strid
         const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
         if (l == 0) {
             dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
-            k_pyramid_base<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, c->d_pyr, c->pyr_slot);
+            k_pyramid_base<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, channels, c->d_pyr, c->pyr_slot);
         } else {
             const LevelDesc& P = cfg.lv[l - 1];
             PyrLevel V;

@@ -451,7 +451,8 @@ __device__ void sincosf_glibc(float y, float* sn, float* cs)
 
 __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     const uint8_t* __restrict__ blur, size_t blur_slot, const SelKp* __restrict__ sel_all, int sel_slot, const int* __restrict__ sel_count,
-    const FrameBatch frames /* by value: one frame struct per slot */, const __grid_constant__ ImgPtrs depth, int depth_stride, int unproject, float depth16_factor /* > 0: the slots hold raw 16-bit depth */, float fx, float fy, float cx, float cy)
+    const FrameBatch frames /* by value: one frame struct per slot */, const __grid_constant__ ImgPtrs depth, int depth_stride, int unproject,
+    const __grid_constant__ FramePrep prep)
 {
     __shared__ __align__(16) signed char s_pattern[1024];
     reinterpret_cast<int*>(s_pattern)[threadIdx.x] = reinterpret_cast<const int*>(g_pattern)[threadIdx.x]; // 256 threads x 4 B
@@ -536,18 +537,44 @@ __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __rest
         kp.class_id = -1;
         F.kps[gi] = kp;
         F.outlier[gi] = 0;
+        // Frame::undistortKeyPoints: cv::undistortPoints(pts, K, distCoef, noArray(), K) -- 5 fixed-point iterations of the
+        // inverse distortion in double, then back through K, narrowed to float (OpenCV undistort.dispatch.cpp)
+        float ux = px, uy = py;
+        if (prep.undistort) {
+            double x = (px - prep.cx) * prep.ifx, y = (py - prep.cy) * prep.ify; // float coordinates widen exactly
+            const double x0 = x, y0 = y;
+            for (int it = 0; it < 5; it++) {
+                const double r2 = x * x + y * y;
+                const double icdist = 1.0 / (1.0 + ((prep.k[4] * r2 + prep.k[1]) * r2 + prep.k[0]) * r2); // k4..k6 are zero: numerator 1
+                if (icdist < 0) {
+                    x = x0, y = y0;
+                    break;
+                }
+                const double dx = 2.0 * prep.k[2] * x * y + prep.k[3] * (r2 + 2.0 * x * x);
+                const double dy = prep.k[2] * (r2 + 2.0 * y * y) + 2.0 * prep.k[3] * x * y;
+                x = (x0 - dx) * icdist;
+                y = (y0 - dy) * icdist;
+            }
+            ux = (float)(prep.fx * x + prep.cx);
+            uy = (float)(prep.fy * y + prep.cy);
+        }
+        F.pt_un[gi] = make_float2(ux, uy);
+        // Frame::posInGrid on the undistorted position
+        {
+            const int gx = (int)roundf(__fmul_rn(__fsub_rn(ux, prep.minX), prep.gridWInv));
+            const int gy = (int)roundf(__fmul_rn(__fsub_rn(uy, prep.minY), prep.gridHInv));
+            F.cell[gi] = (gx < 0 || gx >= 64 || gy < 0 || gy >= 48) ? -1 : gx * 48 + gy;
+        }
         if (unproject) {
-            // Frame::uprojectCamera without lens distortion (mvKeysUn == mvKeys)
-            // the depth slot holds float metres, or the raw 16-bit image: then cv::Mat::convertTo(CV_32F, factor) happens here
+            // Frame::uprojectCamera: depth at the raw position, back-projection of the undistorted one.  The depth image is
+            // float metres, or the raw 16-bit image: then cv::Mat::convertTo(CV_32F, factor) happens here
             const size_t di = (size_t)(int)py * depth_stride + (int)px;
-            const float z = depth16_factor > 0.0f
-                ? __fmul_rn((float)static_cast<const unsigned short*>(depth.p[slot])[di], depth16_factor)
-                : static_cast<const float*>(depth.p[slot])[di];
+            const float z = prep.depth16_factor > 0.0f ? __fmul_rn((float)static_cast<const unsigned short*>(depth.p[slot])[di], prep.depth16_factor)
+                                                       : static_cast<const float*>(depth.p[slot])[di];
             rgbdfe_point3f P = { 0.f, 0.f, 0.f };
             if (z > 0) {
-                const float invfx = __fdiv_rn(1.0f, fx), invfy = __fdiv_rn(1.0f, fy);
-                P.x = __fmul_rn(__fmul_rn(__fsub_rn(px, cx), z), invfx);
-                P.y = __fmul_rn(__fmul_rn(__fsub_rn(py, cy), z), invfy);
+                P.x = __fmul_rn(__fmul_rn(__fsub_rn(ux, prep.cxf), z), prep.invfx);
+                P.y = __fmul_rn(__fmul_rn(__fsub_rn(uy, prep.cyf), z), prep.invfy);
                 P.z = z;
             }
             F.xyz[gi] = P;
@@ -578,8 +605,7 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
     return RGBDFE_OK;
 }
 
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, float depth16_factor,
-    float fx, float fy, float cx, float cy)
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep)
 {
     if (!g_pattern_uploaded[c->device]) {
         CUDA_TRY(c, cudaMemcpyToSymbolAsync(g_pattern, kBriefPattern, 1024, 0, cudaMemcpyHostToDevice, c->stream));
@@ -588,7 +614,7 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
     const int warps = c->kp_cap + 1; // one extra warp publishes the count
     ProfScope prof(c, KID_DESCRIBE);
     k_orient_describe<<<dim3((warps + 7) / 8, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot, c->d_sel,
-        c->sel_slot, c->d_sel_count, frames, depth, depth_stride, unproject ? 1 : 0, depth16_factor, fx, fy, cx, cy);
+        c->sel_slot, c->d_sel_count, frames, depth, depth_stride, unproject ? 1 : 0, prep);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;

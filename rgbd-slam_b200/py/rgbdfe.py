@@ -78,6 +78,13 @@ class Frame:
         n = n.value
         return kps[:n].copy(), desc[:n].copy(), xyz[:n].copy(), outl[:n].copy()
 
+    def download_undistorted(self):
+        pts = np.zeros((self.ctx.kp_cap, 2), np.float32)
+        cell = np.zeros(self.ctx.kp_cap, np.int32)
+        n = C.c_int()
+        self.ctx._chk(lib().rgbdfe_frame_download_undistorted(self.ctx.h, self.h, _p(pts), _p(cell), self.ctx.kp_cap, C.byref(n)))
+        return pts[: n.value].copy(), cell[: n.value].copy()
+
     def close(self):
         if self.h:
             lib().rgbdfe_frame_destroy(self.ctx.h, self.h)
@@ -95,6 +102,11 @@ def device_partition(device, latency_sms):
     if rc != 0:
         return None
     return a.value, b.value
+
+
+class Camera(C.Structure):
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("dist", C.c_float * 5),
+                ("depth_map_factor", C.c_float)]
 
 
 class Context:
@@ -301,6 +313,18 @@ class Context:
                 C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"]),
             )
         )
+
+    def frames_from_images(self, frames, images, depths16, cam):
+        """N1: images are gray (H, W) or BGR (H, W, 3) uint8; cam: fx fy cx cy dist[5] factor (DepthMapFactor)."""
+        n = len(frames)
+        fr = (C.c_void_p * n)(*[f.h for f in frames])
+        ip = (C.c_void_p * n)(*[g.ctypes.data for g in images])
+        dp = (C.c_void_p * n)(*[d.ctypes.data for d in depths16])
+        h, w = images[0].shape[:2]
+        ch = 1 if images[0].ndim == 2 else images[0].shape[2]
+        cs = Camera(cam["fx"], cam["fy"], cam["cx"], cam["cy"], (C.c_float * 5)(*[float(v) for v in cam.get("dist", [0] * 5)]),
+                    float(np.float32(1.0) / np.float32(cam["factor"])))
+        self._chk(lib().rgbdfe_frames_from_images(self.h, fr, n, ip, ch, w, h, images[0].strides[0], dp, depths16[0].strides[0] // 2, C.byref(cs)))
 
     def track(self, ref, cur, slot, ratio=0.9, discard=True, iters=200, min_inl=10, max_mahal=3.0, sample=4, update_f2=True):
         self._chk(

@@ -1,7 +1,10 @@
 #!/usr/bin/env python
 """Generates the golden vectors under tests/golden/ (run once, in the build container; outputs are committed).
 
-Two files:
+Three files:
+
+  frame_prep_cv2.npz   cv2 4.13 outputs for Frame's preprocessing (row N1): cvtColor(BGR2GRAY) of a colour image and
+                       cv::undistortPoints of 3000 points with the TUM fr1 intrinsics / distortion.
 
   cv2_primitives.npz   outputs of the REAL third-party code the reference calls on this path, produced here with
                        cv2 4.13 (the image's OpenCV), glibc's srand/rand and libstdc++'s std::sort:
@@ -178,7 +181,33 @@ def make_pipeline(path):
     return out
 
 
+TUM_FR1 = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989,
+               dist=[0.262383, -0.953104, -0.005358, 0.002628, 1.163314], factor=5000.0)
+
+
+def make_frame_prep(path):
+    """cv2 outputs for Frame's preprocessing (row N1): cvtColor(BGR2GRAY) and undistortPoints with the TUM fr1 camera."""
+    import cv2
+
+    rng = np.random.default_rng(20241105)
+    bgr = np.stack([smooth_image(rng, 320, 240) for _ in range(3)], 2)
+    out = {"bgr": bgr, "gray": cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY)}
+    c = TUM_FR1
+    K = np.array([[c["fx"], 0, c["cx"]], [0, c["fy"], c["cy"]], [0, 0, 1]], np.float32)
+    D = np.array(c["dist"], np.float32).reshape(5, 1)
+    pts = np.stack([rng.uniform(0, 640, 3000), rng.uniform(0, 480, 3000)], 1).astype(np.float32)
+    pts[:4] = [[0, 0], [640, 0], [0, 480], [640, 480]]           # the corners computeImageBounds undistorts
+    pts[4:1004] = np.rint(pts[4:1004] * 1.2) / np.float32(1.2)   # keypoint-like positions (integer * scale factor)
+    out["pts"] = pts
+    out["pts_un"] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+    out["cam"] = np.array([c["fx"], c["fy"], c["cx"], c["cy"]] + c["dist"] + [c["factor"]], np.float64)
+    np.savez_compressed(path, **out)
+    return out
+
+
 if __name__ == "__main__":
+    make_frame_prep(os.path.join(HERE, "frame_prep_cv2.npz"))
+    print("frame_prep_cv2.npz", os.path.getsize(os.path.join(HERE, "frame_prep_cv2.npz")), "bytes")
     a = make_primitives(os.path.join(HERE, "cv2_primitives.npz"))
     b = make_pipeline(os.path.join(HERE, "pipeline_oracle.npz"))
     for n in ("cv2_primitives.npz", "pipeline_oracle.npz"):
