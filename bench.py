@@ -419,6 +419,61 @@ def main():
         "ms_per_launch": {k: (v[0] / v[1] if v[1] else None) for k, v in kernels.items()},
     }
 
+    # ---- row N1: Frame preprocessing (BGR -> gray, 16-bit depth, undistortion, grid cells) + extraction, end to end ----
+    frame_prep = None
+    try:
+        tum = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989, dist=[0.262383, -0.953104, -0.005358, 0.002628, 1.163314],
+                   factor=DEPTH_FACTOR)
+        nseq = 8
+        bgr_h = torch.from_numpy(np.stack([np.stack([np.roll(f[0], k, 1) for k in (0, 3, 7)], 2) for f in frames[:B]])).pin_memory()
+        pctx = [rgbdfe.Context(local_rank, W, H, NFEAT, B) for _ in range(nseq)]
+        pfr = []
+        for cx_ in pctx:
+            cx_.orb_configure(NFEAT, 1.2, 8, 20, 7)
+            pfr.append([rgbdfe.Frame(cx_) for _ in range(B)])
+        bn, dn = bgr_h.numpy(), depth_h.numpy()
+
+        def pstep():
+            for cx_, fr_ in zip(pctx, pfr):
+                cx_.frames_from_images(fr_, [bn[i] for i in range(B)], [dn[i] for i in range(B)], tum)
+
+        for _ in range(2):
+            pstep()
+        for cx_ in pctx:
+            cx_.sync()
+        t0 = time.perf_counter()
+        psteps = 4
+        for _ in range(psteps):
+            pstep()
+        for cx_ in pctx:
+            cx_.sync()
+        dt = time.perf_counter() - t0
+        frame_prep = {"value": psteps * nseq * B / dt, "unit": "frames/s",
+                      "what": "rgbdfe_frames_from_images: pinned BGR u8 + 16-bit depth -> gray, pyramid, ORB, undistorted keypoints, grid cells, 3D points "
+                              "(TUM fr1 distortion), 8 contexts x 64-frame batches, host clock around enqueue + sync",
+                      "h2d_bytes_per_frame": W * H * 3 + NFEAT * 32}
+        try:
+            import cv2
+
+            K = np.array([[tum["fx"], 0, tum["cx"]], [0, tum["fy"], tum["cy"]], [0, 0, 1]], np.float32)
+            D = np.array(tum["dist"], np.float32)
+            pts = np.random.default_rng(0).uniform(0, 480, (NFEAT, 1, 2)).astype(np.float32)
+            t0 = time.perf_counter()
+            for i in range(20):
+                cv2.cvtColor(bn[i], cv2.COLOR_BGR2GRAY)
+                dn[i].astype(np.float32) * np.float32(1.0 / DEPTH_FACTOR)
+                cv2.undistortPoints(pts, K, D, None, K)
+            frame_prep["cpu_preprocessing_only_frames_per_s"] = 20 / (time.perf_counter() - t0)
+            frame_prep["cpu_note"] = "cv2 cvtColor + depth scale + undistortPoints alone on one host core (no extraction)"
+        except Exception:
+            pass
+        for cx_, fr_ in zip(pctx, pfr):
+            for f in fr_:
+                f.close()
+            cx_.close()
+    except Exception as ex:
+        frame_prep = {"error": str(ex)[:200]}
+
     # ---- sharded loop-pair verification (the part of the path that shards), N >= 1 ----
     verify = None
     try:
@@ -491,7 +546,7 @@ def main():
                     "d2h_bytes_per_step": S * B * 84,
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep,
         }))
     for q in seqs:
         q.close()
