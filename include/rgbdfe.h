@@ -218,6 +218,37 @@ int rgbdfe_frames_from_images(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int 
 /* mvKeysUn[i].pt (2 floats per keypoint) and the grid cell x * 48 + y (-1: outside the grid) of a frame; every
  * extraction entry point fills them (without distortion mvKeysUn == mvKeys).  Pointers may be NULL. */
 int rgbdfe_frame_download_undistorted(rgbdfe_ctx* ctx, rgbdfe_frame* frame, float* pts_un, int* grid_cell, int cap, int* n);
+/* ---- Matcher::projectionMatch (Features/Matcher.cpp:35-104), scope row N2 ---- */
+/* Everything the function reads besides the keypoint arrays: F1's camera (:37-40) and world pose (mRwc, mOw of
+ * Frame::unprojectWorld, Core/Frame.cpp:317-327), F2's pose (getRotation / getTranslation, :42-43), the static image
+ * bounds and grid cell sizes of Frame (mnMinX.., mfGridElementWidthInv/HeightInv, Core/Frame.cpp:63-66,283-316)
+ * and the search radius th (Matcher.h:26, default 5).  Matrices are row-major CV_32F as in the reference. */
+typedef struct rgbdfe_projection {
+    float fx, fy, cx, cy;
+    float Rwc1[9], Ow1[3];
+    float Rcw2[9], tcw2[3];
+    float min_x, max_x, min_y, max_y;
+    float grid_w_inv, grid_h_inv;
+    float th;
+} rgbdfe_projection;
+/* Frame::computeImageBounds + the grid cell sizes for a camera and image size: bounds = {mnMinX, mnMaxX, mnMinY,
+ * mnMaxY}, grid_inv = {mfGridElementWidthInv, mfGridElementHeightInv}.  Host arithmetic only. */
+int rgbdfe_camera_bounds(const rgbdfe_camera* cam, int w, int h, float bounds[4], float grid_inv[2]);
+/* projectionMatch on host arrays (what the Matcher shim binds): q_* = F1 (mDescriptors, mvKeys3Dc, mvbOutlier as
+ * bytes or NULL), t_* = F2 (mDescriptors, mvKeys3Dc, mvKeysUn[i].pt as 2 floats per keypoint; the mGrid cell of each
+ * is recomputed on the device with Frame::posInGrid).  out receives DMatch(i1, bestIdx2, bestDist) in query order,
+ * imgIdx -1 as the cv::DMatch constructor leaves it; *n is the number found (RGBDFE_E_CAPACITY when > cap). */
+int rgbdfe_projection_match(rgbdfe_ctx* ctx, const uint8_t* q_desc, int nq, const rgbdfe_point3f* q_xyz, const uint8_t* q_outlier,
+    const uint8_t* t_desc, int nt, const rgbdfe_point3f* t_xyz, const float* t_pts_un, const rgbdfe_projection* proj, rgbdfe_dmatch* out,
+    int cap, int* n);
+/* The same for npairs (F1, F2) pairs of device-resident frames in one pass (descriptors, 3-D points, outlier flags,
+ * undistorted points and grid cells are the ones the extraction left on the device).  out is [npairs][cap_per_pair],
+ * n is [npairs].  Blocking. */
+int rgbdfe_frames_projection_match(rgbdfe_ctx* ctx, rgbdfe_frame* const* f1, rgbdfe_frame* const* f2, const rgbdfe_projection* proj, int npairs,
+    rgbdfe_dmatch* out, int cap_per_pair, int* n);
+/* Diagnostic: rounds the ordered-claim fixpoint of the last projection call took per pair (1 + the longest chain of
+ * keypoints that lost their first choice to an earlier one). */
+int rgbdfe_projection_rounds(rgbdfe_ctx* ctx, int* rounds, int npairs);
 /* Copy a frame's data back (any pointer may be NULL). */
 int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
     uint8_t* outlier, int cap, int* n);

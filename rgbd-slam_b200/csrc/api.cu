@@ -339,6 +339,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     cudaStreamSynchronize(c->stream);
     free_orb_workspaces(c);
     free_pair_workspaces(c);
+    free_proj_workspace(c);
     free_frame(c->scratch);
     free_frame(c->scratch2);
     if (c->order_evt)
@@ -608,7 +609,7 @@ FramePrep make_frame_prep(int w, int h, float fx, float fy, float cx, float cy, 
         minX = std::min(x[0], x[2]), maxX = std::max(x[1], x[3]);
         minY = std::min(y[0], y[1]), maxY = std::max(y[2], y[3]);
     }
-    P.minX = minX, P.minY = minY;
+    P.minX = minX, P.minY = minY, P.maxX = maxX, P.maxY = maxY;
     P.gridWInv = 64.0f / (maxX - minX); // FRAME_GRID_COLS / (mnMaxX - mnMinX)
     P.gridHInv = 48.0f / (maxY - minY);
     return P;
@@ -795,6 +796,16 @@ int rgbdfe_orb_stage_candidates(rgbdfe_ctx* c, int level, rgbdfe_keypoint* out, 
             out[i].class_id = -1;
         }
     }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_camera_bounds(const rgbdfe_camera* cam, int w, int h, float bounds[4], float grid_inv[2])
+{
+    if (!cam || !bounds || !grid_inv || w <= 0 || h <= 0)
+        return RGBDFE_E_ARG;
+    const FramePrep P = make_frame_prep(w, h, cam->fx, cam->fy, cam->cx, cam->cy, cam->dist, 0.0f);
+    bounds[0] = P.minX, bounds[1] = P.maxX, bounds[2] = P.minY, bounds[3] = P.maxY;
+    grid_inv[0] = P.gridWInv, grid_inv[1] = P.gridHInv;
     return RGBDFE_OK;
 }
 

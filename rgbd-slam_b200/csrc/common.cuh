@@ -90,6 +90,7 @@ struct FramePrep {
     double k[5];              // k1 k2 p1 p2 k3
     float cxf, cyf, invfx, invfy; // uprojectCamera (float arithmetic)
     float minX, minY, gridWInv, gridHInv; // computeImageBounds / mfGridElement*Inv
+    float maxX, maxY;
     float depth16_factor;     // > 0: the depth images are raw 16-bit, z = float(d) * factor
 };
 
@@ -252,6 +253,7 @@ struct rgbdfe_ctx {
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
     int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
+    struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
     int dbg_on = 0;
 
@@ -338,6 +340,8 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);
 int knn_splits_for(const rgbdfe_ctx* c, int npairs);
+// projection.cu
+void free_proj_workspace(rgbdfe_ctx* c);
 // ransac.cu
 // Pairs occupy workspace slots [slot0, slot0 + npairs); results go to d_results[0 .. npairs).  With `ff` the
 // Matcher::match filter (K8) runs inside k_se3_prepare on the kNN partials of the same slots.

@@ -109,6 +109,31 @@ class Camera(C.Structure):
                 ("depth_map_factor", C.c_float)]
 
 
+class Projection(C.Structure):
+    """rgbdfe_projection: what Matcher::projectionMatch reads besides the keypoint arrays."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("Rwc1", C.c_float * 9), ("Ow1", C.c_float * 3),
+                ("Rcw2", C.c_float * 9), ("tcw2", C.c_float * 3), ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float),
+                ("max_y", C.c_float), ("grid_w_inv", C.c_float), ("grid_h_inv", C.c_float), ("th", C.c_float)]
+
+    @classmethod
+    def make(cls, proj, th=5.0):
+        """proj: dict(fx fy cx cy, Rwc1, Ow1, Rcw2, tcw2, bounds=(minX, maxX, minY, maxY), inv=(wInv, hInv))."""
+        f = lambda v, k: (C.c_float * k)(*[float(x) for x in np.asarray(v, np.float32).reshape(-1)])
+        b, i = proj["bounds"], proj["inv"]
+        return cls(proj["fx"], proj["fy"], proj["cx"], proj["cy"], f(proj["Rwc1"], 9), f(proj["Ow1"], 3), f(proj["Rcw2"], 9), f(proj["tcw2"], 3),
+                   float(b[0]), float(b[1]), float(b[2]), float(b[3]), float(i[0]), float(i[1]), float(th))
+
+
+def camera_bounds(cam, w, h):
+    """Frame::computeImageBounds + grid cell sizes -> ((minX, maxX, minY, maxY), (wInv, hInv)) as float32."""
+    c = Camera(cam["fx"], cam["fy"], cam["cx"], cam["cy"], (C.c_float * 5)(*[float(v) for v in cam.get("dist", [0.0] * 5)]), 1.0)
+    b, g = (C.c_float * 4)(), (C.c_float * 2)()
+    rc = lib().rgbdfe_camera_bounds(C.byref(c), w, h, b, g)
+    if rc != 0:
+        raise RgbdfeError(f"rgbdfe_camera_bounds: {rc}")
+    return tuple(np.float32(v) for v in b), tuple(np.float32(v) for v in g)
+
+
 class Context:
     def __init__(self, device=0, max_w=640, max_h=480, max_feats=1000, max_batch=1):
         self.h = C.c_void_p()
@@ -219,6 +244,37 @@ class Context:
             )
         )
         return out[: n.value].copy()
+
+    def projection_match(self, q_desc, q_xyz, q_outlier, t_desc, t_xyz, t_pts_un, proj, th=5.0):
+        """Matcher::projectionMatch on host arrays (Features/Matcher.cpp:35-104)."""
+        q_desc = np.ascontiguousarray(q_desc, np.uint8)
+        t_desc = np.ascontiguousarray(t_desc, np.uint8)
+        q_xyz = np.ascontiguousarray(q_xyz, np.float32)
+        t_xyz = np.ascontiguousarray(t_xyz, np.float32)
+        t_pts_un = np.ascontiguousarray(t_pts_un, np.float32)
+        if q_outlier is not None:
+            q_outlier = np.ascontiguousarray(q_outlier, np.uint8)
+        P = proj if isinstance(proj, Projection) else Projection.make(proj, th)
+        out = np.zeros(max(len(q_desc), 1), DM_DTYPE)
+        n = C.c_int()
+        self._chk(lib().rgbdfe_projection_match(self.h, _p(q_desc), len(q_desc), _p(q_xyz), _p(q_outlier), _p(t_desc), len(t_desc), _p(t_xyz),
+                                                _p(t_pts_un), C.byref(P), _p(out), len(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def frames_projection_match(self, f1, f2, projs):
+        """projectionMatch for device-resident frame pairs; projs: one Projection (or dict) per pair.  Returns a list of match arrays."""
+        npairs = len(f1)
+        P = (Projection * npairs)(*[p if isinstance(p, Projection) else Projection.make(p, p.get("th", 5.0)) for p in projs])
+        out = np.zeros((npairs, self.kp_cap), DM_DTYPE)
+        n = np.zeros(npairs, np.int32)
+        self._chk(lib().rgbdfe_frames_projection_match(self.h, (C.c_void_p * npairs)(*[f.h for f in f1]), (C.c_void_p * npairs)(*[f.h for f in f2]),
+                                                       P, npairs, _p(out), self.kp_cap, _p(n)))
+        return [out[i, : n[i]].copy() for i in range(npairs)]
+
+    def projection_rounds(self, npairs=1):
+        r = np.zeros(npairs, np.int32)
+        self._chk(lib().rgbdfe_projection_rounds(self.h, _p(r), npairs))
+        return r
 
     # ---- Random ----
     def rng_seed(self, seed):

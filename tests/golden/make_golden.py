@@ -205,7 +205,33 @@ def make_frame_prep(path):
     return out
 
 
+def make_projection(path):
+    """cv2 outputs for the primitives of Matcher::projectionMatch (row N2): the 3x3 * 3x1 + 3x1 cv::Mat expression
+    (cv::gemm) of Frame::unprojectWorld / Matcher.cpp:52 and the Hamming norm of descriptorDistance."""
+    import cv2
+
+    rng = np.random.default_rng(20241106)
+    n = 4000
+    A = rng.normal(0, 1, (n, 3, 3)).astype(np.float32)
+    A[: n // 2] = np.stack([cv2.Rodrigues(rng.normal(0, 0.4, 3))[0] for _ in range(n // 2)]).astype(np.float32)  # rotations
+    b = (rng.normal(0, 2, (n, 3)) * rng.choice([1e-3, 1, 50], (n, 1))).astype(np.float32)
+    c = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    g = np.stack([cv2.gemm(A[i], b[i].reshape(3, 1), 1.0, c[i].reshape(3, 1), 1.0).reshape(3) for i in range(n)])
+    da = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    db = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    db[:100] = da[:100] ^ (rng.random((100, 32)) < 0.1).astype(np.uint8)
+    ham = np.array([cv2.norm(da[i], db[i], cv2.NORM_HAMMING) for i in range(len(da))], np.float64)
+    out = {"A": A, "b": b, "c": c, "gemm": g.astype(np.float32), "desc_a": da, "desc_b": db, "hamming": ham}
+    np.savez_compressed(path, **out)
+    return out
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "projection":  # the other fixtures stay as committed
+        make_projection(os.path.join(HERE, "projection_cv2.npz"))
+        print("projection_cv2.npz", os.path.getsize(os.path.join(HERE, "projection_cv2.npz")), "bytes")
+        sys.exit(0)
+    make_projection(os.path.join(HERE, "projection_cv2.npz"))
     make_frame_prep(os.path.join(HERE, "frame_prep_cv2.npz"))
     print("frame_prep_cv2.npz", os.path.getsize(os.path.join(HERE, "frame_prep_cv2.npz")), "bytes")
     a = make_primitives(os.path.join(HERE, "cv2_primitives.npz"))
