@@ -149,6 +149,56 @@ def cpu_track(frames, cam, idx, threads=1):
     return sum(done) / dt, dt
 
 
+def projection_leg(rgbdfe, ctx, fr, cam, B, no_cpu):
+    """Row N2: Matcher::projectionMatch for the B-1 consecutive pairs of a device-resident batch, poses from the
+    device's own RansacSE3 (identity pose for the first frame of each pair).  Host clock around the blocking call:
+    four launches for all pairs, one count read-back in the middle, the matches copied to the host."""
+    ctx.rng_seed(42)
+    ctx.track_sequence(fr, 0)
+    res = ctx.track_results(0, B - 1)
+    bounds, inv = rgbdfe.camera_bounds(cam, W, H)
+    eye = np.eye(3, dtype=np.float32)
+    projs = []
+    for i in range(B - 1):
+        T = res[i]["T21"].reshape(4, 4).astype(np.float32)
+        projs.append(rgbdfe.Projection.make(dict(fx=cam["fx"], fy=cam["fy"], cx=cam["cx"], cy=cam["cy"], Rwc1=eye, Ow1=np.zeros(3, np.float32),
+                                                 Rcw2=T[:3, :3], tcw2=T[:3, 3], bounds=bounds, inv=inv), 5.0))
+    f1, f2 = fr[:-1], fr[1:]
+    got = None
+    for _ in range(3):
+        got = ctx.frames_projection_match(f1, f2, projs)
+    reps = 20
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ctx.frames_projection_match(f1, f2, projs)
+    dt = (time.perf_counter() - t0) / reps
+    nm = [len(g) for g in got]
+    out = {"value": (B - 1) / dt, "unit": "pairs/s", "ms_per_call": dt * 1e3, "pairs_per_call": B - 1,
+           "matches_per_pair": float(np.mean(nm)), "claim_rounds_max": int(ctx.projection_rounds(B - 1).max()),
+           "what": "rgbdfe_frames_projection_match, th = 5, device-resident frames (TUM fr1 distortion), matches copied to the host"}
+    # one pair through the host-array entry point (what the Matcher shim calls)
+    k0, d0, p0, o0 = fr[0].download()
+    k1, d1, p1, _ = fr[1].download()
+    un1, _ = fr[1].download_undistorted()
+    t0 = time.perf_counter()
+    for _ in range(20):
+        ctx.projection_match(d0, p0, o0, d1, p1, un1, projs[0])
+    out["host_arrays_ms_per_pair"] = (time.perf_counter() - t0) / 20 * 1e3
+    if not no_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import projection as pj
+
+        T = res[0]["T21"].reshape(4, 4).astype(np.float32)
+        pd = dict(fx=cam["fx"], fy=cam["fy"], cx=cam["cx"], cy=cam["cy"], Rwc1=eye, Ow1=np.zeros(3, np.float32), Rcw2=T[:3, :3], tcw2=T[:3, 3],
+                  bounds=bounds, inv=inv)
+        t0 = time.perf_counter()
+        ref = pj.projection_match(dict(desc=d0, xyz=p0, outlier=o0.astype(bool)), dict(desc=d1, xyz=p1, pts_un=un1), pd, 5.0)
+        out["cpu_oracle_pairs_per_s"] = 1.0 / (time.perf_counter() - t0)
+        out["cpu_note"] = "numpy restatement (oracle/projection.py) on one host core, one pair; the reference never calls this function"
+        out["parity_first_pair"] = [(int(a["queryIdx"]), int(a["trainIdx"]), float(a["distance"])) for a in got[0]] == ref
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -420,7 +470,7 @@ def main():
     }
 
     # ---- row N1: Frame preprocessing (BGR -> gray, 16-bit depth, undistortion, grid cells) + extraction, end to end ----
-    frame_prep = None
+    frame_prep = projection = None
     try:
         tum = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989, dist=[0.262383, -0.953104, -0.005358, 0.002628, 1.163314],
                    factor=DEPTH_FACTOR)
@@ -467,6 +517,11 @@ def main():
             frame_prep["cpu_note"] = "cv2 cvtColor + depth scale + undistortPoints alone on one host core (no extraction)"
         except Exception:
             pass
+        # ---- row N2: Matcher::projectionMatch on the frames one of those contexts just produced ----
+        try:
+            projection = projection_leg(rgbdfe, pctx[0], pfr[0], tum, B, args.no_cpu)
+        except Exception as ex:
+            projection = {"error": str(ex)[:200]}
         for cx_, fr_ in zip(pctx, pfr):
             for f in fr_:
                 f.close()
@@ -546,7 +601,7 @@ def main():
                     "d2h_bytes_per_step": S * B * 84,
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep, "projection_match": projection,
         }))
     for q in seqs:
         q.close()

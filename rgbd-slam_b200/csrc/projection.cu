@@ -4,11 +4,13 @@
 // around the projection (Frame::getFeaturesInArea, Core/Frame.cpp:179-229), keeps the closest descriptor among
 // those no earlier keypoint has taken, and takes it when the distance is <= TH_HIGH.
 //
-// Device form, three launches for any number of pairs:
+// Device form, five launches for any number of pairs:
+//   k_proj_grid               one CTA per pair: F2's mGrid as a CSR table (cell -> keypoint indices with a valid
+//                             depth), counting sort in shared memory; the order inside a cell is free, see below
 //   k_proj_candidates<false>  one warp per F1 keypoint: projection (float, no FMA, the order cv::gemm's 3x3 path
-//                             uses), then all of F2's keypoints against the cell range + window + valid depth +
-//                             Hamming <= TH_HIGH tests; counts the survivors
-//   k_proj_offsets            exclusive scan of the counts
+//                             uses), then the keypoints of the cell range -- one contiguous CSR run per grid
+//                             column -- against the window and Hamming <= TH_HIGH tests; counts the survivors
+//   k_proj_offsets            exclusive scan of each pair's counts; the host reads the totals and sizes the key store
 //   k_proj_candidates<true>   the same walk, survivors stored as sortable keys  dist << 32 | cell << 16 | index
 //                             (the reference meets candidates cell by cell, x outer, y inner, in keypoint order
 //                             inside a cell, and keeps the first of equal distances: that is the smallest key)
@@ -25,6 +27,7 @@
 #define PROJ_WARPS 8
 #define GRID_ROWS 48 // FRAME_GRID_ROWS, Core/Frame.h:16
 #define GRID_COLS 64
+#define GRID_CELLS (GRID_COLS * GRID_ROWS)
 
 struct ProjPair {
     const uint8_t* q_desc;
@@ -42,10 +45,13 @@ struct ProjPair {
 struct ProjWorkspace {
     int pair_cap = 0;
     ProjPair* d_pairs = nullptr;
+    int* d_gstart = nullptr;             // [pairs][GRID_CELLS + 1] CSR of F2's grid
+    int* d_gitems = nullptr;             // [pairs][kp_cap]
     int* d_cnt = nullptr;                // [pairs][kp_cap]
-    unsigned* d_off = nullptr;           // [pairs * kp_cap + 1]
-    unsigned long long* d_keys = nullptr;
-    size_t key_cap = 0;
+    unsigned* d_off = nullptr;           // [pairs][kp_cap + 1], the pair's total last
+    unsigned long long* d_keys = nullptr; // [pairs][key_stride]
+    size_t key_stride = 0, key_cap = 0;
+    unsigned* h_tot = nullptr;           // pinned [pairs]
     rgbdfe_dmatch* d_out = nullptr;      // [pairs][kp_cap]
     int* d_n = nullptr;                  // [pairs]
     int* d_rounds = nullptr;             // [pairs] fixpoint rounds of the last call (diagnostic)
@@ -59,7 +65,9 @@ void rgbdfe::free_proj_workspace(rgbdfe_ctx* c)
     if (!w)
         return;
     cudaFree(w->d_pairs), cudaFree(w->d_cnt), cudaFree(w->d_off), cudaFree(w->d_keys), cudaFree(w->d_out), cudaFree(w->d_n);
-    cudaFree(w->d_rounds), cudaFree(w->d_pt), cudaFree(w->d_cell);
+    cudaFree(w->d_rounds), cudaFree(w->d_pt), cudaFree(w->d_cell), cudaFree(w->d_gstart), cudaFree(w->d_gitems);
+    if (w->h_tot)
+        cudaFreeHost(w->h_tot);
     delete w;
     c->proj = nullptr;
 }
@@ -93,9 +101,71 @@ __global__ void k_proj_cells(const float2* __restrict__ pt, int n, float minX, f
     cell[i] = (gx < 0 || gx >= GRID_COLS || gy < 0 || gy >= GRID_ROWS) ? -1 : gx * GRID_ROWS + gy;
 }
 
+// Exclusive prefix of v over the 1024 threads of the CTA; *total receives the sum.
+__device__ __forceinline__ int block_scan_1024(int v, int* s_warp, int* total)
+{
+    int inc = v;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, inc, d);
+        if ((threadIdx.x & 31) >= d)
+            inc += o;
+    }
+    if ((threadIdx.x & 31) == 31)
+        s_warp[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int w = s_warp[threadIdx.x];
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, w, d);
+            if (threadIdx.x >= d)
+                w += o;
+        }
+        s_warp[threadIdx.x] = w;
+    }
+    __syncthreads();
+    *total = s_warp[31];
+    return inc - v + ((threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0);
+}
+
+// Frame::assignFeaturesToGrid (Core/Frame.cpp:75-89) of F2 as a CSR table.  Keypoints without a valid depth are left
+// out (Matcher.cpp:80 skips them); the order inside a cell does not matter because the candidate key carries it.
+__global__ void __launch_bounds__(1024) k_proj_grid(const ProjPair* __restrict__ pairs, int kp_cap, int* __restrict__ gstart, int* __restrict__ gitems)
+{
+    __shared__ int s_cnt[GRID_CELLS];
+    __shared__ int s_warp[32];
+    const ProjPair& pp = pairs[blockIdx.x];
+    const int nt = min(*pp.nt, kp_cap);
+    int* start = gstart + (size_t)blockIdx.x * (GRID_CELLS + 1);
+    int* items = gitems + (size_t)blockIdx.x * kp_cap;
+    for (int i = threadIdx.x; i < GRID_CELLS; i += 1024)
+        s_cnt[i] = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < nt; t += 1024) {
+        const int cell = pp.t_cell[t];
+        if (cell >= 0 && pp.t_xyz[t].z > 0.0f)
+            atomicAdd(&s_cnt[cell], 1);
+    }
+    __syncthreads();
+    const int c3 = threadIdx.x * 3; // GRID_CELLS == 3 * 1024
+    const int a = s_cnt[c3], b = s_cnt[c3 + 1], d = s_cnt[c3 + 2];
+    int total;
+    const int ex = block_scan_1024(a + b + d, s_warp, &total);
+    start[c3] = ex, start[c3 + 1] = ex + a, start[c3 + 2] = ex + a + b;
+    s_cnt[c3] = ex, s_cnt[c3 + 1] = ex + a, s_cnt[c3 + 2] = ex + a + b; // now the fill cursors
+    if (threadIdx.x == 0)
+        start[GRID_CELLS] = total;
+    __syncthreads();
+    for (int t = threadIdx.x; t < nt; t += 1024) {
+        const int cell = pp.t_cell[t];
+        if (cell >= 0 && pp.t_xyz[t].z > 0.0f)
+            items[atomicAdd(&s_cnt[cell], 1)] = t;
+    }
+}
+
 template <bool FILL>
-__global__ void __launch_bounds__(PROJ_WARPS * 32) k_proj_candidates(const ProjPair* __restrict__ pairs, int kp_cap, int* __restrict__ cnt,
-    const unsigned* __restrict__ off, unsigned long long* __restrict__ keys)
+__global__ void __launch_bounds__(PROJ_WARPS * 32) k_proj_candidates(const ProjPair* __restrict__ pairs, int kp_cap,
+    const int* __restrict__ gstart, const int* __restrict__ gitems, int* __restrict__ cnt, const unsigned* __restrict__ off,
+    unsigned long long* __restrict__ keys, size_t key_stride)
 {
     const int pair = blockIdx.y;
     const int lane = threadIdx.x & 31;
@@ -136,76 +206,63 @@ __global__ void __launch_bounds__(PROJ_WARPS * 32) k_proj_candidates(const ProjP
     if (live) {
         const uint4* qd = reinterpret_cast<const uint4*>(pp.q_desc + (size_t)q * 32);
         const uint4 qa = __ldg(qd), qb = __ldg(qd + 1);
-        unsigned long long* dst = FILL ? keys + off[(size_t)pair * kp_cap + q] : nullptr;
-        for (int t0 = 0; t0 < nt; t0 += 32) {
-            const int t = t0 + lane;
-            bool hit = false;
-            unsigned long long key = 0;
-            if (t < nt) {
-                const int cell = __ldg(pp.t_cell + t);
-                const int gx = cell / GRID_ROWS, gy = cell - gx * GRID_ROWS;
-                if (cell >= 0 && gx >= c0 && gx <= c1 && gy >= r0 && gy <= r1) {
+        unsigned long long* dst = FILL ? keys + (size_t)pair * key_stride + off[(size_t)pair * (kp_cap + 1) + q] : nullptr;
+        const int* start = gstart + (size_t)pair * (GRID_CELLS + 1);
+        const int* items = gitems + (size_t)pair * kp_cap;
+        for (int gx = c0; gx <= c1; gx++) {
+            // cells (gx, r0 .. r1) follow each other in the table: one run of keypoints per grid column
+            const int kb = __ldg(start + gx * GRID_ROWS + r0), ke = __ldg(start + gx * GRID_ROWS + r1 + 1);
+            for (int k0 = kb; k0 < ke; k0 += 32) {
+                const int k = k0 + lane;
+                bool hit = false;
+                unsigned long long key = 0;
+                if (k < ke) {
+                    const int t = __ldg(items + k);
                     const float2 pt = __ldg(pp.t_pt + t);
-                    if (fabsf(pt.x - u) < r && fabsf(pt.y - v) < r && pp.t_xyz[t].z > 0.0f) { // :221-224, Matcher.cpp:80
+                    if (fabsf(pt.x - u) < r && fabsf(pt.y - v) < r) { // Core/Frame.cpp:221-224
                         const uint4* td = reinterpret_cast<const uint4*>(pp.t_desc + (size_t)t * 32);
                         const uint4 ta = __ldg(td), tb = __ldg(td + 1);
                         const int d = __popc(qa.x ^ ta.x) + __popc(qa.y ^ ta.y) + __popc(qa.z ^ ta.z) + __popc(qa.w ^ ta.w) + __popc(qb.x ^ tb.x)
                             + __popc(qb.y ^ tb.y) + __popc(qb.z ^ tb.z) + __popc(qb.w ^ tb.w);
                         hit = d <= PROJ_TH_HIGH;
-                        key = ((unsigned long long)d << 32) | ((unsigned)cell << 16) | (unsigned)t;
+                        key = ((unsigned long long)d << 32) | ((unsigned)__ldg(pp.t_cell + t) << 16) | (unsigned)t;
                     }
                 }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (FILL && hit)
+                    dst[total + __popc(m & ((1u << lane) - 1u))] = key;
+                total += __popc(m);
             }
-            const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (FILL && hit)
-                dst[total + __popc(m & ((1u << lane) - 1u))] = key;
-            total += __popc(m);
         }
     }
     if (!FILL && lane == 0)
         cnt[(size_t)pair * kp_cap + q] = total;
 }
 
-// Exclusive scan of m counts into off[0..m] (one CTA).
-__global__ void __launch_bounds__(1024) k_proj_offsets(const int* __restrict__ cnt, int m, unsigned* __restrict__ off)
+// Exclusive scan of a pair's candidate counts: off[pair][0 .. kp_cap], the pair's total in off[pair][kp_cap].
+__global__ void __launch_bounds__(1024) k_proj_offsets(const int* __restrict__ cnt, int kp_cap, unsigned* __restrict__ off)
 {
-    __shared__ unsigned s_warp[32];
-    const int per = (m + 1023) / 1024;
-    const int b = threadIdx.x * per, e = min(m, b + per);
-    unsigned sum = 0;
+    __shared__ int s_warp[32];
+    const int* c = cnt + (size_t)blockIdx.x * kp_cap;
+    unsigned* o = off + (size_t)blockIdx.x * (kp_cap + 1);
+    const int per = (kp_cap + 1023) / 1024;
+    const int b = threadIdx.x * per, e = min(kp_cap, b + per);
+    int sum = 0;
     for (int i = b; i < e; i++)
-        sum += (unsigned)cnt[i];
-    unsigned inc = sum;
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned o = __shfl_up_sync(0xffffffffu, inc, d);
-        if ((threadIdx.x & 31) >= d)
-            inc += o;
-    }
-    if ((threadIdx.x & 31) == 31)
-        s_warp[threadIdx.x >> 5] = inc;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        unsigned w = s_warp[threadIdx.x];
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned o = __shfl_up_sync(0xffffffffu, w, d);
-            if (threadIdx.x >= d)
-                w += o;
-        }
-        s_warp[threadIdx.x] = w;
-    }
-    __syncthreads();
-    unsigned run = inc - sum + ((threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0u);
+        sum += c[i];
+    int total;
+    int run = block_scan_1024(sum, s_warp, &total);
     for (int i = b; i < e; i++) {
-        off[i] = run;
-        run += (unsigned)cnt[i];
+        o[i] = (unsigned)run;
+        run += c[i];
     }
-    if (threadIdx.x == 1023)
-        off[m] = s_warp[31];
+    if (threadIdx.x == 0)
+        o[kp_cap] = (unsigned)total;
 }
 
 // The serial claim of Matcher.cpp:45-101 for one pair per CTA.  choice[i] packs dist << 16 | train index, -1: none.
 __global__ void __launch_bounds__(1024) k_proj_resolve(const ProjPair* __restrict__ pairs, int kp_cap, const unsigned* __restrict__ off,
-    const unsigned long long* __restrict__ keys, rgbdfe_dmatch* __restrict__ out, int* __restrict__ n_out, int* __restrict__ rounds_out)
+    const unsigned long long* __restrict__ keys_all, size_t key_stride, rgbdfe_dmatch* __restrict__ out, int* __restrict__ n_out, int* __restrict__ rounds_out)
 {
     extern __shared__ int s_mem[];
     int* owner = s_mem;            // [kp_cap] smallest query index currently holding a train keypoint
@@ -215,7 +272,8 @@ __global__ void __launch_bounds__(1024) k_proj_resolve(const ProjPair* __restric
     const int pair = blockIdx.x;
     const ProjPair& pp = pairs[pair];
     const int nq = min(*pp.nq, kp_cap), nt = min(*pp.nt, kp_cap);
-    const unsigned* o = off + (size_t)pair * kp_cap;
+    const unsigned* o = off + (size_t)pair * (kp_cap + 1);
+    const unsigned long long* keys = keys_all + (size_t)pair * key_stride;
     for (int i = threadIdx.x; i < nq; i += blockDim.x)
         choice[i] = -1;
     int rounds = 0;
@@ -296,12 +354,20 @@ static int ensure_proj(rgbdfe_ctx* c, int npairs)
     if (npairs <= w->pair_cap)
         return RGBDFE_OK;
     cudaFree(w->d_pairs), cudaFree(w->d_cnt), cudaFree(w->d_off), cudaFree(w->d_out), cudaFree(w->d_n), cudaFree(w->d_rounds);
+    cudaFree(w->d_gstart), cudaFree(w->d_gitems);
     w->d_pairs = nullptr, w->d_cnt = nullptr, w->d_off = nullptr, w->d_out = nullptr, w->d_n = nullptr, w->d_rounds = nullptr;
+    w->d_gstart = nullptr, w->d_gitems = nullptr;
     w->pair_cap = 0;
     const size_t m = (size_t)npairs * c->kp_cap;
     CUDA_TRY(c, cudaMalloc((void**)&w->d_pairs, sizeof(ProjPair) * npairs));
+    CUDA_TRY(c, cudaMalloc((void**)&w->d_gstart, sizeof(int) * (size_t)npairs * (GRID_CELLS + 1)));
+    CUDA_TRY(c, cudaMalloc((void**)&w->d_gitems, sizeof(int) * m));
     CUDA_TRY(c, cudaMalloc((void**)&w->d_cnt, sizeof(int) * m));
-    CUDA_TRY(c, cudaMalloc((void**)&w->d_off, sizeof(unsigned) * (m + 1)));
+    CUDA_TRY(c, cudaMalloc((void**)&w->d_off, sizeof(unsigned) * (m + npairs)));
+    if (w->h_tot)
+        cudaFreeHost(w->h_tot);
+    w->h_tot = nullptr;
+    CUDA_TRY(c, cudaMallocHost((void**)&w->h_tot, sizeof(unsigned) * npairs));
     CUDA_TRY(c, cudaMalloc((void**)&w->d_out, sizeof(rgbdfe_dmatch) * m));
     CUDA_TRY(c, cudaMalloc((void**)&w->d_n, sizeof(int) * npairs));
     CUDA_TRY(c, cudaMalloc((void**)&w->d_rounds, sizeof(int) * npairs));
@@ -327,38 +393,45 @@ static int run_projection(rgbdfe_ctx* c, const std::vector<ProjPair>& h_pairs, r
     ProjWorkspace* w = c->proj;
     cudaStream_t s = c->stream;
     const int cap = c->kp_cap;
-    const int m = npairs * cap;
     CUDA_TRY(c, cudaMemcpyAsync(w->d_pairs, h_pairs.data(), sizeof(ProjPair) * npairs, cudaMemcpyHostToDevice, s));
     const dim3 grid((cap + PROJ_WARPS - 1) / PROJ_WARPS, npairs);
-    k_proj_candidates<false><<<grid, PROJ_WARPS * 32, 0, s>>>(w->d_pairs, cap, w->d_cnt, nullptr, nullptr);
-    k_proj_offsets<<<1, 1024, 0, s>>>(w->d_cnt, m, w->d_off);
-    unsigned total = 0;
-    CUDA_TRY(c, cudaMemcpyAsync(&total, w->d_off + m, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+    k_proj_grid<<<npairs, 1024, 0, s>>>(w->d_pairs, cap, w->d_gstart, w->d_gitems);
+    k_proj_candidates<false><<<grid, PROJ_WARPS * 32, 0, s>>>(w->d_pairs, cap, w->d_gstart, w->d_gitems, w->d_cnt, nullptr, nullptr, 0);
+    k_proj_offsets<<<npairs, 1024, 0, s>>>(w->d_cnt, cap, w->d_off);
+    CUDA_TRY(c, cudaMemcpy2DAsync(w->h_tot, sizeof(unsigned), w->d_off + cap, sizeof(unsigned) * (cap + 1), sizeof(unsigned), npairs,
+        cudaMemcpyDeviceToHost, s));
     CUDA_TRY(c, cudaStreamSynchronize(s));
-    if ((size_t)total > w->key_cap) { // candidate storage follows the data: th = 5 needs a few keys per keypoint
-        cudaFree(w->d_keys);
-        w->d_keys = nullptr, w->key_cap = 0;
-        const size_t want = std::max<size_t>((size_t)total + total / 2, (size_t)16 * cap);
-        CUDA_TRY(c, cudaMalloc((void**)&w->d_keys, sizeof(unsigned long long) * want));
-        w->key_cap = want;
+    size_t most = 0;
+    for (int p = 0; p < npairs; p++)
+        most = std::max<size_t>(most, w->h_tot[p]);
+    if (most > w->key_stride || (size_t)npairs * w->key_stride > w->key_cap) { // candidate storage follows the data: th = 5 needs a key or two per keypoint
+        const size_t stride = std::max<size_t>(std::max(most + most / 2, w->key_stride), (size_t)4 * cap);
+        if ((size_t)npairs * stride > w->key_cap) {
+            cudaFree(w->d_keys);
+            w->d_keys = nullptr, w->key_cap = 0;
+            CUDA_TRY(c, cudaMalloc((void**)&w->d_keys, sizeof(unsigned long long) * npairs * stride));
+            w->key_cap = (size_t)npairs * stride;
+        }
+        w->key_stride = stride;
     }
-    k_proj_candidates<true><<<grid, PROJ_WARPS * 32, 0, s>>>(w->d_pairs, cap, nullptr, w->d_off, w->d_keys);
+    k_proj_candidates<true><<<grid, PROJ_WARPS * 32, 0, s>>>(w->d_pairs, cap, w->d_gstart, w->d_gitems, nullptr, w->d_off, w->d_keys, w->key_stride);
     const size_t smem = sizeof(int) * 3 * (size_t)cap;
     if (smem > 48 * 1024)
         CUDA_TRY(c, cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_proj_resolve<<<npairs, 1024, smem, s>>>(w->d_pairs, cap, w->d_off, w->d_keys, w->d_out, w->d_n, w->d_rounds);
-    c->launches += 4;
+    k_proj_resolve<<<npairs, 1024, smem, s>>>(w->d_pairs, cap, w->d_off, w->d_keys, w->key_stride, w->d_out, w->d_n, w->d_rounds);
+    c->launches += 5;
     CUDA_TRY(c, cudaGetLastError());
     CUDA_TRY(c, cudaMemcpyAsync(n, w->d_n, sizeof(int) * npairs, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(c, cudaStreamSynchronize(s));
     bool over = false;
+    int widest = 0;
     for (int p = 0; p < npairs; p++) {
-        const int k = std::min(n[p], cap_per_pair);
+        widest = std::max(widest, std::min(n[p], cap_per_pair));
         over |= n[p] > cap_per_pair;
-        if (k > 0 && out)
-            CUDA_TRY(c, cudaMemcpyAsync(out + (size_t)p * cap_per_pair, w->d_out + (size_t)p * cap, sizeof(rgbdfe_dmatch) * k, cudaMemcpyDeviceToHost, s));
     }
-    CUDA_TRY(c, cudaStreamSynchronize(s));
+    if (widest > 0 && out) // one strided copy: the first `widest` matches of every pair
+        CUDA_TRY(c, cudaMemcpy2D(out, sizeof(rgbdfe_dmatch) * cap_per_pair, w->d_out, sizeof(rgbdfe_dmatch) * cap, sizeof(rgbdfe_dmatch) * widest, npairs,
+            cudaMemcpyDeviceToHost));
     return over ? RGBDFE_E_CAPACITY : RGBDFE_OK;
 }
 

@@ -3,6 +3,49 @@
 #include "Frame.h"
 #include "../Features/Extractor.h"
 
+float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
+float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+bool Frame::mbInitialComputations = true;
+
+cv::Mat Frame::getRotation() const
+{
+    cv::Mat R(3, 3, CV_32F);
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++)
+            R.at<float>(r, c) = mTcw.at<float>(r, c);
+    return R;
+}
+
+cv::Mat Frame::getTranslation() const
+{
+    cv::Mat t(3, 1, CV_32F);
+    for (int r = 0; r < 3; r++)
+        t.at<float>(r, 0) = mTcw.at<float>(r, 3);
+    return t;
+}
+
+cv::Mat Frame::getRotationInverse() const
+{
+    cv::Mat R(3, 3, CV_32F);
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++)
+            R.at<float>(r, c) = mTcw.at<float>(c, r);
+    return R;
+}
+
+cv::Mat Frame::getCameraCenter() const
+{
+    // -mRcw.t() * mtcw: cv::gemm(GEMM_1_T, alpha = -1) accumulates each row in double and narrows once
+    cv::Mat o(3, 1, CV_32F);
+    for (int r = 0; r < 3; r++) {
+        double s = 0.0;
+        for (int k = 0; k < 3; k++)
+            s += (double)mTcw.at<float>(k, r) * (double)mTcw.at<float>(k, 3);
+        o.at<float>(r, 0) = (float)(-s);
+    }
+    return o;
+}
+
 Frame::Frame(const cv::Mat& imGray, const cv::Mat& imDepth, const double& timeStamp, Extractor::Ptr pExtractor, RGBDcamera* pRGBDcamera)
     : mImGray(imGray)
     , mImDepth(imDepth)
@@ -12,6 +55,13 @@ Frame::Frame(const cv::Mat& imGray, const cv::Mat& imDepth, const double& timeSt
     , N(0)
 {
     mTcw = cv::Mat::eye(4, 4, CV_32F);
+
+    if (mbInitialComputations) { // Core/Frame.cpp:60-70 for distCoef[0] == 0 (computeImageBounds :306-311)
+        mnMinX = 0.0f, mnMaxX = (float)imGray.cols, mnMinY = 0.0f, mnMaxY = (float)imGray.rows;
+        mfGridElementWidthInv = 64.0f / (mnMaxX - mnMinX);  // FRAME_GRID_COLS
+        mfGridElementHeightInv = 48.0f / (mnMaxY - mnMinY); // FRAME_GRID_ROWS
+        mbInitialComputations = false;
+    }
 
     // Feature extraction
     extractFeatures();

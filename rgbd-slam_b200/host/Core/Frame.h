@@ -17,6 +17,8 @@ class Extractor;
 struct RGBDcamera {
     float mfx, mfy, mcx, mcy;
     float mDepthMapFactor; // multiplies the raw depth (Core/Frame.cpp:48)
+    float fx() const { return mfx; }
+    float fy() const { return mfy; }
     float cx() const { return mcx; }
     float cy() const { return mcy; }
     float invfx() const { return 1.0f / mfx; }
@@ -36,6 +38,11 @@ public:
 
     void setPose(cv::Mat Tcw) { mTcw = Tcw.clone(); }
     cv::Mat getPose() const { return mTcw.clone(); }
+    // pose blocks of Frame::updatePoseMatrices (Core/Frame.cpp:137-151), read by Matcher::projectionMatch
+    cv::Mat getRotation() const;        // mRcw
+    cv::Mat getTranslation() const;     // mtcw
+    cv::Mat getRotationInverse() const; // mRwc = mRcw.t()
+    cv::Mat getCameraCenter() const;    // mOw = -mRcw.t() * mtcw
 
     bool isInlier(const size_t& idx) const { return mvbOutlier[idx] == false; }
     bool isOutlier(const size_t& idx) const { return mvbOutlier[idx] == true; }
@@ -64,6 +71,12 @@ public:
 
     // Flag to identify outlier associations.
     std::vector<bool> mvbOutlier;
+
+    // Undistorted image bounds and grid cell sizes (static in the reference, Core/Frame.h:158-166; set by the first
+    // frame, Core/Frame.cpp:60-70)
+    static float mfGridElementWidthInv, mfGridElementHeightInv;
+    static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+    static bool mbInitialComputations;
 
 private:
     void uprojectCamera();

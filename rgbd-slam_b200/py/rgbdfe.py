@@ -265,7 +265,7 @@ class Context:
         """projectionMatch for device-resident frame pairs; projs: one Projection (or dict) per pair.  Returns a list of match arrays."""
         npairs = len(f1)
         P = (Projection * npairs)(*[p if isinstance(p, Projection) else Projection.make(p, p.get("th", 5.0)) for p in projs])
-        out = np.zeros((npairs, self.kp_cap), DM_DTYPE)
+        out = np.empty((npairs, self.kp_cap), DM_DTYPE)
         n = np.zeros(npairs, np.int32)
         self._chk(lib().rgbdfe_frames_projection_match(self.h, (C.c_void_p * npairs)(*[f.h for f in f1]), (C.c_void_p * npairs)(*[f.h for f in f2]),
                                                        P, npairs, _p(out), self.kp_cap, _p(n)))

@@ -88,6 +88,17 @@ int main(int argc, char** argv)
             for (size_t k = 0; k < cur->N; k++)
                 nout += cur->isOutlier(k) ? 1 : 0;
             fprintf(out, "outliers %d %d\n", i, nout);
+            // Matcher::projectionMatch with the poses the solver just set (dead code in the reference, scope row N2);
+            // the pose blocks are printed so that the test can hand the oracle the very same floats
+            vector<cv::DMatch> vProj;
+            const int np = matcher.projectionMatch(ref, cur, vProj, 5.0f);
+            fprintf(out, "proj %d n %d m %016llx P", i, np, fnv(vProj.data(), vProj.size() * sizeof(cv::DMatch)));
+            const cv::Mat blocks[4] = { ref->getRotationInverse(), ref->getCameraCenter(), cur->getRotation(), cur->getTranslation() };
+            for (const cv::Mat& b : blocks)
+                for (int r = 0; r < b.rows; r++)
+                    for (int c = 0; c < b.cols; c++)
+                        fprintf(out, " %.9g", b.at<float>(r, c));
+            fprintf(out, "\n");
             if (i == 1) {
                 // class Ransac on the same matches (dead code in the reference, named by the north star);
                 // a copy of the frame keeps the tracking state untouched

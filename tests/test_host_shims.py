@@ -3,6 +3,7 @@ a C++ caller written like Tracking::visualOdometry (tests/cpp/host_track.cpp) is
 outputs are compared with the CPU oracle, bit for bit (poses within 1e-5)."""
 import os
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -32,6 +33,7 @@ def test_host_library_exports_the_reference_classes():
         "ORBextractor::operator()(",
         "Matcher::Matcher(float)",
         "Matcher::match(std::shared_ptr<Frame>, std::shared_ptr<Frame>, std::vector<cv::DMatch",
+        "Matcher::projectionMatch(std::shared_ptr<Frame>, std::shared_ptr<Frame>, std::vector<cv::DMatch",
         "Matcher::descriptorDistance(cv::Mat const&, cv::Mat const&)",
         "RansacSE3::RansacSE3(int, unsigned int, float, unsigned int)",
         "RansacSE3::compute(std::shared_ptr<Frame>, std::shared_ptr<Frame>, std::vector<cv::DMatch",
@@ -69,6 +71,11 @@ def test_visual_odometry_through_the_class_shims(oracle, seq_vga, tmp_path):
     assert np.float32(rec["scale7"][0][0]) == np.float32(tab["scale"][7]) and np.float32(rec["scale7"][0][2]) == np.float32(tab["inv_sigma2"][7])
     rng, latch = oracle.Rng(42), oracle.Latch()
     prev, pose_prev = None, np.eye(4, dtype=np.float32)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    import orclib
+    import projection as pj
+
+    orclib_dm, nproj = orclib.DM_DTYPE, 0
     ti = 0
     for i, (g, d) in enumerate(frames):
         k, de = orb.extract(g)
@@ -95,6 +102,20 @@ def test_visual_odometry_through_the_class_shims(oracle, seq_vga, tmp_path):
             assert np.abs(pose - want).max() <= 1e-5
             pose_prev = pose
             assert int(rec["outliers"][ti][1]) == int(outl.sum())
+            # Matcher::projectionMatch through the shim against the numpy oracle, with the pose blocks the shim read
+            pr = rec["proj"][ti]
+            blk = np.array([np.float32(x) for x in pr[6:30]], np.float32)
+            proj = dict(fx=cam["fx"], fy=cam["fy"], cx=cam["cx"], cy=cam["cy"], Rwc1=blk[0:9].reshape(3, 3), Ow1=blk[9:12], Rcw2=blk[12:21].reshape(3, 3),
+                        tcw2=blk[21:24], bounds=(0.0, 640.0, 0.0, 480.0), inv=(np.float32(64) / np.float32(640), np.float32(48) / np.float32(480)))
+            f1 = dict(desc=prev[1], xyz=prev[2], outlier=prev[3].astype(bool))
+            f2 = dict(desc=de, xyz=p3, pts_un=np.stack([k["x"], k["y"]], 1).astype(np.float32))
+            pm = pj.projection_match(f1, f2, proj, 5.0)
+            dm = np.zeros(len(pm), orclib_dm)
+            if pm:
+                dm["queryIdx"], dm["trainIdx"], dm["distance"] = (np.array(v) for v in zip(*pm))
+            dm["imgIdx"] = -1
+            assert int(pr[2]) == len(pm) and int(pr[4], 16) == fnv(dm)
+            nproj += len(pm)
             if i == 1:
                 u = oracle.ransac_umeyama(prev[2], p3, m, rng, 0, 0.02, 0.2, 10, 3)
                 ur = rec["umeyama"][0]
@@ -102,3 +123,4 @@ def test_visual_odometry_through_the_class_shims(oracle, seq_vga, tmp_path):
                 assert int(rec["randomInt"][0][0]) == rng.random_int(0, 999)
             ti += 1
         prev = (k, de, p3, outl)
+    assert nproj > 100, "the tracked poses must let projectionMatch find most of the matches"
