@@ -146,6 +146,24 @@ int rgbdfe_orb_pyramid_level(rgbdfe_ctx* ctx, int level, uint8_t* dst, int dst_s
 int rgbdfe_orb_stage_candidates(rgbdfe_ctx* ctx, int level, rgbdfe_keypoint* out, int cap, int* n);
 int rgbdfe_orb_stage_blurred(rgbdfe_ctx* ctx, int level, uint8_t* dst, int dst_stride);
 
+/* ---- Extractor(ORB, ORB): the cv::ORB branch --------- */
+/* Extractor::eType values the library implements: ORB2 = the in-tree ORBextractor (rgbdfe_orb_configure),
+ * ORB = OpenCV's cv::ORB with Harris scoring (Features/Extractor.cpp:163-166,216-218). */
+#define RGBDFE_EXTRACTOR_ORB2 0
+#define RGBDFE_EXTRACTOR_ORB 1
+/* Extractor(ORB, ORB).setParameters(nfeatures, scaleFactor, nlevels, ...) (Features/Extractor.cpp:24-48,163-166):
+ * from now on every extraction entry point of this context (rgbdfe_orb_extract, rgbdfe_frames_extract,
+ * rgbdfe_frames_extract_raw) runs Extractor::detectAndCompute's non-ORB2 branch (Features/Extractor.cpp:55-59):
+ * cv::ORB::create(nfeatures, scaleFactor, nlevels)->detect, retainBest(nfeatures), cv::ORB::create()->compute.
+ * rgbdfe_orb_configure switches back.  scaleFactor must be 1.2f: the reference's descriptor object is a default
+ * cv::ORB, whose pyramid only coincides with the detector's at that value.  Gray input only. */
+int rgbdfe_cvorb_configure(rgbdfe_ctx* ctx, int nfeatures, float scaleFactor, int nlevels);
+/* Stage outputs of slot 0 of the last cv::ORB extraction, for stage-by-stage parity tests: the level image
+ * (which = 0), the blurred level (1) or the non-max-suppressed FAST score map (2), tight w x h; and the keypoints
+ * that entered the second retainBest (after retainBest(2 N_l) and HarrisResponses), level coordinates. */
+int rgbdfe_cvorb_stage_level(rgbdfe_ctx* ctx, int level, int which, uint8_t* dst, int dst_stride, int* w, int* h);
+int rgbdfe_cvorb_stage_harris(rgbdfe_ctx* ctx, int level, rgbdfe_keypoint* out, int cap, int* n);
+
 /* ---- Matcher ---------------------------------------------------------- */
 /* Matcher::match (Features/Matcher.cpp:106-139): kNN k=2 Hamming + ratio test +
  * unique-train + outlier / valid-depth filters.  q_outlier may be NULL. */

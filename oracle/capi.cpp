@@ -11,6 +11,54 @@ using namespace orc;
 
 extern "C" {
 
+// ---------------- cv::ORB branch (row N3) ----------------
+void* orc_cvorb_create(int nfeatures, float scale, int nlevels) { return new CvOrb(nfeatures, scale, nlevels); }
+void orc_cvorb_destroy(void* h) { delete (CvOrb*)h; }
+int orc_cvorb_extract(void* h, const uint8_t* img, int w, int ht, int stride, KeyPoint* kps, uint8_t* desc, int cap)
+{
+    CvOrb* e = (CvOrb*)h;
+    std::vector<KeyPoint> k;
+    std::vector<uint8_t> d;
+    e->extract(img, w, ht, stride, k, d);
+    int n = std::min((int)k.size(), cap);
+    if (n > 0) {
+        memcpy(kps, k.data(), (size_t)n * sizeof(KeyPoint));
+        memcpy(desc, d.data(), (size_t)n * 32);
+    }
+    return (int)k.size();
+}
+void orc_cvorb_level_size(void* h, int level, int* w, int* ht, int* quota, int* n_fast, int* n_harris)
+{
+    CvOrb* e = (CvOrb*)h;
+    *w = e->levels[level].w;
+    *ht = e->levels[level].h;
+    *quota = e->quota.empty() ? 0 : e->quota[level];
+    *n_fast = e->levels[level].n_fast;
+    *n_harris = (int)e->levels[level].harris_in.size();
+}
+// un-padded level image / blurred level (w x h, tight) of the last extract()
+void orc_cvorb_level_image(void* h, int level, uint8_t* dst, int blurred)
+{
+    CvOrb* e = (CvOrb*)h;
+    const CvOrbLevel& L = e->levels[level];
+    for (int y = 0; y < L.h; y++)
+        memcpy(dst + (size_t)y * L.w, blurred ? L.blurred.data() + (size_t)y * L.w : L.image() + (size_t)y * L.stride, L.w);
+}
+int orc_cvorb_level_harris(void* h, int level, KeyPoint* out, int cap)
+{
+    CvOrb* e = (CvOrb*)h;
+    const auto& v = e->levels[level].harris_in;
+    int n = std::min((int)v.size(), cap);
+    if (n > 0)
+        memcpy(out, v.data(), (size_t)n * sizeof(KeyPoint));
+    return (int)v.size();
+}
+void orc_gauss7_float(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride) { gauss7_float_u8(src, w, h, sstride, dst, dstride); }
+void orc_resize_linear_exact(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride)
+{
+    resize_linear_exact_u8(src, sw, sh, sstride, dst, dw, dh, dstride);
+}
+
 // ---------------- ORB ----------------
 void* orc_orb_create(int nfeatures, float scale, int nlevels, int iniTh, int minTh)
 {

@@ -130,5 +130,30 @@ void ransac_umeyama(const Point3f* p1, const Point3f* p2, const std::vector<DMat
     GlibcRand& rng, UmeyamaResult& res);
 void umeyama3(const float* src, const float* dst, int n, float T[16]);
 
+// ---- cvorb.cpp : the Extractor(ORB, ORB) branch = cv::ORB (Features/Extractor.cpp:55-59,163-166,216-218) ----
+void resize_linear_exact_u8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride);
+void gauss7_float_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride);
+struct CvOrbLevel {
+    int w, h, stride; // stride = w + 2 * border
+    float scale;
+    int n_fast;       // FAST corners inside the border, before retainBest
+    std::vector<uint8_t> padded, blurred;
+    std::vector<KeyPoint> harris_in; // after retainBest(2 N_l) + Harris response, level coordinates
+    const uint8_t* image() const { return padded.data() + 32 * stride + 32; }
+};
+class CvOrb {
+public:
+    CvOrb(int nfeatures_, float scaleFactor_, int nlevels_) : nfeatures(nfeatures_), scaleFactor((double)scaleFactor_), nlevels(nlevels_) {}
+    // detect + compute as Extractor::detectAndCompute does for the ORB/ORB pair; the descriptor object is a default
+    // cv::ORB (scale 1.2f), so the restatement shares one pyramid and requires scaleFactor == 1.2f
+    void extract(const uint8_t* img, int w, int h, int stride, std::vector<KeyPoint>& kps, std::vector<uint8_t>& desc);
+    int nfeatures;
+    double scaleFactor;
+    int nlevels;
+    int edgeThreshold = 31, fastThreshold = 20, border = 32;
+    std::vector<int> quota;
+    std::vector<CvOrbLevel> levels;
+};
+
 } // namespace orc
 #endif

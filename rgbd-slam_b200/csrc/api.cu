@@ -340,6 +340,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_orb_workspaces(c);
     free_pair_workspaces(c);
     free_proj_workspace(c);
+    free_cvorb_workspace(c);
     free_frame(c->scratch);
     free_frame(c->scratch2);
     if (c->order_evt)
@@ -423,6 +424,7 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
     }
     cudaSetDevice(c->device);
     c->nfeatures = nfeatures, c->scaleFactorF = scaleFactor, c->nlevels = nlevels, c->iniTh = iniThFAST, c->minTh = minThFAST;
+    c->extractor = RGBDFE_EXTRACTOR_ORB2;
     // ORBextractor constructor tables (ORBextractor.cpp:348-383); scaleFactor is a double member
     const double sf = (double)scaleFactor;
     c->scale.assign(nlevels, 1.0f), c->sigma2.assign(nlevels, 1.0f), c->inv_scale.assign(nlevels, 1.0f), c->inv_sigma2.assign(nlevels, 1.0f);
@@ -650,14 +652,19 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
     const float* const* depth, int depth_stride, float fx, float fy, float cx, float cy, const uint16_t* const* depth16 = nullptr,
     float depth16_factor = 0.0f, int channels = 1, const float* dist = nullptr)
 {
+    const bool cvorb = c->extractor == RGBDFE_EXTRACTOR_ORB; // Extractor(ORB, ORB): the cv::ORB branch (orb_cv.cu)
     if (!c->configured)
         return RGBDFE_E_STATE;
     if (count < 1 || count > c->max_batch || !gray || !frames) {
         c->set_error("extract: count outside [1, max_batch]");
         return RGBDFE_E_ARG;
     }
+    if (cvorb && channels != 1) {
+        c->set_error("extract: the cv::ORB branch takes gray images");
+        return RGBDFE_E_ARG;
+    }
     cudaSetDevice(c->device);
-    int rc = build_level_config(c, w, h);
+    int rc = cvorb ? RGBDFE_OK : build_level_config(c, w, h);
     if (rc != RGBDFE_OK)
         return rc;
     FrameBatch fb;
@@ -695,6 +702,9 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
             return rc;
         dstride = w;
     }
+    if (cvorb)
+        return launch_cvorb(c, count, w, h, gp, gstride, fb, dany != nullptr, dp, dstride,
+            make_frame_prep(w, h, fx, fy, cx, cy, dist, depth16 ? depth16_factor : 0.0f));
     if ((rc = launch_pyramid(c, count, gp, gstride, channels)) != RGBDFE_OK)
         return rc;
     if ((rc = launch_fast(c, count)) != RGBDFE_OK)
@@ -745,6 +755,35 @@ int rgbdfe_orb_extract(rgbdfe_ctx* c, const uint8_t* gray, int w, int h, int str
     if (rc != RGBDFE_OK)
         return rc;
     return rgbdfe_frame_download(c, f, kps, desc, nullptr, nullptr, cap, n);
+}
+
+int rgbdfe_cvorb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nlevels)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    const int rc = cvorb_configure(c, nfeatures, scaleFactor, nlevels);
+    if (rc == RGBDFE_OK) {
+        c->extractor = RGBDFE_EXTRACTOR_ORB;
+        c->configured = true;
+    }
+    return rc;
+}
+
+int rgbdfe_cvorb_stage_level(rgbdfe_ctx* c, int level, int which, uint8_t* dst, int dst_stride, int* w, int* h)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    return cvorb_stage_level(c, level, which, dst, dst_stride, w, h);
+}
+
+int rgbdfe_cvorb_stage_harris(rgbdfe_ctx* c, int level, rgbdfe_keypoint* out, int cap, int* n)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    return cvorb_stage_harris(c, level, out, cap, n);
 }
 
 int rgbdfe_orb_pyramid_level(rgbdfe_ctx* c, int level, uint8_t* dst, int dst_stride, int* w, int* h)

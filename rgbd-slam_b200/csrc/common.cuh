@@ -253,6 +253,8 @@ struct rgbdfe_ctx {
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
     int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
+    struct CvOrbWorkspace* cvorb = nullptr; // the cv::ORB branch of Extractor (row N3, orb_cv.cu), allocated by rgbdfe_cvorb_configure
+    int extractor = 0;                      // RGBDFE_EXTRACTOR_ORB2 / RGBDFE_EXTRACTOR_ORB: which one the extraction entry points run
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
     int dbg_on = 0;
@@ -342,6 +344,13 @@ int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, i
 int knn_splits_for(const rgbdfe_ctx* c, int npairs);
 // projection.cu
 void free_proj_workspace(rgbdfe_ctx* c);
+// orb_cv.cu
+void free_cvorb_workspace(rgbdfe_ctx* c);
+int cvorb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nlevels);
+int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, int gray_stride, const FrameBatch& frames, bool unproject,
+    const ImgPtrs& depth, int depth_stride, const FramePrep& prep);
+int cvorb_stage_level(rgbdfe_ctx* c, int level, int which, uint8_t* dst, int dst_stride, int* w, int* h);
+int cvorb_stage_harris(rgbdfe_ctx* c, int level, rgbdfe_keypoint* out, int cap, int* n);
 // ransac.cu
 // Pairs occupy workspace slots [slot0, slot0 + npairs); results go to d_results[0 .. npairs).  With `ff` the
 // Matcher::match filter (K8) runs inside k_se3_prepare on the kNN partials of the same slots.

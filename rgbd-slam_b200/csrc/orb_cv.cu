@@ -1,0 +1,928 @@
+// Row N3: the `Extractor(ORB, ORB)` branch of the reference = OpenCV's cv::ORB with Harris scoring.
+//   mpDetector   = cv::ORB::create(nfeatures, scaleFactor, nlevels)   Features/Extractor.cpp:163-166
+//   mpDescriptor = cv::ORB::create()                                  Features/Extractor.cpp:216-218
+//   detect -> retainBest(nfeatures) -> compute                        Features/Extractor.cpp:55-59
+// The arithmetic is OpenCV's (features2d/src/orb.cpp, imgproc resize.cpp / filter.simd.hpp, keypoint.cpp); the CPU
+// restatement pinned against cv2 4.13 is oracle/cvorb.cpp.  Kernels (sm_100a, no FMA except where OpenCV's build fuses):
+//   k_cv_pyr_base / k_cv_pyr_level  pyramid chain resize(INTER_LINEAR_EXACT) (8.8 fixed point) + 32 px REFLECT_101 ring
+//   k_cv_fast                        whole-level FAST-9 (threshold 20) + 3x3 NMS + border 31 -> dense score map
+//   k_cv_blur                        GaussianBlur(7x7, 2) as sepFilter2D's float path (see oracle/cvorb.cpp)
+//   k_cv_select                      row-major compaction, retainBest(2 N_l) on the FAST score, Harris response,
+//                                    retainBest(N_l): std::nth_element / std::partition permutation-exact (introselect.cuh)
+//   k_cv_gather                      level lists -> frame order (+ Extractor.cpp:56-57's retainBest when ties overshoot)
+//   k_cv_orient_describe             IC angle, steered BRIEF, cv::KeyPoint + Frame fields
+#include "brief_pattern.h"
+#include "common.cuh"
+#include "fast_core.cuh"
+#include "frame_tail.cuh"
+#include "introselect.cuh"
+#include "orb_math.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#define CV_RING 32
+#define CV_EDGE 31
+#define CV_FAST_TH 20
+#define CV_TW 64
+#define CV_TH 32
+#define CV_KCAP 24576 // FAST candidates of one level handled in shared memory (else in the global scratch)
+#define CV_HCAP 12288 // Harris-stage entries handled in shared memory
+#define CV_SEL_THREADS 1024
+
+struct CvLevel {
+    int w, h, pstride, bstride;
+    unsigned pyr_off;  // byte offset of level pixel (0, 0) inside a frame slot's pyramid (32 px ring around it)
+    unsigned blur_off; // blurred level and FAST score map share this geometry (w x h, pitch bstride)
+    int quota;         // nfeaturesPerLevel
+    int cand_off, cand_cap;
+    int out_off, out_cap;
+    int tabx_off, taby_off;
+    int tile0;         // first 64 x 32 tile of this level in the FAST / blur grids
+    int vec_end, unr_end; // sepFilter2D row pass: [0, vec_end) vector body, [vec_end, unr_end) unrolled scalar, rest tail
+    float scale, inv_scale;
+};
+struct CvCfg {
+    int nlevels, nfeatures, w, h, tiles;
+    int cand_total, out_total;
+    float harris_scale4;
+    int umax[16];
+    float gk[7];
+    CvLevel lv[RGBDFE_MAX_LEVELS];
+};
+struct HKey {
+    float r;
+    unsigned xy; // y << 16 | x, level coordinates
+};
+struct CvSel { // a selected keypoint, level coordinates
+    short x, y;
+    int level;
+    float response;
+};
+
+struct CvOrbWorkspace {
+    CvCfg cfg;
+    bool configured = false;
+    int nfeatures = 0, nlevels = 0;
+    float scaleFactor = 1.2f;
+    size_t pyr_slot = 0, blur_slot = 0;
+    uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
+    unsigned* d_cand = nullptr;          // [slot][cand_total]
+    unsigned short* d_lr = nullptr;      // [slot][2][cand_total] stopper positions when a level does not fit shared memory
+    HKey* d_hkey = nullptr;              // [slot][cand_total] Harris-stage list (also the test tap)
+    int* d_hcount = nullptr;             // [slot][levels]
+    CvSel* d_out = nullptr;              // [slot][out_total]
+    int* d_out_count = nullptr;          // [slot][levels], -1 = capacity overflow
+    int* d_final = nullptr;              // [slot][out_total] indices into d_out in output order
+    int* d_final_count = nullptr;        // [slot]
+    HKey* d_gscratch = nullptr;          // [slot][out_total] k_cv_gather's rare retainBest path
+    int* d_tab_ofs = nullptr;
+    unsigned short* d_tab_c1 = nullptr;
+    int tab_cap = 0;
+    int slots = 0;
+    signed char* d_pattern = nullptr;
+};
+
+namespace rgbdfe {
+
+__device__ __forceinline__ int cv_reflect(int p, int len)
+{
+    if (p < 0)
+        p = -p;
+    if (p >= len)
+        p = 2 * (len - 1) - p;
+    return p;
+}
+
+// ------------------------------------------------------------------ pyramid ----
+// Level 0: copyMakeBorder(image, BORDER_REFLECT_101) with a 32 px ring; one thread = 4 padded bytes.
+__global__ void __launch_bounds__(256) k_cv_pyr_base(const __grid_constant__ CvCfg C, const __grid_constant__ ImgPtrs img, int img_stride,
+    uint8_t* __restrict__ pyr, size_t pyr_slot)
+{
+    const CvLevel& L = C.lv[0];
+    const int slot = blockIdx.z;
+    const int wq = blockIdx.x * blockDim.x + threadIdx.x; // word within the padded row
+    const int py = blockIdx.y * blockDim.y + threadIdx.y - CV_RING;
+    if (4 * wq >= L.pstride || py >= L.h + CV_RING)
+        return;
+    const uint8_t* src = static_cast<const uint8_t*>(img.p[slot]) + (size_t)cv_reflect(py, L.h) * img_stride;
+    unsigned v = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int px = 4 * wq + j - CV_RING;
+        if (px < L.w + CV_RING)
+            v |= (unsigned)src[cv_reflect(px, L.w)] << (8 * j);
+    }
+    *reinterpret_cast<unsigned*>(pyr + slot * pyr_slot + L.pyr_off + (ptrdiff_t)py * L.pstride - CV_RING + 4 * wq) = v;
+}
+
+// Level l >= 1: resize(prev, INTER_LINEAR_EXACT) + copyMakeBorder(REFLECT_101 | ISOLATED).  resize_bitExact: horizontal
+// blend in ufixedpoint16 (8 fractional bits), vertical blend of two such rows in ufixedpoint32, (v + 2^15) >> 16.
+// Tables hold, per destination index, the source offset and the second coefficient (first = 256 - second); indices
+// left of min / right of max are encoded as coefficient pairs (256, 0) / (0, 256) on a valid source pair.
+__global__ void __launch_bounds__(256) k_cv_pyr_level(const __grid_constant__ CvCfg C, int level, uint8_t* __restrict__ pyr, size_t pyr_slot,
+    const int* __restrict__ tab_ofs, const unsigned short* __restrict__ tab_c1)
+{
+    const CvLevel& L = C.lv[level];
+    const CvLevel& P = C.lv[level - 1];
+    const int slot = blockIdx.z;
+    const int wq = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = blockIdx.y * blockDim.y + threadIdx.y - CV_RING;
+    if (4 * wq >= L.pstride || py >= L.h + CV_RING)
+        return;
+    uint8_t* base = pyr + slot * pyr_slot;
+    const int ry = cv_reflect(py, L.h);
+    const int oy = tab_ofs[L.taby_off + ry];
+    const unsigned cy1 = tab_c1[L.taby_off + ry], cy0 = 256u - cy1;
+    const uint8_t* s0 = base + P.pyr_off + (size_t)oy * P.pstride;
+    const uint8_t* s1 = s0 + P.pstride;
+    unsigned v = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int px = 4 * wq + j - CV_RING;
+        if (px < L.w + CV_RING) {
+            const int rx = cv_reflect(px, L.w);
+            const int ox = tab_ofs[L.tabx_off + rx];
+            const unsigned cx1 = tab_c1[L.tabx_off + rx], cx0 = 256u - cx1;
+            const unsigned h0 = cx0 * s0[ox] + cx1 * s0[ox + 1];
+            const unsigned h1 = cx0 * s1[ox] + cx1 * s1[ox + 1];
+            v |= ((h0 * cy0 + h1 * cy1 + 32768u) >> 16) << (8 * j);
+        }
+    }
+    *reinterpret_cast<unsigned*>(base + L.pyr_off + (ptrdiff_t)py * L.pstride - CV_RING + 4 * wq) = v;
+}
+
+__device__ __forceinline__ int cv_find_level(const CvCfg& C, int tile)
+{
+    int level = 0;
+    while (level + 1 < C.nlevels && tile >= C.lv[level + 1].tile0)
+        level++;
+    return level;
+}
+
+// ------------------------------------------------------------------ FAST ----
+// cv::FAST(threshold 20, nonmaxSuppression) over the whole level + KeyPointsFilter::runByImageBorder(31): the tile
+// computes the corner strength S on its 66 x 34 neighbourhood, applies the 3x3 non-max rule (a neighbour that is not
+// a corner scores 0) and writes response = S - 1 of the survivors into the level's score map, 0 elsewhere.
+__global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    uint8_t* __restrict__ score, size_t score_slot)
+{
+    const int level = cv_find_level(C, blockIdx.x);
+    const CvLevel& L = C.lv[level];
+    const int t = blockIdx.x - L.tile0;
+    const int tiles_x = (L.w + CV_TW - 1) / CV_TW;
+    const int ty = t / tiles_x, x0 = (t - ty * tiles_x) * CV_TW, y0 = ty * CV_TH;
+    const int slot = blockIdx.y, tid = threadIdx.x;
+    constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 8;
+    __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
+    __shared__ __align__(16) uint8_t s_S[ROWS][PITCH];
+    // staged window: level rows y0-4 .. y0+35, columns x0-4 .. x0+67 (the ring covers 4 px outside the image; rows and
+    // words beyond the padded level are clamped: those pixels lie outside the detection region and are never used)
+    const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
+    const int max_word = (L.pstride - CV_RING - 4) >> 2; // last whole word of a padded row, relative to column 0
+    for (int i = tid; i < ROWS * (PITCH / 4); i += 256) {
+        const int r = i / (PITCH / 4), q = i - r * (PITCH / 4);
+        const int y = min(y0 - 4 + r, L.h + CV_RING - 1);
+        const int wq = min((x0 - 4) / 4 + q, max_word);
+        *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
+        *reinterpret_cast<unsigned*>(&s_S[r][4 * q]) = 0u;
+    }
+    __syncthreads();
+    // strengths on the emit region + 1 px halo, inside cv::FAST's detection region [3, w-3) x [3, h-3)
+    for (int i = tid; i < (CV_TH + 2) * (CV_TW + 2); i += 256) {
+        const int rr = i / (CV_TW + 2), cc = i - rr * (CV_TW + 2);
+        const int r = rr + 3, c = cc + 3; // window coordinates
+        const int x = x0 - 4 + c, y = y0 - 4 + r;
+        if (x < 3 || x >= L.w - 3 || y < 3 || y >= L.h - 3)
+            continue;
+        const uint8_t* p = &s_img[r][c];
+        // any 9-arc of the 16-ring holds at least two of the four compass pixels
+        const int v = p[0], hi = v + CV_FAST_TH, lo = v - CV_FAST_TH;
+        const int a0 = p[3 * PITCH], a4 = p[3], a8 = p[-3 * PITCH], a12 = p[-3];
+        const int nb = (a0 > hi) + (a4 > hi) + (a8 > hi) + (a12 > hi), nd = (a0 < lo) + (a4 < lo) + (a8 < lo) + (a12 < lo);
+        if (nb < 2 && nd < 2)
+            continue;
+        const int S = fast_strength(p, PITCH, CV_FAST_TH);
+        s_S[r][c] = (uint8_t)min(S, 255);
+    }
+    __syncthreads();
+    // NMS + border filter, 4 pixels per thread, one 32-bit store
+    uint8_t* out = score + slot * score_slot + L.blur_off;
+    for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
+        const int rr = i / (CV_TW / 4), q = i - rr * (CV_TW / 4);
+        const int y = y0 + rr;
+        if (y >= L.h)
+            continue;
+        unsigned word = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int r = rr + 4, c = 4 * q + j + 4;
+            const int x = x0 + 4 * q + j;
+            const int S = s_S[r][c];
+            if (S == 0 || x < CV_EDGE || x >= L.w - CV_EDGE || y < CV_EDGE || y >= L.h - CV_EDGE)
+                continue;
+            const int m = max(max(max(s_S[r - 1][c - 1], s_S[r - 1][c]), max(s_S[r - 1][c + 1], s_S[r][c - 1])),
+                max(max(s_S[r][c + 1], s_S[r + 1][c - 1]), max(s_S[r + 1][c], s_S[r + 1][c + 1])));
+            if (S > m) // score = S - 1 on both sides; non-corners hold 0 and a corner's S is >= 21
+                word |= (unsigned)(S - 1) << (8 * j);
+        }
+        *reinterpret_cast<unsigned*>(out + (size_t)y * L.bstride + x0 + 4 * q) = word;
+    }
+}
+
+// ------------------------------------------------------------------ blur ----
+// GaussianBlur(level, 7x7, sigma 2, BORDER_REFLECT_101) on a submatrix = sepFilter2D with the float kernel: row pass
+// left to right (FMA in the 32-pixel vector body and in the last w % 4 pixels, separate multiply / add in the
+// 4-way unrolled part between them), column pass centre tap + symmetric pairs with FMA, cvRound, saturate.
+__global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    uint8_t* __restrict__ blur, size_t blur_slot)
+{
+    const int level = cv_find_level(C, blockIdx.x);
+    const CvLevel& L = C.lv[level];
+    const int t = blockIdx.x - L.tile0;
+    const int tiles_x = (L.w + CV_TW - 1) / CV_TW;
+    const int ty = t / tiles_x, x0 = (t - ty * tiles_x) * CV_TW, y0 = ty * CV_TH;
+    const int slot = blockIdx.y, tid = threadIdx.x;
+    constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 6;
+    __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
+    __shared__ float s_h[ROWS][CV_TW];
+    const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
+    const int max_word = (L.pstride - CV_RING - 4) >> 2;
+    for (int i = tid; i < ROWS * (PITCH / 4); i += 256) { // rows y0-3 .. y0+34, columns x0-4 .. x0+67
+        const int r = i / (PITCH / 4), q = i - r * (PITCH / 4);
+        const int y = min(y0 - 3 + r, L.h + CV_RING - 1);
+        const int wq = min((x0 - 4) / 4 + q, max_word);
+        *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
+    }
+    __syncthreads();
+    for (int i = tid; i < ROWS * CV_TW; i += 256) {
+        const int r = i / CV_TW, c = i - r * CV_TW;
+        const int x = x0 + c;
+        const uint8_t* p = &s_img[r][c + 1]; // column x - 3
+        float acc = __fmul_rn(C.gk[0], (float)p[0]);
+        if (x < L.vec_end || x >= L.unr_end) {
+#pragma unroll
+            for (int j = 1; j < 7; j++)
+                acc = __fmaf_rn(C.gk[j], (float)p[j], acc);
+        } else {
+#pragma unroll
+            for (int j = 1; j < 7; j++)
+                acc = __fadd_rn(acc, __fmul_rn(C.gk[j], (float)p[j]));
+        }
+        s_h[r][c] = acc;
+    }
+    __syncthreads();
+    uint8_t* out = blur + slot * blur_slot + L.blur_off;
+    for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
+        const int rr = i / (CV_TW / 4), q = i - rr * (CV_TW / 4);
+        const int y = y0 + rr;
+        if (y >= L.h)
+            continue;
+        unsigned word = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int c = 4 * q + j;
+            float acc = __fmul_rn(C.gk[3], s_h[rr + 3][c]);
+#pragma unroll
+            for (int k = 1; k <= 3; k++)
+                acc = __fmaf_rn(C.gk[3 + k], __fadd_rn(s_h[rr + 3 + k][c], s_h[rr + 3 - k][c]), acc);
+            const int v = min(max(__float2int_rn(acc), 0), 255);
+            word |= (unsigned)v << (8 * j);
+        }
+        *reinterpret_cast<unsigned*>(out + (size_t)y * L.bstride + x0 + 4 * q) = word;
+    }
+}
+
+// ------------------------------------------------------------------ selection ----
+struct FastGreater { // KeypointResponseGreater on packed candidates (response in the top byte)
+    __device__ bool operator()(unsigned a, unsigned b) const { return (a >> 24) > (b >> 24); }
+};
+struct HarrisGreater {
+    __device__ bool operator()(const HKey& a, const HKey& b) const { return a.r > b.r; }
+};
+
+// cv::KeyPointsFilter::retainBest by warp 0 of the CTA; returns the new size (valid in every lane of warp 0).
+template <class T, class C, class P>
+__device__ int warp_retain_best(T* a, int n, int n_points, unsigned short* Lpos, unsigned short* Rpos, int lane, C comp, P make_pred)
+{
+    if (n_points < 0 || n <= n_points)
+        return n;
+    if (n_points == 0)
+        return 0;
+    warp_nth_element(a, n_points - 1, n, Lpos, Rpos, lane, comp);
+    const T amb = a[n_points - 1];
+    return warp_partition(a, n_points, n, Lpos, Rpos, lane, make_pred(amb));
+}
+
+// One CTA per (level, frame).  Dynamic shared memory: keys[KCAP] u32 | Lpos[KCAP] u16 | Rpos[KCAP] u16 | rowoff[h + 1]
+__global__ void __launch_bounds__(CV_SEL_THREADS) k_cv_select(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    const uint8_t* __restrict__ score, size_t score_slot, unsigned* __restrict__ cand_all, unsigned short* __restrict__ lr_all,
+    HKey* __restrict__ hkey_all, int* __restrict__ hcount, CvSel* __restrict__ out_all, int* __restrict__ out_count)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned* s_keys = reinterpret_cast<unsigned*>(smem);
+    unsigned short* s_L = reinterpret_cast<unsigned short*>(smem + (size_t)CV_KCAP * 4);
+    unsigned short* s_R = s_L + CV_KCAP;
+    int* s_rowoff = reinterpret_cast<int*>(smem + (size_t)CV_KCAP * 8);
+    __shared__ int s_n, s_carry;
+    const int level = blockIdx.x, slot = blockIdx.y;
+    const CvLevel& L = C.lv[level];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = CV_SEL_THREADS / 32;
+    const uint8_t* sc = score + slot * score_slot + L.blur_off;
+    const int words = (L.w + 3) >> 2;
+
+    // ---- row-major compaction of the score map (cv::FAST emits keypoints row by row) ----
+    for (int y = warp; y < L.h; y += nwarps) {
+        int cnt = 0;
+        const unsigned* row = reinterpret_cast<const unsigned*>(sc + (size_t)y * L.bstride);
+        for (int q = lane; q < words; q += 32) {
+            const unsigned v = row[q];
+            cnt += ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0)
+            s_rowoff[y] = cnt;
+    }
+    if (tid == 0)
+        s_carry = 0;
+    __syncthreads();
+    if (warp == 0) { // exclusive scan over the rows
+        int carry = 0;
+        for (int y0 = 0; y0 < L.h; y0 += 32) {
+            const int y = y0 + lane;
+            const int v = y < L.h ? s_rowoff[y] : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o)
+                    inc += u;
+            }
+            if (y < L.h)
+                s_rowoff[y] = carry + inc - v;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) {
+            s_rowoff[L.h] = carry;
+            s_n = carry;
+        }
+    }
+    __syncthreads();
+    int n = s_n;
+    const bool overflow = n > L.cand_cap || n > 65535;
+    if (overflow)
+        n = 0; // reported through out_count = -1
+    unsigned* g_keys = cand_all + (size_t)slot * C.cand_total + L.cand_off;
+    const bool in_smem = n <= CV_KCAP;
+    unsigned* keys = in_smem ? s_keys : g_keys;
+    unsigned short* Lpos = in_smem ? s_L : lr_all + ((size_t)slot * 2) * C.cand_total + L.cand_off;
+    unsigned short* Rpos = in_smem ? s_R : lr_all + ((size_t)slot * 2 + 1) * C.cand_total + L.cand_off;
+    if (n > 0) {
+        for (int y = warp; y < L.h; y += nwarps) {
+            int pos = s_rowoff[y];
+            if (s_rowoff[y + 1] == pos)
+                continue;
+            const unsigned* row = reinterpret_cast<const unsigned*>(sc + (size_t)y * L.bstride);
+            for (int q0 = 0; q0 < words; q0 += 32) {
+                const int q = q0 + lane;
+                const unsigned v = q < words ? row[q] : 0u;
+                const int c = ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0);
+                int inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int u = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o)
+                        inc += u;
+                }
+                int w = pos + inc - c;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const unsigned b = (v >> (8 * j)) & 0xffu;
+                    if (b)
+                        keys[w++] = b << 24 | (unsigned)y << 12 | (unsigned)(4 * q + j);
+                }
+                pos += __shfl_sync(0xffffffffu, inc, 31);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- retainBest(2 * N_l) on the FAST score ----
+    if (warp == 0) {
+        const int m = warp_retain_best(keys, n, 2 * L.quota, Lpos, Rpos, lane, FastGreater(),
+            [](unsigned amb) { return [amb](unsigned k) { return (k >> 24) >= (amb >> 24); }; });
+        if (lane == 0)
+            s_n = m;
+    }
+    __syncthreads();
+    const int n1 = s_n;
+
+    // ---- HarrisResponses(blockSize 7, k 0.04) ----
+    HKey* g_h = hkey_all + (size_t)slot * C.cand_total + L.cand_off;
+    const uint8_t* img = pyr + slot * pyr_slot + L.pyr_off;
+    const int step = L.pstride;
+    for (int i = tid; i < n1; i += CV_SEL_THREADS) {
+        const unsigned k = keys[i];
+        const int x0 = k & 0xfff, y0 = (k >> 12) & 0xfff;
+        const uint8_t* ptr0 = img + (ptrdiff_t)(y0 - 3) * step + x0 - 3;
+        int a = 0, b = 0, c = 0;
+        // 9 x 9 window rows held three at a time
+        for (int r = 0; r < 7; r++) {
+            const uint8_t* pm = ptr0 + (ptrdiff_t)(r - 1) * step - 1;
+            const uint8_t* pc = pm + step;
+            const uint8_t* pp = pc + step;
+            int m0 = pm[0], m1 = pm[1], c0 = pc[0], c1 = pc[1], p0 = pp[0], p1 = pp[1];
+#pragma unroll
+            for (int j = 0; j < 7; j++) {
+                const int m2 = pm[j + 2], c2 = pc[j + 2], p2 = pp[j + 2];
+                const int Ix = (c2 - c0) * 2 + (m2 - m0) + (p2 - p0);
+                const int Iy = (p1 - m1) * 2 + (p0 - m0) + (p2 - m2);
+                a += Ix * Ix;
+                b += Iy * Iy;
+                c += Ix * Iy;
+                m0 = m1, m1 = m2, c0 = c1, c1 = c2, p0 = p1, p1 = p2;
+            }
+        }
+        const float fa = (float)a, fb = (float)b, fc = (float)c;
+        const float sum = __fadd_rn(fa, fb);
+        const float resp = __fmul_rn(__fsub_rn(__fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc)), __fmul_rn(__fmul_rn(0.04f, sum), sum)), C.harris_scale4);
+        HKey h;
+        h.r = resp;
+        h.xy = (unsigned)y0 << 16 | (unsigned)x0;
+        g_h[i] = h;
+    }
+    if (tid == 0)
+        hcount[slot * RGBDFE_MAX_LEVELS + level] = n1;
+    __syncthreads();
+    // ---- retainBest(N_l) on the Harris response ----
+    const bool h_in_smem = n1 <= CV_HCAP;
+    HKey* hk = h_in_smem ? reinterpret_cast<HKey*>(smem) : g_h; // the FAST keys are dead: their shared memory is reused
+    if (h_in_smem)
+        for (int i = tid; i < n1; i += CV_SEL_THREADS)
+            hk[i] = g_h[i];
+    __syncthreads();
+    if (warp == 0) {
+        // stopper lists: the Harris list never exceeds the candidate capacity, so the global scratch always fits
+        unsigned short* L2 = lr_all + ((size_t)slot * 2) * C.cand_total + L.cand_off;
+        unsigned short* R2 = lr_all + ((size_t)slot * 2 + 1) * C.cand_total + L.cand_off;
+        if (h_in_smem) {
+            L2 = s_L;
+            R2 = s_R;
+        }
+        const int m = warp_retain_best(hk, n1, L.quota, L2, R2, lane, HarrisGreater(),
+            [](HKey amb) { return [amb](const HKey& k) { return k.r >= amb.r; }; });
+        if (lane == 0)
+            s_n = m;
+    }
+    __syncthreads();
+    const int n2 = s_n;
+    CvSel* out = out_all + (size_t)slot * C.out_total + L.out_off;
+    for (int i = tid; i < min(n2, L.out_cap); i += CV_SEL_THREADS) {
+        CvSel s;
+        s.x = (short)(hk[i].xy & 0xffff);
+        s.y = (short)(hk[i].xy >> 16);
+        s.level = level;
+        s.response = hk[i].r;
+        out[i] = s;
+    }
+    if (tid == 0)
+        out_count[slot * RGBDFE_MAX_LEVELS + level] = (overflow || n2 > L.out_cap) ? -1 : n2;
+}
+
+// One CTA per frame: output order = levels in sequence.  If ties pushed the total above nfeatures, Extractor.cpp:56-57
+// runs retainBest(nfeatures) over the whole list and cv::ORB's compute() then regroups the survivors by level
+// (stable); that rare path runs on one thread.
+__global__ void __launch_bounds__(256) k_cv_gather(const __grid_constant__ CvCfg C, const CvSel* __restrict__ out_all, const int* __restrict__ out_count,
+    int* __restrict__ final_all, int* __restrict__ final_count, HKey* __restrict__ scratch_all)
+{
+    const int slot = blockIdx.x, tid = threadIdx.x;
+    __shared__ int s_off[RGBDFE_MAX_LEVELS + 1];
+    __shared__ int s_bad;
+    if (tid == 0) {
+        int acc = 0, bad = 0;
+        for (int l = 0; l < C.nlevels; l++) {
+            s_off[l] = acc;
+            const int n = out_count[slot * RGBDFE_MAX_LEVELS + l];
+            if (n < 0)
+                bad = 1;
+            acc += max(n, 0);
+        }
+        s_off[C.nlevels] = acc;
+        s_bad = bad;
+    }
+    __syncthreads();
+    int* fin = final_all + (size_t)slot * C.out_total;
+    const int total = s_off[C.nlevels];
+    if (s_bad) {
+        if (tid == 0)
+            final_count[slot] = -1;
+        return;
+    }
+    if (total <= C.nfeatures) {
+        for (int l = 0; l < C.nlevels; l++)
+            for (int i = tid; i < s_off[l + 1] - s_off[l]; i += 256)
+                fin[s_off[l] + i] = C.lv[l].out_off + i;
+        if (tid == 0)
+            final_count[slot] = total;
+        return;
+    }
+    if (tid == 0) {
+        HKey* g = scratch_all + (size_t)slot * C.out_total;
+        const CvSel* out = out_all + (size_t)slot * C.out_total;
+        int n = 0;
+        for (int l = 0; l < C.nlevels; l++)
+            for (int i = 0; i < s_off[l + 1] - s_off[l]; i++) {
+                g[n].r = out[C.lv[l].out_off + i].response;
+                g[n].xy = (unsigned)(C.lv[l].out_off + i);
+                n++;
+            }
+        struct G {
+            __device__ bool operator()(const HKey& a, const HKey& b) const { return a.r > b.r; }
+        };
+        std_nth_element(g, C.nfeatures - 1, n, G());
+        const float amb = g[C.nfeatures - 1].r;
+        const int m = std_partition(g, C.nfeatures, n, [amb](const HKey& k) { return k.r >= amb; });
+        int w = 0;
+        for (int l = 0; l < C.nlevels; l++)
+            for (int i = 0; i < m; i++)
+                if (out[g[i].xy].level == l)
+                    fin[w++] = (int)g[i].xy;
+        final_count[slot] = m;
+    }
+}
+
+// ------------------------------------------------------------------ orientation + descriptor ----
+__global__ void __launch_bounds__(256) k_cv_orient_describe(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+    const uint8_t* __restrict__ blur, size_t blur_slot, const CvSel* __restrict__ out_all, const int* __restrict__ final_all,
+    const int* __restrict__ final_count, const signed char* __restrict__ pattern, const FrameBatch frames, const __grid_constant__ ImgPtrs depth,
+    int depth_stride, int unproject, const __grid_constant__ FramePrep prep)
+{
+    __shared__ __align__(16) signed char s_pattern[1024];
+    reinterpret_cast<int*>(s_pattern)[threadIdx.x] = reinterpret_cast<const int*>(pattern)[threadIdx.x];
+    __syncthreads();
+    const int slot = blockIdx.y, lane = threadIdx.x & 31;
+    const int gi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const rgbdfe_frame F = frames.f[slot];
+    const int total = final_count[slot];
+    if (gi == 0 && lane == 0)
+        *F.n = total < 0 ? -1 : min(total, F.cap);
+    if (gi >= total || gi >= F.cap)
+        return;
+    const CvSel s = out_all[(size_t)slot * C.out_total + final_all[(size_t)slot * C.out_total + gi]];
+    const CvLevel& L = C.lv[s.level];
+    // ICAngles: integer moments over the 31 px disc of the un-blurred level
+    const uint8_t* center = pyr + slot * pyr_slot + L.pyr_off + (ptrdiff_t)s.y * L.pstride + s.x;
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int u = lane - 15, au = abs(u);
+        m10 = u * center[u];
+        for (int v = 1; v <= 15; v++)
+            if (au <= C.umax[v]) {
+                const int vp = center[u + v * L.pstride], vm = center[u - v * L.pstride];
+                m10 += u * (vp + vm);
+                m01 += v * (vp - vm);
+            }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    const float ptx = __fmul_rn((float)s.x, L.scale), pty = __fmul_rn((float)s.y, L.scale); // allKeypoints[i].pt *= scale
+    // computeOrbDescriptors: centre = cvRound(pt * (1 / layerScale)) on the blurred level
+    const int cx = __float2int_rn(__fmul_rn(ptx, L.inv_scale)), cy = __float2int_rn(__fmul_rn(pty, L.inv_scale));
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float a, b;
+    sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);
+    const uint8_t* bc = blur + slot * blur_slot + L.blur_off + (size_t)cy * L.bstride + cx;
+    signed char pat[32];
+    *reinterpret_cast<uint4*>(pat) = *reinterpret_cast<const uint4*>(s_pattern + lane * 32);
+    *reinterpret_cast<uint4*>(pat + 16) = *reinterpret_cast<const uint4*>(s_pattern + lane * 32 + 16);
+    unsigned val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float x0 = (float)pat[k * 4], y0 = (float)pat[k * 4 + 1], x1 = (float)pat[k * 4 + 2], y1 = (float)pat[k * 4 + 3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = bc[r0 * L.bstride + c0], t1 = bc[r1 * L.bstride + c1];
+        val |= (unsigned)(t0 < t1) << k;
+    }
+    F.desc[(size_t)gi * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        rgbdfe_keypoint kp;
+        kp.x = ptx;
+        kp.y = pty;
+        kp.size = __fmul_rn(31.0f, L.scale);
+        kp.angle = angle;
+        kp.response = s.response;
+        kp.octave = s.level;
+        kp.class_id = -1;
+        store_frame_keypoint(F, gi, kp, prep, depth.p[slot], depth_stride, unproject);
+    }
+}
+
+// ------------------------------------------------------------------ host ----
+namespace {
+template <class T>
+cudaError_t dmalloc(T** p, size_t bytes)
+{
+    return cudaMalloc(reinterpret_cast<void**>(p), bytes);
+}
+void free_buffers(CvOrbWorkspace* W)
+{
+    cudaFree(W->d_pyr), cudaFree(W->d_blur), cudaFree(W->d_score), cudaFree(W->d_cand), cudaFree(W->d_lr), cudaFree(W->d_hkey);
+    cudaFree(W->d_hcount), cudaFree(W->d_out), cudaFree(W->d_out_count), cudaFree(W->d_final), cudaFree(W->d_final_count);
+    cudaFree(W->d_tab_ofs), cudaFree(W->d_tab_c1), cudaFree(W->d_gscratch);
+    W->d_gscratch = nullptr;
+    W->d_pyr = W->d_blur = W->d_score = nullptr;
+    W->d_cand = nullptr, W->d_lr = nullptr, W->d_hkey = nullptr, W->d_hcount = nullptr, W->d_out = nullptr, W->d_out_count = nullptr;
+    W->d_final = nullptr, W->d_final_count = nullptr, W->d_tab_ofs = nullptr, W->d_tab_c1 = nullptr;
+}
+int cv_round_f(float v) { return (int)lrintf(v); }
+// interpolationLinear<uchar>::getCoeffs (resize.cpp), arithmetic in IEEE double (= softdouble)
+void exact_table(int srcsize, int dstsize, int* ofs, unsigned short* c1)
+{
+    const double scale = 1.0 / ((double)dstsize / srcsize);
+    for (int v = 0; v < dstsize; v++) {
+        const double fval = scale * ((double)v + 0.5) - 0.5;
+        const int ival = (int)std::floor(fval);
+        if (ival >= 0 && srcsize > 1) {
+            if (ival < srcsize - 1) {
+                ofs[v] = ival;
+                const double frac = fval - (double)ival;
+                c1[v] = frac < 0 ? 0 : (unsigned short)std::nearbyint(frac * 256.0);
+            } else { // right of max: src[last] -- as pair (last - 1, last) with coefficients (0, 256)
+                ofs[v] = srcsize - 2;
+                c1[v] = 256;
+            }
+        } else { // left of min: src[0]
+            ofs[v] = 0;
+            c1[v] = 0;
+        }
+    }
+}
+} // namespace
+
+void free_cvorb_workspace(rgbdfe_ctx* c)
+{
+    if (!c->cvorb)
+        return;
+    free_buffers(c->cvorb);
+    cudaFree(c->cvorb->d_pattern);
+    delete c->cvorb;
+    c->cvorb = nullptr;
+}
+
+int cvorb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nlevels)
+{
+    if (nfeatures < 1 || nfeatures > c->max_feats || nlevels < 1 || nlevels > RGBDFE_MAX_LEVELS || !(scaleFactor > 1.0f)) {
+        c->set_error("cvorb_configure: nfeatures in [1, max_feats], nlevels in [1, 12], scaleFactor > 1");
+        return RGBDFE_E_ARG;
+    }
+    if (scaleFactor != 1.2f) {
+        // the reference's descriptor object is a default cv::ORB (scale 1.2f, Extractor.cpp:217): with another detector
+        // scale its compute() would sample a different pyramid than detect() used
+        c->set_error("cvorb_configure: the ORB/ORB pair of the reference is only consistent for scaleFactor == 1.2f");
+        return RGBDFE_E_ARG;
+    }
+    if (!c->cvorb)
+        c->cvorb = new CvOrbWorkspace();
+    CvOrbWorkspace* W = c->cvorb;
+    W->nfeatures = nfeatures, W->nlevels = nlevels, W->scaleFactor = scaleFactor;
+    W->configured = true;
+    W->cfg.w = W->cfg.h = 0; // tables are rebuilt on the next extraction
+    return RGBDFE_OK;
+}
+
+static int cvorb_prepare(rgbdfe_ctx* c, int w, int h)
+{
+    CvOrbWorkspace* W = c->cvorb;
+    if (W->cfg.w == w && W->cfg.h == h && W->slots == c->max_batch)
+        return RGBDFE_OK;
+    if (w > c->max_w || h > c->max_h || w > 4095 || h > 4095) {
+        c->set_error("cvorb: image larger than the context (or than 4095 px)");
+        return RGBDFE_E_ARG;
+    }
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    free_buffers(W);
+    CvCfg& C = W->cfg;
+    memset(&C, 0, sizeof(C));
+    C.nlevels = W->nlevels, C.nfeatures = W->nfeatures, C.w = w, C.h = h;
+    const double sf = (double)W->scaleFactor;
+    // nfeaturesPerLevel (orb.cpp computeKeyPoints)
+    {
+        const float factor = (float)(1.0 / sf);
+        float ndesired = W->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)W->nlevels));
+        int sum = 0;
+        for (int l = 0; l < W->nlevels - 1; l++) {
+            C.lv[l].quota = cv_round_f(ndesired);
+            sum += C.lv[l].quota;
+            ndesired *= factor;
+        }
+        C.lv[W->nlevels - 1].quota = std::max(W->nfeatures - sum, 0);
+    }
+    {
+        const int half = 15;
+        int umax[17] = { 0 };
+        int v, v0, vmax = (int)std::floor(half * std::sqrt(2.f) / 2 + 1), vmin = (int)std::ceil(half * std::sqrt(2.f) / 2);
+        for (v = 0; v <= vmax; ++v)
+            umax[v] = (int)std::nearbyint(std::sqrt((double)half * half - v * v));
+        for (v = half, v0 = 0; v >= vmin; --v) {
+            while (umax[v0] == umax[v0 + 1])
+                ++v0;
+            umax[v] = v0;
+            ++v0;
+        }
+        for (v = 0; v < 16; v++)
+            C.umax[v] = umax[v];
+    }
+    {
+        double t[7], sum = 0; // getGaussianKernel(7, 2, CV_32F)
+        for (int i = 0; i < 7; i++) {
+            const double x = i - 3.0;
+            t[i] = std::exp(-0.5 / 4.0 * x * x);
+            sum += t[i];
+        }
+        sum = 1. / sum;
+        for (int i = 0; i < 7; i++)
+            C.gk[i] = (float)(t[i] * sum);
+        const float s = 1.f / ((1 << 2) * 7 * 255.f);
+        C.harris_scale4 = s * s * s * s;
+    }
+    size_t pyr = 0, blur = 0;
+    int tiles = 0, cand = 0, out = 0, tab = 0;
+    for (int l = 0; l < C.nlevels; l++) {
+        CvLevel& L = C.lv[l];
+        L.scale = (float)std::pow(sf, (double)l);
+        L.inv_scale = 1.0f / L.scale;
+        L.w = cv_round_f((float)w * L.inv_scale), L.h = cv_round_f((float)h * L.inv_scale);
+        if (L.w < CV_RING + 2 || L.h < CV_RING + 2) { // the REFLECT_101 ring must fold at most once
+            c->set_error("cvorb: image too small for the pyramid");
+            return RGBDFE_E_ARG;
+        }
+        L.pstride = align_up(L.w + 2 * CV_RING, 64);
+        L.bstride = align_up(L.w, 64);
+        L.pyr_off = (unsigned)(pyr + (size_t)CV_RING * L.pstride + CV_RING);
+        pyr += (size_t)L.pstride * (L.h + 2 * CV_RING);
+        L.blur_off = (unsigned)blur;
+        blur += (size_t)L.bstride * align_up(L.h, CV_TH);
+        L.tile0 = tiles;
+        tiles += ((L.w + CV_TW - 1) / CV_TW) * ((L.h + CV_TH - 1) / CV_TH);
+        L.cand_off = cand;
+        L.cand_cap = std::min(65535, std::max(4096, L.w * L.h / 16));
+        cand += align_up(L.cand_cap, 16);
+        L.out_off = out;
+        L.out_cap = L.quota + 64;
+        out += L.out_cap;
+        L.vec_end = L.w / 32 * 32;
+        L.unr_end = L.vec_end + (L.w - L.vec_end) / 4 * 4;
+        L.tabx_off = tab;
+        tab += L.w;
+        L.taby_off = tab;
+        tab += L.h;
+    }
+    C.tiles = tiles, C.cand_total = cand, C.out_total = out;
+    W->pyr_slot = align_up((int)pyr, 256) + 256, W->blur_slot = align_up((int)blur, 256);
+    const int S = c->max_batch;
+    W->slots = S;
+    CUDA_TRY(c, dmalloc(&W->d_pyr, W->pyr_slot * S));
+    CUDA_TRY(c, dmalloc(&W->d_blur, W->blur_slot * S));
+    CUDA_TRY(c, dmalloc(&W->d_score, W->blur_slot * S));
+    CUDA_TRY(c, dmalloc(&W->d_cand, (size_t)cand * S * sizeof(unsigned)));
+    CUDA_TRY(c, dmalloc(&W->d_lr, (size_t)cand * S * 2 * sizeof(unsigned short)));
+    CUDA_TRY(c, dmalloc(&W->d_hkey, (size_t)cand * S * sizeof(HKey)));
+    CUDA_TRY(c, dmalloc(&W->d_hcount, (size_t)S * RGBDFE_MAX_LEVELS * sizeof(int)));
+    CUDA_TRY(c, dmalloc(&W->d_out, (size_t)out * S * sizeof(CvSel)));
+    CUDA_TRY(c, dmalloc(&W->d_out_count, (size_t)S * RGBDFE_MAX_LEVELS * sizeof(int)));
+    CUDA_TRY(c, dmalloc(&W->d_final, (size_t)out * S * sizeof(int)));
+    CUDA_TRY(c, dmalloc(&W->d_final_count, (size_t)S * sizeof(int)));
+    CUDA_TRY(c, dmalloc(&W->d_gscratch, (size_t)out * S * sizeof(HKey)));
+    CUDA_TRY(c, dmalloc(&W->d_tab_ofs, (size_t)tab * sizeof(int)));
+    CUDA_TRY(c, dmalloc(&W->d_tab_c1, (size_t)tab * sizeof(unsigned short)));
+    std::vector<int> ofs(tab, 0);
+    std::vector<unsigned short> c1(tab, 0);
+    for (int l = 1; l < C.nlevels; l++) {
+        exact_table(C.lv[l - 1].w, C.lv[l].w, &ofs[C.lv[l].tabx_off], &c1[C.lv[l].tabx_off]);
+        exact_table(C.lv[l - 1].h, C.lv[l].h, &ofs[C.lv[l].taby_off], &c1[C.lv[l].taby_off]);
+    }
+    CUDA_TRY(c, cudaMemcpy(W->d_tab_ofs, ofs.data(), (size_t)tab * sizeof(int), cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(W->d_tab_c1, c1.data(), (size_t)tab * sizeof(unsigned short), cudaMemcpyHostToDevice));
+    if (!W->d_pattern) {
+        CUDA_TRY(c, dmalloc(&W->d_pattern, 1024));
+        CUDA_TRY(c, cudaMemcpy(W->d_pattern, kBriefPattern, 1024, cudaMemcpyHostToDevice));
+    }
+    return RGBDFE_OK;
+}
+
+// The whole cv::ORB branch for `count` frames whose gray images are reachable from the device through `gray`.
+int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, int gray_stride, const FrameBatch& frames, bool unproject,
+    const ImgPtrs& depth, int depth_stride, const FramePrep& prep)
+{
+    CvOrbWorkspace* W = c->cvorb;
+    if (!W || !W->configured)
+        return RGBDFE_E_STATE;
+    int rc = cvorb_prepare(c, w, h);
+    if (rc != RGBDFE_OK)
+        return rc;
+    const CvCfg& C = W->cfg;
+    {
+        ProfScope prof(c, KID_PYRAMID);
+        for (int l = 0; l < C.nlevels; l++) {
+            const CvLevel& L = C.lv[l];
+            dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (L.h + 2 * CV_RING + 3) / 4, count);
+            if (l == 0)
+                k_cv_pyr_base<<<grd, blk, 0, c->stream>>>(C, gray, gray_stride, W->d_pyr, W->pyr_slot);
+            else
+                k_cv_pyr_level<<<grd, blk, 0, c->stream>>>(C, l, W->d_pyr, W->pyr_slot, W->d_tab_ofs, W->d_tab_c1);
+            c->launches++;
+        }
+    }
+    {
+        ProfScope prof(c, KID_FAST);
+        k_cv_fast<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot);
+        c->launches++;
+    }
+    {
+        ProfScope prof(c, KID_BLUR);
+        k_cv_blur<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_blur, W->blur_slot);
+        c->launches++;
+    }
+    {
+        ProfScope prof(c, KID_QUADTREE); // the selection stage takes the quadtree's place
+        const size_t smem = (size_t)CV_KCAP * 8 + (size_t)(h + 2) * sizeof(int);
+        static size_t configured[64] = { 0 };
+        if (smem > configured[c->device]) {
+            CUDA_TRY(c, cudaFuncSetAttribute(k_cv_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured[c->device] = smem;
+        }
+        k_cv_select<<<dim3(C.nlevels, count), CV_SEL_THREADS, smem, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot, W->d_cand,
+            W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count);
+        k_cv_gather<<<count, 256, 0, c->stream>>>(C, W->d_out, W->d_out_count, W->d_final, W->d_final_count, W->d_gscratch);
+        c->launches += 2;
+    }
+    {
+        ProfScope prof(c, KID_DESCRIBE);
+        const int warps = std::min(c->kp_cap, C.out_total);
+        k_cv_orient_describe<<<dim3((warps + 7) / 8, count), 256, 0, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_blur, W->blur_slot, W->d_out,
+            W->d_final, W->d_final_count, W->d_pattern, frames, depth, depth_stride, unproject ? 1 : 0, prep);
+        c->launches++;
+    }
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+// Test taps: level image / blurred level (tight w x h) and the Harris-stage list of slot 0 after the last extraction.
+int cvorb_stage_level(rgbdfe_ctx* c, int level, int which, uint8_t* dst, int dst_stride, int* w, int* h)
+{
+    CvOrbWorkspace* W = c->cvorb;
+    if (!W || W->cfg.w == 0 || level < 0 || level >= W->cfg.nlevels)
+        return RGBDFE_E_STATE;
+    const CvLevel& L = W->cfg.lv[level];
+    if (w)
+        *w = L.w;
+    if (h)
+        *h = L.h;
+    if (dst) {
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        if (which == 0)
+            CUDA_TRY(c, cudaMemcpy2D(dst, dst_stride, W->d_pyr + L.pyr_off, L.pstride, L.w, L.h, cudaMemcpyDeviceToHost));
+        else
+            CUDA_TRY(c, cudaMemcpy2D(dst, dst_stride, (which == 1 ? W->d_blur : W->d_score) + L.blur_off, L.bstride, L.w, L.h, cudaMemcpyDeviceToHost));
+    }
+    return RGBDFE_OK;
+}
+
+int cvorb_stage_harris(rgbdfe_ctx* c, int level, rgbdfe_keypoint* out, int cap, int* n)
+{
+    CvOrbWorkspace* W = c->cvorb;
+    if (!W || W->cfg.w == 0 || level < 0 || level >= W->cfg.nlevels || !n)
+        return RGBDFE_E_STATE;
+    const CvLevel& L = W->cfg.lv[level];
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int cnt = 0;
+    CUDA_TRY(c, cudaMemcpy(&cnt, W->d_hcount + level, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = cnt;
+    const int m = std::min(cnt, cap);
+    if (m > 0 && out) {
+        std::vector<HKey> tmp(m);
+        CUDA_TRY(c, cudaMemcpy(tmp.data(), W->d_hkey + L.cand_off, (size_t)m * sizeof(HKey), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < m; i++) {
+            out[i].x = (float)(tmp[i].xy & 0xffff);
+            out[i].y = (float)(tmp[i].xy >> 16);
+            out[i].size = 31 * L.scale;
+            out[i].angle = -1.f;
+            out[i].response = tmp[i].r;
+            out[i].octave = level;
+            out[i].class_id = -1;
+        }
+    }
+    return RGBDFE_OK;
+}
+
+} // namespace rgbdfe

@@ -227,6 +227,26 @@ class Context:
         self._chk(lib().rgbdfe_orb_stage_candidates(self.h, level, _p(out), cap, C.byref(n)))
         return out[: n.value].copy()
 
+    # ---- Extractor(ORB, ORB): the cv::ORB branch (row N3) ----
+    def cvorb_configure(self, nfeatures=1000, scale=1.2, nlevels=8):
+        """Extractor(ORB, ORB).setParameters: the extraction entry points now run cv::ORB (Extractor.cpp:55-59,163-166)."""
+        self._chk(lib().rgbdfe_cvorb_configure(self.h, nfeatures, C.c_float(scale), nlevels))
+        self.nlevels = nlevels
+
+    def cvorb_stage_level(self, level, which=0):
+        w, h = C.c_int(), C.c_int()
+        self._chk(lib().rgbdfe_cvorb_stage_level(self.h, level, which, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        self._chk(lib().rgbdfe_cvorb_stage_level(self.h, level, which, _p(out), out.strides[0], C.byref(w), C.byref(h)))
+        return out
+
+    def cvorb_stage_harris(self, level):
+        cap = 1 << 16
+        out = np.zeros(cap, KP_DTYPE)
+        n = C.c_int()
+        self._chk(lib().rgbdfe_cvorb_stage_harris(self.h, level, _p(out), cap, C.byref(n)))
+        return out[: n.value].copy()
+
     # ---- Matcher ----
     def match(self, qdesc, tdesc, q_outlier, q_xyz, t_xyz, ratio=0.9, discard_outliers=True):
         qdesc = np.ascontiguousarray(qdesc, np.uint8)

@@ -66,6 +66,9 @@ def lib():
         L.orc_orb_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
         L.orc_orb_destroy.argtypes = [C.c_void_p]
         L.orc_mahal2.restype = C.c_double
+        L.orc_cvorb_create.restype = C.c_void_p
+        L.orc_cvorb_create.argtypes = [C.c_int, C.c_float, C.c_int]
+        L.orc_cvorb_destroy.argtypes = [C.c_void_p]
         for name in (
             "orc_orb_extract",
             "orc_orb_tables",
@@ -129,6 +132,63 @@ def knn2(q, t):
     dist = np.empty((len(q), 2), np.int32)
     lib().orc_knn2_hamming(_p(q), len(q), _p(t), len(t), _p(idx), _p(dist))
     return idx, dist
+
+
+def resize_linear_exact(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_exact(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def gauss7_float(img):
+    """the blur cv::ORB applies to its pyramid levels (float sepFilter2D path, oracle/cvorb.cpp)"""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    dst = np.empty_like(img)
+    lib().orc_gauss7_float(_p(img), w, h, img.strides[0], _p(dst), w)
+    return dst
+
+
+class CvOrb:
+    """Extractor(ORB, ORB): cv::ORB::create(nfeatures, scale, nlevels).detect + cv::ORB::create().compute
+    (Features/Extractor.cpp:55-59,163-166,216-218), restated in oracle/cvorb.cpp."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8):
+        self.h = C.c_void_p(lib().orc_cvorb_create(nfeatures, scale, nlevels))
+        self.nlevels = nlevels
+        self.cap = 4 * nfeatures + 64
+
+    def extract(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = lib().orc_cvorb_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc), self.cap)
+        assert n <= self.cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level_info(self, level):
+        v = [C.c_int() for _ in range(5)]
+        lib().orc_cvorb_level_size(self.h, level, *[C.byref(x) for x in v])
+        return dict(zip(("w", "h", "quota", "n_fast", "n_harris"), (x.value for x in v)))
+
+    def level_image(self, level, blurred=False):
+        i = self.level_info(level)
+        out = np.empty((i["h"], i["w"]), np.uint8)
+        lib().orc_cvorb_level_image(self.h, level, _p(out), int(blurred))
+        return out
+
+    def level_harris(self, level):
+        i = self.level_info(level)
+        out = np.zeros(max(i["n_harris"], 1), KP_DTYPE)
+        n = lib().orc_cvorb_level_harris(self.h, level, _p(out), len(out))
+        return out[:n].copy()
+
+    def __del__(self):
+        try:
+            lib().orc_cvorb_destroy(self.h)
+        except Exception:
+            pass
 
 
 class Rng:
