@@ -199,6 +199,73 @@ def projection_leg(rgbdfe, ctx, fr, cam, B, no_cpu):
     return out
 
 
+def cvorb_leg(rgbdfe, torch, local_rank, gray_d, depth_d, cam, inv_factor, B, nfeat, no_cpu, frames):
+    """Row N3: Extractor(ORB, ORB) = cv::ORB with Harris scoring (Features/Extractor.cpp:55-59,163-166), batched
+    extraction of device-resident frames through rgbdfe_frames_extract_raw after rgbdfe_cvorb_configure."""
+    L = rgbdfe.lib()
+    nseq = 4
+    ctxs = [rgbdfe.Context(local_rank, W, H, nfeat, B) for _ in range(nseq)]
+    frs = []
+    for cx in ctxs:
+        cx.cvorb_configure(nfeat, 1.2, 8)
+        frs.append([rgbdfe.Frame(cx) for _ in range(B)])
+
+    def step():
+        for k, (cx, fr) in enumerate(zip(ctxs, frs)):
+            idx = [(k * 17 + i) % gray_d.shape[0] for i in range(B)]
+            fa = (C.c_void_p * B)(*[f.h for f in fr])
+            gp = (C.c_void_p * B)(*[gray_d[i].data_ptr() for i in idx])
+            dp = (C.c_void_p * B)(*[depth_d[i].data_ptr() for i in idx])
+            cx._chk(L.rgbdfe_frames_extract_raw(cx.h, fa, B, gp, W, H, W, dp, W, C.c_float(inv_factor), C.c_float(cam["fx"]),
+                                                C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = 6
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    for cx in ctxs:
+        cx.sync()
+    dt = time.perf_counter() - t0
+    out = {"value": steps * nseq * B / dt, "unit": "frames/s",
+           "what": f"rgbdfe_cvorb_configure({nfeat}, 1.2, 8) + rgbdfe_frames_extract_raw: cv::ORB detect + compute + back-projection of "
+                   f"device-resident 640x480 frames, {nseq} contexts x {B}-frame batches, host clock around enqueue + sync",
+           "keypoints_per_frame": float(np.mean([len(frs[0][i].download()[0]) for i in range(4)]))}
+    # per-kernel times of one batch (CUDA events on the context's stream)
+    cx = ctxs[0]
+    L.rgbdfe_profile_name.restype = C.c_char_p
+    cx._chk(L.rgbdfe_profile_enable(cx.h, 1))
+    for _ in range(2):
+        step()
+    a_ms, a_cnt = (C.c_double * 16)(), (C.c_longlong * 16)()
+    cx._chk(L.rgbdfe_profile_read(cx.h, a_ms, a_cnt, 16))
+    cx._chk(L.rgbdfe_profile_enable(cx.h, 0))
+    names = {0: "k_cv_pyr_base+level(x7)", 1: "k_cv_fast", 2: "k_cv_blur", 3: "k_cv_select+gather", 4: "k_cv_orient_describe"}
+    out["ms_per_batch"] = {names[i]: a_ms[i] / max(a_cnt[i], 1) for i in names}
+    if not no_cpu:
+        try:
+            import cv2
+
+            cv2.setNumThreads(1)
+            det, des = cv2.ORB_create(nfeat, 1.2, 8), cv2.ORB_create()
+            t0 = time.perf_counter()
+            for i in range(20):
+                k = det.detect(frames[i][0], None)
+                des.compute(frames[i][0], k)
+            out["cpu_opencv_frames_per_s"] = 20 / (time.perf_counter() - t0)
+            out["cpu_note"] = "the real OpenCV (cv2 4.13, 1 thread): ORB_create(n, 1.2, 8).detect + ORB_create().compute, 20 frames"
+        except Exception:
+            pass
+    for cx, fr in zip(ctxs, frs):
+        for f in fr:
+            f.close()
+        cx.close()
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -529,6 +596,12 @@ def main():
     except Exception as ex:
         frame_prep = {"error": str(ex)[:200]}
 
+    # ---- row N3: the cv::ORB branch of Extractor ----
+    try:
+        cvorb = cvorb_leg(rgbdfe, torch, local_rank, gray_d, depth_d, cam, inv_factor, B, NFEAT, args.no_cpu, frames)
+    except Exception as ex:
+        cvorb = {"error": str(ex)[:200]}
+
     # ---- sharded loop-pair verification (the part of the path that shards), N >= 1 ----
     verify = None
     try:
@@ -601,7 +674,7 @@ def main():
                     "d2h_bytes_per_step": S * B * 84,
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep, "projection_match": projection,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
         }))
     for q in seqs:
         q.close()

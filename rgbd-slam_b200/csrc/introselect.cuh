@@ -227,6 +227,161 @@ __device__ int warp_partition(T* base, int first, int last, unsigned short* Lpos
     __syncwarp();
     return first + nR; // every element passing pred ends up in front
 }
+// ---- CTA-wide forms: every thread of the CTA calls them (barriers inside); s_w = int[68] of shared memory. ----
+// The warps scan disjoint chunks of the range: stopper counts per chunk, a prefix over the chunks, then the positions
+// are written in ascending order for both lists (the R list is read back to front: R_desc[k] = Rasc[nR - 1 - k]).
+#define CTA_PARTITION_MIN 1024 // shorter ranges are partitioned by warp 0 alone
+template <class FL, class FR>
+__device__ __forceinline__ void cta_stopper_lists(int first, int l, int f, unsigned short* Lpos, unsigned short* Rasc, int* s_w, FL isLf, FR isRf,
+    int* nL_out, int* nR_out)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int m = l - first;
+    const int cs = (((m + nwarps - 1) / nwarps) + 31) & ~31;
+    const int cb = first + warp * cs, ce = min(cb + cs, l);
+    int cl = 0, cr = 0;
+    for (int x0 = cb; x0 < ce; x0 += 32) {
+        const int x = x0 + lane;
+        cl += __popc(__ballot_sync(0xffffffffu, x < ce && isLf(x)));
+        cr += __popc(__ballot_sync(0xffffffffu, x < ce && isRf(x)));
+    }
+    if (lane == 0) {
+        s_w[warp] = cl;
+        s_w[32 + warp] = cr;
+    }
+    if (tid == 0)
+        s_w[64] = 0x7fffffff;
+    __syncthreads();
+    int baseL = 0, baseR = 0, nL = 0, nR = 0;
+    for (int w = 0; w < nwarps; w++) {
+        const int a = s_w[w], b = s_w[32 + w];
+        if (w < warp) {
+            baseL += a;
+            baseR += b;
+        }
+        nL += a;
+        nR += b;
+    }
+    const unsigned lt = (1u << lane) - 1;
+    for (int x0 = cb; x0 < ce; x0 += 32) {
+        const int x = x0 + lane;
+        const bool isL = x < ce && isLf(x), isR = x < ce && isRf(x);
+        const unsigned bl = __ballot_sync(0xffffffffu, isL), br = __ballot_sync(0xffffffffu, isR);
+        if (isL)
+            Lpos[baseL + __popc(bl & lt)] = (unsigned short)(x - f);
+        if (isR)
+            Rasc[baseR + __popc(br & lt)] = (unsigned short)(x - f);
+        baseL += __popc(bl);
+        baseR += __popc(br);
+    }
+    __syncthreads();
+    *nL_out = nL;
+    *nR_out = nR;
+}
+
+// number of leading k with Lpos[k] < R_desc[k] (the swaps the sequential loop performs), by all threads
+__device__ __forceinline__ int cta_swap_count(const unsigned short* Lpos, const unsigned short* Rasc, int nL, int nR, int* s_w)
+{
+    const int nmin = min(nL, nR);
+    for (int k = threadIdx.x; k < nmin; k += blockDim.x)
+        if (!(Lpos[k] < Rasc[nR - 1 - k]))
+            atomicMin(&s_w[64], k);
+    __syncthreads();
+    return min(s_w[64], nmin);
+}
+
+template <class T, class C>
+__device__ int cta_partition_pivot(T* a, int f, int l, unsigned short* Lpos, unsigned short* Rasc, int* s_w, C comp)
+{
+    if (threadIdx.x == 0) {
+        const int mid = f + (l - f) / 2;
+        move_median_to_first_(a + f, a + f + 1, a + mid, a + l - 1, comp);
+    }
+    __syncthreads();
+    const T p = a[f];
+    int nL, nR;
+    cta_stopper_lists(f + 1, l, f, Lpos, Rasc, s_w, [&](int x) { return !comp(a[x], p); }, [&](int x) { return !comp(p, a[x]); }, &nL, &nR);
+    const int K = cta_swap_count(Lpos, Rasc, nL, nR, s_w);
+    const int Lk = K < nL ? f + Lpos[K] : l;
+    const int Rprev = K > 0 ? f + Rasc[nR - K] : l;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const int x = f + Lpos[k], y = f + Rasc[nR - 1 - k];
+        const T t = a[x];
+        a[x] = a[y];
+        a[y] = t;
+    }
+    __syncthreads();
+    return min(Lk, Rprev);
+}
+
+template <class T, class C>
+__device__ void cta_nth_element(T* base, int nth, int n, unsigned short* Lpos, unsigned short* Rpos, int* s_w, C comp)
+{
+    if (n == 0 || nth == n)
+        return;
+    int lg = 0;
+    for (int t = n; t > 1; t >>= 1)
+        lg++;
+    int depth = 2 * lg, f = 0, l = n, it = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    while (l - f > 3) {
+        if (depth == 0) {
+            if (threadIdx.x == 0) {
+                heap_select_(base + f, base + nth + 1, base + l, comp);
+                isort_swap(base[f], base[nth]);
+            }
+            __syncthreads();
+            return;
+        }
+        --depth;
+        int cut;
+        if (l - f >= CTA_PARTITION_MIN)
+            cut = cta_partition_pivot(base, f, l, Lpos, Rpos, s_w, comp);
+        else {
+            if (warp == 0) {
+                cut = warp_partition_pivot(base, f, l, Lpos, Rpos, lane, comp);
+                if (lane == 0)
+                    s_w[65 + (it & 1)] = cut;
+            }
+            __syncthreads();
+            cut = s_w[65 + (it & 1)];
+            it++;
+        }
+        if (cut <= nth)
+            f = cut;
+        else
+            l = cut;
+    }
+    if (threadIdx.x == 0)
+        insertion_sort_(base + f, base + l, comp);
+    __syncthreads();
+}
+
+template <class T, class P>
+__device__ int cta_partition(T* base, int first, int last, unsigned short* Lpos, unsigned short* Rasc, int* s_w, P pred)
+{
+    if (last - first < CTA_PARTITION_MIN) {
+        if ((threadIdx.x >> 5) == 0) {
+            const int e = warp_partition(base, first, last, Lpos, Rasc, threadIdx.x & 31, pred);
+            if (threadIdx.x == 0)
+                s_w[67] = e;
+        }
+        __syncthreads();
+        return s_w[67];
+    }
+    int nL, nR;
+    cta_stopper_lists(first, last, first, Lpos, Rasc, s_w, [&](int x) { return !pred(base[x]); }, [&](int x) { return pred(base[x]); }, &nL, &nR);
+    const int K = cta_swap_count(Lpos, Rasc, nL, nR, s_w);
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const int x = first + Lpos[k], y = first + Rasc[nR - 1 - k];
+        const T t = base[x];
+        base[x] = base[y];
+        base[y] = t;
+    }
+    __syncthreads();
+    return first + nR;
+}
 #endif
+
 
 } // namespace rgbdfe

@@ -27,9 +27,7 @@
 #define CV_FAST_TH 20
 #define CV_TW 64
 #define CV_TH 32
-#define CV_KCAP 24576 // FAST candidates of one level handled in shared memory (else in the global scratch)
-#define CV_HCAP 12288 // Harris-stage entries handled in shared memory
-#define CV_SEL_THREADS 1024
+#define CV_SEL_THREADS 512
 
 struct CvLevel {
     int w, h, pstride, bstride;
@@ -189,22 +187,75 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
         *reinterpret_cast<unsigned*>(&s_S[r][4 * q]) = 0u;
     }
     __syncthreads();
-    // strengths on the emit region + 1 px halo, inside cv::FAST's detection region [3, w-3) x [3, h-3)
-    for (int i = tid; i < (CV_TH + 2) * (CV_TW + 2); i += 256) {
-        const int rr = i / (CV_TW + 2), cc = i - rr * (CV_TW + 2);
-        const int r = rr + 3, c = cc + 3; // window coordinates
-        const int x = x0 - 4 + c, y = y0 - 4 + r;
-        if (x < 3 || x >= L.w - 3 || y < 3 || y >= L.h - 3)
-            continue;
-        const uint8_t* p = &s_img[r][c];
-        // any 9-arc of the 16-ring holds at least two of the four compass pixels
-        const int v = p[0], hi = v + CV_FAST_TH, lo = v - CV_FAST_TH;
-        const int a0 = p[3 * PITCH], a4 = p[3], a8 = p[-3 * PITCH], a12 = p[-3];
-        const int nb = (a0 > hi) + (a4 > hi) + (a8 > hi) + (a12 > hi), nd = (a0 < lo) + (a4 < lo) + (a8 < lo) + (a12 < lo);
-        if (nb < 2 && nd < 2)
-            continue;
-        const int S = fast_strength(p, PITCH, CV_FAST_TH);
-        s_S[r][c] = (uint8_t)min(S, 255);
+    // Phase 1: the 4-opposite-pair necessary test (fast_candidate2, four pixels per thread in 16-bit lanes) on the emit
+    // region + 1 px halo, inside cv::FAST's detection region [3, w-3) x [3, h-3); survivors are compacted with ballots.
+    __shared__ unsigned short s_cand[(CV_TH + 2) * (PITCH)];
+    __shared__ int s_ncand;
+    if (tid == 0)
+        s_ncand = 0;
+    __syncthreads();
+    {
+        constexpr int GPR = PITCH / 4;          // 18 word groups per window row
+        constexpr int NG = (CV_TH + 2) * GPR;   // rows 3 .. 36
+        constexpr int RW = PITCH / 4;
+        const unsigned c1 = 0x7fff7fffu - ((unsigned)CV_FAST_TH | (unsigned)CV_FAST_TH << 16);
+        const unsigned lt = (1u << (tid & 31)) - 1;
+        for (int i0 = (tid & ~31); i0 < NG; i0 += 256) { // warp-uniform trip count
+            const int i = i0 + (tid & 31);
+            unsigned rA = 0, rB = 0;
+            int r = 0, g = 0;
+            if (i < NG) {
+                r = 3 + i / GPR;
+                g = i - (r - 3) * GPR;
+                { // groups 0 and 17 read one word across the row end (still inside s_img); only their columns 3 / 68 are kept
+                    const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g;
+                    const unsigned cm = w[-1], cc = w[0], cp = w[1];
+                    const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
+                    const unsigned um = w[-2 * RW - 1], uc = w[-2 * RW], upn = w[-2 * RW + 1];
+                    const unsigned dm = w[2 * RW - 1], dc = w[2 * RW], dpn = w[2 * RW + 1];
+                    const unsigned u4 = __funnelshift_r(cc, cp, 24), u12 = __funnelshift_r(cm, cc, 8);
+                    const unsigned u2 = __funnelshift_r(dc, dpn, 16), u14 = __funnelshift_r(dm, dc, 16);
+                    const unsigned u6 = __funnelshift_r(uc, upn, 16), u10 = __funnelshift_r(um, uc, 16);
+                    rA = fast_candidate2(lanes_lo(cc), lanes_lo(dn3), lanes_lo(up3), lanes_lo(u4), lanes_lo(u12), lanes_lo(u2), lanes_lo(u10),
+                        lanes_lo(u6), lanes_lo(u14), c1);
+                    rB = fast_candidate2(lanes_hi(cc), lanes_hi(dn3), lanes_hi(up3), lanes_hi(u4), lanes_hi(u12), lanes_hi(u2), lanes_hi(u10),
+                        lanes_hi(u6), lanes_hi(u14), c1);
+                }
+            }
+            // window column c = 4g + j is level column x0 - 4 + c; window row r is level row y0 - 4 + r
+            const int y = y0 - 4 + r, xb = x0 - 4 + 4 * g;
+            const bool yok = y >= 3 && y < L.h - 3;
+            auto ok = [&](int j) { const int c = 4 * g + j, x = xb + j; return yok && c >= 3 && c < CV_TW + 5 && x >= 3 && x < L.w - 3; };
+            const bool k0 = (rA & 0x8000u) && ok(0), k1 = (rA >> 31) && ok(1), k2 = (rB & 0x8000u) && ok(2), k3 = (rB >> 31) && ok(3);
+            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+            const unsigned b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
+            const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
+            if (b0 | b1 | b2 | b3) {
+                int base = 0;
+                if ((tid & 31) == 0)
+                    base = atomicAdd(&s_ncand, n0 + n1 + n2 + n3);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const int key = r << 8 | (4 * g);
+                if (k0)
+                    s_cand[base + __popc(b0 & lt)] = (unsigned short)key;
+                if (k1)
+                    s_cand[base + n0 + __popc(b1 & lt)] = (unsigned short)(key + 1);
+                if (k2)
+                    s_cand[base + n0 + n1 + __popc(b2 & lt)] = (unsigned short)(key + 2);
+                if (k3)
+                    s_cand[base + n0 + n1 + n2 + __popc(b3 & lt)] = (unsigned short)(key + 3);
+            }
+        }
+    }
+    __syncthreads();
+    // Phase 2: corner strength of the candidates (dense warps)
+    {
+        const int ncand = s_ncand;
+        for (int i = tid; i < ncand; i += 256) {
+            const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
+            const int S = fast_strength(&s_img[r][c], PITCH, CV_FAST_TH);
+            s_S[r][c] = (uint8_t)min(S, 255);
+        }
     }
     __syncthreads();
     // NMS + border filter, 4 pixels per thread, one 32-bit store
@@ -246,7 +297,7 @@ __global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C
     const int slot = blockIdx.y, tid = threadIdx.x;
     constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 6;
     __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
-    __shared__ float s_h[ROWS][CV_TW];
+    __shared__ __align__(16) float s_h[ROWS][CV_TW];
     const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
     const int max_word = (L.pstride - CV_RING - 4) >> 2;
     for (int i = tid; i < ROWS * (PITCH / 4); i += 256) { // rows y0-3 .. y0+34, columns x0-4 .. x0+67
@@ -256,41 +307,64 @@ __global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C
         *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
     }
     __syncthreads();
-    for (int i = tid; i < ROWS * CV_TW; i += 256) {
-        const int r = i / CV_TW, c = i - r * CV_TW;
-        const int x = x0 + c;
-        const uint8_t* p = &s_img[r][c + 1]; // column x - 3
-        float acc = __fmul_rn(C.gk[0], (float)p[0]);
+    // row pass: 4 adjacent outputs per thread from 3 staged words; a group of 4 never straddles vec_end / unr_end
+    for (int i = tid; i < ROWS * (CV_TW / 4); i += 256) {
+        const int r = i >> 4, q = i & 15;
+        const unsigned* row = reinterpret_cast<const unsigned*>(&s_img[r][0]);
+        const unsigned w0 = row[q], w1 = row[q + 1], w2 = row[q + 2];
+        float p[12];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            p[j] = (float)((w0 >> (8 * j)) & 0xffu);
+            p[4 + j] = (float)((w1 >> (8 * j)) & 0xffu);
+            p[8 + j] = (float)((w2 >> (8 * j)) & 0xffu);
+        }
+        const int x = x0 + 4 * q;
+        float acc[4];
         if (x < L.vec_end || x >= L.unr_end) {
 #pragma unroll
-            for (int j = 1; j < 7; j++)
-                acc = __fmaf_rn(C.gk[j], (float)p[j], acc);
+            for (int j = 0; j < 4; j++) {
+                acc[j] = __fmul_rn(C.gk[0], p[j + 1]); // staged column c + 1 is level column x - 3
+#pragma unroll
+                for (int t = 1; t < 7; t++)
+                    acc[j] = __fmaf_rn(C.gk[t], p[j + 1 + t], acc[j]);
+            }
         } else {
 #pragma unroll
-            for (int j = 1; j < 7; j++)
-                acc = __fadd_rn(acc, __fmul_rn(C.gk[j], (float)p[j]));
+            for (int j = 0; j < 4; j++) {
+                acc[j] = __fmul_rn(C.gk[0], p[j + 1]);
+#pragma unroll
+                for (int t = 1; t < 7; t++)
+                    acc[j] = __fadd_rn(acc[j], __fmul_rn(C.gk[t], p[j + 1 + t]));
+            }
         }
-        s_h[r][c] = acc;
+        *reinterpret_cast<float4*>(&s_h[r][4 * q]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    }
+    __syncthreads();
+    // column pass: one thread = one column x 8 output rows (14 row sums held in registers); results staged as bytes
+    uint8_t(*s_out)[CV_TW] = reinterpret_cast<uint8_t(*)[CV_TW]>(&s_img[0][0]); // the staged image is dead
+    {
+        const int c = tid & 63, band = tid >> 6;
+        float v[14];
+#pragma unroll
+        for (int k = 0; k < 14; k++)
+            v[k] = s_h[band * 8 + k][c];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            float acc = __fmul_rn(C.gk[3], v[k + 3]);
+#pragma unroll
+            for (int t = 1; t <= 3; t++)
+                acc = __fmaf_rn(C.gk[3 + t], __fadd_rn(v[k + 3 + t], v[k + 3 - t]), acc);
+            s_out[band * 8 + k][c] = (uint8_t)min(max(__float2int_rn(acc), 0), 255);
+        }
     }
     __syncthreads();
     uint8_t* out = blur + slot * blur_slot + L.blur_off;
     for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
-        const int rr = i / (CV_TW / 4), q = i - rr * (CV_TW / 4);
+        const int rr = i >> 4, q = i & 15;
         const int y = y0 + rr;
-        if (y >= L.h)
-            continue;
-        unsigned word = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int c = 4 * q + j;
-            float acc = __fmul_rn(C.gk[3], s_h[rr + 3][c]);
-#pragma unroll
-            for (int k = 1; k <= 3; k++)
-                acc = __fmaf_rn(C.gk[3 + k], __fadd_rn(s_h[rr + 3 + k][c], s_h[rr + 3 - k][c]), acc);
-            const int v = min(max(__float2int_rn(acc), 0), 255);
-            word |= (unsigned)v << (8 * j);
-        }
-        *reinterpret_cast<unsigned*>(out + (size_t)y * L.bstride + x0 + 4 * q) = word;
+        if (y < L.h)
+            *reinterpret_cast<unsigned*>(out + (size_t)y * L.bstride + x0 + 4 * q) = *reinterpret_cast<const unsigned*>(&s_out[rr][4 * q]);
     }
 }
 
@@ -302,50 +376,139 @@ struct HarrisGreater {
     __device__ bool operator()(const HKey& a, const HKey& b) const { return a.r > b.r; }
 };
 
-// cv::KeyPointsFilter::retainBest by warp 0 of the CTA; returns the new size (valid in every lane of warp 0).
+// cv::KeyPointsFilter::retainBest by the whole CTA (every thread calls it); returns the new size.
 template <class T, class C, class P>
-__device__ int warp_retain_best(T* a, int n, int n_points, unsigned short* Lpos, unsigned short* Rpos, int lane, C comp, P make_pred)
+__device__ int cta_retain_best(T* a, int n, int n_points, unsigned short* Lpos, unsigned short* Rpos, int* s_w, C comp, P make_pred)
 {
     if (n_points < 0 || n <= n_points)
         return n;
     if (n_points == 0)
         return 0;
-    warp_nth_element(a, n_points - 1, n, Lpos, Rpos, lane, comp);
+    cta_nth_element(a, n_points - 1, n, Lpos, Rpos, s_w, comp);
     const T amb = a[n_points - 1];
-    return warp_partition(a, n_points, n, Lpos, Rpos, lane, make_pred(amb));
+    return cta_partition(a, n_points, n, Lpos, Rpos, s_w, make_pred(amb));
 }
 
-// One CTA per (level, frame).  Dynamic shared memory: keys[KCAP] u32 | Lpos[KCAP] u16 | Rpos[KCAP] u16 | rowoff[h + 1]
-__global__ void __launch_bounds__(CV_SEL_THREADS) k_cv_select(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+__device__ __forceinline__ int cv_nz(unsigned v) { return ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0); }
+__device__ __forceinline__ int cv_nz4(const uint4& v) { return cv_nz(v.x) + cv_nz(v.y) + cv_nz(v.z) + cv_nz(v.w); }
+
+// Row-major compaction of a level's score map.  A lane owns UPL consecutive 16-byte units of a row (so one warp scan
+// per row keeps the order) and a warp keeps R = 8 / UPL rows in flight to overlap the memory latency.
+// Pass 1 leaves the per-row counts in s_rowoff; pass 2 (after the scan) writes the packed candidates.
+template <int UPL>
+__device__ void cv_count_rows(const uint8_t* sc, int bstride, int h, int units, int* s_rowoff, int warp, int nwarps, int lane)
+{
+    constexpr int R = 8 / UPL;
+    const int ua = lane * UPL;
+    for (int yb = warp * R; yb < h; yb += nwarps * R) {
+        uint4 seg[R][UPL];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const int y = yb + r;
+            const bool in = y >= CV_EDGE && y < h - CV_EDGE; // rows outside the border filter hold zeros
+#pragma unroll
+            for (int k = 0; k < UPL; k++)
+                seg[r][k] = (in && ua + k < units) ? reinterpret_cast<const uint4*>(sc + (size_t)y * bstride)[ua + k] : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            int cnt = 0;
+#pragma unroll
+            for (int k = 0; k < UPL; k++)
+                cnt += cv_nz4(seg[r][k]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+            if (lane == 0 && yb + r < h)
+                s_rowoff[yb + r] = cnt;
+        }
+    }
+}
+
+template <int UPL>
+__device__ void cv_emit_rows(const uint8_t* sc, int bstride, int h, int units, const int* s_rowoff, unsigned* keys, int warp, int nwarps, int lane)
+{
+    constexpr int R = 8 / UPL;
+    const int ua = lane * UPL;
+    for (int yb = warp * R; yb < h; yb += nwarps * R) {
+        uint4 seg[R][UPL];
+        const int last = min(yb + R, h);
+        if (s_rowoff[last] == s_rowoff[yb])
+            continue;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const int y = yb + r;
+            const bool in = y < h && s_rowoff[min(y + 1, h)] != s_rowoff[min(y, h)];
+#pragma unroll
+            for (int k = 0; k < UPL; k++)
+                seg[r][k] = (in && ua + k < units) ? reinterpret_cast<const uint4*>(sc + (size_t)y * bstride)[ua + k] : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const int y = yb + r;
+            if (y >= h)
+                break;
+            int c = 0;
+#pragma unroll
+            for (int k = 0; k < UPL; k++)
+                c += cv_nz4(seg[r][k]);
+            int inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o)
+                    inc += u;
+            }
+            int w = s_rowoff[y] + inc - c;
+            if (c) {
+#pragma unroll
+                for (int k = 0; k < UPL; k++) {
+                    const unsigned vv[4] = { seg[r][k].x, seg[r][k].y, seg[r][k].z, seg[r][k].w };
+#pragma unroll
+                    for (int m = 0; m < 4; m++)
+                        if (vv[m]) {
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                const unsigned bb = (vv[m] >> (8 * j)) & 0xffu;
+                                if (bb)
+                                    keys[w++] = bb << 24 | (unsigned)y << 12 | (unsigned)(16 * (ua + k) + 4 * m + j);
+                            }
+                        }
+                }
+            }
+        }
+    }
+}
+
+// One CTA per (level, frame).  Dynamic shared memory: keys[kcap] u32 | Lpos[kcap] u16 | Rpos[kcap] u16 | rowoff[h + 1];
+// kcap = FAST candidates of one level handled in shared memory (sized from the image so that several CTAs share an SM);
+// a level with more candidates works in the global scratch instead.  The Harris stage reuses the key area (kcap / 2 entries).
+__global__ void __launch_bounds__(CV_SEL_THREADS, 2) k_cv_select(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     const uint8_t* __restrict__ score, size_t score_slot, unsigned* __restrict__ cand_all, unsigned short* __restrict__ lr_all,
-    HKey* __restrict__ hkey_all, int* __restrict__ hcount, CvSel* __restrict__ out_all, int* __restrict__ out_count)
+    HKey* __restrict__ hkey_all, int* __restrict__ hcount, CvSel* __restrict__ out_all, int* __restrict__ out_count, int kcap, int phase_stop)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned* s_keys = reinterpret_cast<unsigned*>(smem);
-    unsigned short* s_L = reinterpret_cast<unsigned short*>(smem + (size_t)CV_KCAP * 4);
-    unsigned short* s_R = s_L + CV_KCAP;
-    int* s_rowoff = reinterpret_cast<int*>(smem + (size_t)CV_KCAP * 8);
+    unsigned short* s_L = reinterpret_cast<unsigned short*>(smem + (size_t)kcap * 4);
+    unsigned short* s_R = s_L + kcap;
+    int* s_rowoff = reinterpret_cast<int*>(smem + (size_t)kcap * 8);
     __shared__ int s_n, s_carry;
+    __shared__ int s_w[68];
     const int level = blockIdx.x, slot = blockIdx.y;
     const CvLevel& L = C.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = CV_SEL_THREADS / 32;
     const uint8_t* sc = score + slot * score_slot + L.blur_off;
-    const int words = (L.w + 3) >> 2;
 
     // ---- row-major compaction of the score map (cv::FAST emits keypoints row by row) ----
-    for (int y = warp; y < L.h; y += nwarps) {
-        int cnt = 0;
-        const unsigned* row = reinterpret_cast<const unsigned*>(sc + (size_t)y * L.bstride);
-        for (int q = lane; q < words; q += 32) {
-            const unsigned v = row[q];
-            cnt += ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        if (lane == 0)
-            s_rowoff[y] = cnt;
-    }
+    const int units = (L.w + 15) >> 4, upl = (units + 31) >> 5; // 16-byte units per row / per lane (<= 8 for w <= 4095)
+    if (upl <= 1)
+        cv_count_rows<1>(sc, L.bstride, L.h, units, s_rowoff, warp, nwarps, lane);
+    else if (upl <= 2)
+        cv_count_rows<2>(sc, L.bstride, L.h, units, s_rowoff, warp, nwarps, lane);
+    else if (upl <= 4)
+        cv_count_rows<4>(sc, L.bstride, L.h, units, s_rowoff, warp, nwarps, lane);
+    else
+        cv_count_rows<8>(sc, L.bstride, L.h, units, s_rowoff, warp, nwarps, lane);
     if (tid == 0)
         s_carry = 0;
     __syncthreads();
@@ -376,109 +539,98 @@ __global__ void __launch_bounds__(CV_SEL_THREADS) k_cv_select(const __grid_const
     if (overflow)
         n = 0; // reported through out_count = -1
     unsigned* g_keys = cand_all + (size_t)slot * C.cand_total + L.cand_off;
-    const bool in_smem = n <= CV_KCAP;
+    const bool in_smem = n <= kcap;
     unsigned* keys = in_smem ? s_keys : g_keys;
     unsigned short* Lpos = in_smem ? s_L : lr_all + ((size_t)slot * 2) * C.cand_total + L.cand_off;
     unsigned short* Rpos = in_smem ? s_R : lr_all + ((size_t)slot * 2 + 1) * C.cand_total + L.cand_off;
     if (n > 0) {
-        for (int y = warp; y < L.h; y += nwarps) {
-            int pos = s_rowoff[y];
-            if (s_rowoff[y + 1] == pos)
-                continue;
-            const unsigned* row = reinterpret_cast<const unsigned*>(sc + (size_t)y * L.bstride);
-            for (int q0 = 0; q0 < words; q0 += 32) {
-                const int q = q0 + lane;
-                const unsigned v = q < words ? row[q] : 0u;
-                const int c = ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0);
-                int inc = c;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int u = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o)
-                        inc += u;
-                }
-                int w = pos + inc - c;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const unsigned b = (v >> (8 * j)) & 0xffu;
-                    if (b)
-                        keys[w++] = b << 24 | (unsigned)y << 12 | (unsigned)(4 * q + j);
-                }
-                pos += __shfl_sync(0xffffffffu, inc, 31);
-            }
-        }
+        if (upl <= 1)
+            cv_emit_rows<1>(sc, L.bstride, L.h, units, s_rowoff, keys, warp, nwarps, lane);
+        else if (upl <= 2)
+            cv_emit_rows<2>(sc, L.bstride, L.h, units, s_rowoff, keys, warp, nwarps, lane);
+        else if (upl <= 4)
+            cv_emit_rows<4>(sc, L.bstride, L.h, units, s_rowoff, keys, warp, nwarps, lane);
+        else
+            cv_emit_rows<8>(sc, L.bstride, L.h, units, s_rowoff, keys, warp, nwarps, lane);
     }
     __syncthreads();
+    if (phase_stop == 1)
+        return;
 
     // ---- retainBest(2 * N_l) on the FAST score ----
-    if (warp == 0) {
-        const int m = warp_retain_best(keys, n, 2 * L.quota, Lpos, Rpos, lane, FastGreater(),
-            [](unsigned amb) { return [amb](unsigned k) { return (k >> 24) >= (amb >> 24); }; });
-        if (lane == 0)
-            s_n = m;
-    }
-    __syncthreads();
-    const int n1 = s_n;
+    const int n1 = cta_retain_best(keys, n, 2 * L.quota, Lpos, Rpos, s_w, FastGreater(),
+        [](unsigned amb) { return [amb](unsigned k) { return (k >> 24) >= (amb >> 24); }; });
+    if (phase_stop == 2)
+        return;
 
     // ---- HarrisResponses(blockSize 7, k 0.04) ----
     HKey* g_h = hkey_all + (size_t)slot * C.cand_total + L.cand_off;
     const uint8_t* img = pyr + slot * pyr_slot + L.pyr_off;
     const int step = L.pstride;
-    for (int i = tid; i < n1; i += CV_SEL_THREADS) {
-        const unsigned k = keys[i];
-        const int x0 = k & 0xfff, y0 = (k >> 12) & 0xfff;
-        const uint8_t* ptr0 = img + (ptrdiff_t)(y0 - 3) * step + x0 - 3;
-        int a = 0, b = 0, c = 0;
-        // 9 x 9 window rows held three at a time
-        for (int r = 0; r < 7; r++) {
-            const uint8_t* pm = ptr0 + (ptrdiff_t)(r - 1) * step - 1;
-            const uint8_t* pc = pm + step;
-            const uint8_t* pp = pc + step;
-            int m0 = pm[0], m1 = pm[1], c0 = pc[0], c1 = pc[1], p0 = pp[0], p1 = pp[1];
+    // one warp per keypoint, four keypoints in flight: lane p (and p + 32) takes pixel p of the 7 x 7 block, the integer
+    // sums are reduced with shuffles
+    for (int i0 = warp * 4; i0 < n1; i0 += nwarps * 4) {
+        int a[4], b[4], c[4];
+        unsigned kk[4];
 #pragma unroll
-            for (int j = 0; j < 7; j++) {
-                const int m2 = pm[j + 2], c2 = pc[j + 2], p2 = pp[j + 2];
-                const int Ix = (c2 - c0) * 2 + (m2 - m0) + (p2 - p0);
-                const int Iy = (p1 - m1) * 2 + (p0 - m0) + (p2 - m2);
-                a += Ix * Ix;
-                b += Iy * Iy;
-                c += Ix * Iy;
-                m0 = m1, m1 = m2, c0 = c1, c1 = c2, p0 = p1, p1 = p2;
+        for (int q = 0; q < 4; q++) {
+            a[q] = b[q] = c[q] = 0;
+            kk[q] = keys[min(i0 + q, n1 - 1)];
+            const int x0 = kk[q] & 0xfff, y0 = (kk[q] >> 12) & 0xfff;
+            const uint8_t* ptr0 = img + (ptrdiff_t)(y0 - 3) * step + x0 - 3;
+#pragma unroll
+            for (int rnd = 0; rnd < 2; rnd++) {
+                const int p = lane + 32 * rnd;
+                if (p < 49) {
+                    const int r = p / 7, j = p - 7 * r;
+                    const uint8_t* ptr = ptr0 + (ptrdiff_t)r * step + j;
+                    const int m0 = ptr[-step - 1], m1 = ptr[-step], m2 = ptr[-step + 1];
+                    const int c0 = ptr[-1], c2 = ptr[1];
+                    const int p0 = ptr[step - 1], p1 = ptr[step], p2 = ptr[step + 1];
+                    const int Ix = (c2 - c0) * 2 + (m2 - m0) + (p2 - p0);
+                    const int Iy = (p1 - m1) * 2 + (p0 - m0) + (p2 - m2);
+                    a[q] += Ix * Ix;
+                    b[q] += Iy * Iy;
+                    c[q] += Ix * Iy;
+                }
             }
         }
-        const float fa = (float)a, fb = (float)b, fc = (float)c;
-        const float sum = __fadd_rn(fa, fb);
-        const float resp = __fmul_rn(__fsub_rn(__fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc)), __fmul_rn(__fmul_rn(0.04f, sum), sum)), C.harris_scale4);
-        HKey h;
-        h.r = resp;
-        h.xy = (unsigned)y0 << 16 | (unsigned)x0;
-        g_h[i] = h;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a[q] += __shfl_xor_sync(0xffffffffu, a[q], o);
+                b[q] += __shfl_xor_sync(0xffffffffu, b[q], o);
+                c[q] += __shfl_xor_sync(0xffffffffu, c[q], o);
+            }
+            if (lane == q && i0 + q < n1) {
+                const float fa = (float)a[q], fb = (float)b[q], fc = (float)c[q];
+                const float sum = __fadd_rn(fa, fb);
+                const float resp
+                    = __fmul_rn(__fsub_rn(__fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc)), __fmul_rn(__fmul_rn(0.04f, sum), sum)), C.harris_scale4);
+                HKey hh;
+                hh.r = resp;
+                hh.xy = ((kk[q] >> 12) & 0xfff) << 16 | (kk[q] & 0xfff);
+                g_h[i0 + q] = hh;
+            }
+        }
     }
     if (tid == 0)
         hcount[slot * RGBDFE_MAX_LEVELS + level] = n1;
     __syncthreads();
+    if (phase_stop == 3)
+        return;
     // ---- retainBest(N_l) on the Harris response ----
-    const bool h_in_smem = n1 <= CV_HCAP;
+    const bool h_in_smem = n1 <= kcap / 2;
     HKey* hk = h_in_smem ? reinterpret_cast<HKey*>(smem) : g_h; // the FAST keys are dead: their shared memory is reused
     if (h_in_smem)
         for (int i = tid; i < n1; i += CV_SEL_THREADS)
             hk[i] = g_h[i];
     __syncthreads();
-    if (warp == 0) {
-        // stopper lists: the Harris list never exceeds the candidate capacity, so the global scratch always fits
-        unsigned short* L2 = lr_all + ((size_t)slot * 2) * C.cand_total + L.cand_off;
-        unsigned short* R2 = lr_all + ((size_t)slot * 2 + 1) * C.cand_total + L.cand_off;
-        if (h_in_smem) {
-            L2 = s_L;
-            R2 = s_R;
-        }
-        const int m = warp_retain_best(hk, n1, L.quota, L2, R2, lane, HarrisGreater(),
-            [](HKey amb) { return [amb](const HKey& k) { return k.r >= amb.r; }; });
-        if (lane == 0)
-            s_n = m;
-    }
-    __syncthreads();
-    const int n2 = s_n;
+    // stopper lists: the Harris list never exceeds the candidate capacity, so the global scratch always fits
+    unsigned short* L2 = h_in_smem ? s_L : lr_all + ((size_t)slot * 2) * C.cand_total + L.cand_off;
+    unsigned short* R2 = h_in_smem ? s_R : lr_all + ((size_t)slot * 2 + 1) * C.cand_total + L.cand_off;
+    const int n2 = cta_retain_best(hk, n1, L.quota, L2, R2, s_w, HarrisGreater(), [](HKey amb) { return [amb](const HKey& k) { return k.r >= amb.r; }; });
     CvSel* out = out_all + (size_t)slot * C.out_total + L.out_off;
     for (int i = tid; i < min(n2, L.out_cap); i += CV_SEL_THREADS) {
         CvSel s;
@@ -855,14 +1007,19 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
     }
     {
         ProfScope prof(c, KID_QUADTREE); // the selection stage takes the quadtree's place
-        const size_t smem = (size_t)CV_KCAP * 8 + (size_t)(h + 2) * sizeof(int);
+        static const int phase_stop = getenv("RGBDFE_CV_PHASE_STOP") ? atoi(getenv("RGBDFE_CV_PHASE_STOP")) : 0; // timing aid: leave k_cv_select early
+        int kcap = 4096; // ~ 2x the FAST corners a textured level-0 image yields (w * h / 48), within [4096, 24576]
+        while (kcap < w * h / 48 && kcap < 24576)
+            kcap *= 2;
+        kcap = std::min(kcap, 24576);
+        const size_t smem = (size_t)kcap * 8 + (size_t)(h + 2) * sizeof(int);
         static size_t configured[64] = { 0 };
         if (smem > configured[c->device]) {
             CUDA_TRY(c, cudaFuncSetAttribute(k_cv_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             configured[c->device] = smem;
         }
         k_cv_select<<<dim3(C.nlevels, count), CV_SEL_THREADS, smem, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot, W->d_cand,
-            W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count);
+            W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count, kcap, phase_stop);
         k_cv_gather<<<count, 256, 0, c->stream>>>(C, W->d_out, W->d_out_count, W->d_final, W->d_final_count, W->d_gscratch);
         c->launches += 2;
     }
