@@ -1,6 +1,8 @@
 // Extractor — same public interface as the reference's Features/Extractor.h:9-72.
 // The ORB2/ORB2 combination (the north-star path, Features/Extractor.cpp:52-53,203-205,244-247)
-// runs on the GPU through ORBextractor -> librgbdfe.  The other detector / descriptor types of
+// runs on the GPU through ORBextractor -> librgbdfe; the ORB/ORB combination (OpenCV's cv::ORB with
+// Harris scoring, Features/Extractor.cpp:55-59,163-166,216-218) through rgbdfe_cvorb_configure.
+// The other detector / descriptor types of
 // the reference are thin wrappers over OpenCV (xfeatures2d) classes and are outside the hot
 // path this library replaces: asking for them ends the process the way the reference does for
 // an invalid type (std::terminate, Extractor.cpp:39,209,251).

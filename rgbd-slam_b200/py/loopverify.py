@@ -62,6 +62,36 @@ class ShardedVerifier:
         self.lo, self.hi = shard_range(n_kf, rank, world)
         self.local_verify = local_verify
 
+    def verify_many(self, q_descs, q_xyzs, seed, dtype):
+        """Batched relocalisation (BASELINE configs[4]: Q query frames x n_kf keyframes, all pairs): every rank verifies
+        all Q queries against its keyframe block, then ONE all_gather moves the Q x block results.  Pair (q, k) uses the
+        stream srand(seed + q * n_kf + k), so the result is independent of the sharding.  Returns [Q, n_kf] records."""
+        import torch
+
+        Q = len(q_descs)
+        per = -(-self.n_kf // self.world)
+        buf = torch.zeros(Q * per * RESULT_BYTES, dtype=torch.uint8)
+        view = buf.view(Q, per * RESULT_BYTES)
+        for q in range(Q):
+            local = self.local_verify(self.lo, self.hi, q_descs[q], q_xyzs[q], seed + q * self.n_kf)
+            raw = torch.from_numpy(np.ascontiguousarray(local).view(np.uint8).reshape(-1).copy())
+            view[q, : raw.numel()] = raw
+        buf = buf.to(self.device)
+        if self.world == 1:
+            out = buf.view(1, Q, per, RESULT_BYTES)
+        else:
+            import torch.distributed as dist
+
+            out = torch.empty(self.world * buf.numel(), dtype=torch.uint8, device=buf.device)
+            dist.all_gather_into_tensor(out, buf)
+            out = out.view(self.world, Q, per, RESULT_BYTES)
+        rows = []
+        for r in range(self.world):
+            lo, hi = shard_range(self.n_kf, r, self.world)
+            rows.append(out[r, :, : hi - lo])
+        g = torch.cat(rows, 1).contiguous()  # [Q, n_kf, 84]
+        return np.frombuffer(g.cpu().numpy().tobytes(), dtype=dtype).reshape(Q, self.n_kf)
+
     def verify(self, q_desc, q_xyz, seed, dtype):
         local = self.local_verify(self.lo, self.hi, q_desc, q_xyz, seed)
         g = gather_results(local, self.n_kf, self.rank, self.world, self.device)

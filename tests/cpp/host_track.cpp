@@ -1,7 +1,7 @@
 // Caller-side test of the class shims: the hot part of Tracking::visualOdometry
 // (System/Tracking.cpp:121-163) and of the Frame constructor (Core/Frame.cpp:34-73), written
 // against the reference's class interfaces exactly as the reference's callers use them.
-//   host_track <in.bin> <out.txt> [seed]
+//   host_track <in.bin> <out.txt> [seed] [orb]      ("orb": Extractor(ORB, ORB) = cv::ORB instead of ORB2)
 // in.bin : int32 n, w, h, nfeatures; float fx, fy, cx, cy; then n x (gray w*h u8, depth w*h f32 metres)
 // out.txt: one block per frame (keypoint / descriptor checksums, match + RANSAC results, outlier flags)
 #include "Core/Frame.h"
@@ -14,6 +14,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 using namespace std;
@@ -48,7 +49,9 @@ int main(int argc, char** argv)
     rgbdfe_host::seed(seed); // tests pin the stream; the reference seeds from time(NULL)
 
     RGBDcamera cam = { intr[0], intr[1], intr[2], intr[3], 1.0f };
-    Extractor::Ptr extractor(new Extractor(Extractor::ORB2, Extractor::ORB2, Extractor::NORMAL)); // main.cpp:31 with the ORB path
+    const bool cvorb = argc > 4 && std::string(argv[4]) == "orb";
+    const Extractor::eType et = cvorb ? Extractor::ORB : Extractor::ORB2;
+    Extractor::Ptr extractor(new Extractor(et, et, Extractor::NORMAL)); // main.cpp:31 with the ORB path
     extractor->setParameters(nfeat, 1.2f, 8, 20, 7);
 
     FILE* out = fopen(argv[2], "w");

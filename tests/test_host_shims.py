@@ -124,3 +124,57 @@ def test_visual_odometry_through_the_class_shims(oracle, seq_vga, tmp_path):
             ti += 1
         prev = (k, de, p3, outl)
     assert nproj > 100, "the tracked poses must let projectionMatch find most of the matches"
+
+
+@pytest.mark.gpu
+def test_extractor_orb_orb_pair_through_the_class_shims(oracle, seq_vga, tmp_path):
+    """Extractor(ORB, ORB) (cv::ORB with Harris scoring, Features/Extractor.cpp:55-59,163-166,216-218) through the
+    same caller: features, Matcher::match and RansacSE3 against the oracle fed with the oracle's cv::ORB features."""
+    import synth
+
+    cam, frames = seq_vga
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.txt"
+    with open(inp, "wb") as f:
+        np.array([len(frames), 640, 480, 1000], np.int32).tofile(f)
+        np.array([cam["fx"], cam["fy"], cam["cx"], cam["cy"]], np.float32).tofile(f)
+        for g, d in frames:
+            np.ascontiguousarray(g, np.uint8).tofile(f)
+            np.ascontiguousarray(d, np.float32).tofile(f)
+    subprocess.check_call([os.path.join(LIB, "host_track"), str(inp), str(outp), "42", "orb"])
+    rec = {}
+    for ln in open(outp).read().splitlines():
+        t = ln.split()
+        rec.setdefault(t[0], []).append(t[1:])
+    assert rec["levels"][0][0] == "8" and rec["levels"][0][4] == "6"  # nlevels, NORM_HAMMING
+    assert np.float32(rec["levels"][0][2]) == np.float32(np.float64(np.float32(1.2)))  # getScaleFactor(): the double member
+    s7 = np.float32(1.0)
+    for _ in range(7):  # Extractor::init (Extractor.cpp:63-80): float = float * double
+        s7 = np.float32(np.float64(s7) * np.float64(np.float32(1.2)))
+    assert np.float32(rec["scale7"][0][0]) == s7
+    orb = oracle.CvOrb(1000, 1.2, 8)
+    rng, latch = oracle.Rng(42), oracle.Latch()
+    prev, ti = None, 0
+    for i, (g, d) in enumerate(frames):
+        k, de = orb.extract(g)
+        p3 = synth.unproject(cam, np.stack([k["x"], k["y"]], 1), d)
+        fr = rec["frame"][i]
+        assert int(fr[2]) == len(k)
+        assert int(fr[4], 16) == fnv(k) and int(fr[6], 16) == fnv(de) and int(fr[8], 16) == fnv(p3)
+        outl = np.zeros(len(k), np.uint8)
+        if prev is not None:
+            m = oracle.match(prev[1], de, prev[3], prev[2], p3, 0.9, True)
+            r = oracle.ransac_se3(prev[2], p3, m, rng, latch, 200, 10, 3.0, 4)
+            if len(m) >= 10:
+                outl[m["trainIdx"]] = 1
+            if r["ok"]:
+                outl[r["inliers"]["trainIdx"]] = 0
+            tr = rec["track"][ti]
+            assert int(tr[2]) == len(m) and int(tr[4], 16) == fnv(m)
+            assert int(tr[6]) == int(r["ok"]) and int(tr[8]) == len(r["inliers"]) and int(tr[10], 16) == fnv(r["inliers"])
+            T = np.array([np.float32(x) for x in tr[14:30]], np.float32).reshape(4, 4)
+            assert np.abs(T - r["T"]).max() <= 1e-5
+            if i == 1:  # the caller also runs class Ransac and Random here: keep the oracle's rand() stream in step
+                oracle.ransac_umeyama(prev[2], p3, m, rng, 0, 0.02, 0.2, 10, 3)
+                rng.random_int(0, 999)
+            ti += 1
+        prev = (k, de, p3, outl)

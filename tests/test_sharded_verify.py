@@ -50,7 +50,11 @@ def _worker(rank, world, port, q):
     qd, qp, kd, kp, _ = synth.synth_pair_sets(N_KF, N_FEAT, seed=31, overlap_frac=0.7)
     v = loopverify.ShardedVerifier(N_KF, rank, world, _oracle_verify(kd, kp))
     res = v.verify(qd, qp, SEED, rgbdfe.SE3_DTYPE)
-    q.put((rank, res.tobytes(), (v.lo, v.hi)))
+    # batched relocalisation (configs[4] shape): 3 queries x N_KF keyframes, one all_gather for the whole batch
+    qs = [qd, np.roll(qd, 5, axis=0), qd[::-1].copy()]
+    ps = [qp, np.roll(qp, 5, axis=0), qp[::-1].copy()]
+    many = v.verify_many(qs, ps, SEED, rgbdfe.SE3_DTYPE)
+    q.put((rank, res.tobytes(), (v.lo, v.hi), many.tobytes()))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -86,7 +90,13 @@ def test_two_rank_gloo_gather_equals_single_process():
     assert all(p.exitcode == 0 for p in procs)
     blocks = sorted(g[2] for g in got)
     assert blocks == [(0, 4), (4, 7)]
-    for _, raw, _ in got:  # every rank holds the full list, in keyframe order
+    run = _oracle_verify(kd, kp)
+    qs = [qd, np.roll(qd, 5, axis=0), qd[::-1].copy()]
+    ps = [qp, np.roll(qp, 5, axis=0), qp[::-1].copy()]
+    many_single = np.stack([run(0, N_KF, qs[i], ps[i], SEED + i * N_KF) for i in range(3)])
+    assert many_single[1]["ok"].sum() >= 2  # a permuted query still closes its loops
+    for _, raw, _, many in got:  # every rank holds the full list, in keyframe order
         res = np.frombuffer(raw, dtype=rgbdfe.SE3_DTYPE)
         assert len(res) == N_KF and res.tobytes() == single.tobytes()
+        assert many == many_single.tobytes()  # [3, N_KF] records, independent of the sharding
     assert loopverify.first_success(single) == int(np.nonzero(single["ok"])[0][0])
