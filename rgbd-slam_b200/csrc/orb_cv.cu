@@ -175,6 +175,20 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
     constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 8;
     __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
     __shared__ __align__(16) uint8_t s_S[ROWS][PITCH];
+    __shared__ __align__(16) uint8_t s_out[CV_TH][CV_TW];
+    __shared__ unsigned short s_cand[(CV_TH + 2) * (PITCH)];
+    __shared__ int s_ncand;
+    uint8_t* out = score + slot * score_slot + L.blur_off;
+    // the part of the tile that survives runByImageBorder(31); strengths are needed there and on its 1 px halo only
+    const int ex0 = max(x0, CV_EDGE), ex1 = min(x0 + CV_TW, L.w - CV_EDGE), ey0 = max(y0, CV_EDGE), ey1 = min(y0 + CV_TH, L.h - CV_EDGE);
+    if (ex0 >= ex1 || ey0 >= ey1) { // a border tile: all zeros
+        for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
+            const int rr = i >> 4, q = i & 15;
+            if (y0 + rr < L.h)
+                *reinterpret_cast<unsigned*>(out + (size_t)(y0 + rr) * L.bstride + x0 + 4 * q) = 0u;
+        }
+        return;
+    }
     // staged window: level rows y0-4 .. y0+35, columns x0-4 .. x0+67 (the ring covers 4 px outside the image; rows and
     // words beyond the padded level are clamped: those pixels lie outside the detection region and are never used)
     const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
@@ -186,18 +200,21 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
         *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
         *reinterpret_cast<unsigned*>(&s_S[r][4 * q]) = 0u;
     }
-    __syncthreads();
-    // Phase 1: the 4-opposite-pair necessary test (fast_candidate2, four pixels per thread in 16-bit lanes) on the emit
-    // region + 1 px halo, inside cv::FAST's detection region [3, w-3) x [3, h-3); survivors are compacted with ballots.
-    __shared__ unsigned short s_cand[(CV_TH + 2) * (PITCH)];
-    __shared__ int s_ncand;
+    for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256)
+        reinterpret_cast<unsigned*>(&s_out[0][0])[i] = 0u;
     if (tid == 0)
         s_ncand = 0;
     __syncthreads();
+    // Phase 1: the 4-opposite-pair necessary test (fast_candidate2, four pixels per thread in 16-bit lanes) on the kept
+    // region + 1 px halo (which lies inside cv::FAST's detection region [3, w-3) x [3, h-3)); survivors are compacted
+    // with ballots.  Window column c is level column x0 - 4 + c, window row r is level row y0 - 4 + r.
     {
-        constexpr int GPR = PITCH / 4;          // 18 word groups per window row
-        constexpr int NG = (CV_TH + 2) * GPR;   // rows 3 .. 36
         constexpr int RW = PITCH / 4;
+        const int r_lo = ey0 - 1 - (y0 - 4), nrows = ey1 - ey0 + 2;
+        const int c_lo = ex0 - 1 - (x0 - 4), c_hi = ex1 - (x0 - 4); // first / last needed window column
+        const int g_lo = c_lo >> 2, ngr = (c_hi >> 2) - g_lo + 1;  // <= 18 word groups per row
+        const unsigned inv_ngr = 0xffffffffu / (unsigned)ngr + 1u;
+        const int NG = nrows * ngr;
         const unsigned c1 = 0x7fff7fffu - ((unsigned)CV_FAST_TH | (unsigned)CV_FAST_TH << 16);
         const unsigned lt = (1u << (tid & 31)) - 1;
         for (int i0 = (tid & ~31); i0 < NG; i0 += 256) { // warp-uniform trip count
@@ -205,28 +222,26 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
             unsigned rA = 0, rB = 0;
             int r = 0, g = 0;
             if (i < NG) {
-                r = 3 + i / GPR;
-                g = i - (r - 3) * GPR;
-                { // groups 0 and 17 read one word across the row end (still inside s_img); only their columns 3 / 68 are kept
-                    const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g;
-                    const unsigned cm = w[-1], cc = w[0], cp = w[1];
-                    const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
-                    const unsigned um = w[-2 * RW - 1], uc = w[-2 * RW], upn = w[-2 * RW + 1];
-                    const unsigned dm = w[2 * RW - 1], dc = w[2 * RW], dpn = w[2 * RW + 1];
-                    const unsigned u4 = __funnelshift_r(cc, cp, 24), u12 = __funnelshift_r(cm, cc, 8);
-                    const unsigned u2 = __funnelshift_r(dc, dpn, 16), u14 = __funnelshift_r(dm, dc, 16);
-                    const unsigned u6 = __funnelshift_r(uc, upn, 16), u10 = __funnelshift_r(um, uc, 16);
-                    rA = fast_candidate2(lanes_lo(cc), lanes_lo(dn3), lanes_lo(up3), lanes_lo(u4), lanes_lo(u12), lanes_lo(u2), lanes_lo(u10),
-                        lanes_lo(u6), lanes_lo(u14), c1);
-                    rB = fast_candidate2(lanes_hi(cc), lanes_hi(dn3), lanes_hi(up3), lanes_hi(u4), lanes_hi(u12), lanes_hi(u2), lanes_hi(u10),
-                        lanes_hi(u6), lanes_hi(u14), c1);
-                }
+                const int rr = (int)__umulhi((unsigned)i, inv_ngr);
+                r = r_lo + rr;
+                g = g_lo + (i - rr * ngr);
+                // groups 0 and 17 read one word across the row end (still inside s_img); only their columns 3 / 68 are kept
+                const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g;
+                const unsigned cm = w[-1], cc = w[0], cp = w[1];
+                const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
+                const unsigned um = w[-2 * RW - 1], uc = w[-2 * RW], upn = w[-2 * RW + 1];
+                const unsigned dm = w[2 * RW - 1], dc = w[2 * RW], dpn = w[2 * RW + 1];
+                const unsigned u4 = __funnelshift_r(cc, cp, 24), u12 = __funnelshift_r(cm, cc, 8);
+                const unsigned u2 = __funnelshift_r(dc, dpn, 16), u14 = __funnelshift_r(dm, dc, 16);
+                const unsigned u6 = __funnelshift_r(uc, upn, 16), u10 = __funnelshift_r(um, uc, 16);
+                rA = fast_candidate2(lanes_lo(cc), lanes_lo(dn3), lanes_lo(up3), lanes_lo(u4), lanes_lo(u12), lanes_lo(u2), lanes_lo(u10),
+                    lanes_lo(u6), lanes_lo(u14), c1);
+                rB = fast_candidate2(lanes_hi(cc), lanes_hi(dn3), lanes_hi(up3), lanes_hi(u4), lanes_hi(u12), lanes_hi(u2), lanes_hi(u10),
+                    lanes_hi(u6), lanes_hi(u14), c1);
             }
-            // window column c = 4g + j is level column x0 - 4 + c; window row r is level row y0 - 4 + r
-            const int y = y0 - 4 + r, xb = x0 - 4 + 4 * g;
-            const bool yok = y >= 3 && y < L.h - 3;
-            auto ok = [&](int j) { const int c = 4 * g + j, x = xb + j; return yok && c >= 3 && c < CV_TW + 5 && x >= 3 && x < L.w - 3; };
-            const bool k0 = (rA & 0x8000u) && ok(0), k1 = (rA >> 31) && ok(1), k2 = (rB & 0x8000u) && ok(2), k3 = (rB >> 31) && ok(3);
+            const int cb = 4 * g;
+            const bool k0 = (rA & 0x8000u) && cb >= c_lo && cb <= c_hi, k1 = (rA >> 31) && cb + 1 >= c_lo && cb + 1 <= c_hi;
+            const bool k2 = (rB & 0x8000u) && cb + 2 >= c_lo && cb + 2 <= c_hi, k3 = (rB >> 31) && cb + 3 >= c_lo && cb + 3 <= c_hi;
             const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
             const unsigned b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
             const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
@@ -235,7 +250,7 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
                 if ((tid & 31) == 0)
                     base = atomicAdd(&s_ncand, n0 + n1 + n2 + n3);
                 base = __shfl_sync(0xffffffffu, base, 0);
-                const int key = r << 8 | (4 * g);
+                const int key = r << 8 | cb;
                 if (k0)
                     s_cand[base + __popc(b0 & lt)] = (unsigned short)key;
                 if (k1)
@@ -249,36 +264,31 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
     }
     __syncthreads();
     // Phase 2: corner strength of the candidates (dense warps)
-    {
-        const int ncand = s_ncand;
-        for (int i = tid; i < ncand; i += 256) {
-            const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
-            const int S = fast_strength(&s_img[r][c], PITCH, CV_FAST_TH);
-            s_S[r][c] = (uint8_t)min(S, 255);
-        }
+    const int ncand = s_ncand;
+    for (int i = tid; i < ncand; i += 256) {
+        const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
+        const int S = fast_strength(&s_img[r][c], PITCH, CV_FAST_TH);
+        s_S[r][c] = (uint8_t)min(S, 255);
     }
     __syncthreads();
-    // NMS + border filter, 4 pixels per thread, one 32-bit store
-    uint8_t* out = score + slot * score_slot + L.blur_off;
-    for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
-        const int rr = i / (CV_TW / 4), q = i - rr * (CV_TW / 4);
-        const int y = y0 + rr;
-        if (y >= L.h)
+    // Phase 3: 3x3 non-max suppression of the corners inside the kept region (a neighbour that is not a corner holds 0,
+    // a corner's S is >= 21, and score = S - 1 on both sides of the comparison)
+    for (int i = tid; i < ncand; i += 256) {
+        const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
+        const int x = x0 - 4 + c, y = y0 - 4 + r;
+        const int S = s_S[r][c];
+        if (S == 0 || x < ex0 || x >= ex1 || y < ey0 || y >= ey1)
             continue;
-        unsigned word = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int r = rr + 4, c = 4 * q + j + 4;
-            const int x = x0 + 4 * q + j;
-            const int S = s_S[r][c];
-            if (S == 0 || x < CV_EDGE || x >= L.w - CV_EDGE || y < CV_EDGE || y >= L.h - CV_EDGE)
-                continue;
-            const int m = max(max(max(s_S[r - 1][c - 1], s_S[r - 1][c]), max(s_S[r - 1][c + 1], s_S[r][c - 1])),
-                max(max(s_S[r][c + 1], s_S[r + 1][c - 1]), max(s_S[r + 1][c], s_S[r + 1][c + 1])));
-            if (S > m) // score = S - 1 on both sides; non-corners hold 0 and a corner's S is >= 21
-                word |= (unsigned)(S - 1) << (8 * j);
-        }
-        *reinterpret_cast<unsigned*>(out + (size_t)y * L.bstride + x0 + 4 * q) = word;
+        const int m = max(max(max(s_S[r - 1][c - 1], s_S[r - 1][c]), max(s_S[r - 1][c + 1], s_S[r][c - 1])),
+            max(max(s_S[r][c + 1], s_S[r + 1][c - 1]), max(s_S[r + 1][c], s_S[r + 1][c + 1])));
+        if (S > m)
+            s_out[r - 4][c - 4] = (uint8_t)(S - 1);
+    }
+    __syncthreads();
+    for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
+        const int rr = i >> 4, q = i & 15;
+        if (y0 + rr < L.h)
+            *reinterpret_cast<unsigned*>(out + (size_t)(y0 + rr) * L.bstride + x0 + 4 * q) = *reinterpret_cast<const unsigned*>(&s_out[rr][4 * q]);
     }
 }
 
@@ -314,10 +324,10 @@ __global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C
         const unsigned w0 = row[q], w1 = row[q + 1], w2 = row[q + 2];
         float p[12];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            p[j] = (float)((w0 >> (8 * j)) & 0xffu);
-            p[4 + j] = (float)((w1 >> (8 * j)) & 0xffu);
-            p[8 + j] = (float)((w2 >> (8 * j)) & 0xffu);
+        for (int j = 0; j < 4; j++) { // byte -> float on the ALU: 0x4B0000bb is 2^23 + b (keeps the conversion off the XU pipe)
+            p[j] = __fsub_rn(__uint_as_float(__byte_perm(w0, 0x4B000000u, 0x7650 + j)), 8388608.0f);
+            p[4 + j] = __fsub_rn(__uint_as_float(__byte_perm(w1, 0x4B000000u, 0x7650 + j)), 8388608.0f);
+            p[8 + j] = __fsub_rn(__uint_as_float(__byte_perm(w2, 0x4B000000u, 0x7650 + j)), 8388608.0f);
         }
         const int x = x0 + 4 * q;
         float acc[4];
@@ -355,7 +365,9 @@ __global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C
 #pragma unroll
             for (int t = 1; t <= 3; t++)
                 acc = __fmaf_rn(C.gk[3 + t], __fadd_rn(v[k + 3 + t], v[k + 3 - t]), acc);
-            s_out[band * 8 + k][c] = (uint8_t)min(max(__float2int_rn(acc), 0), 255);
+            // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits
+            const int iv = __float_as_int(__fadd_rn(acc, 12582912.0f)) - 0x4B400000;
+            s_out[band * 8 + k][c] = (uint8_t)min(max(iv, 0), 255);
         }
     }
     __syncthreads();

@@ -5,6 +5,9 @@
 
 namespace rgbdfe {
 
+// cvRound (round half to even) for |v| < 2^22 without the XU pipe: adding 1.5 * 2^23 leaves the integer in the low mantissa bits
+__device__ __forceinline__ int cv_round_fast(float v) { return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000; }
+
 __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 {
     // cv::fastAtan2 (scalar), evaluated without FMA
