@@ -133,22 +133,6 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
             yofs.resize(ty + L.h);
             yb.resize(2 * (ty + L.h));
             resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xofs.data() + tx, xa.data() + 2 * tx, yofs.data() + ty, yb.data() + 2 * ty);
-            // staged source window of the worst k_pyramid_resize tile of this level
-            const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD, srch = g.lv[l - 1].h;
-            int max_cols = 0, max_rows = 0;
-            for (int p0 = 0; p0 < pw; p0 += PYR_TW) {
-                int lo, hi;
-                ring_tile_range(p0, std::min(p0 + PYR_TW - 1, pw - 1), L.w, lo, hi);
-                max_cols = std::max(max_cols, xofs[tx + hi] + 1 - xofs[tx + lo] + 1);
-            }
-            for (int p0 = 0; p0 < ph; p0 += PYR_TH) {
-                int lo, hi;
-                ring_tile_range(p0, std::min(p0 + PYR_TH - 1, ph - 1), L.h, lo, hi);
-                const int s0 = std::min(std::max(yofs[ty + lo], 0), srch - 1), s1 = std::min(std::max(yofs[ty + hi] + 1, 0), srch - 1);
-                max_rows = std::max(max_rows, s1 - s0 + 1);
-            }
-            L.rs_cols = align_up(max_cols + 3, 16); // + up to 3 bytes of load alignment
-            L.rs_rows = max_rows;
             tx += L.w;
             ty += L.h;
         }

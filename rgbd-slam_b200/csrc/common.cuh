@@ -29,7 +29,6 @@ struct LevelDesc {
     int quota;           // mnFeaturesPerLevel
     int sel_off, sel_cap;
     int tab_x_off, tab_y_off; // resize coefficient tables (level > 0)
-    int rs_cols, rs_rows;     // k_pyramid_resize: staged source bytes per row (multiple of 16) / rows, worst tile of the level
     float scale;         // mvScaleFactor[level]
     int patch_size;      // int(31 * scale)
 };
@@ -128,17 +127,6 @@ __host__ __device__ inline int reflect101(int p, int len)
     if (p < 0)
         p = -p;
     return p;
-}
-// k_pyramid_resize tiles the PADDED level (ring included): positions [p0, p1] of a padded row or column of a
-// level with n pixels touch level coordinates [lo, hi] (the reflection is piecewise monotone)
-#define PYR_TW 128
-#define PYR_TH 16
-__host__ __device__ inline void ring_tile_range(int p0, int p1, int n, int& lo, int& hi)
-{
-    const int a = reflect101(p0 - EDGE_THRESHOLD, n), b = reflect101(p1 - EDGE_THRESHOLD, n);
-    const int last = EDGE_THRESHOLD + n - 1;
-    lo = (p0 <= EDGE_THRESHOLD && EDGE_THRESHOLD <= p1) ? 0 : (a < b ? a : b);
-    hi = (p0 <= last && last <= p1) ? n - 1 : (a > b ? a : b);
 }
 __host__ __device__ inline unsigned pack_cand(int x, int y, int s) { return (unsigned)x | ((unsigned)y << 12) | ((unsigned)s << 24); }
 __host__ __device__ inline int cand_x(unsigned c) { return c & 0xfff; }

@@ -497,7 +497,7 @@ __device__ void cv_emit_rows(const uint8_t* sc, int bstride, int h, int units, c
 // a level with more candidates works in the global scratch instead.  The Harris stage reuses the key area (kcap / 2 entries).
 __global__ void __launch_bounds__(CV_SEL_THREADS, 2) k_cv_select(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     const uint8_t* __restrict__ score, size_t score_slot, unsigned* __restrict__ cand_all, unsigned short* __restrict__ lr_all,
-    HKey* __restrict__ hkey_all, int* __restrict__ hcount, CvSel* __restrict__ out_all, int* __restrict__ out_count, int kcap, int phase_stop)
+    HKey* __restrict__ hkey_all, int* __restrict__ hcount, CvSel* __restrict__ out_all, int* __restrict__ out_count, int kcap)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned* s_keys = reinterpret_cast<unsigned*>(smem);
@@ -566,14 +566,10 @@ __global__ void __launch_bounds__(CV_SEL_THREADS, 2) k_cv_select(const __grid_co
             cv_emit_rows<8>(sc, L.bstride, L.h, units, s_rowoff, keys, warp, nwarps, lane);
     }
     __syncthreads();
-    if (phase_stop == 1)
-        return;
 
     // ---- retainBest(2 * N_l) on the FAST score ----
     const int n1 = cta_retain_best(keys, n, 2 * L.quota, Lpos, Rpos, s_w, FastGreater(),
         [](unsigned amb) { return [amb](unsigned k) { return (k >> 24) >= (amb >> 24); }; });
-    if (phase_stop == 2)
-        return;
 
     // ---- HarrisResponses(blockSize 7, k 0.04) ----
     HKey* g_h = hkey_all + (size_t)slot * C.cand_total + L.cand_off;
@@ -630,8 +626,6 @@ __global__ void __launch_bounds__(CV_SEL_THREADS, 2) k_cv_select(const __grid_co
     if (tid == 0)
         hcount[slot * RGBDFE_MAX_LEVELS + level] = n1;
     __syncthreads();
-    if (phase_stop == 3)
-        return;
     // ---- retainBest(N_l) on the Harris response ----
     const bool h_in_smem = n1 <= kcap / 2;
     HKey* hk = h_in_smem ? reinterpret_cast<HKey*>(smem) : g_h; // the FAST keys are dead: their shared memory is reused
@@ -1019,7 +1013,6 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
     }
     {
         ProfScope prof(c, KID_QUADTREE); // the selection stage takes the quadtree's place
-        static const int phase_stop = getenv("RGBDFE_CV_PHASE_STOP") ? atoi(getenv("RGBDFE_CV_PHASE_STOP")) : 0; // timing aid: leave k_cv_select early
         int kcap = 4096; // ~ 2x the FAST corners a textured level-0 image yields (w * h / 48), within [4096, 24576]
         while (kcap < w * h / 48 && kcap < 24576)
             kcap *= 2;
@@ -1031,7 +1024,7 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
             configured[c->device] = smem;
         }
         k_cv_select<<<dim3(C.nlevels, count), CV_SEL_THREADS, smem, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot, W->d_cand,
-            W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count, kcap, phase_stop);
+            W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count, kcap);
         k_cv_gather<<<count, 256, 0, c->stream>>>(C, W->d_out, W->d_out_count, W->d_final, W->d_final_count, W->d_gscratch);
         c->launches += 2;
     }

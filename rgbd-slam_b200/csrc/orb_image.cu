@@ -59,77 +59,46 @@ __global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride,
 }
 
 // Level l >= 1: cv::resize(INTER_LINEAR) of level l-1 (8-bit fixed point, 11-bit coefficients, one rounding per
-// pass as in OpenCV's resize.cpp) + ring, in one pass over 128 x 16 tiles of the PADDED level.  The source
-// window of a tile is staged in shared memory with aligned word loads, the horizontal blend is done once per
-// (source row, output column) and kept as 16-bit (h >> 4), the vertical blend packs 8 outputs per thread.
-// Ring pixels are resampled at their reflected coordinates, which is what copyMakeBorder would copy.
+// pass as in OpenCV's resize.cpp) + ring in one pass over the PADDED level: ring pixels are resampled at their
+// reflected coordinates, which is what copyMakeBorder would copy.  One thread per 4 horizontally adjacent padded
+// pixels, the source read where it lies (level l-1 was written by the previous launch and sits in L2; neighbouring
+// threads share its sectors through L1): no staging, no barriers.  (A tiled form that staged the source window in
+// shared memory and blended horizontally once per source row measured slightly slower and was dropped.)
 struct PyrLevel {
     int w, h, pstride;           // this level
     unsigned pyr_off;
     int pw_src, ph_src, pstride_src; // level l-1 (interior size, padded pitch)
     unsigned pyr_off_src;
     int tab_x_off, tab_y_off;
-    int rs_cols, rs_rows;
 };
-__global__ void __launch_bounds__(256) k_pyramid_resize(const __grid_constant__ PyrLevel V, uint8_t* __restrict__ pyr, size_t pyr_slot,
+__global__ void __launch_bounds__(256) k_pyramid_resize_direct(const __grid_constant__ PyrLevel V, uint8_t* __restrict__ pyr, size_t pyr_slot,
     const int* __restrict__ xofs, const short* __restrict__ xa, const int* __restrict__ yofs, const short* __restrict__ yb)
 {
-    extern __shared__ __align__(16) unsigned char s_raw[];
-    uint8_t* s_src = s_raw;                                                                   // [rs_rows][rs_cols]
-    unsigned short* s_H = reinterpret_cast<unsigned short*>(s_raw + V.rs_rows * V.rs_cols);    // [rs_rows][PYR_TW]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int pw = V.w + 2 * EDGE_THRESHOLD, ph = V.h + 2 * EDGE_THRESHOLD;
-    const int p0x = blockIdx.x * PYR_TW, p1x = min(p0x + PYR_TW - 1, pw - 1);
-    const int p0y = blockIdx.y * PYR_TH, p1y = min(p0y + PYR_TH - 1, ph - 1);
-    const int* xo = xofs + V.tab_x_off;
-    const short* al = xa + 2 * V.tab_x_off;
-    const int* yo = yofs + V.tab_y_off;
-    const short* be = yb + 2 * V.tab_y_off;
-    int xlo, xhi, ylo, yhi;
-    ring_tile_range(p0x, p1x, V.w, xlo, xhi);
-    ring_tile_range(p0y, p1y, V.h, ylo, yhi);
-    const int sx_lo = xo[xlo], ncols = xo[xhi] + 1 - sx_lo + 1; // column sx + 1 may be the source's first ring column (coefficient 0)
-    const int sy_lo = min(max(yo[ylo], 0), V.ph_src - 1), nrows = min(max(yo[yhi] + 1, 0), V.ph_src - 1) - sy_lo + 1;
-    uint8_t* slot_base = pyr + blockIdx.z * pyr_slot;
-    const uint8_t* src = slot_base + V.pyr_off_src + (size_t)(EDGE_THRESHOLD + sy_lo) * V.pstride_src + EDGE_THRESHOLD + sx_lo;
-    const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
-    const int wpr = (ncols + mis + 3) >> 2;
-    for (int r = warp; r < nrows; r += 8)
-        for (int q = lane; q < wpr; q += 32)
-            *reinterpret_cast<unsigned*>(s_src + r * V.rs_cols + 4 * q) = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * V.pstride_src + 4 * q);
-    __syncthreads();
-    {
-        // horizontal blend: thread = output column, every second staged row
-        const int cx = tid & (PYR_TW - 1);
-        const int x = reflect101(min(p0x + cx, pw - 1) - EDGE_THRESHOLD, V.w);
-        const int a0 = al[2 * x], a1 = al[2 * x + 1];
-        const uint8_t* p = s_src + (xo[x] - sx_lo + mis);
-        for (int j = tid >> 7; j < nrows; j += 2) {
-            const uint8_t* q = p + j * V.rs_cols;
-            s_H[j * PYR_TW + cx] = (unsigned short)((q[0] * a0 + q[1] * a1) >> 4);
-        }
-    }
-    __syncthreads();
-    // vertical blend: thread = 8 adjacent outputs of one row
-    const int py = p0y + (tid >> 4), cg = (tid & 15) * 8;
-    if (py >= ph || p0x + cg >= pw)
+    const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int py = blockIdx.y * blockDim.y + threadIdx.y;
+    if (px0 >= V.pstride || py >= ph)
         return;
+    const int* xo = xofs + V.tab_x_off;
+    const short2* al = reinterpret_cast<const short2*>(xa) + V.tab_x_off;
+    uint8_t* slot_base = pyr + blockIdx.z * pyr_slot;
     const int y = reflect101(py - EDGE_THRESHOLD, V.h);
-    const int s0 = yo[y];
-    const int j0 = min(max(s0, 0), V.ph_src - 1) - sy_lo, j1 = min(max(s0 + 1, 0), V.ph_src - 1) - sy_lo;
-    const int b0 = be[2 * y], b1 = be[2 * y + 1];
-    const uint4 h0 = *reinterpret_cast<const uint4*>(s_H + j0 * PYR_TW + cg), h1 = *reinterpret_cast<const uint4*>(s_H + j1 * PYR_TW + cg);
-    const unsigned hw0[4] = { h0.x, h0.y, h0.z, h0.w }, hw1[4] = { h1.x, h1.y, h1.z, h1.w };
-    unsigned out[2] = { 0u, 0u };
+    const int s0 = yofs[V.tab_y_off + y];
+    const int r0 = min(max(s0, 0), V.ph_src - 1), r1 = min(max(s0 + 1, 0), V.ph_src - 1);
+    const short2 be = reinterpret_cast<const short2*>(yb)[V.tab_y_off + y];
+    const uint8_t* src0 = slot_base + V.pyr_off_src + (size_t)(EDGE_THRESHOLD + r0) * V.pstride_src + EDGE_THRESHOLD;
+    const uint8_t* src1 = slot_base + V.pyr_off_src + (size_t)(EDGE_THRESHOLD + r1) * V.pstride_src + EDGE_THRESHOLD;
+    unsigned out = 0;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const int t0 = (k & 1) ? (int)(hw0[k >> 1] >> 16) : (int)(hw0[k >> 1] & 0xffffu);
-        const int t1 = (k & 1) ? (int)(hw1[k >> 1] >> 16) : (int)(hw1[k >> 1] & 0xffffu);
-        const int v = min((((b0 * t0) >> 16) + ((b1 * t1) >> 16) + 2) >> 2, 255);
-        out[k >> 2] |= (unsigned)v << (8 * (k & 3));
+    for (int k = 0; k < 4; k++) {
+        const int x = reflect101(min(px0 + k, pw - 1) - EDGE_THRESHOLD, V.w);
+        const int sx = xo[x];
+        const short2 a = al[x];
+        const int t0 = (src0[sx] * a.x + src0[sx + 1] * a.y) >> 4, t1 = (src1[sx] * a.x + src1[sx + 1] * a.y) >> 4;
+        const int v = min((((be.x * t0) >> 16) + ((be.y * t1) >> 16) + 2) >> 2, 255);
+        out |= (unsigned)v << (8 * k);
     }
-    // pstride is a multiple of 64 and cg of 8: the store never leaves the row (bytes past pw are pitch padding)
-    *reinterpret_cast<uint2*>(slot_base + V.pyr_off + (size_t)py * V.pstride + p0x + cg) = make_uint2(out[0], out[1]);
+    *reinterpret_cast<unsigned*>(slot_base + V.pyr_off + (size_t)py * V.pstride + px0) = out; // bytes past pw are pitch padding
 }
 
 // ------------------------------------------------------------------ K5 ----
@@ -412,14 +381,9 @@ int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_strid
             PyrLevel V;
             V.w = L.w, V.h = L.h, V.pstride = L.pstride, V.pyr_off = L.pyr_off;
             V.pw_src = P.w, V.ph_src = P.h, V.pstride_src = P.pstride, V.pyr_off_src = P.pyr_off;
-            V.tab_x_off = L.tab_x_off, V.tab_y_off = L.tab_y_off, V.rs_cols = L.rs_cols, V.rs_rows = L.rs_rows;
-            const size_t smem = (size_t)L.rs_rows * L.rs_cols + (size_t)L.rs_rows * PYR_TW * sizeof(unsigned short);
-            if (smem > 48 * 1024) {
-                c->set_error("pyramid scale factor too large for the resize tile");
-                return RGBDFE_E_CAPACITY;
-            }
-            dim3 grd((pw + PYR_TW - 1) / PYR_TW, (ph + PYR_TH - 1) / PYR_TH, count);
-            k_pyramid_resize<<<grd, 256, smem, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xofs, c->d_tab_xa, c->d_tab_yofs, c->d_tab_yb);
+            V.tab_x_off = L.tab_x_off, V.tab_y_off = L.tab_y_off;
+            dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (ph + 3) / 4, count);
+            k_pyramid_resize_direct<<<grd, blk, 0, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xofs, c->d_tab_xa, c->d_tab_yofs, c->d_tab_yb);
         }
         c->launches++;
     }
