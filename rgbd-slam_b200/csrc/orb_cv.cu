@@ -401,7 +401,7 @@ __device__ int cta_retain_best(T* a, int n, int n_points, unsigned short* Lpos, 
     return cta_partition(a, n_points, n, Lpos, Rpos, s_w, make_pred(amb));
 }
 
-__device__ __forceinline__ int cv_nz(unsigned v) { return ((v & 0xffu) != 0) + ((v & 0xff00u) != 0) + ((v & 0xff0000u) != 0) + ((v >> 24) != 0); }
+__device__ __forceinline__ int cv_nz(unsigned v) { return __popc(__vcmpne4(v, 0u)) >> 3; } // non-zero bytes of a word
 __device__ __forceinline__ int cv_nz4(const uint4& v) { return cv_nz(v.x) + cv_nz(v.y) + cv_nz(v.z) + cv_nz(v.w); }
 
 // Row-major compaction of a level's score map.  A lane owns UPL consecutive 16-byte units of a row (so one warp scan
@@ -477,15 +477,14 @@ __device__ void cv_emit_rows(const uint8_t* sc, int bstride, int h, int units, c
                 for (int k = 0; k < UPL; k++) {
                     const unsigned vv[4] = { seg[r][k].x, seg[r][k].y, seg[r][k].z, seg[r][k].w };
 #pragma unroll
-                    for (int m = 0; m < 4; m++)
-                        if (vv[m]) {
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                const unsigned bb = (vv[m] >> (8 * j)) & 0xffu;
-                                if (bb)
-                                    keys[w++] = bb << 24 | (unsigned)y << 12 | (unsigned)(16 * (ua + k) + 4 * m + j);
-                            }
+                    for (int m = 0; m < 4; m++) {
+                        unsigned mk = __vcmpne4(vv[m], 0u); // 0xff per surviving corner (at most 2 per word: NMS)
+                        while (mk) {
+                            const int j = (__ffs(mk) - 1) >> 3;
+                            keys[w++] = ((vv[m] >> (8 * j)) & 0xffu) << 24 | (unsigned)y << 12 | (unsigned)(16 * (ua + k) + 4 * m + j);
+                            mk &= ~(0xffu << (8 * j));
                         }
+                    }
                 }
             }
         }
