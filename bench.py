@@ -326,7 +326,22 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # NCCL prints its version banner on stdout when NCCL_DEBUG is set in the environment: stdout carries the one JSON
+        # line only, so file descriptor 1 points at stderr while the communicator comes up (first collective included)
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            warm = torch.ones(1, device="cuda")
+            dist.all_reduce(warm)
+            g0 = torch.empty(world, device="cuda")
+            dist.all_gather_into_tensor(g0, warm / world)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
 
     B, F = args.batch, args.frames
     cam, frames = make_sequence(F)
