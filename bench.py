@@ -628,18 +628,29 @@ def main():
         vctx = rgbdfe.Context(local_rank, W, H, 1000, 1)
         vctx.depth_cov_set(1, (0.01 * 2.0 * 2.0) ** 2)
         db = vctx.kfdb_create(kd, kp)
-        res_dev = torch.empty(n_kf * 84, dtype=torch.uint8, device="cuda")
+        # two result buffers: the all_gather of query i runs on torch's stream while the verify kernels of query i + 1
+        # run on the context's stream (a buffer is only rewritten after its gather has finished)
+        res_dev = [torch.empty(n_kf * 84, dtype=torch.uint8, device="cuda") for _ in range(2)]
+        gathered = [None, None]
         vstream = torch.cuda.ExternalStream(vctx.stream, device=local_rank)
+        vcount = [0]
 
         import loopverify
 
         def vstep():
             # this rank's keyframe block through the C ABI, then the one exchange step of the path (loopverify.py)
-            vctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rank * n_kf, results_dev=res_dev.data_ptr(), want_host=False)
+            b = vcount[0] & 1
+            vcount[0] += 1
+            if gathered[b] is not None:
+                vstream.wait_event(gathered[b])
+            vctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rank * n_kf, results_dev=res_dev[b].data_ptr(), want_host=False)
             if world > 1:
-                torch.cuda.current_stream().wait_stream(vstream)
-                loopverify.gather_results(res_dev, world * n_kf, rank, world)
-                vstream.wait_stream(torch.cuda.current_stream())
+                done = torch.cuda.Event()
+                done.record(vstream)
+                torch.cuda.current_stream().wait_event(done)
+                loopverify.gather_results(res_dev[b], world * n_kf, rank, world)
+                gathered[b] = torch.cuda.Event()
+                gathered[b].record()
 
         for _ in range(2):
             vstep()
@@ -648,17 +659,18 @@ def main():
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(vstream)
-        vs = 4
+        vs = 8
         for _ in range(vs):
             vstep()
-        e1.record(vstream)
+        torch.cuda.current_stream().wait_stream(vstream)  # the last gather is on torch's stream
+        e1.record()
         torch.cuda.synchronize()
         vms = e0.elapsed_time(e1)
         if world > 1:
             t = torch.tensor([vms], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             vms = float(t.item())
-        verify = {"value": vs * n_kf * world / (vms * 1e-3), "unit": "pairs/s", "pairs_per_gpu": n_kf, "features": 1000, "sharding": "keyframes block-sharded, NCCL all_gather of 84 B/pair" if world > 1 else "single GPU"}
+        verify = {"value": vs * n_kf * world / (vms * 1e-3), "unit": "pairs/s", "pairs_per_gpu": n_kf, "features": 1000, "sharding": "keyframes block-sharded, NCCL all_gather of 84 B/pair, overlapped with the next query's kernels" if world > 1 else "single GPU"}
         vctx.kfdb_destroy(db)
         vctx.close()
     except Exception as ex:  # the headline metric does not depend on this leg

@@ -346,3 +346,82 @@ def test_config3_full_hd_4000_features(oracle):
         assert np.abs(res["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
     finally:
         ctx.close()
+
+
+def test_config4_full_size_shard_independence_and_poses(oracle):
+    """BASELINE configs[3] at full size: 1 query x 4096 keyframes x 1000 features.  Size-independent properties:
+    the result of a keyframe does not depend on how the database is sharded (whole database == two halves with
+    first_pair_index offsets, byte for byte); overlapping keyframes verify with a pose that inverts the generator's
+    transform; a sample of pairs equals the oracle."""
+    import rgbdfe
+    import synth
+
+    n_kf, n_feat = 4096, 1000
+    qd, qp, kd, kp, T = synth.synth_pair_sets(n_kf, n_feat, seed=5678, overlap_frac=0.05)
+    cov = (0.01 * 2.0 * 2.0) ** 2
+    ctx = rgbdfe.Context(0, 640, 480, n_feat, 1)
+    try:
+        ctx.depth_cov_set(1, cov)
+        db = ctx.kfdb_create(kd, kp)
+        whole = ctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=0)
+        ctx.kfdb_destroy(db)
+        halves = []
+        for lo, hi in ((0, 2048), (2048, 4096)):
+            db = ctx.kfdb_create(kd[lo:hi], kp[lo:hi])
+            halves.append(ctx.verify_batch(db, hi - lo, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=lo))
+            ctx.kfdb_destroy(db)
+        assert np.concatenate(halves).tobytes() == whole.tobytes()
+        overlap = np.nonzero(np.abs(T - np.eye(4, dtype=np.float32)).reshape(n_kf, -1).max(1) > 0)[0]
+        assert 150 < len(overlap) < 260
+        assert whole["ok"][overlap].mean() > 0.95 and whole["ok"].sum() <= len(overlap)  # no false loop closures
+        for k in overlap[whole["ok"][overlap] != 0][:64]:
+            err = whole[k]["T21"].reshape(4, 4).astype(np.float64) @ T[k].astype(np.float64) - np.eye(4)
+            assert np.abs(err).max() < 0.05, k  # sensor noise 0.0012 z^2 on ~400 correspondences
+        for k in list(overlap[:6]) + [0, 1, 2]:
+            m = oracle.match(kd[k], qd, np.zeros(n_feat, np.uint8), kp[k], qp, 0.9, True)
+            assert whole[k]["n_matches"] == len(m)
+            if len(m) < 30:
+                assert whole[k]["ok"] == 0
+                continue
+            rng, latch = oracle.Rng(42 + int(k)), oracle.Latch()
+            latch.latched.value, latch.cov.value = 1, cov
+            r = oracle.ransac_se3(kp[k], qp, m, rng, latch, 200, 30, 3.0, 4)
+            assert bool(whole[k]["ok"]) == r["ok"] and whole[k]["n_inliers"] == len(r["inliers"]), k
+            assert np.abs(whole[k]["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
+    finally:
+        ctx.close()
+
+
+def test_config5_batched_relocalisation_queries_are_independent(oracle):
+    """BASELINE configs[4] shape (Q queries x 1024 keyframes, all pairs) at full keyframe count and Q = 12: running the
+    queries one after the other on one context gives, for every query, exactly what a fresh context gives for it
+    alone (per-pair streams srand(seed + q * n_kf + k): no state leaks from query to query)."""
+    import rgbdfe
+    import synth
+
+    n_kf, n_feat, Q = 1024, 1000, 12
+    qd, qp, kd, kp, _ = synth.synth_pair_sets(n_kf, n_feat, seed=6789, overlap_frac=0.1)
+    rs = np.random.default_rng(1)
+    queries = [(qd, qp)] + [(lambda p: (qd[p], qp[p]))(rs.permutation(n_feat)) for _ in range(Q - 1)]
+    cov = (0.01 * 2.0 * 2.0) ** 2
+
+    def run(ctx, db, q):
+        return ctx.verify_batch(db, n_kf, queries[q][0], queries[q][1], 0.9, 30, 200, 30, 3.0, 4, seed=7, first_pair_index=q * n_kf)
+
+    ctx = rgbdfe.Context(0, 640, 480, n_feat, 1)
+    ctx.depth_cov_set(1, cov)
+    db = ctx.kfdb_create(kd, kp)
+    batch = [run(ctx, db, q) for q in range(Q)]
+    ctx.kfdb_destroy(db)
+    ctx.close()
+    assert all(b["ok"].sum() > 50 for b in batch)
+    for q in (0, 5, Q - 1):
+        c2 = rgbdfe.Context(0, 640, 480, n_feat, 1)
+        c2.depth_cov_set(1, cov)
+        d2 = c2.kfdb_create(kd, kp)
+        alone = run(c2, d2, q)
+        c2.kfdb_destroy(d2)
+        c2.close()
+        assert alone.tobytes() == batch[q].tobytes()
+    # a permuted query sees the same scene: the same keyframes close their loops
+    assert (batch[3]["ok"] != 0).sum() == (batch[0]["ok"] != 0).sum() or abs(int(batch[3]["ok"].sum()) - int(batch[0]["ok"].sum())) <= 3
