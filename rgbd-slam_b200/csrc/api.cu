@@ -904,7 +904,7 @@ int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, 
     CUDA_TRY(c, cudaMemcpy(&cnt, f->n, sizeof(int), cudaMemcpyDeviceToHost));
     *n = cnt;
     if (cnt < 0) {
-        c->set_error("quadtree node capacity overflow");
+        c->set_error("extractor capacity overflow (quadtree nodes, or more than 65535 / w*h/8 FAST corners on one level of the cv::ORB branch)");
         return RGBDFE_E_CAPACITY;
     }
     const int m = std::min(cnt, cap);

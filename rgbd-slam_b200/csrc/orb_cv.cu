@@ -932,7 +932,7 @@ static int cvorb_prepare(rgbdfe_ctx* c, int w, int h)
         L.tile0 = tiles;
         tiles += ((L.w + CV_TW - 1) / CV_TW) * ((L.h + CV_TH - 1) / CV_TH);
         L.cand_off = cand;
-        L.cand_cap = std::min(65535, std::max(4096, L.w * L.h / 16));
+        L.cand_cap = std::min(65535, std::max(4096, L.w * L.h / 8)); // 3x3 NMS leaves at most 1 corner per 4 pixels; white noise reaches 1 per 13
         cand += align_up(L.cand_cap, 16);
         L.out_off = out;
         L.out_cap = L.quota + 64;

@@ -167,3 +167,62 @@ def test_gpu_cvorb_1080p_and_switch_back():
     o2k, o2d = orclib.Orb(1000).extract(g)
     assert _same_kps(k2, o2k) and (d2 == o2d).all()
     ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,nf", [(517, 333, 500), (322, 241, 40), (640, 480, 3)])
+def test_gpu_cvorb_odd_sizes_and_tiny_quotas(w, h, nf):
+    """widths / heights that are not multiples of 4 (row pitch padding, word staging) and feature counts so small that
+    some levels get a quota of 0 (retainBest(0) clears the level) or 1"""
+    cv2 = pytest.importorskip("cv2")
+    cam, frames = synth.sequence("tum_fr1", n=1, seed=61)
+    g = np.ascontiguousarray(cv2.resize(frames[0][0], (w, h), interpolation=cv2.INTER_AREA))
+    ok, od = orclib.CvOrb(nf, 1.2, 8).extract(g)
+    ctx = _ctx(w, h, nf)
+    k, d = ctx.orb_extract(g)
+    assert _same_kps(k, ok) and (d == od).all()
+    # a strided view (row pitch != width) gives the same result
+    big = np.zeros((h, w + 13), np.uint8)
+    big[:, :w] = g
+    import ctypes as C
+
+    import rgbdfe
+
+    kps = np.zeros(ctx.kp_cap, rgbdfe.KP_DTYPE)
+    desc = np.zeros((ctx.kp_cap, 32), np.uint8)
+    n = C.c_int()
+    ctx._chk(rgbdfe.lib().rgbdfe_orb_extract(ctx.h, big.ctypes.data_as(C.c_void_p), w, h, big.strides[0], kps.ctypes.data_as(C.c_void_p),
+                                             desc.ctypes.data_as(C.c_void_p), ctx.kp_cap, C.byref(n)))
+    assert _same_kps(kps[: n.value], ok) and (desc[: n.value] == od).all()
+    ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("blurred", [True, False])
+def test_gpu_cvorb_many_corners_takes_the_global_memory_path(blurred):
+    """a noisy image yields more FAST corners per level than the selection kernel keeps in shared memory (8192 at
+    640x480): the same permutation-exact retainBest then runs on the global scratch"""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(5)
+    g = rng.integers(0, 256, (480, 640), dtype=np.uint8)
+    if blurred:
+        g = cv2.GaussianBlur(g, (3, 3), 0.8)
+    o = orclib.CvOrb(1000, 1.2, 8)
+    ok, od = o.extract(g)
+    assert o.level_info(0)["n_fast"] > 8192, o.level_info(0)
+    ctx = _ctx(640, 480, 1000)
+    k, d = ctx.orb_extract(g)
+    assert _same_kps(k, ok) and (d == od).all()
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_gpu_cvorb_capacity_overflow_is_an_error_not_garbage():
+    """white noise at 1920x1080 has > 65535 FAST corners on level 0 (16-bit stopper positions): the call must fail"""
+    import rgbdfe
+
+    g = np.random.default_rng(6).integers(0, 256, (1080, 1920), dtype=np.uint8)
+    ctx = _ctx(1920, 1080, 1000)
+    with pytest.raises(rgbdfe.RgbdfeError):
+        ctx.orb_extract(g)
+    ctx.close()
