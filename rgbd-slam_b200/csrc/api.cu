@@ -325,6 +325,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_pair_workspaces(c);
     free_proj_workspace(c);
     free_cvorb_workspace(c);
+    free_fast_state(c);
     free_frame(c->scratch);
     free_frame(c->scratch2);
     if (c->order_evt)

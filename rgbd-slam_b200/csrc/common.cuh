@@ -241,6 +241,9 @@ struct rgbdfe_ctx {
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
     int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
+    // K2 state (orb_image.cu): host copy of the kernel's parameter block (tensor maps of the pyramid levels) and the cell table
+    void* fast_grid = nullptr; void* d_fast_cells = nullptr; void* d_fast_maps = nullptr; bool fast_ready = false;
+    const void* fast_key_pyr = nullptr; int fast_key_w = 0, fast_key_h = 0, fast_key_levels = 0, fast_key_slots = 0;
     struct CvOrbWorkspace* cvorb = nullptr; // the cv::ORB branch of Extractor (row N3, orb_cv.cu), allocated by rgbdfe_cvorb_configure
     int extractor = 0;                      // RGBDFE_EXTRACTOR_ORB2 / RGBDFE_EXTRACTOR_ORB: which one the extraction entry points run
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
@@ -323,6 +326,7 @@ namespace rgbdfe {
 int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_stride, int channels);
 int launch_blur(rgbdfe_ctx* c, int count);
 int launch_fast(rgbdfe_ctx* c, int count);
+void free_fast_state(rgbdfe_ctx* c);
 // orb_keypoints.cu
 int launch_quadtree(rgbdfe_ctx* c, int count);
 int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep);

@@ -9,6 +9,11 @@
 // blockIdx.z (or .y) is the frame slot: every kernel processes a batch of frames.
 #include "common.cuh"
 #include "fast_core.cuh"
+#include "tma.cuh"
+
+#include <memory>
+#include <string>
+#include <vector>
 
 namespace rgbdfe {
 
@@ -182,66 +187,59 @@ __global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cf
 // Geometry of the FAST cell grid of every level, passed by value (constant bank): the kernel's prologue has no
 // dependent global loads.
 struct FastGrid {
-    int nlevels, iniTh, minTh;
-    int cell_off[RGBDFE_MAX_LEVELS + 1];
-    int nCols[RGBDFE_MAX_LEVELS], wCell[RGBDFE_MAX_LEVELS], hCell[RGBDFE_MAX_LEVELS];
-    int maxBorderX[RGBDFE_MAX_LEVELS], maxBorderY[RGBDFE_MAX_LEVELS], pstride[RGBDFE_MAX_LEVELS];
-    unsigned pyr_off[RGBDFE_MAX_LEVELS];
-    unsigned inv_nCols[RGBDFE_MAX_LEVELS]; // 0xffffffff / nCols + 1: cell / nCols == umulhi(cell, inv_nCols)
-    unsigned inv_small[32];                // the same reciprocal for divisors 1..31 (words / groups per cell row)
+    int iniTh, minTh;
+    unsigned inv_small[32]; // 0xffffffff / d + 1 for d = 1..31: i / d == umulhi(i, inv_small[d]) (groups per cell row)
+};
+// Tensor maps of the pyramid levels, resident in global memory (one 128-byte descriptor per level): the padded level of
+// every frame slot as a (pstride, h + 38, slots) u8 tensor, box = (96, hCell + 6, 1).
+struct FastMaps {
+    CUtensorMap map[RGBDFE_MAX_LEVELS];
+};
+// One FAST cell, precomputed on the host (ORBextractor.cpp:636-653): window origin and size in level coordinates
+// (minBorder-relative), origin of the cell in the output coordinates, level; cw == 0 marks a skipped cell.
+struct FastCell {
+    short iniX, iniY, cw, ch;
+    short outX, outY, level, box_rows; // box_rows = hCell + 6: rows of the level's TMA box
 };
 
 #define FAST_THREADS 256
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FastGrid G, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FastGrid G, const FastMaps* __restrict__ maps, const FastCell* __restrict__ cells,
     int* __restrict__ cell_count, unsigned* __restrict__ cell_list, int cell_slot)
 {
-    int level = 0;
-    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.cell_off[level + 1])
-        level++;
-    const int cell = blockIdx.x - G.cell_off[level];
-    const int nCols = G.nCols[level], wCell = G.wCell[level], hCell = G.hCell[level], pstride = G.pstride[level];
-    const int ci = (int)__umulhi((unsigned)cell, G.inv_nCols[level]), cj = cell - ci * nCols;
+    const FastCell cd = cells[blockIdx.x];
     const int slot = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31;
     int* out_count = cell_count + (size_t)slot * cell_slot + blockIdx.x;
     unsigned* out_list = cell_list + ((size_t)slot * cell_slot + blockIdx.x) * CELL_CAP;
-
-    const int iniY = 16 + ci * hCell, iniX = 16 + cj * wCell;
-    int maxY = iniY + hCell + 6, maxX = iniX + wCell + 6;
-    const int maxBorderX = G.maxBorderX[level], maxBorderY = G.maxBorderY[level];
-    bool skip = (iniY >= maxBorderY - 3) || (iniX >= maxBorderX - 6);
-    if (maxY > maxBorderY)
-        maxY = maxBorderY;
-    if (maxX > maxBorderX)
-        maxX = maxBorderX;
-    const int cw = maxX - iniX, ch = maxY - iniY;
-    if (skip || cw < 7 || ch < 7) {
+    const int cw = cd.cw, ch = cd.ch;
+    if (cw == 0) {
         if (tid == 0)
             *out_count = 0;
         return;
     }
-    constexpr int PITCH = CELL_MAX_DIM + 8;
-    __shared__ __align__(16) uint8_t s_img[CELL_MAX_DIM][PITCH];
+    constexpr int PITCH = CELL_MAX_DIM + 24; // window + up to 15 bytes of alignment shift, multiple of 16
+    __shared__ __align__(128) uint8_t s_img[CELL_MAX_DIM][PITCH];
     __shared__ __align__(16) uint8_t s_S[CELL_MAX_DIM][PITCH];
     __shared__ unsigned short s_cand[CELL_MAX_DIM * CELL_MAX_DIM]; // pixels that pass the pair test: r << 8 | c
     __shared__ unsigned short s_keep[CELL_MAX_DIM * CELL_MAX_DIM]; // NMS survivors of this attempt: r << 8 | c, unordered
     __shared__ int s_ncand, s_n;
-    const uint8_t* src = pyr + slot * pyr_slot + G.pyr_off[level] + (size_t)(EDGE_THRESHOLD + iniY) * pstride + EDGE_THRESHOLD + iniX;
-    // rows are staged as 32-bit words from the 4-byte aligned address at or below the cell's first column
-    const int mis = (int)(reinterpret_cast<size_t>(src) & 3);
-    const int wpr = (cw + mis + 3) >> 2; // words per row
-    const unsigned inv_wpr = G.inv_small[wpr]; // wpr <= (CELL_MAX_DIM + 6) / 4
-    for (int i = tid; i < wpr * ch; i += FAST_THREADS) {
-        const int r = (int)__umulhi((unsigned)i, inv_wpr), wq = i - r * wpr;
-        const unsigned wv = *reinterpret_cast<const unsigned*>(src - mis + (size_t)r * pstride + 4 * wq);
-        *reinterpret_cast<unsigned*>(&s_img[r][4 * wq]) = wv;
-        *reinterpret_cast<unsigned*>(&s_S[r][4 * wq]) = 0u;
-    }
+    __shared__ __align__(8) uint64_t s_bar;
+    // The cell's window is staged by the TMA unit: one thread arms the barrier and issues the tensor copy (box 96 x
+    // (hCell + 6) bytes; the box must start at a 16-byte aligned address, so it starts up to 15 columns left of the
+    // window: image column c lives at s_img[r][c + mis]; the 19 px ring keeps every window inside the level), the other
+    // threads clear the strength map meanwhile.
+    const int wx = EDGE_THRESHOLD + cd.iniX, mis = wx & 15;
     if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_expect_tx(&s_bar, (unsigned)PITCH * (unsigned)cd.box_rows);
+        tma_load_3d(&s_img[0][0], &maps->map[cd.level], wx - mis, EDGE_THRESHOLD + cd.iniY, slot, &s_bar);
         s_ncand = 0;
         s_n = 0;
     }
+    for (int i = tid; i < (PITCH / 4) * ch; i += FAST_THREADS)
+        reinterpret_cast<unsigned*>(&s_S[0][0])[i] = 0u;
     __syncthreads();
+    mbar_wait(&s_bar, 0);
     // image column c lives at s_img[r][c + mis]; s_S uses the same shift
     const int dw = cw - 6, dh = ch - 6;
     const int th_lo = min(G.iniTh, G.minTh);
@@ -358,7 +356,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             rank += s_keep[j] < key;
         if (rank < CELL_CAP) {
             const int r = key >> 8, c = key & 255;
-            out_list[rank] = pack_cand(c + cj * wCell, r + ci * hCell, s_S[r][c + mis] - 1);
+            out_list[rank] = pack_cand(c + cd.outX, r + cd.outY, s_S[r][c + mis] - 1);
         }
     }
     if (tid == 0)
@@ -402,27 +400,107 @@ int launch_blur(rgbdfe_ctx* c, int count)
     return RGBDFE_OK;
 }
 
-int launch_fast(rgbdfe_ctx* c, int count)
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn()
 {
-    ProfScope prof(c, KID_FAST);
-    FastGrid G;
-    memset(&G, 0, sizeof(G));
-    const OrbConfig& cfg = c->cfg;
-    G.nlevels = cfg.nlevels, G.iniTh = cfg.iniTh, G.minTh = cfg.minTh;
-    for (int l = 0; l < cfg.nlevels; l++) {
-        const LevelDesc& L = cfg.lv[l];
-        G.cell_off[l] = L.cell_off, G.nCols[l] = L.nCols, G.wCell[l] = L.wCell, G.hCell[l] = L.hCell;
-        G.maxBorderX[l] = L.maxBorderX, G.maxBorderY[l] = L.maxBorderY, G.pstride[l] = L.pstride, G.pyr_off[l] = L.pyr_off;
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
     }
-    G.cell_off[cfg.nlevels] = cfg.total_cells;
-    for (int l = 0; l < cfg.nlevels; l++)
-        G.inv_nCols[l] = 0xffffffffu / (unsigned)cfg.lv[l].nCols + 1u;
+    return fn;
+}
+
+// Per-configuration state of K2: the cell table and the tensor maps of the pyramid levels (rebuilt when the level
+// geometry or the pyramid buffer changes).
+static int prepare_fast(rgbdfe_ctx* c)
+{
+    const OrbConfig& cfg = c->cfg;
+    if (c->fast_ready && c->fast_key_pyr == c->d_pyr && c->fast_key_w == cfg.w && c->fast_key_h == cfg.h && c->fast_key_levels == cfg.nlevels
+        && c->fast_key_slots == c->max_batch)
+        return RGBDFE_OK;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) {
+        c->set_error("cuTensorMapEncodeTiled is not available from this driver (TMA staging needs CUDA >= 12)");
+        return RGBDFE_E_CUDA;
+    }
+    FastGrid& G = *static_cast<FastGrid*>(c->fast_grid);
+    memset(&G, 0, sizeof(G));
     for (int d = 1; d < 32; d++)
         G.inv_small[d] = 0xffffffffu / (unsigned)d + 1u;
-    k_fast_cells<<<dim3(cfg.total_cells, count), FAST_THREADS, 0, c->stream>>>(G, c->d_pyr, c->pyr_slot, c->d_cell_count, c->d_cell_list, c->cell_slot);
+    FastMaps* hm = new FastMaps();
+    std::unique_ptr<FastMaps> hm_owner(hm);
+    std::vector<FastCell> cells(cfg.total_cells);
+    for (int l = 0; l < cfg.nlevels; l++) {
+        const LevelDesc& L = cfg.lv[l];
+        for (int ci = 0; ci < L.nRows; ci++)
+            for (int cj = 0; cj < L.nCols; cj++) {
+                // ORBextractor.cpp:636-653 (coordinates relative to minBorder = EDGE_THRESHOLD - 3 = 16)
+                FastCell& f = cells[L.cell_off + ci * L.nCols + cj];
+                const int iniY = 16 + ci * L.hCell, iniX = 16 + cj * L.wCell;
+                int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+                const bool skip = (iniY >= L.maxBorderY - 3) || (iniX >= L.maxBorderX - 6);
+                maxY = std::min(maxY, L.maxBorderY);
+                maxX = std::min(maxX, L.maxBorderX);
+                const int cw = maxX - iniX, ch = maxY - iniY;
+                f.iniX = (short)iniX, f.iniY = (short)iniY;
+                f.cw = (short)((skip || cw < 7 || ch < 7) ? 0 : cw), f.ch = (short)ch;
+                f.outX = (short)(cj * L.wCell), f.outY = (short)(ci * L.hCell);
+                f.level = (short)l, f.box_rows = (short)(L.hCell + 6);
+            }
+        const cuuint64_t dims[3] = { (cuuint64_t)L.pstride, (cuuint64_t)(L.h + 2 * EDGE_THRESHOLD), (cuuint64_t)c->max_batch };
+        const cuuint64_t strides[2] = { (cuuint64_t)L.pstride, (cuuint64_t)c->pyr_slot };
+        const cuuint32_t box[3] = { CELL_MAX_DIM + 24, (cuuint32_t)(L.hCell + 6), 1 };
+        const cuuint32_t estr[3] = { 1, 1, 1 };
+        const CUresult r = enc(&hm->map[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, c->d_pyr + L.pyr_off, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            c->set_error("cuTensorMapEncodeTiled failed for a pyramid level (code " + std::to_string((int)r) + ")");
+            return RGBDFE_E_CUDA;
+        }
+    }
+    cudaFree(c->d_fast_cells);
+    cudaFree(c->d_fast_maps);
+    c->d_fast_cells = nullptr, c->d_fast_maps = nullptr;
+    CUDA_TRY(c, cudaMalloc(&c->d_fast_maps, sizeof(FastMaps)));
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_fast_maps, hm, sizeof(FastMaps), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMalloc(&c->d_fast_cells, cells.size() * sizeof(FastCell)));
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_fast_cells, cells.data(), cells.size() * sizeof(FastCell), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream)); // `cells` is a local
+    c->fast_ready = true;
+    c->fast_key_pyr = c->d_pyr, c->fast_key_w = cfg.w, c->fast_key_h = cfg.h, c->fast_key_levels = cfg.nlevels, c->fast_key_slots = c->max_batch;
+    return RGBDFE_OK;
+}
+
+int launch_fast(rgbdfe_ctx* c, int count)
+{
+    if (!c->fast_grid)
+        c->fast_grid = new FastGrid();
+    const int rc = prepare_fast(c);
+    if (rc != RGBDFE_OK)
+        return rc;
+    ProfScope prof(c, KID_FAST);
+    FastGrid& G = *static_cast<FastGrid*>(c->fast_grid);
+    G.iniTh = c->cfg.iniTh, G.minTh = c->cfg.minTh;
+    k_fast_cells<<<dim3(c->cfg.total_cells, count), FAST_THREADS, 0, c->stream>>>(G, static_cast<const FastMaps*>(c->d_fast_maps), static_cast<const FastCell*>(c->d_fast_cells), c->d_cell_count,
+        c->d_cell_list, c->cell_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;
+}
+
+void free_fast_state(rgbdfe_ctx* c)
+{
+    cudaFree(c->d_fast_cells);
+    cudaFree(c->d_fast_maps);
+    c->d_fast_cells = nullptr, c->d_fast_maps = nullptr;
+    delete static_cast<FastGrid*>(c->fast_grid);
+    c->fast_grid = nullptr;
+    c->fast_ready = false;
 }
 
 } // namespace rgbdfe
