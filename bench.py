@@ -52,13 +52,13 @@ ALG_BYTES = {
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
 # captures summarised in profiles/r1_ncu_full_brief.txt, and the unit that actually limits each kernel there.
 NCU_TRAFFIC_64 = {
-    "k_fast_cells": 62.85e6 + 2.91e6, "k_gauss7": 72.91e6 + 34.82e6, "k_orient_describe": 139.09e6 + 9.22e6,
+    "k_fast_cells": 65.02e6 + 3.64e6, "k_gauss7": 72.84e6 + 31.39e6, "k_orient_describe": 139.05e6 + 9.66e6,
     "k_knn2_hamming": 4.20e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
 NCU_LIMITER = {
-    "k_fast_cells": "issue slots 79 % busy, ALU pipe 57 % (16-bit-lane min/max work): instruction-bound; DRAM traffic = 1.0x algorithmic, 3 % of peak",
+    "k_fast_cells": "issue slots 79 % busy, ALU pipe 62 % (16-bit-lane min/max work), tiles staged by TMA: instruction-bound; DRAM traffic = 1.1x algorithmic, 4 % of peak",
     "k_gauss7": "issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 59 %; DRAM 17 % of peak",
-    "k_orient_describe": "XU 53 % (atan2 / sin / cos), L1 74 %, issue 74 %; DRAM 16 % of peak",
+    "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 74 %; DRAM 16 % of peak",
     "k_knn2_hamming": "tensor pipe (u8 IMMA m16n8k32) 65 % busy while active = 57 % of the 0.5 IMMA/clk/SM measured peak; DRAM < 1 % of peak",
     "k_quadtree": "latency (shared-memory atomics and scans, one CTA per level and frame): issue 32 %",
 }

@@ -150,38 +150,6 @@ __device__ int warp_partition_pivot(T* a, int f, int l, unsigned short* Lpos, un
     return cut;
 }
 
-// std::nth_element by one warp (all 32 lanes call it; the array must be visible to the warp)
-template <class T, class C>
-__device__ void warp_nth_element(T* base, int nth, int n, unsigned short* Lpos, unsigned short* Rpos, int lane, C comp)
-{
-    if (n == 0 || nth == n)
-        return;
-    int lg = 0;
-    for (int t = n; t > 1; t >>= 1)
-        lg++;
-    int depth = 2 * lg;
-    int f = 0, l = n;
-    while (l - f > 3) {
-        if (depth == 0) {
-            if (lane == 0) {
-                heap_select_(base + f, base + nth + 1, base + l, comp);
-                isort_swap(base[f], base[nth]);
-            }
-            __syncwarp();
-            return;
-        }
-        --depth;
-        const int cut = warp_partition_pivot(base, f, l, Lpos, Rpos, lane, comp);
-        if (cut <= nth)
-            f = cut;
-        else
-            l = cut;
-    }
-    if (lane == 0)
-        insertion_sort_(base + f, base + l, comp);
-    __syncwarp();
-}
-
 // std::partition(base + first, base + last, pred) by one warp: the k-th swap exchanges the k-th element failing pred
 // (ascending) with the k-th element passing it (descending) while the former lies before the latter.
 template <class T, class P>

@@ -17,16 +17,21 @@
 #include "frame_tail.cuh"
 #include "introselect.cuh"
 #include "orb_math.cuh"
+#include "tma.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #define CV_RING 32
 #define CV_EDGE 31
 #define CV_FAST_TH 20
 #define CV_TW 64
 #define CV_TH 32
+#define CV_WOFF 16  // a staged window starts 16 columns left of its tile: TMA boxes start on 16-byte boundaries
+#define CV_PITCH 96 // bytes per staged row: 16 + 64 + halo, multiple of 16
+#define CV_BOX_ROWS 40
 #define CV_SEL_THREADS 512
 
 struct CvLevel {
@@ -80,6 +85,7 @@ struct CvOrbWorkspace {
     int tab_cap = 0;
     int slots = 0;
     signed char* d_pattern = nullptr;
+    CUtensorMap* d_maps = nullptr;       // per level: the padded pyramid level of every frame slot as a (pstride, h + 64, slots) u8 tensor, box 96 x 40
 };
 
 namespace rgbdfe {
@@ -163,8 +169,8 @@ __device__ __forceinline__ int cv_find_level(const CvCfg& C, int tile)
 // cv::FAST(threshold 20, nonmaxSuppression) over the whole level + KeyPointsFilter::runByImageBorder(31): the tile
 // computes the corner strength S on its 66 x 34 neighbourhood, applies the 3x3 non-max rule (a neighbour that is not
 // a corner scores 0) and writes response = S - 1 of the survivors into the level's score map, 0 elsewhere.
-__global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
-    uint8_t* __restrict__ score, size_t score_slot)
+__global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C, const CUtensorMap* __restrict__ maps, uint8_t* __restrict__ score,
+    size_t score_slot)
 {
     const int level = cv_find_level(C, blockIdx.x);
     const CvLevel& L = C.lv[level];
@@ -172,11 +178,12 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
     const int tiles_x = (L.w + CV_TW - 1) / CV_TW;
     const int ty = t / tiles_x, x0 = (t - ty * tiles_x) * CV_TW, y0 = ty * CV_TH;
     const int slot = blockIdx.y, tid = threadIdx.x;
-    constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 8;
-    __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
+    constexpr int PITCH = CV_PITCH, ROWS = CV_BOX_ROWS;
+    __shared__ __align__(128) uint8_t s_img[ROWS][PITCH];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(16) uint8_t s_S[ROWS][PITCH];
     __shared__ __align__(16) uint8_t s_out[CV_TH][CV_TW];
-    __shared__ unsigned short s_cand[(CV_TH + 2) * (PITCH)];
+    __shared__ unsigned short s_cand[(CV_TH + 2) * (CV_TW + 4)]; // at most the 34 x 66 kept region + halo
     __shared__ int s_ncand;
     uint8_t* out = score + slot * score_slot + L.blur_off;
     // the part of the tile that survives runByImageBorder(31); strengths are needed there and on its 1 px halo only
@@ -189,30 +196,30 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
         }
         return;
     }
-    // staged window: level rows y0-4 .. y0+35, columns x0-4 .. x0+67 (the ring covers 4 px outside the image; rows and
-    // words beyond the padded level are clamped: those pixels lie outside the detection region and are never used)
-    const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
-    const int max_word = (L.pstride - CV_RING - 4) >> 2; // last whole word of a padded row, relative to column 0
-    for (int i = tid; i < ROWS * (PITCH / 4); i += 256) {
-        const int r = i / (PITCH / 4), q = i - r * (PITCH / 4);
-        const int y = min(y0 - 4 + r, L.h + CV_RING - 1);
-        const int wq = min((x0 - 4) / 4 + q, max_word);
-        *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
-        *reinterpret_cast<unsigned*>(&s_S[r][4 * q]) = 0u;
+    // staged window: level rows y0-4 .. y0+35, columns x0-16 .. x0+79, brought in by the TMA unit (box 96 x 40; whatever
+    // lies beyond the padded level arrives as zeros and is outside the detection region); the threads clear the strength
+    // map and the output tile meanwhile
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_expect_tx(&s_bar, PITCH * ROWS);
+        tma_load_3d(&s_img[0][0], &maps[level], x0 - CV_WOFF + CV_RING, y0 - 4 + CV_RING, slot, &s_bar);
     }
+    for (int i = tid; i < ROWS * (PITCH / 4); i += 256)
+        reinterpret_cast<unsigned*>(&s_S[0][0])[i] = 0u;
     for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256)
         reinterpret_cast<unsigned*>(&s_out[0][0])[i] = 0u;
     if (tid == 0)
         s_ncand = 0;
     __syncthreads();
+    mbar_wait(&s_bar, 0);
     // Phase 1: the 4-opposite-pair necessary test (fast_candidate2, four pixels per thread in 16-bit lanes) on the kept
     // region + 1 px halo (which lies inside cv::FAST's detection region [3, w-3) x [3, h-3)); survivors are compacted
-    // with ballots.  Window column c is level column x0 - 4 + c, window row r is level row y0 - 4 + r.
+    // with ballots.  Window column c is level column x0 - 16 + c, window row r is level row y0 - 4 + r.
     {
         constexpr int RW = PITCH / 4;
         const int r_lo = ey0 - 1 - (y0 - 4), nrows = ey1 - ey0 + 2;
-        const int c_lo = ex0 - 1 - (x0 - 4), c_hi = ex1 - (x0 - 4); // first / last needed window column
-        const int g_lo = c_lo >> 2, ngr = (c_hi >> 2) - g_lo + 1;  // <= 18 word groups per row
+        const int c_lo = ex0 - 1 - (x0 - CV_WOFF), c_hi = ex1 - (x0 - CV_WOFF); // first / last needed window column
+        const int g_lo = c_lo >> 2, ngr = (c_hi >> 2) - g_lo + 1;  // <= 18 of the 24 word groups of a row
         const unsigned inv_ngr = 0xffffffffu / (unsigned)ngr + 1u;
         const int NG = nrows * ngr;
         const unsigned c1 = 0x7fff7fffu - ((unsigned)CV_FAST_TH | (unsigned)CV_FAST_TH << 16);
@@ -225,7 +232,6 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
                 const int rr = (int)__umulhi((unsigned)i, inv_ngr);
                 r = r_lo + rr;
                 g = g_lo + (i - rr * ngr);
-                // groups 0 and 17 read one word across the row end (still inside s_img); only their columns 3 / 68 are kept
                 const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g;
                 const unsigned cm = w[-1], cc = w[0], cp = w[1];
                 const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
@@ -275,14 +281,14 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
     // a corner's S is >= 21, and score = S - 1 on both sides of the comparison)
     for (int i = tid; i < ncand; i += 256) {
         const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
-        const int x = x0 - 4 + c, y = y0 - 4 + r;
+        const int x = x0 - CV_WOFF + c, y = y0 - 4 + r;
         const int S = s_S[r][c];
         if (S == 0 || x < ex0 || x >= ex1 || y < ey0 || y >= ey1)
             continue;
         const int m = max(max(max(s_S[r - 1][c - 1], s_S[r - 1][c]), max(s_S[r - 1][c + 1], s_S[r][c - 1])),
             max(max(s_S[r][c + 1], s_S[r + 1][c - 1]), max(s_S[r + 1][c], s_S[r + 1][c + 1])));
         if (S > m)
-            s_out[r - 4][c - 4] = (uint8_t)(S - 1);
+            s_out[r - 4][c - CV_WOFF] = (uint8_t)(S - 1);
     }
     __syncthreads();
     for (int i = tid; i < CV_TH * (CV_TW / 4); i += 256) {
@@ -296,8 +302,8 @@ __global__ void __launch_bounds__(256) k_cv_fast(const __grid_constant__ CvCfg C
 // GaussianBlur(level, 7x7, sigma 2, BORDER_REFLECT_101) on a submatrix = sepFilter2D with the float kernel: row pass
 // left to right (FMA in the 32-pixel vector body and in the last w % 4 pixels, separate multiply / add in the
 // 4-way unrolled part between them), column pass centre tap + symmetric pairs with FMA, cvRound, saturate.
-__global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C, const uint8_t* __restrict__ pyr, size_t pyr_slot,
-    uint8_t* __restrict__ blur, size_t blur_slot)
+__global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C, const CUtensorMap* __restrict__ maps, uint8_t* __restrict__ blur,
+    size_t blur_slot)
 {
     const int level = cv_find_level(C, blockIdx.x);
     const CvLevel& L = C.lv[level];
@@ -305,23 +311,23 @@ __global__ void __launch_bounds__(256) k_cv_blur(const __grid_constant__ CvCfg C
     const int tiles_x = (L.w + CV_TW - 1) / CV_TW;
     const int ty = t / tiles_x, x0 = (t - ty * tiles_x) * CV_TW, y0 = ty * CV_TH;
     const int slot = blockIdx.y, tid = threadIdx.x;
-    constexpr int PITCH = CV_TW + 8, ROWS = CV_TH + 6;
-    __shared__ __align__(16) uint8_t s_img[ROWS][PITCH];
+    constexpr int PITCH = CV_PITCH, ROWS = CV_TH + 6;
+    __shared__ __align__(128) uint8_t s_img[CV_BOX_ROWS][PITCH];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(16) float s_h[ROWS][CV_TW];
-    const uint8_t* lvl = pyr + slot * pyr_slot + L.pyr_off;
-    const int max_word = (L.pstride - CV_RING - 4) >> 2;
-    for (int i = tid; i < ROWS * (PITCH / 4); i += 256) { // rows y0-3 .. y0+34, columns x0-4 .. x0+67
-        const int r = i / (PITCH / 4), q = i - r * (PITCH / 4);
-        const int y = min(y0 - 3 + r, L.h + CV_RING - 1);
-        const int wq = min((x0 - 4) / 4 + q, max_word);
-        *reinterpret_cast<unsigned*>(&s_img[r][4 * q]) = *reinterpret_cast<const unsigned*>(lvl + (ptrdiff_t)y * L.pstride + 4 * wq);
+    // staged window: level rows y0-3 .. y0+36, columns x0-16 .. x0+79 (TMA box 96 x 40, see k_cv_fast)
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_expect_tx(&s_bar, PITCH * CV_BOX_ROWS);
+        tma_load_3d(&s_img[0][0], &maps[level], x0 - CV_WOFF + CV_RING, y0 - 3 + CV_RING, slot, &s_bar);
     }
     __syncthreads();
+    mbar_wait(&s_bar, 0);
     // row pass: 4 adjacent outputs per thread from 3 staged words; a group of 4 never straddles vec_end / unr_end
     for (int i = tid; i < ROWS * (CV_TW / 4); i += 256) {
         const int r = i >> 4, q = i & 15;
         const unsigned* row = reinterpret_cast<const unsigned*>(&s_img[r][0]);
-        const unsigned w0 = row[q], w1 = row[q + 1], w2 = row[q + 2];
+        const unsigned w0 = row[q + 3], w1 = row[q + 4], w2 = row[q + 5]; // level columns x0 + 4q - 4 .. x0 + 4q + 7
         float p[12];
 #pragma unroll
         for (int j = 0; j < 4; j++) { // byte -> float on the ALU: 0x4B0000bb is 2^23 + b (keeps the conversion off the XU pipe)
@@ -795,8 +801,8 @@ void free_buffers(CvOrbWorkspace* W)
 {
     cudaFree(W->d_pyr), cudaFree(W->d_blur), cudaFree(W->d_score), cudaFree(W->d_cand), cudaFree(W->d_lr), cudaFree(W->d_hkey);
     cudaFree(W->d_hcount), cudaFree(W->d_out), cudaFree(W->d_out_count), cudaFree(W->d_final), cudaFree(W->d_final_count);
-    cudaFree(W->d_tab_ofs), cudaFree(W->d_tab_c1), cudaFree(W->d_gscratch);
-    W->d_gscratch = nullptr;
+    cudaFree(W->d_tab_ofs), cudaFree(W->d_tab_c1), cudaFree(W->d_gscratch), cudaFree(W->d_maps);
+    W->d_gscratch = nullptr, W->d_maps = nullptr;
     W->d_pyr = W->d_blur = W->d_score = nullptr;
     W->d_cand = nullptr, W->d_lr = nullptr, W->d_hkey = nullptr, W->d_hcount = nullptr, W->d_out = nullptr, W->d_out_count = nullptr;
     W->d_final = nullptr, W->d_final_count = nullptr, W->d_tab_ofs = nullptr, W->d_tab_c1 = nullptr;
@@ -970,6 +976,30 @@ static int cvorb_prepare(rgbdfe_ctx* c, int w, int h)
     }
     CUDA_TRY(c, cudaMemcpy(W->d_tab_ofs, ofs.data(), (size_t)tab * sizeof(int), cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(W->d_tab_c1, c1.data(), (size_t)tab * sizeof(unsigned short), cudaMemcpyHostToDevice));
+    {
+        EncodeTiledFn enc = encode_tiled_fn();
+        if (!enc) {
+            c->set_error("cuTensorMapEncodeTiled is not available from this driver (TMA staging needs CUDA >= 12)");
+            return RGBDFE_E_CUDA;
+        }
+        std::vector<CUtensorMap> hm(RGBDFE_MAX_LEVELS);
+        for (int l = 0; l < C.nlevels; l++) {
+            const CvLevel& L = C.lv[l];
+            const cuuint64_t dims[3] = { (cuuint64_t)L.pstride, (cuuint64_t)(L.h + 2 * CV_RING), (cuuint64_t)S };
+            const cuuint64_t strides[2] = { (cuuint64_t)L.pstride, (cuuint64_t)W->pyr_slot };
+            const cuuint32_t box[3] = { CV_PITCH, CV_BOX_ROWS, 1 }, estr[3] = { 1, 1, 1 };
+            // the tensor starts at the padded level's first byte (row -32, column -32)
+            void* base = W->d_pyr + L.pyr_off - (size_t)CV_RING * L.pstride - CV_RING;
+            const CUresult r = enc(&hm[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) {
+                c->set_error("cuTensorMapEncodeTiled failed for a cv::ORB pyramid level");
+                return RGBDFE_E_CUDA;
+            }
+        }
+        CUDA_TRY(c, dmalloc(&W->d_maps, hm.size() * sizeof(CUtensorMap)));
+        CUDA_TRY(c, cudaMemcpy(W->d_maps, hm.data(), hm.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+    }
     if (!W->d_pattern) {
         CUDA_TRY(c, dmalloc(&W->d_pattern, 1024));
         CUDA_TRY(c, cudaMemcpy(W->d_pattern, kBriefPattern, 1024, cudaMemcpyHostToDevice));
@@ -1002,12 +1032,12 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
     }
     {
         ProfScope prof(c, KID_FAST);
-        k_cv_fast<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot);
+        k_cv_fast<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_maps, W->d_score, W->blur_slot);
         c->launches++;
     }
     {
         ProfScope prof(c, KID_BLUR);
-        k_cv_blur<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_blur, W->blur_slot);
+        k_cv_blur<<<dim3(C.tiles, count), 256, 0, c->stream>>>(C, W->d_maps, W->d_blur, W->blur_slot);
         c->launches++;
     }
     {

@@ -400,21 +400,6 @@ int launch_blur(rgbdfe_ctx* c, int count)
     return RGBDFE_OK;
 }
 
-// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time dependency on libcuda)
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_tiled_fn()
-{
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    return fn;
-}
-
 // Per-configuration state of K2: the cell table and the tensor maps of the pyramid levels (rebuilt when the level
 // geometry or the pyramid buffer changes).
 static int prepare_fast(rgbdfe_ctx* c)
