@@ -380,6 +380,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         c->host_zero_copy = value != 0;
         return RGBDFE_OK;
     }
+    if (!strcmp(name, "knn_umma")) {
+        c->knn_umma = value != 0;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "ransac_first_chunk")) {
         if (value < 1 || value > MAX_ITERS)
             return RGBDFE_E_ARG;

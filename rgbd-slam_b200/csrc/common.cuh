@@ -218,6 +218,7 @@ struct rgbdfe_ctx {
     // match / RANSAC workspaces for pair_cap pairs
     int pair_cap = 0;
     int knn_splits = 8;
+    int knn_umma = 1; // K7 on tcgen05 (match_umma.cu); 0 = the mma.sync kernel (option "knn_umma")
     MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
     int4* d_partial = nullptr;      // [pairs][splits][kp_cap]
     rgbdfe_dmatch* d_matches = nullptr; // [pairs][kp_cap]  Matcher::match output (query order)
@@ -334,6 +335,7 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);
 int knn_splits_for(const rgbdfe_ctx* c, int npairs);
+int launch_knn_umma(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);
 // projection.cu
 void free_proj_workspace(rgbdfe_ctx* c);
 // orb_cv.cu

@@ -180,7 +180,8 @@ __global__ void __launch_bounds__(256) k_ratio_filter(const MatchPair* __restric
 // buffer (max(npairs, 64 * knn_splits) rows).
 int knn_splits_for(const rgbdfe_ctx* c, int npairs)
 {
-    const int qblocks = (c->kp_cap + KNN_QPB - 1) / KNN_QPB;
+    const int qpb = c->knn_umma ? 128 : KNN_QPB; // queries per CTA of the selected kernel
+    const int qblocks = (c->kp_cap + qpb - 1) / qpb;
     const int want = (6 * 2 * 148 + qblocks * npairs - 1) / (qblocks * npairs);
     const int room = std::max(npairs, 64 * c->knn_splits) / npairs;
     return std::max(1, std::min(std::min(want, c->knn_splits), room));
@@ -195,10 +196,12 @@ int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, i
         c->set_error("kNN: train index does not fit the 16-bit field of the candidate word");
         return RGBDFE_E_CAPACITY;
     }
-    dim3 grd((max_nq + KNN_QPB - 1) / KNN_QPB, splits, npairs);
     ProfScope prof(c, KID_KNN);
-    k_knn2_hamming<<<grd, KNN_THREADS, 0, c->stream>>>(d_pairs, slot0, c->d_partial, c->kp_cap, splits);
     c->launches++;
+    if (c->knn_umma) // the tcgen05 form (match_umma.cu); the mma.sync form below stays for A/B measurements
+        return launch_knn_umma(c, d_pairs, slot0, npairs, max_nq, splits);
+    dim3 grd((max_nq + KNN_QPB - 1) / KNN_QPB, splits, npairs);
+    k_knn2_hamming<<<grd, KNN_THREADS, 0, c->stream>>>(d_pairs, slot0, c->d_partial, c->kp_cap, splits);
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;
 }

@@ -1,0 +1,262 @@
+// K7 on the 5th-generation tensor cores: k_knn2_umma — cv::BFMatcher(NORM_HAMMING)::knnMatch(k = 2) of
+// Matcher::match (Features/Matcher.cpp:106-139) as hamming(q, t) = |q| + |t| - 2 (q . t), the q . t of a 128-query x
+// 128-train tile being ONE accumulator of tcgen05.mma.kind::i8 (u8 x u8 -> s32, M = 128, N = 128, K = 32 per
+// instruction, 8 instructions per tile) held in tensor memory.
+//
+//   * operands: the 256-bit descriptors expanded to 256 bytes of 0 / 1 in shared memory, K-major without swizzle
+//     ("interleaved" canonical layout: 8 rows x 16 bytes core matrices; chunk kc of row r at kc * 2048 + r * 16,
+//     so LBO = 2048 (next 16 bytes of K), SBO = 128 (next 8 rows)).  The query tile is expanded once per CTA, the
+//     train tiles are double-buffered.
+//   * pipeline inside the CTA (no warp specialisation; two CTAs per SM fill each other's gaps): while the tensor
+//     pipe multiplies tile i + 1 into TMEM buffer (i + 1) & 1, all 8 warps drain buffer i & 1 with tcgen05.ld
+//     (thread = one query row x 64 columns) into a per-thread top-2 of sortable words (distance << 16 | train index:
+//     unsigned order = OpenCV's (distance, trainIdx) order), then expand tile i + 2.
+//   * completion of a tile's MMAs is signalled by tcgen05.commit on an mbarrier.
+// Output format and train-range splits are those of k_knn2_hamming (match.cu), which stays selectable
+// (option "knn_umma" = 0) for A/B measurements.
+#include "match_filter.cuh"
+#include "tma.cuh"
+
+namespace rgbdfe {
+
+#define UK_THREADS 256
+#define UK_M 128          // queries per CTA = TMEM lanes
+#define UK_N 128          // train descriptors per tile = TMEM columns per buffer
+#define UK_OPERAND_BYTES (UK_M * 256)
+#define UK_LBO 2048u      // bytes between the two 16-byte K chunks of one instruction
+#define UK_SBO 128u       // bytes between 8-row groups
+#define UK_KEY_BIAS 256
+#define UK_EMPTY 0x7fffffffu
+#define UK_PAD 0x7ffe0000u
+#define UK_NONE 0x7fffffff
+#define UK_SMEM (3 * UK_OPERAND_BYTES + 1024) // query tile + 2 train tiles + alignment slack
+
+__device__ __forceinline__ unsigned uk_nibble_bytes(unsigned w, int n) { return (((w >> (4 * n)) & 0xfu) * 0x00204081u) & 0x01010101u; }
+
+// shared-memory matrix descriptor: start address, LBO, SBO in 16-byte units, version 1 (sm_100), no swizzle
+__device__ __forceinline__ uint64_t uk_desc(unsigned saddr)
+{
+    return (uint64_t)((saddr >> 4) & 0x3fffu) | (uint64_t)(UK_LBO >> 4) << 16 | (uint64_t)(UK_SBO >> 4) << 32 | (uint64_t)1 << 46;
+}
+// instruction descriptor: D = s32 (2 << 4), A = B = u8 (0), both K-major (0), N >> 3 at bit 17, M >> 4 at bit 24
+#define UK_IDESC ((2u << 4) | ((unsigned)(UK_N >> 3) << 17) | ((unsigned)(UK_M >> 4) << 24))
+
+__device__ __forceinline__ void uk_mma(unsigned tmem_d, uint64_t da, uint64_t db, unsigned accumulate)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "setp.ne.b32 p, %4, 0;\n"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+                 "}\n" ::"r"(tmem_d),
+                 "l"(da), "l"(db), "r"(UK_IDESC), "r"(accumulate)
+                 : "memory");
+}
+__device__ __forceinline__ void uk_commit(uint64_t* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// a wait that fails loudly instead of hanging the GPU if a completion never arrives
+__device__ __forceinline__ void uk_wait(uint64_t* bar, unsigned phase)
+{
+    unsigned done = 0;
+    for (unsigned spin = 0; !done; spin++) {
+        asm volatile("{\n"
+                     ".reg .pred p;\n"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                     "selp.u32 %0, 1, 0, p;\n"
+                     "}\n"
+                     : "=r"(done)
+                     : "r"(smem_u32(bar)), "r"(phase)
+                     : "memory");
+        if (spin > (1u << 22))
+            __trap();
+    }
+}
+// 32 consecutive TMEM columns of this thread's lane
+__device__ __forceinline__ void uk_tmem_ld32(unsigned taddr, unsigned (&v)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+                 "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
+                 "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+                 "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]),
+                 "=r"(v[31])
+                 : "r"(taddr)
+                 : "memory");
+}
+
+__device__ __forceinline__ void uk_push(unsigned p, unsigned& m0, unsigned& m1)
+{
+    m1 = min(m1, max(m0, p));
+    m0 = min(m0, p);
+}
+
+// Expand 128 descriptors (rows row0 .. row0 + 127 of `desc`, zero beyond `n_valid`) into an operand tile.  Work item
+// = (row, 128-bit half): 8 chunks of 16 bytes; the lanes of a warp write 32 consecutive rows of one chunk (512
+// contiguous bytes: conflict-free).  Optionally leaves the row's base word (|t| + 256) << 16 | index in s_base.
+__device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restrict__ desc, int row0, int n_valid, unsigned* s_base, int tid)
+{
+    const int r = tid & (UK_M - 1), h = tid >> 7;
+    uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
+    const bool valid = row0 + r < n_valid;
+    if (valid) {
+        const uint4* p = reinterpret_cast<const uint4*>(desc + (size_t)(row0 + r) * 32);
+        w0 = __ldg(p), w1 = __ldg(p + 1);
+    }
+    const uint4 mine = h ? w1 : w0;
+    const unsigned wv[4] = { mine.x, mine.y, mine.z, mine.w };
+    uint8_t* dst = tile + (size_t)(8 * h) * UK_LBO + r * 16;
+#pragma unroll
+    for (int c = 0; c < 8; c++) { // chunk 8h + c = bits [16c, 16c + 16) of this half
+        const unsigned v = wv[c >> 1];
+        const int n0 = 4 * (c & 1);
+        *reinterpret_cast<uint4*>(dst + (size_t)c * UK_LBO)
+            = make_uint4(uk_nibble_bytes(v, n0), uk_nibble_bytes(v, n0 + 1), uk_nibble_bytes(v, n0 + 2), uk_nibble_bytes(v, n0 + 3));
+    }
+    if (s_base && h == 0) {
+        const int pop = __popc(w0.x) + __popc(w0.y) + __popc(w0.z) + __popc(w0.w) + __popc(w1.x) + __popc(w1.y) + __popc(w1.z) + __popc(w1.w);
+        s_base[r] = valid ? ((unsigned)(pop + UK_KEY_BIAS) << 16 | (unsigned)(row0 + r)) : UK_PAD;
+    }
+}
+
+// partial: [pair][split][q] -> int4 (d0, i0, d1, i1), as k_knn2_hamming
+__global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __restrict__ pairs, int slot0, int4* __restrict__ partial, int q_cap,
+    int splits)
+{
+    const int pair = slot0 + blockIdx.z;
+    const MatchPair P = pairs[pair];
+    const int nq = *P.nq, nt = *P.nt;
+    const int q_base = blockIdx.x * UK_M;
+    if (q_base >= nq)
+        return;
+    extern __shared__ uint8_t uk_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(uk_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;
+    uint8_t* sB[2] = { smem + UK_OPERAND_BYTES, smem + 2 * UK_OPERAND_BYTES };
+    __shared__ __align__(16) unsigned s_base[3][UK_N]; // tile i uses row i % 3: a fast thread may expand tile i + 2 while others still drain tile i
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ unsigned s_tmem;
+    __shared__ uint2 s_merge[UK_M];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // train range of this split, in whole tiles
+    const int tiles = (nt + UK_N - 1) / UK_N;
+    const int tps = (tiles + splits - 1) / splits;
+    const int t_begin = min(blockIdx.y * tps * UK_N, nt), t_end = min((blockIdx.y + 1) * tps * UK_N, nt);
+    const int T = (t_end - t_begin + UK_N - 1) / UK_N;
+
+    if (warp == 0) { // 2 x 128 accumulator columns; two CTAs per SM use all 512
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&s_tmem)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+    }
+    uk_expand(sA, P.q_desc, q_base, nq, nullptr, tid);
+    if (T > 0)
+        uk_expand(sB[0], P.t_desc, t_begin, t_end, s_base[0], tid);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = s_tmem;
+    const uint64_t dA = uk_desc(smem_u32(sA));
+    if (tid == 0 && T > 0) {
+        const uint64_t dB = uk_desc(smem_u32(sB[0]));
+#pragma unroll
+        for (int s = 0; s < 8; s++) // k-step s = chunks 2s, 2s + 1: start address + 2 * LBO (in 16-byte units)
+            uk_mma(tmem, dA + (uint64_t)(s * 2 * (UK_LBO >> 4)), dB + (uint64_t)(s * 2 * (UK_LBO >> 4)), s > 0);
+        uk_commit(&s_bar[0]);
+    }
+
+    unsigned m0 = UK_EMPTY, m1 = UK_EMPTY;
+    const int quad = warp & 3, half = warp >> 2; // TMEM lane quadrant of this warp, column half it drains
+    for (int i = 0, sb = 0; i < T; i++, sb = sb == 2 ? 0 : sb + 1) {
+        const int b = i & 1, sb1 = sb == 2 ? 0 : sb + 1;
+        if (i + 1 < T) {
+            // buffer b ^ 1 (smem and TMEM) was last used by tile i - 1, whose MMAs and epilogue are complete
+            uk_expand(sB[b ^ 1], P.t_desc, t_begin + (i + 1) * UK_N, t_end, s_base[sb1], tid);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (tid == 0 && i + 1 < T) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t dB = uk_desc(smem_u32(sB[b ^ 1]));
+#pragma unroll
+            for (int s = 0; s < 8; s++)
+                uk_mma(tmem + (unsigned)((b ^ 1) * UK_N), dA + (uint64_t)(s * 2 * (UK_LBO >> 4)), dB + (uint64_t)(s * 2 * (UK_LBO >> 4)), s > 0);
+            uk_commit(&s_bar[b ^ 1]);
+        }
+        uk_wait(&s_bar[b], (unsigned)(i >> 1) & 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // drain: this thread's row (lane quad * 32 + lane), columns [64 * half, 64 * half + 64) of buffer b
+        const unsigned taddr = tmem + ((unsigned)(quad * 32) << 16) + (unsigned)(b * UK_N + half * 64);
+        unsigned v0[32], v1[32];
+        uk_tmem_ld32(taddr, v0);
+        uk_tmem_ld32(taddr + 32u, v1);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const uint4* bp = reinterpret_cast<const uint4*>(&s_base[sb][half * 64]);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint4 bw = bp[j];
+            // distance word = base - 2 (q . t) << 16  (+ |q| at the end); padded columns have q . t = 0
+            uk_push(bw.x - (v0[4 * j] << 17), m0, m1);
+            uk_push(bw.y - (v0[4 * j + 1] << 17), m0, m1);
+            uk_push(bw.z - (v0[4 * j + 2] << 17), m0, m1);
+            uk_push(bw.w - (v0[4 * j + 3] << 17), m0, m1);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint4 bw = bp[8 + j];
+            uk_push(bw.x - (v1[4 * j] << 17), m0, m1);
+            uk_push(bw.y - (v1[4 * j + 1] << 17), m0, m1);
+            uk_push(bw.z - (v1[4 * j + 2] << 17), m0, m1);
+            uk_push(bw.w - (v1[4 * j + 3] << 17), m0, m1);
+        }
+    }
+    // the two column halves of a row meet in shared memory; warps 0-3 own the result
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    if (half == 1)
+        s_merge[quad * 32 + lane] = make_uint2(m0, m1);
+    __syncthreads();
+    if (half == 0) {
+        const uint2 o = s_merge[quad * 32 + lane];
+        const unsigned lo = min(m0, o.x);
+        m1 = min(max(m0, o.x), min(m1, o.y));
+        m0 = lo;
+        const int q = q_base + quad * 32 + lane;
+        if (q < nq) {
+            const uint4* p = reinterpret_cast<const uint4*>(P.q_desc + (size_t)q * 32);
+            const uint4 w0 = __ldg(p), w1 = __ldg(p + 1);
+            const int qpop = __popc(w0.x) + __popc(w0.y) + __popc(w0.z) + __popc(w0.w) + __popc(w1.x) + __popc(w1.y) + __popc(w1.z) + __popc(w1.w);
+            int4 r = make_int4(UK_NONE, -1, UK_NONE, -1);
+            if (m0 < UK_PAD)
+                r.x = qpop + (int)(m0 >> 16) - UK_KEY_BIAS, r.y = (int)(m0 & 0xffffu);
+            if (m1 < UK_PAD)
+                r.z = qpop + (int)(m1 >> 16) - UK_KEY_BIAS, r.w = (int)(m1 & 0xffffu);
+            partial[((size_t)pair * splits + blockIdx.y) * q_cap + q] = r;
+        }
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+    }
+}
+
+// K7 on tcgen05 for pair slots [slot0, slot0 + npairs); same contract as launch_knn's mma.sync kernel
+int launch_knn_umma(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(c, cudaFuncSetAttribute(k_knn2_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, UK_SMEM));
+        attr_set = true;
+    }
+    dim3 grd((max_nq + UK_M - 1) / UK_M, splits, npairs);
+    k_knn2_umma<<<grd, UK_THREADS, UK_SMEM, c->stream>>>(d_pairs, slot0, c->d_partial, c->kp_cap, splits);
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+} // namespace rgbdfe

@@ -10,7 +10,7 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/b
 NCU_BENCH="python bench.py --steps 1 --warmup 1 --no-cpu --frames 66 --sequences 1"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 2500 --csv --log-file gpurun_out/launches.csv $NCU_BENCH > gpurun_out/ncu_bench.log 2>&1
 # -s 3: launches 0-2 of an extraction kernel are priming / warm-up (launch 2 reads host images), 3 is the device-resident step
-for k in k_fast_cells k_orient_describe k_knn2_hamming k_gauss7 k_pyramid_resize k_pyramid_base k_quadtree k_se3_hypotheses k_se3_prepare; do
+for k in k_fast_cells k_orient_describe k_knn2_ k_gauss7 k_pyramid_resize k_pyramid_base k_quadtree k_se3_hypotheses k_se3_prepare; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 3 -c 1 -f -o gpurun_out/full_$k $NCU_BENCH > gpurun_out/ncu_full_$k.log 2>&1
 done
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; cat gpurun_out/bench.json
