@@ -27,7 +27,7 @@ namespace rgbdfe {
 #define UK_SBO 128u       // bytes between 8-row groups
 #define UK_KEY_BIAS 256
 #define UK_EMPTY 0x7fffffffu
-#define UK_PAD 0x7ffe0000u
+#define UK_PAD 0x02010000u // words at or above this are not candidates (a real distance + 256 is <= 512)
 #define UK_NONE 0x7fffffff
 #define UK_SMEM (3 * UK_OPERAND_BYTES + 1024) // query tile + 2 train tiles + alignment slack
 
@@ -85,6 +85,15 @@ __device__ __forceinline__ void uk_tmem_ld32(unsigned taddr, unsigned (&v)[32])
                  : "memory");
 }
 
+// two 16-bit candidates at once (per-lane unsigned min / max)
+__device__ __forceinline__ void uk_push2(unsigned p, unsigned& m0, unsigned& m1)
+{
+    m1 = __vminu2(m1, __vmaxu2(m0, p));
+    m0 = __vminu2(m0, p);
+}
+// 16-bit candidate (distance << 6 | column & 63) -> distance << 16 | train index; 0xffff (no candidate) lands above
+// every real word (distance 1023 > 512)
+__device__ __forceinline__ unsigned uk_widen(unsigned k, unsigned colbase) { return (k >> 6) << 16 | (colbase + (k & 63u)); }
 __device__ __forceinline__ void uk_push(unsigned p, unsigned& m0, unsigned& m1)
 {
     m1 = min(m1, max(m0, p));
@@ -93,8 +102,14 @@ __device__ __forceinline__ void uk_push(unsigned p, unsigned& m0, unsigned& m1)
 
 // Expand 128 descriptors (rows row0 .. row0 + 127 of `desc`, zero beyond `n_valid`) into an operand tile.  Work item
 // = (row, 128-bit half): 8 chunks of 16 bytes; the lanes of a warp write 32 consecutive rows of one chunk (512
-// contiguous bytes: conflict-free).  Optionally leaves the row's base word (|t| + 256) << 16 | index in s_base.
-__device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restrict__ desc, int row0, int n_valid, unsigned* s_base, int tid)
+// contiguous bytes: conflict-free).  The order of the 256 positions along K is free as long as both operands use the
+// same one: output word j (0..7) of a 32-bit descriptor word w holds its bits j, j + 8, j + 16, j + 24, one per byte,
+// i.e. one shift and one mask per 4 bits.  The query tile holds 0 / 1; the train tiles (TRAIN) hold 0 / 128 — shift
+// left and mask 0x80808080, the shift being a multiplication that ptxas can place on the FMA pipe — so that the
+// accumulator is 128 (q . t), exactly what the 16-bit candidate word below subtracts.  TRAIN also leaves the column's
+// base half-word (|t| + 256) << 6 | (column & 63) in s_base (0xffff beyond the end of the train set).
+template <bool TRAIN>
+__device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restrict__ desc, int row0, int n_valid, unsigned short* s_base, int tid)
 {
     const int r = tid & (UK_M - 1), h = tid >> 7;
     uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
@@ -107,15 +122,19 @@ __device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restri
     const unsigned wv[4] = { mine.x, mine.y, mine.z, mine.w };
     uint8_t* dst = tile + (size_t)(8 * h) * UK_LBO + r * 16;
 #pragma unroll
-    for (int c = 0; c < 8; c++) { // chunk 8h + c = bits [16c, 16c + 16) of this half
+    for (int c = 0; c < 8; c++) { // chunk 8h + c = output words 4 (c & 1) .. + 3 of descriptor word c >> 1
         const unsigned v = wv[c >> 1];
-        const int n0 = 4 * (c & 1);
-        *reinterpret_cast<uint4*>(dst + (size_t)c * UK_LBO)
-            = make_uint4(uk_nibble_bytes(v, n0), uk_nibble_bytes(v, n0 + 1), uk_nibble_bytes(v, n0 + 2), uk_nibble_bytes(v, n0 + 3));
+        const int j0 = 4 * (c & 1);
+        uint4 o;
+        if (TRAIN)
+            o = make_uint4((v << (7 - j0)) & 0x80808080u, (v << (6 - j0)) & 0x80808080u, (v << (5 - j0)) & 0x80808080u, (v << (4 - j0)) & 0x80808080u);
+        else
+            o = make_uint4((v >> j0) & 0x01010101u, (v >> (j0 + 1)) & 0x01010101u, (v >> (j0 + 2)) & 0x01010101u, (v >> (j0 + 3)) & 0x01010101u);
+        *reinterpret_cast<uint4*>(dst + (size_t)c * UK_LBO) = o;
     }
-    if (s_base && h == 0) {
+    if (TRAIN && h == 0) {
         const int pop = __popc(w0.x) + __popc(w0.y) + __popc(w0.z) + __popc(w0.w) + __popc(w1.x) + __popc(w1.y) + __popc(w1.z) + __popc(w1.w);
-        s_base[r] = valid ? ((unsigned)(pop + UK_KEY_BIAS) << 16 | (unsigned)(row0 + r)) : UK_PAD;
+        s_base[r] = valid ? (unsigned short)((pop + UK_KEY_BIAS) << 6 | (r & 63)) : (unsigned short)0xffffu;
     }
 }
 
@@ -133,7 +152,7 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(uk_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = smem;
     uint8_t* sB[2] = { smem + UK_OPERAND_BYTES, smem + 2 * UK_OPERAND_BYTES };
-    __shared__ __align__(16) unsigned s_base[3][UK_N]; // tile i uses row i % 3: a fast thread may expand tile i + 2 while others still drain tile i
+    __shared__ __align__(16) unsigned short s_base[3][UK_N]; // tile i uses row i % 3: a fast thread may expand tile i + 2 while others still drain tile i
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ unsigned s_tmem;
     __shared__ uint2 s_merge[UK_M];
@@ -153,9 +172,9 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
     }
-    uk_expand(sA, P.q_desc, q_base, nq, nullptr, tid);
+    uk_expand<false>(sA, P.q_desc, q_base, nq, nullptr, tid);
     if (T > 0)
-        uk_expand(sB[0], P.t_desc, t_begin, t_end, s_base[0], tid);
+        uk_expand<true>(sB[0], P.t_desc, t_begin, t_end, s_base[0], tid);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -176,7 +195,7 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         const int b = i & 1, sb1 = sb == 2 ? 0 : sb + 1;
         if (i + 1 < T) {
             // buffer b ^ 1 (smem and TMEM) was last used by tile i - 1, whose MMAs and epilogue are complete
-            uk_expand(sB[b ^ 1], P.t_desc, t_begin + (i + 1) * UK_N, t_end, s_base[sb1], tid);
+            uk_expand<true>(sB[b ^ 1], P.t_desc, t_begin + (i + 1) * UK_N, t_end, s_base[sb1], tid);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -197,24 +216,33 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         uk_tmem_ld32(taddr, v0);
         uk_tmem_ld32(taddr + 32u, v1);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        // Candidates of this tile as 16-bit words, two columns per register: (|t| + 256 - 2 q.t) << 6 | column & 63
+        // = base half-word - accumulator (128 q.t <= 32768: no borrow between the halves); unsigned order of a half-word
+        // = (distance, column) order.  Packed top-2 with the two-lane min / max instructions: 3 per column pair.
         const uint4* bp = reinterpret_cast<const uint4*>(&s_base[sb][half * 64]);
+        unsigned M0 = 0xffffffffu, M1 = 0xffffffffu;
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
+        for (int j = 0; j < 4; j++) {
             const uint4 bw = bp[j];
-            // distance word = base - 2 (q . t) << 16  (+ |q| at the end); padded columns have q . t = 0
-            uk_push(bw.x - (v0[4 * j] << 17), m0, m1);
-            uk_push(bw.y - (v0[4 * j + 1] << 17), m0, m1);
-            uk_push(bw.z - (v0[4 * j + 2] << 17), m0, m1);
-            uk_push(bw.w - (v0[4 * j + 3] << 17), m0, m1);
+            uk_push2(bw.x - (v0[8 * j + 1] * 65536u + v0[8 * j]), M0, M1);
+            uk_push2(bw.y - (v0[8 * j + 3] * 65536u + v0[8 * j + 2]), M0, M1);
+            uk_push2(bw.z - (v0[8 * j + 5] * 65536u + v0[8 * j + 4]), M0, M1);
+            uk_push2(bw.w - (v0[8 * j + 7] * 65536u + v0[8 * j + 6]), M0, M1);
         }
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const uint4 bw = bp[8 + j];
-            uk_push(bw.x - (v1[4 * j] << 17), m0, m1);
-            uk_push(bw.y - (v1[4 * j + 1] << 17), m0, m1);
-            uk_push(bw.z - (v1[4 * j + 2] << 17), m0, m1);
-            uk_push(bw.w - (v1[4 * j + 3] << 17), m0, m1);
+        for (int j = 0; j < 4; j++) {
+            const uint4 bw = bp[4 + j];
+            uk_push2(bw.x - (v1[8 * j + 1] * 65536u + v1[8 * j]), M0, M1);
+            uk_push2(bw.y - (v1[8 * j + 3] * 65536u + v1[8 * j + 2]), M0, M1);
+            uk_push2(bw.z - (v1[8 * j + 5] * 65536u + v1[8 * j + 4]), M0, M1);
+            uk_push2(bw.w - (v1[8 * j + 7] * 65536u + v1[8 * j + 6]), M0, M1);
         }
+        // the tile's four survivors as 32-bit words distance << 16 | train index, into the running top-2
+        const unsigned colbase = (unsigned)(t_begin + i * UK_N + half * 64);
+        uk_push(uk_widen(M0 & 0xffffu, colbase), m0, m1);
+        uk_push(uk_widen(M0 >> 16, colbase), m0, m1);
+        uk_push(uk_widen(M1 & 0xffffu, colbase), m0, m1);
+        uk_push(uk_widen(M1 >> 16, colbase), m0, m1);
     }
     // the two column halves of a row meet in shared memory; warps 0-3 own the result
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
