@@ -47,19 +47,19 @@ ALG_BYTES = {
     "k_fast_cells": SUM_P,
     "k_gauss7": 2 * SUM_P,
     "k_orient_describe": 60 * NFEAT,
-    "k_knn2_hamming": (NFEAT + NFEAT) * 32 + NFEAT * 16,  # both descriptor sets once + one int4 per query
+    "k_knn2_umma": (NFEAT + NFEAT) * 32 + NFEAT * 16,  # both descriptor sets once + one int4 per query
 }
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
 # captures summarised in profiles/r1_ncu_full_brief.txt, and the unit that actually limits each kernel there.
 NCU_TRAFFIC_64 = {
     "k_fast_cells": 65.02e6 + 3.64e6, "k_gauss7": 72.84e6 + 31.39e6, "k_orient_describe": 139.05e6 + 9.66e6,
-    "k_knn2_hamming": 4.20e6, "k_quadtree": 8.17e6 + 0.01e6,
+    "k_knn2_umma": 4.21e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
 NCU_LIMITER = {
     "k_fast_cells": "issue slots 79 % busy, ALU pipe 62 % (16-bit-lane min/max work), tiles staged by TMA: instruction-bound; DRAM traffic = 1.1x algorithmic, 4 % of peak",
     "k_gauss7": "issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 59 %; DRAM 17 % of peak",
     "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 74 %; DRAM 16 % of peak",
-    "k_knn2_hamming": "tensor pipe (u8 IMMA m16n8k32) 65 % busy while active = 57 % of the 0.5 IMMA/clk/SM measured peak; DRAM < 1 % of peak",
+    "k_knn2_umma": "tcgen05.mma kind::i8 (UTCIMMA), tensor pipe 30 % busy; the 8 warps that expand the operands and drain TMEM into the top-2 issue 45 % of the time (2 CTAs x 8 warps per SM: TMEM-bound occupancy); DRAM < 1 % of peak",
     "k_quadtree": "latency (shared-memory atomics and scans, one CTA per level and frame): issue 32 %",
 }
 METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
@@ -301,6 +301,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=96)
     ap.add_argument("--sequences", type=int, default=32, help="independent tracked sequences in flight on each GPU")
+    ap.add_argument("--knn-waves", type=int, default=0, help="diagnostic: waves of kNN CTAs the train-range split aims for (0 = library default)")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
@@ -371,6 +372,8 @@ def main():
             else:
                 self.ctx_t.set_stream_priority(True)
             self.ctx_t.set_option("ransac_first_chunk", first_chunk)
+            if args.knn_waves:
+                self.ctx_t.set_option("knn_waves", args.knn_waves)
             self.ctx_t.rng_seed(42 + k)
             self.sets = [[rgbdfe.Frame(self.ctx_x) for _ in range(B)] for _ in range(3)]
             self.order = pingpong(F)

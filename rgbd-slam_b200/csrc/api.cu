@@ -380,6 +380,12 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         c->host_zero_copy = value != 0;
         return RGBDFE_OK;
     }
+    if (!strcmp(name, "knn_waves")) {
+        if (value < 1 || value > 64)
+            return RGBDFE_E_ARG;
+        c->knn_waves = value;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "knn_umma")) {
         c->knn_umma = value != 0;
         return RGBDFE_OK;
@@ -1446,7 +1452,7 @@ int rgbdfe_profile_read(rgbdfe_ctx* c, double* ms_per_kernel, long long* launche
 
 const char* rgbdfe_profile_name(int id)
 {
-    static const char* names[KID_COUNT] = { "k_pyramid_level(x levels)", "k_fast_cells", "k_gauss7", "k_quadtree", "k_orient_describe", "k_knn2_hamming",
+    static const char* names[KID_COUNT] = { "k_pyramid_level(x levels)", "k_fast_cells", "k_gauss7", "k_quadtree", "k_orient_describe", "k_knn2_umma",
         "k_ratio_filter", "k_se3_prepare", "k_se3_hypotheses", "k_se3_replay" };
     return (id >= 0 && id < KID_COUNT) ? names[id] : "";
 }

@@ -218,6 +218,7 @@ struct rgbdfe_ctx {
     // match / RANSAC workspaces for pair_cap pairs
     int pair_cap = 0;
     int knn_splits = 8;
+    int knn_waves = 6; // train-range splits are chosen to give about this many waves of kNN CTAs (option "knn_waves")
     int knn_umma = 1; // K7 on tcgen05 (match_umma.cu); 0 = the mma.sync kernel (option "knn_umma")
     MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
     int4* d_partial = nullptr;      // [pairs][splits][kp_cap]

@@ -20,6 +20,10 @@
 namespace rgbdfe {
 
 #define UK_THREADS 256
+#define UK_PARTS (UK_THREADS / 128) // threads per query row in the drain (column parts) and per descriptor in the expansion
+#define UK_WPP (8 / UK_PARTS)       // 32-bit descriptor words per expansion thread
+#define UK_RPW (32 / UK_PARTS)      // descriptor rows per warp in the expansion
+#define UK_COLS (UK_N / UK_PARTS)   // accumulator columns per thread and tile
 #define UK_M 128          // queries per CTA = TMEM lanes
 #define UK_N 128          // train descriptors per tile = TMEM columns per buffer
 #define UK_OPERAND_BYTES (UK_M * 256)
@@ -100,30 +104,48 @@ __device__ __forceinline__ void uk_push(unsigned p, unsigned& m0, unsigned& m1)
     m0 = min(m0, p);
 }
 
-// Expand 128 descriptors (rows row0 .. row0 + 127 of `desc`, zero beyond `n_valid`) into an operand tile.  Work item
-// = (row, 128-bit half): 8 chunks of 16 bytes; the lanes of a warp write 32 consecutive rows of one chunk (512
-// contiguous bytes: conflict-free).  The order of the 256 positions along K is free as long as both operands use the
-// same one: output word j (0..7) of a 32-bit descriptor word w holds its bits j, j + 8, j + 16, j + 24, one per byte,
-// i.e. one shift and one mask per 4 bits.  The query tile holds 0 / 1; the train tiles (TRAIN) hold 0 / 128 — shift
-// left and mask 0x80808080, the shift being a multiplication that ptxas can place on the FMA pipe — so that the
-// accumulator is 128 (q . t), exactly what the 16-bit candidate word below subtracts.  TRAIN also leaves the column's
-// base half-word (|t| + 256) << 6 | (column & 63) in s_base (0xffff beyond the end of the train set).
-template <bool TRAIN>
-__device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restrict__ desc, int row0, int n_valid, unsigned short* s_base, int tid)
+// Expand 128 descriptors (rows row0 .. row0 + 127 of `desc`, zero beyond `n_valid`) into an operand tile.  A warp
+// takes UK_RPW consecutive rows, UK_PARTS threads per row (lane = part * UK_RPW + row): the global loads of a warp are
+// one contiguous run, the 8 lanes of a shared-memory store phase write 8 consecutive rows of one 16-byte chunk
+// (conflict-free), and the row's population count is a butterfly over the parts.  The order of the 256 positions
+// along K is free as long as both operands use the same one: output word j (0..7) of a 32-bit descriptor word w holds
+// its bits j, j + 8, j + 16, j + 24, one per byte, i.e. one shift and one mask per 4 bits.  The query tile holds
+// 0 / 1; the train tiles (TRAIN) hold 0 / 128 — shift left and mask 0x80808080, the shift being a multiplication that
+// ptxas can place on the FMA pipe — so that the accumulator is 128 (q . t), exactly what the 16-bit candidate word
+// below subtracts.  TRAIN also leaves the column's base half-word (|t| + 256) << 6 | (column & 63) in s_base (0xffff
+// beyond the end of the train set).  The load is a separate step so that the kernel can issue it one tile ahead.
+struct UkRow {
+    unsigned w[UK_WPP]; // this thread's words of the row's descriptor, zero beyond the end of the set
+    bool valid;
+};
+__device__ __forceinline__ UkRow uk_load(const uint8_t* __restrict__ desc, int row0, int n_valid, int tid)
 {
-    const int r = tid & (UK_M - 1), h = tid >> 7;
-    uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
-    const bool valid = row0 + r < n_valid;
-    if (valid) {
-        const uint4* p = reinterpret_cast<const uint4*>(desc + (size_t)(row0 + r) * 32);
-        w0 = __ldg(p), w1 = __ldg(p + 1);
-    }
-    const uint4 mine = h ? w1 : w0;
-    const unsigned wv[4] = { mine.x, mine.y, mine.z, mine.w };
-    uint8_t* dst = tile + (size_t)(8 * h) * UK_LBO + r * 16;
+    UkRow R;
+    const int lane = tid & 31, r = (tid >> 5) * UK_RPW + (lane & (UK_RPW - 1)), part = lane / UK_RPW;
 #pragma unroll
-    for (int c = 0; c < 8; c++) { // chunk 8h + c = output words 4 (c & 1) .. + 3 of descriptor word c >> 1
-        const unsigned v = wv[c >> 1];
+    for (int i = 0; i < UK_WPP; i++)
+        R.w[i] = 0u;
+    R.valid = row0 + r < n_valid;
+    if (R.valid) {
+        const uint8_t* p = desc + (size_t)(row0 + r) * 32 + part * (4 * UK_WPP);
+        if (UK_WPP == 2) {
+            const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+            R.w[0] = v.x, R.w[1] = v.y;
+        } else {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+            R.w[0] = v.x, R.w[1] = v.y, R.w[UK_WPP - 2] = v.z, R.w[UK_WPP - 1] = v.w;
+        }
+    }
+    return R;
+}
+template <bool TRAIN>
+__device__ __forceinline__ void uk_expand(uint8_t* tile, const UkRow& R, unsigned short* s_base, int tid)
+{
+    const int lane = tid & 31, r = (tid >> 5) * UK_RPW + (lane & (UK_RPW - 1)), part = lane / UK_RPW;
+    uint8_t* dst = tile + (size_t)(2 * UK_WPP * part) * UK_LBO + r * 16;
+#pragma unroll
+    for (int c = 0; c < 2 * UK_WPP; c++) { // chunk 2 UK_WPP part + c = output words 4 (c & 1) .. + 3 of this thread's word c >> 1
+        const unsigned v = R.w[c >> 1];
         const int j0 = 4 * (c & 1);
         uint4 o;
         if (TRAIN)
@@ -132,9 +154,16 @@ __device__ __forceinline__ void uk_expand(uint8_t* tile, const uint8_t* __restri
             o = make_uint4((v >> j0) & 0x01010101u, (v >> (j0 + 1)) & 0x01010101u, (v >> (j0 + 2)) & 0x01010101u, (v >> (j0 + 3)) & 0x01010101u);
         *reinterpret_cast<uint4*>(dst + (size_t)c * UK_LBO) = o;
     }
-    if (TRAIN && h == 0) {
-        const int pop = __popc(w0.x) + __popc(w0.y) + __popc(w0.z) + __popc(w0.w) + __popc(w1.x) + __popc(w1.y) + __popc(w1.z) + __popc(w1.w);
-        s_base[r] = valid ? (unsigned short)((pop + UK_KEY_BIAS) << 6 | (r & 63)) : (unsigned short)0xffffu;
+    if (TRAIN) {
+        int pop = 0;
+#pragma unroll
+        for (int i = 0; i < UK_WPP; i++)
+            pop += __popc(R.w[i]);
+#pragma unroll
+        for (int x = UK_RPW; x < 32; x <<= 1)
+            pop += __shfl_xor_sync(0xffffffffu, pop, x);
+        if (part == 0)
+            s_base[r] = R.valid ? (unsigned short)((pop + UK_KEY_BIAS) << 6 | (r & 63)) : (unsigned short)0xffffu;
     }
 }
 
@@ -155,7 +184,7 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
     __shared__ __align__(16) unsigned short s_base[3][UK_N]; // tile i uses row i % 3: a fast thread may expand tile i + 2 while others still drain tile i
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ unsigned s_tmem;
-    __shared__ uint2 s_merge[UK_M];
+    __shared__ uint2 s_merge[UK_PARTS - 1][UK_M];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // train range of this split, in whole tiles
@@ -172,9 +201,13 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
     }
-    uk_expand<false>(sA, P.q_desc, q_base, nq, nullptr, tid);
-    if (T > 0)
-        uk_expand<true>(sB[0], P.t_desc, t_begin, t_end, s_base[0], tid);
+    {
+        const UkRow qa = uk_load(P.q_desc, q_base, nq, tid), t0 = uk_load(P.t_desc, t_begin, t_end, tid); // both in flight
+        uk_expand<false>(sA, qa, nullptr, tid);
+        if (T > 0)
+            uk_expand<true>(sB[0], t0, s_base[0], tid);
+    }
+    UkRow nxt = uk_load(P.t_desc, t_begin + UK_N, t_end, tid); // tile 1 (all zero if there is none)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -190,12 +223,13 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
     }
 
     unsigned m0 = UK_EMPTY, m1 = UK_EMPTY;
-    const int quad = warp & 3, half = warp >> 2; // TMEM lane quadrant of this warp, column half it drains
+    const int quad = warp & 3, part = warp >> 2; // TMEM lane quadrant of this warp, column part it drains
     for (int i = 0, sb = 0; i < T; i++, sb = sb == 2 ? 0 : sb + 1) {
         const int b = i & 1, sb1 = sb == 2 ? 0 : sb + 1;
         if (i + 1 < T) {
             // buffer b ^ 1 (smem and TMEM) was last used by tile i - 1, whose MMAs and epilogue are complete
-            uk_expand<true>(sB[b ^ 1], P.t_desc, t_begin + (i + 1) * UK_N, t_end, s_base[sb1], tid);
+            uk_expand<true>(sB[b ^ 1], nxt, s_base[sb1], tid);
+            nxt = uk_load(P.t_desc, t_begin + (i + 2) * UK_N, t_end, tid); // lands while this thread drains tile i
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -210,50 +244,54 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         }
         uk_wait(&s_bar[b], (unsigned)(i >> 1) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // drain: this thread's row (lane quad * 32 + lane), columns [64 * half, 64 * half + 64) of buffer b
-        const unsigned taddr = tmem + ((unsigned)(quad * 32) << 16) + (unsigned)(b * UK_N + half * 64);
-        unsigned v0[32], v1[32];
-        uk_tmem_ld32(taddr, v0);
-        uk_tmem_ld32(taddr + 32u, v1);
+        // drain: this thread's row (lane quad * 32 + lane), columns [UK_COLS * part, UK_COLS * part + UK_COLS) of buffer b
+        const unsigned taddr = tmem + ((unsigned)(quad * 32) << 16) + (unsigned)(b * UK_N + part * UK_COLS);
+        unsigned v[UK_COLS / 32][32];
+#pragma unroll
+        for (int l = 0; l < UK_COLS / 32; l++)
+            uk_tmem_ld32(taddr + 32u * l, v[l]);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         // Candidates of this tile as 16-bit words, two columns per register: (|t| + 256 - 2 q.t) << 6 | column & 63
         // = base half-word - accumulator (128 q.t <= 32768: no borrow between the halves); unsigned order of a half-word
-        // = (distance, column) order.  Packed top-2 with the two-lane min / max instructions: 3 per column pair.
-        const uint4* bp = reinterpret_cast<const uint4*>(&s_base[sb][half * 64]);
-        unsigned M0 = 0xffffffffu, M1 = 0xffffffffu;
+        // = (distance, column) order.  Packed top-2 with the two-lane min / max instructions: 3 per column pair, on
+        // two independent chains.
+        const uint4* bp = reinterpret_cast<const uint4*>(&s_base[sb][part * UK_COLS]);
+        unsigned M0 = 0xffffffffu, M1 = 0xffffffffu, N0 = 0xffffffffu, N1 = 0xffffffffu;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const uint4 bw = bp[j];
-            uk_push2(bw.x - (v0[8 * j + 1] * 65536u + v0[8 * j]), M0, M1);
-            uk_push2(bw.y - (v0[8 * j + 3] * 65536u + v0[8 * j + 2]), M0, M1);
-            uk_push2(bw.z - (v0[8 * j + 5] * 65536u + v0[8 * j + 4]), M0, M1);
-            uk_push2(bw.w - (v0[8 * j + 7] * 65536u + v0[8 * j + 6]), M0, M1);
-        }
+        for (int l = 0; l < UK_COLS / 32; l++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const uint4 bw = bp[4 + j];
-            uk_push2(bw.x - (v1[8 * j + 1] * 65536u + v1[8 * j]), M0, M1);
-            uk_push2(bw.y - (v1[8 * j + 3] * 65536u + v1[8 * j + 2]), M0, M1);
-            uk_push2(bw.z - (v1[8 * j + 5] * 65536u + v1[8 * j + 4]), M0, M1);
-            uk_push2(bw.w - (v1[8 * j + 7] * 65536u + v1[8 * j + 6]), M0, M1);
+            for (int j = 0; j < 4; j++) {
+                const uint4 bw = bp[4 * l + j];
+                uk_push2(bw.x - (v[l][8 * j + 1] * 65536u + v[l][8 * j]), M0, M1);
+                uk_push2(bw.y - (v[l][8 * j + 3] * 65536u + v[l][8 * j + 2]), N0, N1);
+                uk_push2(bw.z - (v[l][8 * j + 5] * 65536u + v[l][8 * j + 4]), M0, M1);
+                uk_push2(bw.w - (v[l][8 * j + 7] * 65536u + v[l][8 * j + 6]), N0, N1);
+            }
+        {
+            const unsigned lo = __vminu2(M0, N0);
+            M1 = __vminu2(__vmaxu2(M0, N0), __vminu2(M1, N1));
+            M0 = lo;
         }
         // the tile's four survivors as 32-bit words distance << 16 | train index, into the running top-2
-        const unsigned colbase = (unsigned)(t_begin + i * UK_N + half * 64);
+        const unsigned colbase = (unsigned)(t_begin + i * UK_N + ((part * UK_COLS) & ~63));
         uk_push(uk_widen(M0 & 0xffffu, colbase), m0, m1);
         uk_push(uk_widen(M0 >> 16, colbase), m0, m1);
         uk_push(uk_widen(M1 & 0xffffu, colbase), m0, m1);
         uk_push(uk_widen(M1 >> 16, colbase), m0, m1);
     }
-    // the two column halves of a row meet in shared memory; warps 0-3 own the result
+    // the column parts of a row meet in shared memory; warps 0-3 own the result
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    if (half == 1)
-        s_merge[quad * 32 + lane] = make_uint2(m0, m1);
+    if (part > 0)
+        s_merge[part - 1][quad * 32 + lane] = make_uint2(m0, m1);
     __syncthreads();
-    if (half == 0) {
-        const uint2 o = s_merge[quad * 32 + lane];
-        const unsigned lo = min(m0, o.x);
-        m1 = min(max(m0, o.x), min(m1, o.y));
-        m0 = lo;
+    if (part == 0) {
+#pragma unroll
+        for (int k = 0; k < UK_PARTS - 1; k++) {
+            const uint2 o = s_merge[k][quad * 32 + lane];
+            const unsigned lo = min(m0, o.x);
+            m1 = min(max(m0, o.x), min(m1, o.y));
+            m0 = lo;
+        }
         const int q = q_base + quad * 32 + lane;
         if (q < nq) {
             const uint4* p = reinterpret_cast<const uint4*>(P.q_desc + (size_t)q * 32);

@@ -110,6 +110,33 @@ def test_match_ties_and_degenerate(ctx, oracle):
     assert len(ctx.match(q[:0], t, z[:0], xyz_q[:0], xyz_t, 0.9, True)) == 0
 
 
+@pytest.mark.parametrize("umma", [1, 0])
+def test_match_tile_edges_both_knn_kernels(ctx, oracle, umma):
+    """Set sizes around the 128-wide tiles of the tcgen05 kernel (and the 256 / 128 of the mma.sync one), clustered
+    descriptors (small distances, many equal ones: the (distance, trainIdx) order decides), several ratios."""
+    ctx.set_option("knn_umma", umma)
+    try:
+        rng = np.random.default_rng(60 + umma)
+        for nq, nt in ((1, 2), (127, 129), (128, 128), (129, 127), (255, 257), (300, 1153), (1000, 2), (2000, 1999)):
+            centers = rng.integers(0, 256, (24, 32), dtype=np.uint8)
+            def cloud(n):
+                d = centers[rng.integers(0, len(centers), n)].copy()
+                flips = rng.integers(0, 256, (n, 3))  # up to 3 flipped bits per descriptor
+                for k in range(3):
+                    d[np.arange(n), flips[:, k] >> 3] ^= (1 << (flips[:, k] & 7)).astype(np.uint8)
+                return d
+            q, t = cloud(nq), cloud(nt)
+            xyz_q = np.ones((nq, 3), np.float32)
+            xyz_t = np.ones((nt, 3), np.float32)
+            z = np.zeros(nq, np.uint8)
+            for ratio in (0.7, 0.95, 4.0):
+                m_o = oracle.match(q, t, z, xyz_q, xyz_t, ratio, True)
+                m_g = ctx.match(q, t, z, xyz_q, xyz_t, ratio, True)
+                assert len(m_o) == len(m_g) and (m_o == m_g).all(), (nq, nt, ratio)
+    finally:
+        ctx.set_option("knn_umma", 1)
+
+
 def _pair(oracle, cam, frames, i, j, nfeat=1000):
     orb = oracle.Orb(nfeat)
     out = []
