@@ -90,7 +90,11 @@ int rgbdfe_sync(rgbdfe_ctx* ctx);
 /* Tuning knobs that never change results.  "ransac_first_chunk" (default 32): how many RANSAC iterations the
  * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
  * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU.
- * "host_zero_copy" (default 1): see rgbdfe_frames_extract. */
+ * "host_zero_copy" (default 1): see rgbdfe_frames_extract.
+ * "knn_umma" (default 1): the Hamming kNN of Matcher::match on tcgen05 (k_knn2_umma); 0 selects the mma.sync kernel
+ * (k_knn2_hamming), kept for A/B measurements — both are held to the same parity tests.
+ * "knn_waves" (default 6): the train range of a pair is split over CTAs so that a kNN launch has about this many
+ * waves of CTAs (latency of single pairs against redundant work for whole chains). */
 int rgbdfe_set_option(rgbdfe_ctx* ctx, const char* name, int value);
 /* Pipelining across contexts of one device (e.g. one context extracts frame batch n+1 while another tracks
  * batch n; rgbdfe_frame handles are plain device buffers and may be used by either): everything enqueued on
