@@ -554,6 +554,15 @@ def main():
         "ms_per_launch": {k: (v[0] / v[1] if v[1] else None) for k, v in kernels.items()},
     }
 
+    # the one tensor-pipe kernel: u8 multiply-accumulates of the 2000 x 256 by 256 x 2000 product of every pair against the
+    # dense int8 rate (2 x the measured bf16 rate of MEASURED_PEAKS.json; nominal 4500 TOP/s if that file is absent)
+    kn = roofline["per_kernel"].get("k_knn2_umma")
+    if kn:
+        tops = 2.0 * NFEAT * NFEAT * 256 * B / (kn["ms"] * 1e-3) / 1e12  # a batch's chain = B pairs of NFEAT x NFEAT descriptors
+        peak_tops = 2.0 * float(peaks.get("bf16_tflops", 2250.0))
+        kn.update({"bound": "tensor", "achieved_TOPs": tops, "peak_TOPs": peak_tops, "frac": tops / peak_tops,
+                   "how": "2 * Nq * Nt * 256 * pairs per launch / launch time; peak = 2 x measured dense bf16"})
+
     # ---- row N1: Frame preprocessing (BGR -> gray, 16-bit depth, undistortion, grid cells) + extraction, end to end ----
     frame_prep = projection = None
     try:

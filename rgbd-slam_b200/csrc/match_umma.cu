@@ -3,17 +3,19 @@
 // 128-train tile being ONE accumulator of tcgen05.mma.kind::i8 (u8 x u8 -> s32, M = 128, N = 128, K = 32 per
 // instruction, 8 instructions per tile) held in tensor memory.
 //
-//   * operands: the 256-bit descriptors expanded to 256 bytes of 0 / 1 in shared memory, K-major without swizzle
-//     ("interleaved" canonical layout: 8 rows x 16 bytes core matrices; chunk kc of row r at kc * 2048 + r * 16,
-//     so LBO = 2048 (next 16 bytes of K), SBO = 128 (next 8 rows)).  The query tile is expanded once per CTA, the
-//     train tiles are double-buffered.
+//   * operands: the 256-bit descriptors expanded to 256 bytes in shared memory (queries 0 / 1, train 0 / 128),
+//     K-major without swizzle ("interleaved" canonical layout: 8 rows x 16 bytes core matrices; chunk kc of row r at
+//     kc * 2048 + r * 16, so LBO = 2048 (next 16 bytes of K), SBO = 128 (next 8 rows)).  The query tile is expanded
+//     once per CTA, the train tiles are double-buffered, their descriptors loaded one tile ahead.
 //   * pipeline inside the CTA (no warp specialisation; two CTAs per SM fill each other's gaps): while the tensor
 //     pipe multiplies tile i + 1 into TMEM buffer (i + 1) & 1, all 8 warps drain buffer i & 1 with tcgen05.ld
-//     (thread = one query row x 64 columns) into a per-thread top-2 of sortable words (distance << 16 | train index:
-//     unsigned order = OpenCV's (distance, trainIdx) order), then expand tile i + 2.
-//   * completion of a tile's MMAs is signalled by tcgen05.commit on an mbarrier.
+//     (thread = one query row x 64 columns) into a packed top-2 of 16-bit candidate words (distance << 6 | column,
+//     two columns per register, VIMNMX.U16x2), widen the tile's four survivors to distance << 16 | train index
+//     (unsigned order = OpenCV's (distance, trainIdx) order) and keep the running top-2.
+//   * completion of a tile's MMAs is signalled by tcgen05.commit on an mbarrier; waits trap instead of hanging.
 // Output format and train-range splits are those of k_knn2_hamming (match.cu), which stays selectable
-// (option "knn_umma" = 0) for A/B measurements.
+// (option "knn_umma" = 0) for A/B measurements.  Measured variants that were slower and dropped: per-warp mbarrier
+// hand-offs instead of the CTA barrier, 512-thread CTAs (UK_THREADS 512 still builds: the code is generic in UK_PARTS).
 #include "match_filter.cuh"
 #include "tma.cuh"
 
@@ -34,8 +36,6 @@ namespace rgbdfe {
 #define UK_PAD 0x02010000u // words at or above this are not candidates (a real distance + 256 is <= 512)
 #define UK_NONE 0x7fffffff
 #define UK_SMEM (3 * UK_OPERAND_BYTES + 1024) // query tile + 2 train tiles + alignment slack
-
-__device__ __forceinline__ unsigned uk_nibble_bytes(unsigned w, int n) { return (((w >> (4 * n)) & 0xfu) * 0x00204081u) & 0x01010101u; }
 
 // shared-memory matrix descriptor: start address, LBO, SBO in 16-byte units, version 1 (sm_100), no swizzle
 __device__ __forceinline__ uint64_t uk_desc(unsigned saddr)
