@@ -301,6 +301,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=96)
     ap.add_argument("--sequences", type=int, default=32, help="independent tracked sequences in flight on each GPU")
+    ap.add_argument("--overlap-blur", type=int, default=0, help="diagnostic: run the blur beside the quadtree on a side stream")
     ap.add_argument("--knn-waves", type=int, default=0, help="diagnostic: waves of kNN CTAs the train-range split aims for (0 = library default)")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
@@ -366,6 +367,8 @@ def main():
             self.ctx_x.orb_configure(NFEAT, 1.2, 8, 20, 7)
             if args.full_upload:
                 self.ctx_x.set_option("host_zero_copy", 0)
+            if args.overlap_blur:
+                self.ctx_x.set_option("overlap_blur", 1)
             if part:
                 self.ctx_x.bind_partition(rgbdfe.PART_THROUGHPUT)
                 self.ctx_t.bind_partition(rgbdfe.PART_LATENCY)

@@ -330,6 +330,11 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_frame(c->scratch2);
     if (c->order_evt)
         cudaEventDestroy(c->order_evt);
+    if (c->side_stream) {
+        cudaStreamDestroy(c->side_stream);
+        cudaEventDestroy(c->side_fork);
+        cudaEventDestroy(c->side_join);
+    }
     if (c->bulk_evt)
         cudaEventDestroy(c->bulk_evt);
     if (c->bulk_stream)
@@ -378,6 +383,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         return RGBDFE_E_ARG;
     if (!strcmp(name, "host_zero_copy")) {
         c->host_zero_copy = value != 0;
+        return RGBDFE_OK;
+    }
+    if (!strcmp(name, "overlap_blur")) {
+        c->overlap_blur = value != 0;
         return RGBDFE_OK;
     }
     if (!strcmp(name, "knn_waves")) {
@@ -704,10 +713,30 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
         return rc;
     if ((rc = launch_fast(c, count)) != RGBDFE_OK)
         return rc;
-    if ((rc = launch_blur(c, count)) != RGBDFE_OK)
-        return rc;
-    if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
-        return rc;
+    if (c->overlap_blur && !c->profiling) {
+        // fork after K2: the blur on the side stream, the quadtree on the context's stream, joined before K6
+        if (!c->side_stream) {
+            CUDA_TRY(c, cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+            CUDA_TRY(c, cudaEventCreateWithFlags(&c->side_fork, cudaEventDisableTiming));
+            CUDA_TRY(c, cudaEventCreateWithFlags(&c->side_join, cudaEventDisableTiming));
+        }
+        CUDA_TRY(c, cudaEventRecord(c->side_fork, c->stream));
+        CUDA_TRY(c, cudaStreamWaitEvent(c->side_stream, c->side_fork, 0));
+        std::swap(c->stream, c->side_stream);
+        rc = launch_blur(c, count);
+        std::swap(c->stream, c->side_stream);
+        if (rc != RGBDFE_OK)
+            return rc;
+        CUDA_TRY(c, cudaEventRecord(c->side_join, c->side_stream));
+        if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
+            return rc;
+        CUDA_TRY(c, cudaStreamWaitEvent(c->stream, c->side_join, 0));
+    } else {
+        if ((rc = launch_blur(c, count)) != RGBDFE_OK)
+            return rc;
+        if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
+            return rc;
+    }
     if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, make_frame_prep(w, h, fx, fy, cx, cy, dist, depth16 ? depth16_factor : 0.0f)))
         != RGBDFE_OK)
         return rc;

@@ -218,7 +218,12 @@ struct rgbdfe_ctx {
     // match / RANSAC workspaces for pair_cap pairs
     int pair_cap = 0;
     int knn_splits = 8;
+    // option "overlap_blur": K3 (blur, needs only the pyramid) runs on a side stream beside K4 (quadtree, latency-bound)
+    int overlap_blur = 0;
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t side_fork = nullptr, side_join = nullptr;
     int knn_waves = 6; // train-range splits are chosen to give about this many waves of kNN CTAs (option "knn_waves")
+    bool knn_umma_ready = false; // k_knn2_umma's dynamic shared memory attribute set on this context's device
     int knn_umma = 1; // K7 on tcgen05 (match_umma.cu); 0 = the mma.sync kernel (option "knn_umma")
     MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
     int4* d_partial = nullptr;      // [pairs][splits][kp_cap]

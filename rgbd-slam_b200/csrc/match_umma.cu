@@ -314,10 +314,9 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
 // K7 on tcgen05 for pair slots [slot0, slot0 + npairs); same contract as launch_knn's mma.sync kernel
 int launch_knn_umma(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!c->knn_umma_ready) { // per context: the attribute belongs to the device the context lives on
         CUDA_TRY(c, cudaFuncSetAttribute(k_knn2_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, UK_SMEM));
-        attr_set = true;
+        c->knn_umma_ready = true;
     }
     dim3 grd((max_nq + UK_M - 1) / UK_M, splits, npairs);
     k_knn2_umma<<<grd, UK_THREADS, UK_SMEM, c->stream>>>(d_pairs, slot0, c->d_partial, c->kp_cap, splits);

@@ -53,6 +53,25 @@ def test_orb_stages_bit_exact(ctx, oracle, seq_vga, nfeat):
         assert (desc_o == desc_g).all(), "descriptors"
 
 
+def test_orb_blur_on_side_stream_same_result(ctx, oracle, seq_vga):
+    """Option overlap_blur: K3 beside K4 on a side stream; several back-to-back extractions, same keypoints and descriptors."""
+    cam, frames = seq_vga
+    ctx.orb_configure(1000, 1.2, 8, 20, 7)
+    orb = oracle.Orb(1000)
+    ctx.set_option("overlap_blur", 1)
+    try:
+        for gray, _ in frames[:3]:
+            kps_o, desc_o = orb.extract(gray)
+            kps_g, desc_g = ctx.orb_extract(gray)
+            assert len(kps_o) == len(kps_g)
+            for f in ("x", "y", "response", "octave"):
+                assert (kps_o[f] == kps_g[f]).all(), f
+            assert (kps_o["angle"].view(np.uint32) == kps_g["angle"].view(np.uint32)).all()
+            assert (desc_o == desc_g).all()
+    finally:
+        ctx.set_option("overlap_blur", 0)
+
+
 def test_orb_fast_threshold_fallback(ctx, oracle):
     """Low-contrast image: cells with no FAST corner at 20 but some at 7 (ORBextractor.cpp:658-661)."""
     rng = np.random.default_rng(11)
