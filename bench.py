@@ -301,6 +301,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=96)
     ap.add_argument("--sequences", type=int, default=32, help="independent tracked sequences in flight on each GPU")
+    ap.add_argument("--extract-streams", type=int, default=0, help="extraction contexts share this many streams (0 = one stream each)")
     ap.add_argument("--overlap-blur", type=int, default=0, help="diagnostic: run the blur beside the quadtree on a side stream")
     ap.add_argument("--knn-waves", type=int, default=0, help="diagnostic: waves of kNN CTAs the train-range split aims for (0 = library default)")
     ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
@@ -356,6 +357,8 @@ def main():
 
     part = rgbdfe.device_partition(local_rank, args.latency_sms) if args.latency_sms > 0 else None
 
+    stream_owners = []
+
     class Seq:
         """One tracked sequence: two contexts of one device — ctx_x extracts frame batch n+1 (throughput-bound, big
         grids) while ctx_t runs the sequential match/RANSAC chain of batch n on a high-priority stream;
@@ -369,6 +372,10 @@ def main():
                 self.ctx_x.set_option("host_zero_copy", 0)
             if args.overlap_blur:
                 self.ctx_x.set_option("overlap_blur", 1)
+            if args.extract_streams and k >= args.extract_streams:
+                self.ctx_x.share_stream(stream_owners[k % args.extract_streams])
+            else:
+                stream_owners.append(self.ctx_x)
             if part:
                 self.ctx_x.bind_partition(rgbdfe.PART_THROUGHPUT)
                 self.ctx_t.bind_partition(rgbdfe.PART_LATENCY)
@@ -718,7 +725,7 @@ def main():
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
         }))
-    for q in seqs:
+    for q in reversed(seqs):  # contexts that share a stream close before its owner
         q.close()
     if world > 1:
         dist.destroy_process_group()

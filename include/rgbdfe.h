@@ -103,6 +103,11 @@ int rgbdfe_stream_wait(rgbdfe_ctx* waiter, rgbdfe_ctx* signaler);
 /* high != 0: the context's stream gets the device's highest priority (for the latency-bound match/RANSAC
  * chain next to a throughput-bound extraction context).  Synchronises the context. */
 int rgbdfe_set_stream_priority(rgbdfe_ctx* ctx, int high);
+/* `ctx` gives up its own stream and enqueues on `owner`'s from now on (same device; `owner` must outlive `ctx` or
+ * `ctx` must get a stream of its own again through rgbdfe_set_stream_priority).  For many throughput-bound extraction
+ * contexts on one GPU: their big grids gain nothing from a stream each, while every extra stream aliases onto the 32
+ * hardware work queues and can serialise an unrelated latency-bound chain behind them.  Synchronises `ctx`. */
+int rgbdfe_share_stream(rgbdfe_ctx* ctx, rgbdfe_ctx* owner);
 /* SM partitioning (CUDA green contexts) for the same split, stronger than priorities: the device's SMs are
  * divided once per process into a latency partition of about `latency_sms` SMs (the driver rounds to its
  * granularity, 8 SMs on sm_90+) and a throughput partition with the rest; the sizes actually provisioned are

@@ -341,7 +341,8 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
         cudaStreamDestroy(c->bulk_stream);
     cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
-    cudaStreamDestroy(c->stream);
+    if (c->owns_stream)
+        cudaStreamDestroy(c->stream);
     delete c;
 }
 
@@ -372,8 +373,23 @@ int rgbdfe_set_stream_priority(rgbdfe_ctx* c, int high)
     CUDA_TRY(c, cudaDeviceGetStreamPriorityRange(&lo, &hi)); // numerically lower = higher priority
     cudaStream_t s = nullptr;
     CUDA_TRY(c, cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, high ? hi : lo));
-    cudaStreamDestroy(c->stream);
+    if (c->owns_stream)
+        cudaStreamDestroy(c->stream);
     c->stream = s;
+    c->owns_stream = true;
+    return RGBDFE_OK;
+}
+
+int rgbdfe_share_stream(rgbdfe_ctx* c, rgbdfe_ctx* owner)
+{
+    if (!c || !owner || c == owner || c->device != owner->device)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    if (c->owns_stream)
+        cudaStreamDestroy(c->stream);
+    c->stream = owner->stream;
+    c->owns_stream = false;
     return RGBDFE_OK;
 }
 

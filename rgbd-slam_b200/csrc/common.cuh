@@ -219,6 +219,7 @@ struct rgbdfe_ctx {
     int pair_cap = 0;
     int knn_splits = 8;
     // option "overlap_blur": K3 (blur, needs only the pyramid) runs on a side stream beside K4 (quadtree, latency-bound)
+    bool owns_stream = true; // false after rgbdfe_share_stream
     int overlap_blur = 0;
     cudaStream_t side_stream = nullptr;
     cudaEvent_t side_fork = nullptr, side_join = nullptr;

@@ -55,6 +55,18 @@ __device__ __forceinline__ void uk_mma(unsigned tmem_d, uint64_t da, uint64_t db
                  "l"(da), "l"(db), "r"(UK_IDESC), "r"(accumulate)
                  : "memory");
 }
+// one lane of a converged warp
+__device__ __forceinline__ bool uk_elect()
+{
+    unsigned p;
+    asm volatile("{\n"
+                 ".reg .pred q;\n"
+                 "elect.sync _|q, 0xffffffff;\n"
+                 "selp.u32 %0, 1, 0, q;\n"
+                 "}\n"
+                 : "=r"(p));
+    return p != 0;
+}
 __device__ __forceinline__ void uk_commit(uint64_t* bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -214,7 +226,7 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const unsigned tmem = s_tmem;
     const uint64_t dA = uk_desc(smem_u32(sA));
-    if (tid == 0 && T > 0) {
+    if (warp == 0 && T > 0 && uk_elect()) { // warp-uniform branch + elect.sync: the descriptors stay in uniform registers
         const uint64_t dB = uk_desc(smem_u32(sB[0]));
 #pragma unroll
         for (int s = 0; s < 8; s++) // k-step s = chunks 2s, 2s + 1: start address + 2 * LBO (in 16-byte units)
@@ -234,7 +246,7 @@ __global__ void __launch_bounds__(UK_THREADS, 2) k_knn2_umma(const MatchPair* __
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
-        if (tid == 0 && i + 1 < T) {
+        if (warp == 0 && i + 1 < T && uk_elect()) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint64_t dB = uk_desc(smem_u32(sB[b ^ 1]));
 #pragma unroll

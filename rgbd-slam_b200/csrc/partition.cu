@@ -144,7 +144,9 @@ int rgbdfe_bind_partition(rgbdfe_ctx* c, int role)
         s_main = (cudaStream_t)a;
         s_bulk = (cudaStream_t)b;
     }
-    cudaStreamDestroy(c->stream);
+    if (c->owns_stream)
+        cudaStreamDestroy(c->stream);
+    c->owns_stream = true;
     if (c->bulk_stream)
         cudaStreamDestroy(c->bulk_stream);
     c->stream = s_main;

@@ -179,6 +179,9 @@ class Context:
         """role: PART_NONE / PART_THROUGHPUT / PART_LATENCY (after device_partition() split the device)."""
         self._chk(lib().rgbdfe_bind_partition(self.h, int(role)))
 
+    def share_stream(self, owner):
+        self._chk(lib().rgbdfe_share_stream(self.h, owner.h))
+
     def set_option(self, name, value):
         self._chk(lib().rgbdfe_set_option(self.h, name.encode(), int(value)))
 

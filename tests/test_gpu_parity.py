@@ -72,6 +72,29 @@ def test_orb_blur_on_side_stream_same_result(ctx, oracle, seq_vga):
         ctx.set_option("overlap_blur", 0)
 
 
+def test_contexts_sharing_one_stream(ctx, oracle, seq_vga):
+    """rgbdfe_share_stream: a second context enqueues on the first one's stream; interleaved extractions stay exact."""
+    import rgbdfe
+
+    cam, frames = seq_vga
+    other = rgbdfe.Context(0, 640, 480, 1000, 2)
+    try:
+        other.share_stream(ctx)
+        assert other.stream() == ctx.stream()
+        ctx.orb_configure(1000, 1.2, 8, 20, 7)
+        other.orb_configure(500, 1.2, 8, 20, 7)
+        o1, o2 = oracle.Orb(1000), oracle.Orb(500)
+        for gray, _ in frames[:2]:
+            k1, d1 = ctx.orb_extract(gray)
+            k2, d2 = other.orb_extract(gray)
+            ko1, do1 = o1.extract(gray)
+            ko2, do2 = o2.extract(gray)
+            assert len(k1) == len(ko1) and (d1 == do1).all() and (k1["x"] == ko1["x"]).all()
+            assert len(k2) == len(ko2) and (d2 == do2).all() and (k2["x"] == ko2["x"]).all()
+    finally:
+        other.close()
+
+
 def test_orb_fast_threshold_fallback(ctx, oracle):
     """Low-contrast image: cells with no FAST corner at 20 but some at 7 (ORBextractor.cpp:658-661)."""
     rng = np.random.default_rng(11)
