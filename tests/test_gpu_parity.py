@@ -80,7 +80,7 @@ def test_contexts_sharing_one_stream(ctx, oracle, seq_vga):
     other = rgbdfe.Context(0, 640, 480, 1000, 2)
     try:
         other.share_stream(ctx)
-        assert other.stream() == ctx.stream()
+        assert other.stream == ctx.stream
         ctx.orb_configure(1000, 1.2, 8, 20, 7)
         other.orb_configure(500, 1.2, 8, 20, 7)
         o1, o2 = oracle.Orb(1000), oracle.Orb(500)
