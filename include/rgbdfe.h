@@ -179,6 +179,21 @@ int rgbdfe_cvorb_stage_harris(rgbdfe_ctx* ctx, int level, rgbdfe_keypoint* out, 
 int rgbdfe_match_knn2(rgbdfe_ctx* ctx, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt, const uint8_t* q_outlier,
     const rgbdfe_point3f* q_xyz, const rgbdfe_point3f* t_xyz, float ratio, int discard_outliers, rgbdfe_dmatch* out, int cap, int* n);
 
+/* Matcher::match for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same result as
+ * rgbdfe_match_knn2 (the mma.sync kNN kernel + the ratio / unique-train / outlier / depth filter), but every pointer
+ * is a DEVICE pointer supplied by the caller, the call is asynchronous on `stream` (a cudaStream_t; NULL = the
+ * context's stream) and it calls no cudaMalloc / cudaFree / allocating routine: the kernels' scratch (pair
+ * descriptor, counts, top-2 partials) is one static __device__ array of 256 KB + 256 B that every GPU loading the
+ * library holds until exit.  Limit: nq, nt <= 4096, beyond that RGBDFE_E_CAPACITY with a message in
+ * rgbdfe_last_error.  out_dev receives at most cap matches in query order, *n_dev = min(number found, cap).
+ * All calls of a process share that array per device: calls that overlap on the GPU (two streams without an
+ * ordering between them) race; calls on one stream, or ordered by events, are safe.  ctx supplies the device,
+ * the default stream and the error string only. */
+int rgbdfe_match_knn2_noalloc(rgbdfe_ctx* ctx, void* stream, const uint8_t* q_desc_dev, int nq, const uint8_t* t_desc_dev, int nt,
+    const uint8_t* q_outlier_dev, const rgbdfe_point3f* q_xyz_dev, const rgbdfe_point3f* t_xyz_dev, float ratio, int discard_outliers,
+    rgbdfe_dmatch* out_dev, int cap, int* n_dev);
+
 /* ---- Random (System/Random.cpp) --------------------------------------- */
 /* The context owns one glibc-rand()-compatible stream (TYPE_3).  state is 35
  * int32: 34 ring words + the linear output index. */

@@ -15,6 +15,7 @@
 // subroutine of 24 MOVM transposes + 8 IMMA per call: slower than the integer pipes.)
 // Neighbour order is lexicographic (distance, trainIdx) as in OpenCV.
 #include <algorithm>
+#include <mutex>
 
 #include "match_filter.cuh"
 
@@ -224,4 +225,82 @@ int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq
     return RGBDFE_OK;
 }
 
+// ---- rgbdfe_match_knn2_noalloc: Matcher::match without any allocation ----------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  The scratch of K7 / K8 —
+// the pair descriptor, the two device counts and the [split][query] top-2 partials — lives in ONE file-scope
+// device array that every GPU loading the library holds until exit.  Its name is a host-side stand-in in host
+// code: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// All calls share the array: calls that overlap on the GPU (different streams without an ordering) race.
+#define NOALLOC_MAX_DESC 4096 // most query / train descriptors per call
+#define NOALLOC_SPLITS 4      // train-range splits of K7 (fixed: the partials are sized for it)
+struct NoallocScratch {
+    MatchPair pair;
+    int nq, nt;
+    int pad[46];
+    int4 partial[NOALLOC_SPLITS * NOALLOC_MAX_DESC]; // 256 KB
+};
+static_assert(sizeof(MatchPair) == 64 && sizeof(NoallocScratch) == 256 + 16 * NOALLOC_SPLITS * NOALLOC_MAX_DESC, "scratch layout");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoallocScratch)];
+
+// Fills the header (everything the two kernels read before writing).  The partials need no clearing: K7 writes
+// every [split][q < nq] entry, also for an empty train range, before K8 reads exactly those.
+__global__ void k_noalloc_setup(NoallocScratch* s, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt, const uint8_t* q_outlier,
+    const rgbdfe_point3f* q_xyz, const rgbdfe_point3f* t_xyz, int* n_out)
+{
+    s->nq = nq, s->nt = nt;
+    s->pair = MatchPair { q_desc, t_desc, &s->nq, &s->nt, q_outlier, q_xyz, t_xyz, nullptr };
+    *n_out = 0;
+}
+
+static std::mutex g_noalloc_mu;
+static NoallocScratch* g_noalloc_ptr[64]; // device address of g_noalloc_scratch, per device ordinal
+
 } // namespace rgbdfe
+
+using namespace rgbdfe;
+
+extern "C" int rgbdfe_match_knn2_noalloc(rgbdfe_ctx* c, void* stream, const uint8_t* q_desc_dev, int nq, const uint8_t* t_desc_dev, int nt,
+    const uint8_t* q_outlier_dev, const rgbdfe_point3f* q_xyz_dev, const rgbdfe_point3f* t_xyz_dev, float ratio, int discard_outliers,
+    rgbdfe_dmatch* out_dev, int cap, int* n_dev)
+{
+    if (!c)
+        return RGBDFE_E_ARG;
+    if (nq < 0 || nt < 0 || cap < 0 || !n_dev || (nq > 0 && (!q_desc_dev || !q_xyz_dev)) || (nt > 0 && (!t_desc_dev || !t_xyz_dev))
+        || (cap > 0 && !out_dev)) {
+        c->set_error("match_knn2_noalloc: null pointer or negative size");
+        return RGBDFE_E_ARG;
+    }
+    if (nq > NOALLOC_MAX_DESC || nt > NOALLOC_MAX_DESC) {
+        c->set_error("match_knn2_noalloc: " + std::to_string(std::max(nq, nt)) + " descriptors exceed the static scratch (at most "
+            + std::to_string(NOALLOC_MAX_DESC) + " per side); use rgbdfe_match_knn2");
+        return RGBDFE_E_CAPACITY;
+    }
+    if (c->device < 0 || c->device >= 64) {
+        c->set_error("match_knn2_noalloc: device ordinal out of range");
+        return RGBDFE_E_ARG;
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    NoallocScratch* scr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[c->device]) { // set-up, once per device, with that device current
+            void* p = nullptr;
+            CUDA_TRY(c, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[c->device] = static_cast<NoallocScratch*>(p);
+        }
+        scr = g_noalloc_ptr[c->device];
+    }
+    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : c->stream;
+    k_noalloc_setup<<<1, 1, 0, s>>>(scr, q_desc_dev, nq, t_desc_dev, nt, q_outlier_dev, q_xyz_dev, t_xyz_dev, n_dev);
+    c->launches++;
+    if (nq > 0 && nt > 0) {
+        const int match_cap = std::min(cap, NOALLOC_MAX_DESC);
+        dim3 grd((nq + KNN_QPB - 1) / KNN_QPB, NOALLOC_SPLITS, 1);
+        k_knn2_hamming<<<grd, KNN_THREADS, 0, s>>>(&scr->pair, 0, scr->partial, NOALLOC_MAX_DESC, NOALLOC_SPLITS);
+        k_ratio_filter<<<1, 256, (size_t)nt * sizeof(int), s>>>(&scr->pair, 0, scr->partial, NOALLOC_MAX_DESC, NOALLOC_SPLITS, ratio, discard_outliers,
+            out_dev, match_cap, n_dev, nullptr);
+        c->launches += 2;
+    }
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
