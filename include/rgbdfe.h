@@ -314,7 +314,7 @@ int rgbdfe_track_results(rgbdfe_ctx* ctx, int first, int count, rgbdfe_se3_resul
 
 /* ---- batched loop-pair verification (PoseGraph.cpp:135-154,260-284) ---- */
 /* A keyframe shard: n_kf keyframes x n_feat features each, resident on the
- * device.  desc: n_kf*n_feat*32 B, xyz: n_kf*n_feat*12 B (host pointers). */
+ * device.  desc: n_kf*n_feat*32 B, xyz: n_kf*n_feat*12 B (host or device pointers). */
 int rgbdfe_kfdb_create(rgbdfe_ctx* ctx, rgbdfe_kfdb** db, int n_kf, int n_feat, const uint8_t* desc, const rgbdfe_point3f* xyz);
 void rgbdfe_kfdb_destroy(rgbdfe_ctx* ctx, rgbdfe_kfdb* db);
 /* For every keyframe k of the shard: Matcher(ratio).match(KF_k, query) then
@@ -327,6 +327,48 @@ void rgbdfe_kfdb_destroy(rgbdfe_ctx* ctx, rgbdfe_kfdb* db);
 int rgbdfe_verify_batch(rgbdfe_ctx* ctx, rgbdfe_kfdb* db, const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, float ratio,
     int min_matches, int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, unsigned seed, int first_pair_index,
     rgbdfe_se3_result* results, void* results_dev);
+
+/* ---- sharded verification over the GPUs of one box (BASELINE configs[3] and [4]) ------------------ */
+/* The keyframe database is block-sharded in keyframe order: rank r of n_ranks owns keyframes [lo, hi) as
+ * rgbdfe_shard_range returns them (block sizes differ by at most one) and keeps them resident as one rgbdfe_kfdb.
+ * Every rank is handed the same query frame(s); each verifies its block exactly as rgbdfe_verify_batch does
+ * (the loop body of PoseGraph.cpp:135-154,260-284) and ONE ncclAllGather of the 84-byte results per call rebuilds
+ * the full list on every rank -- the only exchange step of the path.  Pair (query q, keyframe k) draws from the
+ * stream srand(seed + q * n_kf_total + k), k the GLOBAL keyframe index, so results do not depend on n_ranks.
+ * The first success in candidate order (PoseGraph.cpp:283) stays a host pick over the returned list.
+ * The depth-covariance latch must be set (rgbdfe_depth_cov_set, or a tracked pair before): RGBDFE_E_STATE otherwise,
+ * here and in rgbdfe_verify_batch -- the reference latches it from the first pair processed; a batch has no order. */
+void rgbdfe_shard_range(int n_kf_total, int rank, int n_ranks, int* lo, int* hi);
+typedef struct rgbdfe_verify_params {
+    float ratio;            /* Matcher(ratio) */
+    int min_matches;        /* PoseGraph.cpp:142-144 */
+    int iterations;         /* RansacSE3(iterations, min_inlier_th, max_mahal, sample_size) */
+    unsigned min_inlier_th;
+    float max_mahal;
+    unsigned sample_size;
+    unsigned seed;
+} rgbdfe_verify_params;
+/* NCCL is resolved at run time (dlopen of libnccl.so.2, or the path in RGBDFE_NCCL_LIB), so the library also loads
+ * where NCCL is absent.  unique_id: 128 bytes made by rank 0 and handed to every rank by the application (any
+ * bootstrap: file, socket, MPI, torch.distributed); comm_create is ncclCommInitRank on the context's device and
+ * returns an ncclComm_t.  An ncclComm_t the application created itself from the same NCCL library works as well. */
+int rgbdfe_nccl_unique_id(void* id128);
+int rgbdfe_nccl_comm_create(rgbdfe_ctx* ctx, int n_ranks, int rank, const void* id128, void** comm);
+int rgbdfe_nccl_comm_destroy(void* comm);
+/* Asynchronous half: verifies n_queries query frames (q_desc [n_queries][nq][32], q_xyz [n_queries][nq]; host
+ * memory, or device memory that is then read in place) against this rank's block on the context stream, then --
+ * on a communication stream of the context, so that the next enqueue's kernels overlap it -- the all-gather
+ * (skipped for n_ranks == 1, nccl_comm may be NULL) and the copy of the gathered results to pinned host memory.
+ * slot in [0, 4) names the result buffers used; a slot must be collected before it is enqueued again. */
+int rgbdfe_verify_sharded_enqueue(rgbdfe_ctx* ctx, rgbdfe_kfdb* db, void* nccl_comm, int n_ranks, int rank, int n_kf_total, const uint8_t* q_desc,
+    const rgbdfe_point3f* q_xyz, int nq, int n_queries, const rgbdfe_verify_params* params, int slot);
+/* Waits for the slot and writes results[q * n_kf_total + k] for every query q and GLOBAL keyframe k (NULL: wait only). */
+int rgbdfe_verify_sharded_collect(rgbdfe_ctx* ctx, int slot, rgbdfe_se3_result* results);
+/* Blocking form: enqueue on slot 0 + collect. */
+int rgbdfe_verify_sharded(rgbdfe_ctx* ctx, rgbdfe_kfdb* db, void* nccl_comm, int n_ranks, int rank, int n_kf_total, const uint8_t* q_desc,
+    const rgbdfe_point3f* q_xyz, int nq, int n_queries, const rgbdfe_verify_params* params, rgbdfe_se3_result* results);
+/* Host arithmetic only: the gathered layout [rank][query][ceil(n_kf_total / n_ranks)] -> [query][n_kf_total]. */
+int rgbdfe_gathered_to_keyframe_order(const rgbdfe_se3_result* gathered, int n_ranks, int n_queries, int n_kf_total, rgbdfe_se3_result* out);
 
 #ifdef __cplusplus
 }

@@ -324,6 +324,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
     free_orb_workspaces(c);
     free_pair_workspaces(c);
     free_proj_workspace(c);
+    free_verify_state(c);
     free_cvorb_workspace(c);
     free_fast_state(c);
     free_frame(c->scratch);
@@ -1109,6 +1110,7 @@ int rgbdfe_depth_cov_set(rgbdfe_ctx* c, int latched, double cov)
     if (!c)
         return RGBDFE_E_ARG;
     DepthLatch l = { latched, 0, cov };
+    c->latch_known = latched != 0;
     cudaSetDevice(c->device);
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     CUDA_TRY(c, cudaMemcpy(c->d_latch, &l, sizeof(l), cudaMemcpyHostToDevice));
@@ -1352,95 +1354,13 @@ int rgbdfe_track_results(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result*
     return RGBDFE_OK;
 }
 
-int rgbdfe_kfdb_create(rgbdfe_ctx* c, rgbdfe_kfdb** out, int n_kf, int n_feat, const uint8_t* desc, const rgbdfe_point3f* xyz)
-{
-    if (!c || !out || n_kf < 1 || n_feat < 1 || !desc || !xyz)
-        return RGBDFE_E_ARG;
-    if (n_feat > c->kp_cap) {
-        c->set_error("kfdb: n_feat exceeds max_feats + 64");
-        return RGBDFE_E_CAPACITY;
-    }
-    cudaSetDevice(c->device);
-    rgbdfe_kfdb* db = new (std::nothrow) rgbdfe_kfdb();
-    if (!db)
-        return RGBDFE_E_ARG;
-    db->n_kf = n_kf, db->n_feat = n_feat, db->desc = nullptr, db->xyz = nullptr;
-    const size_t N = (size_t)n_kf * n_feat;
-    CUDA_TRY(c, dmalloc(&db->desc, N * 32));
-    CUDA_TRY(c, dmalloc(&db->xyz, N));
-    CUDA_TRY(c, cudaMemcpy(db->desc, desc, N * 32, cudaMemcpyHostToDevice));
-    CUDA_TRY(c, cudaMemcpy(db->xyz, xyz, N * sizeof(rgbdfe_point3f), cudaMemcpyHostToDevice));
-    *out = db;
-    return RGBDFE_OK;
-}
-
-void rgbdfe_kfdb_destroy(rgbdfe_ctx* c, rgbdfe_kfdb* db)
-{
-    if (!db)
-        return;
-    if (c) {
-        cudaSetDevice(c->device);
-        cudaStreamSynchronize(c->stream);
-    }
-    cudaFree(db->desc);
-    cudaFree(db->xyz);
-    delete db;
-}
-
-int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, float ratio, int min_matches,
-    int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, unsigned seed, int first_pair_index,
-    rgbdfe_se3_result* results, void* results_dev)
-{
-    if (!c || !db || !q_desc || !q_xyz || nq < 1 || (!results && !results_dev))
-        return RGBDFE_E_ARG;
-    if (nq > c->kp_cap)
-        return RGBDFE_E_CAPACITY;
-    cudaSetDevice(c->device);
-    const int np = db->n_kf;
-    int rc = ensure_pairs(c, np);
-    if (rc != RGBDFE_OK)
-        return rc;
-    cudaStream_t s = c->stream;
-    rgbdfe_frame* Q = c->scratch; // the current frame = train side of every pair
-    CUDA_TRY(c, cudaMemcpyAsync(Q->desc, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, q_xyz, (size_t)nq * 12, cudaMemcpyHostToDevice, s));
-    k_set_int<<<1, 1, 0, s>>>(c->d_const_n + 0, db->n_feat);
-    k_set_int<<<1, 1, 0, s>>>(c->d_const_n + 1, nq);
-    c->launches += 2;
-    // Matcher(0.9).match(KF_k, cur): query = keyframe k, train = current frame (PoseGraph.cpp:139-141)
-    std::vector<MatchPair> hp(np);
-    for (int k = 0; k < np; k++)
-        hp[k] = MatchPair { db->desc + (size_t)k * db->n_feat * 32, Q->desc, c->d_const_n + 0, c->d_const_n + 1, nullptr,
-            db->xyz + (size_t)k * db->n_feat, Q->xyz, nullptr };
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_pairs, hp.data(), (size_t)np * sizeof(MatchPair), cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaStreamSynchronize(s)); // hp is pageable
-    if ((rc = launch_match(c, c->d_pairs, np, db->n_feat, nq, ratio, 1, nullptr)) != RGBDFE_OK)
-        return rc;
-    rgbdfe_se3_result* d_res = results_dev ? (rgbdfe_se3_result*)results_dev : nullptr;
-    rgbdfe_se3_result* tmp = nullptr;
-    if (!d_res) {
-        CUDA_TRY(c, dmalloc(&tmp, (size_t)np));
-        d_res = tmp;
-    }
-    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
-    rc = launch_ransac_se3(c, c->d_pairs, 0, np, prm, 0, 1, seed, first_pair_index, min_matches, d_res, nullptr);
-    if (rc == RGBDFE_OK && results) {
-        cudaError_t e = cudaMemcpyAsync(results, d_res, (size_t)np * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost, s);
-        if (e == cudaSuccess)
-            e = cudaStreamSynchronize(s);
-        if (e != cudaSuccess) {
-            c->set_error(std::string("verify_batch copy: ") + cudaGetErrorString(e));
-            rc = RGBDFE_E_CUDA;
-        }
-    }
-    if (tmp) {
-        cudaStreamSynchronize(s);
-        cudaFree(tmp);
-    }
-    return rc;
-}
-
 } // extern "C"
+
+namespace rgbdfe { // helpers of this file used by verify.cu
+int api_ensure_pairs(rgbdfe_ctx* c, int npairs) { return ensure_pairs(c, npairs); }
+Se3Params api_make_params(rgbdfe_ctx* c, int iterations, unsigned min_inl, float max_mahal, unsigned sample) { return make_params(c, iterations, min_inl, max_mahal, sample); }
+int api_pointer_kind(const void* p, const void** dev) { return pointer_kind(p, dev); }
+}
 
 extern "C" {
 

@@ -114,6 +114,7 @@ struct rgbdfe_kfdb {
     int n_kf, n_feat;
     uint8_t* desc;
     rgbdfe_point3f* xyz;
+    int device;
 };
 
 // packed FAST candidate: x (12 bits) | y (12 bits) << 12 | score << 24
@@ -255,6 +256,8 @@ struct rgbdfe_ctx {
     struct CvOrbWorkspace* cvorb = nullptr; // the cv::ORB branch of Extractor (row N3, orb_cv.cu), allocated by rgbdfe_cvorb_configure
     int extractor = 0;                      // RGBDFE_EXTRACTOR_ORB2 / RGBDFE_EXTRACTOR_ORB: which one the extraction entry points run
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
+    struct VerifyState* verify = nullptr; // sharded verification: comm stream, result slots, query staging (verify.cu)
+    bool latch_known = false;       // the host has seen the depth-covariance latch set (batched verification requires it)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
     int dbg_on = 0;
 
@@ -362,6 +365,12 @@ struct FusedFilter {
 };
 int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng,
     unsigned seed, int first_pair_index, int min_matches, rgbdfe_se3_result* d_results, const FusedFilter* ff);
+// api.cu
+int api_ensure_pairs(rgbdfe_ctx* c, int npairs);
+Se3Params api_make_params(rgbdfe_ctx* c, int iterations, unsigned min_inl, float max_mahal, unsigned sample);
+int api_pointer_kind(const void* p, const void** dev); // 0 pageable host, 1 device, 2 pinned host
+// verify.cu
+void free_verify_state(rgbdfe_ctx* c);
 // ransac_umeyama.cu
 int launch_ransac_umeyama(rgbdfe_ctx* c, int nm, const rgbdfe_point3f* d_xyz1, const rgbdfe_point3f* d_xyz2, int used_pairs, int iters0,
     const int* d_iters_tab, int iters_min, double th0, int adaptive, double min_ratio, UmeState* d_state, rgbdfe_umeyama_result* d_res);

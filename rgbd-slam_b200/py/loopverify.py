@@ -21,32 +21,6 @@ def shard_range(n_kf, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def gather_results(local, n_kf, rank, world, device="cpu"):
-    """all_gather the per-pair result structs of every rank into keyframe order.  `local`: structured array of
-    this rank's block (or a device uint8 tensor with the same bytes).  Returns a uint8 torch tensor [n_kf, 84]."""
-    import torch
-    import torch.distributed as dist
-
-    per = -(-n_kf // world)  # equal-size slots for all_gather_into_tensor; short blocks are padded
-    if isinstance(local, np.ndarray):
-        buf = torch.zeros(per * RESULT_BYTES, dtype=torch.uint8, device=device)
-        raw = torch.from_numpy(np.ascontiguousarray(local).view(np.uint8).reshape(-1).copy())
-        buf[: raw.numel()] = raw.to(device)
-    else:
-        buf = local
-        assert buf.numel() == per * RESULT_BYTES
-    if world == 1:
-        return buf.view(per, RESULT_BYTES)[:n_kf]
-    out = torch.empty(world * per * RESULT_BYTES, dtype=torch.uint8, device=buf.device)
-    dist.all_gather_into_tensor(out, buf)
-    out = out.view(world, per, RESULT_BYTES)
-    rows = []
-    for r in range(world):
-        lo, hi = shard_range(n_kf, r, world)
-        rows.append(out[r, : hi - lo])
-    return torch.cat(rows, 0)
-
-
 def first_success(results, min_index=0):
     """detectLoop takes the FIRST candidate, in candidate order, whose RansacSE3 succeeds (PoseGraph.cpp:283)."""
     ok = np.nonzero(results["ok"][min_index:] != 0)[0]
@@ -54,8 +28,10 @@ def first_success(results, min_index=0):
 
 
 class ShardedVerifier:
-    """Keyframe block of this rank + the verify call.  `local_verify(kf_lo, kf_hi, q_desc, q_xyz, seed)` must return
-    the structured results of keyframes [kf_lo, kf_hi) with per-pair stream srand(seed + global index)."""
+    """Host logic of the sharded path with a pluggable per-block verifier (the CPU gloo tests drive it with the oracle):
+    `local_verify(kf_lo, kf_hi, q_desc, q_xyz, seed)` returns the structured results of keyframes [kf_lo, kf_hi) with
+    per-pair stream srand(seed + global index).  The exchanged layout and its unpacking are the C ABI's
+    ([rank][query][ceil(n_kf / world)] records -> rgbdfe_gathered_to_keyframe_order)."""
 
     def __init__(self, n_kf, rank, world, local_verify, device="cpu"):
         self.n_kf, self.rank, self.world, self.device = n_kf, rank, world, device
@@ -68,31 +44,65 @@ class ShardedVerifier:
         stream srand(seed + q * n_kf + k), so the result is independent of the sharding.  Returns [Q, n_kf] records."""
         import torch
 
+        import rgbdfe
+
         Q = len(q_descs)
         per = -(-self.n_kf // self.world)
-        buf = torch.zeros(Q * per * RESULT_BYTES, dtype=torch.uint8)
-        view = buf.view(Q, per * RESULT_BYTES)
+        block = np.zeros((Q, per), dtype)
         for q in range(Q):
-            local = self.local_verify(self.lo, self.hi, q_descs[q], q_xyzs[q], seed + q * self.n_kf)
-            raw = torch.from_numpy(np.ascontiguousarray(local).view(np.uint8).reshape(-1).copy())
-            view[q, : raw.numel()] = raw
-        buf = buf.to(self.device)
+            block[q, : self.hi - self.lo] = self.local_verify(self.lo, self.hi, q_descs[q], q_xyzs[q], seed + q * self.n_kf)
+        buf = torch.from_numpy(block.view(np.uint8).reshape(-1).copy()).to(self.device)
         if self.world == 1:
-            out = buf.view(1, Q, per, RESULT_BYTES)
+            out = buf
         else:
             import torch.distributed as dist
 
             out = torch.empty(self.world * buf.numel(), dtype=torch.uint8, device=buf.device)
             dist.all_gather_into_tensor(out, buf)
-            out = out.view(self.world, Q, per, RESULT_BYTES)
-        rows = []
-        for r in range(self.world):
-            lo, hi = shard_range(self.n_kf, r, self.world)
-            rows.append(out[r, :, : hi - lo])
-        g = torch.cat(rows, 1).contiguous()  # [Q, n_kf, 84]
-        return np.frombuffer(g.cpu().numpy().tobytes(), dtype=dtype).reshape(Q, self.n_kf)
+        gathered = np.frombuffer(out.cpu().numpy().tobytes(), dtype=dtype)
+        return rgbdfe.gathered_to_keyframe_order(gathered, self.world, Q, self.n_kf)
 
     def verify(self, q_desc, q_xyz, seed, dtype):
-        local = self.local_verify(self.lo, self.hi, q_desc, q_xyz, seed)
-        g = gather_results(local, self.n_kf, self.rank, self.world, self.device)
-        return np.frombuffer(g.cpu().numpy().tobytes(), dtype=dtype)
+        return self.verify_many([q_desc], [q_xyz], seed, dtype)[0]
+
+
+class CudaShardedVerifier:
+    """One rank of the sharded verification through the C ABI only (what a C++ PoseGraph would call): this rank's
+    keyframe block resident in a rgbdfe_kfdb, an NCCL communicator made by rgbdfe_nccl_comm_create from a 128-byte id
+    that the application moved to every rank (`id128`), and rgbdfe_verify_sharded_enqueue / _collect."""
+
+    def __init__(self, device, rank, world, n_kf_total, kf_desc_block, kf_xyz_block, id128=None, max_feats=1000, depth_cov=(0.01 * 2.0 * 2.0) ** 2):
+        import rgbdfe
+
+        self.rgbdfe, self.rank, self.world, self.n_kf = rgbdfe, rank, world, n_kf_total
+        self.lo, self.hi = rgbdfe.shard_range(n_kf_total, rank, world)
+        assert len(kf_desc_block) == self.hi - self.lo
+        self.ctx = rgbdfe.Context(device, 640, 480, max_feats, 1)
+        self.ctx.depth_cov_set(1, depth_cov)  # the latch must be pinned: results then do not depend on pair order
+        self.db = self.ctx.kfdb_create(kf_desc_block, kf_xyz_block)
+        self.comm = self.ctx.nccl_comm_create(world, rank, id128) if world > 1 else None
+        self.params = rgbdfe.VerifyParams(0.9, 30, 200, 30, 3.0, 4, 42)
+
+    def enqueue(self, q_desc, q_xyz, nq, n_queries, slot, seed=42):
+        self.params.seed = seed
+        self.ctx.verify_sharded_enqueue(self.db, self.comm, self.world, self.rank, self.n_kf, q_desc, q_xyz, nq, n_queries, self.params, slot)
+
+    def collect(self, slot, n_queries, want=True):
+        return self.ctx.verify_sharded_collect(slot, n_queries, self.n_kf, want)
+
+    def verify(self, q_desc, q_xyz, seed=42):
+        q_desc = np.ascontiguousarray(q_desc, np.uint8)
+        q_xyz = np.ascontiguousarray(q_xyz, np.float32)
+        nq = q_desc.shape[-2]
+        n_queries = 1 if q_desc.ndim == 2 else q_desc.shape[0]
+        self.enqueue(q_desc, q_xyz, nq, n_queries, 0, seed)
+        return self.collect(0, n_queries)
+
+    def close(self):
+        if self.comm:
+            self.rgbdfe.lib().rgbdfe_nccl_comm_destroy(self.comm)
+            self.comm = None
+        if self.ctx:
+            self.ctx.kfdb_destroy(self.db)
+            self.ctx.close()
+            self.ctx = None

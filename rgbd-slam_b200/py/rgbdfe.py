@@ -35,6 +35,11 @@ class UmeParams(C.Structure):  # rgbdfe_umeyama_params
                 ("minimalNumberOfMatches", C.c_int), ("usedPairs", C.c_int)]
 
 
+class VerifyParams(C.Structure):  # rgbdfe_verify_params
+    _fields_ = [("ratio", C.c_float), ("min_matches", C.c_int), ("iterations", C.c_int), ("min_inlier_th", C.c_uint),
+                ("max_mahal", C.c_float), ("sample_size", C.c_uint), ("seed", C.c_uint)]
+
+
 class UmeResult(C.Structure):  # rgbdfe_umeyama_result
     _fields_ = [("ok", C.c_int), ("T", C.c_float * 16), ("n_inliers", C.c_int), ("iters_executed", C.c_int)]
 
@@ -451,3 +456,45 @@ class Context:
             )
         )
         return res
+
+    # ---- sharded verification (rgbdfe_verify_sharded_*; NCCL communicator created through the C ABI) ----
+    def nccl_comm_create(self, n_ranks, rank, id128):
+        comm = C.c_void_p()
+        self._chk(lib().rgbdfe_nccl_comm_create(self.h, n_ranks, rank, id128, C.byref(comm)))
+        return comm
+
+    def verify_sharded_enqueue(self, db, comm, n_ranks, rank, n_kf_total, q_desc, q_xyz, nq, n_queries, params, slot):
+        """q_desc / q_xyz: numpy arrays (host) or integer device addresses."""
+        pd = _p(q_desc) if isinstance(q_desc, np.ndarray) else C.c_void_p(int(q_desc))
+        px = _p(q_xyz) if isinstance(q_xyz, np.ndarray) else C.c_void_p(int(q_xyz))
+        self._chk(lib().rgbdfe_verify_sharded_enqueue(self.h, db, comm, n_ranks, rank, n_kf_total, pd, px, nq, n_queries, C.byref(params), slot))
+
+    def verify_sharded_collect(self, slot, n_queries, n_kf_total, want=True):
+        res = np.zeros((n_queries, n_kf_total), SE3_DTYPE) if want else None
+        self._chk(lib().rgbdfe_verify_sharded_collect(self.h, slot, _p(res)))
+        return res
+
+
+def nccl_unique_id():
+    buf = C.create_string_buffer(128)
+    rc = lib().rgbdfe_nccl_unique_id(buf)
+    if rc != 0:
+        raise RgbdfeError(f"rgbdfe_nccl_unique_id: {rc} (NCCL library not found?)")
+    return buf.raw
+
+
+def shard_range(n_kf_total, rank, n_ranks):
+    lo, hi = C.c_int(), C.c_int()
+    lib().rgbdfe_shard_range.restype = None
+    lib().rgbdfe_shard_range(n_kf_total, rank, n_ranks, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
+def gathered_to_keyframe_order(gathered, n_ranks, n_queries, n_kf_total):
+    """gathered: SE3_DTYPE records in the all-gather layout [rank][query][ceil(n_kf_total / n_ranks)]."""
+    g = np.ascontiguousarray(gathered)
+    out = np.zeros((n_queries, n_kf_total), SE3_DTYPE)
+    rc = lib().rgbdfe_gathered_to_keyframe_order(_p(g), n_ranks, n_queries, n_kf_total, _p(out))
+    if rc != 0:
+        raise RgbdfeError(f"rgbdfe_gathered_to_keyframe_order: {rc}")
+    return out
