@@ -266,6 +266,142 @@ def cvorb_leg(rgbdfe, torch, local_rank, gray_d, depth_d, cam, inv_factor, B, nf
     return out
 
 
+def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
+    """BASELINE configs[3] and [4] through the C ABI (rgbdfe_verify_sharded_enqueue / _collect, NCCL made by
+    rgbdfe_nccl_comm_create): a FIXED job -- 1 query vs `--verify-kf` (4096) keyframes of 1000 features, the keyframes
+    block-sharded over the ranks (strong scaling) -- and the batched relocalisation 256 queries x 1024 keyframes.
+    Device time (CUDA events on the context stream around enqueue .. last collect), max over ranks.  Outside the timed
+    region rank 0 recomputes pairs of every other rank's block on its own GPU and compares the gathered bytes."""
+    import loopverify
+    import synth
+
+    N_FEAT = 1000
+    cov = (0.01 * 2.0 * 2.0) ** 2
+
+    def bcast_id():
+        buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            buf = torch.frombuffer(bytearray(rgbdfe.nccl_unique_id()), dtype=torch.uint8).cuda()
+        if world > 1:
+            dist.broadcast(buf, 0)
+        return bytes(buf.cpu().numpy().tobytes())
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    def timed_queries(v, queries, n_queries_per_call, calls, depth=3):
+        """`calls` enqueues of n_queries_per_call queries each, `depth` in flight; returns ms (device, max over ranks)."""
+        stream = torch.cuda.ExternalStream(v.ctx.stream, device=local_rank)
+
+        def run(n):
+            for i in range(n + depth):
+                if i >= depth:
+                    v.collect((i - depth) % 4, n_queries_per_call, want=True)
+                if i < n:
+                    qd, qp = queries[i % len(queries)]
+                    v.enqueue(qd, qp, N_FEAT, n_queries_per_call, i % 4, seed=42)
+
+        run(2)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = v.ctx.launches
+        e0.record(stream)
+        run(calls)
+        e1.record(stream)  # every slot was collected: all kernels, the gathers and the copies to the host have finished
+        e1.synchronize()
+        torch.cuda.synchronize()
+        return max_over_ranks(e0.elapsed_time(e1)), v.ctx.launches - l0
+
+    out = {"unit": "pairs/s", "features": N_FEAT, "api": "rgbdfe_verify_sharded_enqueue/_collect (C ABI), NCCL all-gather of 84 B/pair on the context's communication stream"}
+    ident = bcast_id() if world > 1 else None
+
+    # ---- configs[3]: 1 query vs n_kf keyframes, strong scaling ----
+    n_kf = args.verify_kf
+    qd, qp, kd, kp, _ = synth.synth_pair_sets(n_kf, N_FEAT, seed=5678, overlap_frac=0.05)  # the same data on every rank
+    lo, hi = rgbdfe.shard_range(n_kf, rank, world)
+    v = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf, kd[lo:hi], kp[lo:hi], ident, max_feats=N_FEAT, depth_cov=cov)
+    queries = [(np.ascontiguousarray(np.roll(qd, 13 * i, axis=0)), np.ascontiguousarray(np.roll(qp, 13 * i, axis=0))) for i in range(8)]
+    calls = 48
+    ms, launches = timed_queries(v, queries, 1, calls)
+    out.update({"value": calls * n_kf / (ms * 1e-3), "keyframes_total": n_kf, "keyframes_per_gpu": hi - lo, "ms_per_query": ms / calls,
+                "scaling": "strong (fixed 1 query x %d keyframes job, keyframes block-sharded over %d GPU(s))" % (n_kf, world),
+                "launches_per_query": launches / calls})
+    # parity on hardware: gathered results vs rank 0's own GPU recomputing runs of every block (all pairs at N <= 2)
+    full = v.verify(queries[0][0], queries[0][1], seed=42)[0]
+    parity, checked = True, 0
+    if rank == 0:
+        run = n_kf if world <= 2 else max(64, 512 // world)
+        for r in range(world):
+            rlo, rhi = rgbdfe.shard_range(n_kf, r, world)
+            rhi = min(rhi, rlo + run)
+            db = v.ctx.kfdb_create(kd[rlo:rhi], kp[rlo:rhi])
+            ref = v.ctx.verify_batch(db, rhi - rlo, queries[0][0], queries[0][1], 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rlo)
+            v.ctx.kfdb_destroy(db)
+            parity = parity and ref.tobytes() == full[rlo:rhi].tobytes()
+            checked += rhi - rlo
+    out.update({"parity": bool(parity), "parity_pairs_checked": checked, "loops_found": int(full["ok"].sum()),
+                "parity_how": "rank 0 recomputed runs of every rank's block alone with rgbdfe_verify_batch; gathered bytes must be identical"})
+    v.close()
+    if world > 1:
+        dist.barrier()
+    # the same fixed job on ONE GPU (rank 0 alone), for the strong-scaling efficiency of this very run
+    if world > 1:
+        single = None
+        if rank == 0:
+            v1 = loopverify.CudaShardedVerifier(local_rank, 0, 1, n_kf, kd, kp, None, max_feats=N_FEAT, depth_cov=cov)
+            ms1 = None
+            try:
+                stream = torch.cuda.ExternalStream(v1.ctx.stream, device=local_rank)
+                for _ in range(2):
+                    v1.verify(queries[0][0], queries[0][1])
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                n1 = 16
+                for i in range(n1 + 3):
+                    if i >= 3:
+                        v1.collect((i - 3) % 4, 1)
+                    if i < n1:
+                        v1.enqueue(queries[i % 8][0], queries[i % 8][1], N_FEAT, 1, i % 4, seed=42)
+                e1.record(stream)
+                e1.synchronize()
+                ms1 = e0.elapsed_time(e1) / n1
+            finally:
+                v1.close()
+            single = n_kf / (ms1 * 1e-3)
+        dist.barrier()
+        if rank == 0:
+            out["one_gpu_same_job_pairs_per_s"] = single
+            out["strong_efficiency"] = out["value"] / (world * single)
+    else:
+        out["strong_efficiency"] = 1.0
+
+    # ---- configs[4]: batched relocalisation, 256 queries x 1024 keyframes, one gather per call ----
+    try:
+        Q, n_kf4, per_call = 256, 1024, 64
+        qd4, qp4, kd4, kp4, _ = synth.synth_pair_sets(n_kf4, N_FEAT, seed=777, overlap_frac=0.05)
+        lo, hi = rgbdfe.shard_range(n_kf4, rank, world)
+        v4 = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf4, kd4[lo:hi], kp4[lo:hi], bcast_id() if world > 1 else None,
+                                            max_feats=N_FEAT, depth_cov=cov)
+        qs = np.stack([np.roll(qd4, 7 * i, axis=0) for i in range(per_call)])
+        ps = np.stack([np.roll(qp4, 7 * i, axis=0) for i in range(per_call)])
+        ms4, _ = timed_queries(v4, [(qs, ps)], per_call, Q // per_call, depth=2)
+        out["relocalisation"] = {"value": Q * n_kf4 / (ms4 * 1e-3), "unit": "pairs/s", "queries": Q, "keyframes_total": n_kf4,
+                                 "keyframes_per_gpu": hi - lo, "ms_total": ms4,
+                                 "what": "BASELINE configs[4]: 256 query frames x 1024 keyframes, all pairs match + RansacSE3(200, 30), "
+                                         "%d queries per call, one all-gather per call" % per_call}
+        v4.close()
+    except Exception as ex:
+        out["relocalisation"] = {"error": str(ex)[:200]}
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -310,9 +446,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
-    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial"],
+    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify"],
                     help="diagnostic: time only the extraction half or only the match/RANSAC chains (not a bench value)")
-    ap.add_argument("--verify-kf", type=int, default=512, help="keyframes per GPU for the verification leg (N>1)")
+    ap.add_argument("--verify-kf", type=int, default=4096, help="keyframes of the fixed loop-closure verification job (BASELINE configs[3]), sharded over the GPUs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -345,6 +481,14 @@ def main():
             sys.stdout.flush()
             os.dup2(saved_fd, 1)
             os.close(saved_fd)
+
+    if args.mode == "verify":  # diagnostic: the sharded verification leg alone
+        out = verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world)
+        if rank == 0:
+            print(json.dumps({"n_gpus": world, "verify": out}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     B, F = args.batch, args.frames
     cam, frames = make_sequence(F)
@@ -640,63 +784,10 @@ def main():
         cvorb = {"error": str(ex)[:200]}
 
     # ---- sharded loop-pair verification (the part of the path that shards), N >= 1 ----
-    verify = None
     try:
-        import synth
-
-        n_kf = args.verify_kf
-        qd, qp, kd, kp, _ = synth.synth_pair_sets(n_kf, 1000, seed=5678 + rank, overlap_frac=0.05)
-        qd, qp = np.ascontiguousarray(qd), np.ascontiguousarray(qp)
-        vctx = rgbdfe.Context(local_rank, W, H, 1000, 1)
-        vctx.depth_cov_set(1, (0.01 * 2.0 * 2.0) ** 2)
-        db = vctx.kfdb_create(kd, kp)
-        # two result buffers: the all_gather of query i runs on torch's stream while the verify kernels of query i + 1
-        # run on the context's stream (a buffer is only rewritten after its gather has finished)
-        res_dev = [torch.empty(n_kf * 84, dtype=torch.uint8, device="cuda") for _ in range(2)]
-        gathered = [None, None]
-        vstream = torch.cuda.ExternalStream(vctx.stream, device=local_rank)
-        vcount = [0]
-
-        import loopverify
-
-        def vstep():
-            # this rank's keyframe block through the C ABI, then the one exchange step of the path (loopverify.py)
-            b = vcount[0] & 1
-            vcount[0] += 1
-            if gathered[b] is not None:
-                vstream.wait_event(gathered[b])
-            vctx.verify_batch(db, n_kf, qd, qp, 0.9, 30, 200, 30, 3.0, 4, seed=42, first_pair_index=rank * n_kf, results_dev=res_dev[b].data_ptr(), want_host=False)
-            if world > 1:
-                done = torch.cuda.Event()
-                done.record(vstream)
-                torch.cuda.current_stream().wait_event(done)
-                loopverify.gather_results(res_dev[b], world * n_kf, rank, world)
-                gathered[b] = torch.cuda.Event()
-                gathered[b].record()
-
-        for _ in range(2):
-            vstep()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(vstream)
-        vs = 8
-        for _ in range(vs):
-            vstep()
-        torch.cuda.current_stream().wait_stream(vstream)  # the last gather is on torch's stream
-        e1.record()
-        torch.cuda.synchronize()
-        vms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([vms], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            vms = float(t.item())
-        verify = {"value": vs * n_kf * world / (vms * 1e-3), "unit": "pairs/s", "pairs_per_gpu": n_kf, "features": 1000, "sharding": "keyframes block-sharded, NCCL all_gather of 84 B/pair, overlapped with the next query's kernels" if world > 1 else "single GPU"}
-        vctx.kfdb_destroy(db)
-        vctx.close()
+        verify = verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world)
     except Exception as ex:  # the headline metric does not depend on this leg
-        verify = {"error": str(ex)[:200]}
+        verify = {"error": str(ex)[:300]}
 
     cpu = None
     if rank == 0 and not args.no_cpu:
@@ -717,7 +808,13 @@ def main():
                        "host_threads": args.host_threads,
                        "l2": f"inputs larger than L2: {S} sequences x rotating {F}-frame set ({F * (W * H * 3) / 1e6:.0f} MB) + 58 MB of pyramid per batch",
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
-                       "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"]))},
+                       "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"])),
+                       # the sharded leg (BASELINE configs[3] / [4]); details under the top-level key "verify"
+                       "verify_pairs_per_s": (verify or {}).get("value"), "verify_keyframes_total": (verify or {}).get("keyframes_total"),
+                       "verify_ms_per_query": (verify or {}).get("ms_per_query"), "verify_strong_efficiency": (verify or {}).get("strong_efficiency"),
+                       "verify_one_gpu_same_job_pairs_per_s": (verify or {}).get("one_gpu_same_job_pairs_per_s"),
+                       "verify_parity": (verify or {}).get("parity"), "verify_parity_pairs_checked": (verify or {}).get("parity_pairs_checked"),
+                       "reloc_pairs_per_s": ((verify or {}).get("relocalisation") or {}).get("value"), "verify_error": (verify or {}).get("error")},
             "e2e": {"value": e2e, "unit": "frames/s",
                     "h2d_bytes_per_step": S * B * (W * H * (3 if args.full_upload else 1) + (0 if args.full_upload else NFEAT * 32)),
                     "d2h_bytes_per_step": S * B * 84,

@@ -362,6 +362,9 @@ struct FusedFilter {
     int splits;
     float ratio;
     int discard_outliers;
+    // per-pair streams of a batch of query groups: pair p seeds srand(seed + first_pair_index + (p / seed_group) * seed_stride + p % seed_group);
+    // 0 = one group (seed + first_pair_index + p)
+    int seed_group = 0, seed_stride = 0;
 };
 int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng,
     unsigned seed, int first_pair_index, int min_matches, rgbdfe_se3_result* d_results, const FusedFilter* ff);

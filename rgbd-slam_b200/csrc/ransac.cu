@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(PREP_THREADS) k_se3_prepare(const MatchPair* _
         RngState* s = pair_rng + pair; // working copy, continued by the replay when more chunks are needed
         if (lane == 0) {
             if (per_pair_rng)
-                rng_seed_state(*s, seed + (unsigned)(first_pair_index + (int)blockIdx.x), s_rng);
+                rng_seed_state(*s, seed + (unsigned)(first_pair_index + (ff.seed_group > 0 ? ((int)blockIdx.x / ff.seed_group) * ff.seed_stride + (int)blockIdx.x % ff.seed_group : (int)blockIdx.x)), s_rng);
             else
                 *s = *ctx_rng;
         }
@@ -955,7 +955,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     }
     {
         ProfScope prof(c, KID_SE3_PREPARE);
-        FusedFilter f = { 0, 0.0f, 0 };
+        FusedFilter f = { 0, 0.0f, 0, 0, 0 };
         if (ff)
             f = *ff;
         k_se3_prepare<<<npairs, PREP_THREADS, prep_smem, c->stream>>>(d_pairs, slot0, f, c->d_partial, c->d_matches, c->d_sorted, c->d_P1, c->d_P2, c->d_w, cap, c->d_nmatch,

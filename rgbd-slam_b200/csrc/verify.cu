@@ -22,6 +22,7 @@
 using namespace rgbdfe;
 
 #define VERIFY_SLOTS 4
+#define VERIFY_GROUP_PAIRS 4096 // pairs per pass when several query frames are verified in one call
 
 namespace {
 
@@ -104,15 +105,21 @@ const NcclApi* nccl_api(std::string* why)
 }
 
 // Matcher(ratio).match(KF_k, cur): query side = keyframe k of the block, train side = the current (query) frame
-// (PoseGraph.cpp:139-141).  Also writes the two device counts the pairs point at.
-__global__ void k_build_verify_pairs(MatchPair* __restrict__ dst, int np, const uint8_t* kf_desc, const rgbdfe_point3f* kf_xyz, int n_feat,
-    const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, int* counts)
+// (PoseGraph.cpp:139-141).  Pair p of a group of query frames is (query p / block_max, keyframe p % block_max); the
+// pairs past the end of a short block are empty (both counts 0).  Also writes the device counts the pairs point at.
+__global__ void k_build_verify_pairs(MatchPair* __restrict__ dst, int np, int block_max, int n_block, const uint8_t* kf_desc,
+    const rgbdfe_point3f* kf_xyz, int n_feat, const uint8_t* q_desc, const rgbdfe_point3f* q_xyz, int nq, int* counts)
 {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k == 0)
-        counts[0] = n_feat, counts[1] = nq;
-    if (k < np)
-        dst[k] = MatchPair { kf_desc + (size_t)k * n_feat * 32, q_desc, counts, counts + 1, nullptr, kf_xyz + (size_t)k * n_feat, q_xyz, nullptr };
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p == 0)
+        counts[0] = n_feat, counts[1] = nq, counts[2] = 0;
+    if (p >= np)
+        return;
+    const int q = p / block_max, k = p % block_max;
+    const bool real = k < n_block;
+    const int kk = real ? k : 0;
+    dst[p] = MatchPair { kf_desc + (size_t)kk * n_feat * 32, q_desc + (size_t)q * nq * 32, real ? counts : counts + 2, real ? counts + 1 : counts + 2, nullptr,
+        kf_xyz + (size_t)kk * n_feat, q_xyz + (size_t)q * nq, nullptr };
 }
 
 // The depth-covariance latch (SolverSE3.cpp:282-287) must be set before a batch: the reference latches it from the
@@ -133,19 +140,21 @@ int require_latch(rgbdfe_ctx* c)
     return RGBDFE_OK;
 }
 
-// One query against every keyframe of the block; results d_res[0 .. n_kf).  Asynchronous on the context stream.
-int verify_core(rgbdfe_ctx* c, const rgbdfe_kfdb* db, const uint8_t* dq_desc, const rgbdfe_point3f* dq_xyz, int nq, const rgbdfe_verify_params& vp,
-    unsigned seed, int first_pair_index, rgbdfe_se3_result* d_res)
+// n_q query frames against every keyframe of the block as ONE batch of n_q * block_max pairs; results
+// d_res[q * block_max + k].  Pair (q, k) seeds srand(seed + q * seed_stride + first_pair_index + k).  Asynchronous.
+int verify_core(rgbdfe_ctx* c, const rgbdfe_kfdb* db, const uint8_t* dq_desc, const rgbdfe_point3f* dq_xyz, int nq, int n_q, int block_max,
+    const rgbdfe_verify_params& vp, unsigned seed, int first_pair_index, int seed_stride, rgbdfe_se3_result* d_res)
 {
-    const int np = db->n_kf;
-    k_build_verify_pairs<<<(np + 255) / 256, 256, 0, c->stream>>>(c->d_pairs, np, db->desc, db->xyz, db->n_feat, dq_desc, dq_xyz, nq, c->d_const_n);
+    const int np = n_q * block_max;
+    k_build_verify_pairs<<<(np + 255) / 256, 256, 0, c->stream>>>(c->d_pairs, np, block_max, db->n_kf, db->desc, db->xyz, db->n_feat, dq_desc, dq_xyz, nq,
+        c->d_const_n);
     c->launches++;
     const int splits = knn_splits_for(c, np);
     int rc = launch_knn(c, c->d_pairs, 0, np, db->n_feat, splits);
     if (rc != RGBDFE_OK)
         return rc;
     const Se3Params prm = api_make_params(c, vp.iterations, vp.min_inlier_th, vp.max_mahal, vp.sample_size);
-    const FusedFilter ff = { splits, vp.ratio, 1 }; // K8 runs inside k_se3_prepare
+    const FusedFilter ff = { splits, vp.ratio, 1, n_q > 1 ? block_max : 0, seed_stride }; // K8 runs inside k_se3_prepare
     return launch_ransac_se3(c, c->d_pairs, 0, np, prm, 0, 1, seed, first_pair_index, vp.min_matches, d_res, &ff);
 }
 
@@ -324,7 +333,7 @@ int rgbdfe_verify_batch(rgbdfe_ctx* c, rgbdfe_kfdb* db, const uint8_t* q_desc, c
         d_res = sl.d_block;
     }
     const rgbdfe_verify_params vp = { ratio, min_matches, iterations, min_inlier_th, max_mahal, sample_size, seed };
-    if ((rc = verify_core(c, db, dq_desc, dq_xyz, nq, vp, seed, first_pair_index, d_res)) != RGBDFE_OK)
+    if ((rc = verify_core(c, db, dq_desc, dq_xyz, nq, 1, np, vp, seed, first_pair_index, 0, d_res)) != RGBDFE_OK)
         return rc;
     if (results) {
         CUDA_TRY(c, cudaMemcpyAsync(results, d_res, (size_t)np * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost, c->stream));
@@ -441,7 +450,8 @@ int rgbdfe_verify_sharded_enqueue(rgbdfe_ctx* c, rgbdfe_kfdb* db, void* nccl_com
     const int block_max = (n_kf_total + n_ranks - 1) / n_ranks;
     const size_t block_records = (size_t)n_queries * block_max, all_records = block_records * n_ranks;
     const bool fresh = block_records > sl.cap_block || all_records > sl.cap_all;
-    if ((rc = api_ensure_pairs(c, db->n_kf)) != RGBDFE_OK || (rc = ensure_slot(c, sl, block_records, all_records)) != RGBDFE_OK)
+    const int group = std::max(1, std::min(n_queries, VERIFY_GROUP_PAIRS / block_max));
+    if ((rc = api_ensure_pairs(c, group * block_max)) != RGBDFE_OK || (rc = ensure_slot(c, sl, block_records, all_records)) != RGBDFE_OK)
         return rc;
     cudaStream_t s = c->stream, cs = vs->comm_stream;
     if (sl.used)
@@ -452,10 +462,13 @@ int rgbdfe_verify_sharded_enqueue(rgbdfe_ctx* c, rgbdfe_kfdb* db, void* nccl_com
     const rgbdfe_point3f* dq_xyz;
     if ((rc = stage_queries(c, vs, q_desc, q_xyz, (size_t)n_queries * nq, &dq_desc, &dq_xyz)) != RGBDFE_OK)
         return rc;
-    for (int q = 0; q < n_queries; q++) {
-        // pair (q, k): srand(seed + q * n_kf_total + global keyframe index) -- independent of the sharding
-        const unsigned seed_q = vp->seed + (unsigned)q * (unsigned)n_kf_total;
-        if ((rc = verify_core(c, db, dq_desc + (size_t)q * nq * 32, dq_xyz + (size_t)q * nq, nq, *vp, seed_q, lo, sl.d_block + (size_t)q * block_max))
+    // pair (q, k): srand(seed + q * n_kf_total + global keyframe index) -- independent of the sharding.
+    // Queries go through in groups of about VERIFY_GROUP_PAIRS pairs: one pair table / kNN / prepare / hypotheses pass per group.
+    for (int q0 = 0; q0 < n_queries; q0 += group) {
+        const int g = std::min(group, n_queries - q0);
+        const unsigned seed_q = vp->seed + (unsigned)q0 * (unsigned)n_kf_total;
+        if ((rc = verify_core(c, db, dq_desc + (size_t)q0 * nq * 32, dq_xyz + (size_t)q0 * nq, nq, g, block_max, *vp, seed_q, lo, n_kf_total,
+                 sl.d_block + (size_t)q0 * block_max))
             != RGBDFE_OK)
             return rc;
     }
