@@ -273,3 +273,24 @@ extern "C" int orc_track_sequence(int nframes, const uint8_t* const* gray, const
     }
     return tracked;
 }
+
+// ---------------- numeric pins (tests/test_numeric_pins.py): the third-party restatements, batch form ----------------
+extern "C" {
+// JacobiSVD<Matrix3f> restatement on n row-major 3x3 matrices.
+void orc_jacobi_svd3_batch(int n, const float* A, float* U, float* S, float* V)
+{
+    for (int i = 0; i < n; i++)
+        jacobi_svd3(A + 9 * i, U + 9 * i, S + 3 * i, V + 9 * i);
+}
+// errorFunction2 restatement with the depth covariance pinned to `cov`; out[i] = squared Mahalanobis distance of
+// pair i under T (row-major 4x4 double), full[i] = 1 when the LLT solve ran (0: NaN gate or the error shortcut).
+void orc_mahal2_batch(int n, const Point3f* a, const Point3f* b, const double* T16, double cov, double* out, int* full)
+{
+    for (int i = 0; i < n; i++) {
+        DepthCovLatch l;
+        l.latched = 1;
+        l.cov = cov;
+        out[i] = mahal2(a[i], b[i], T16, l, full + i);
+    }
+}
+}

@@ -9,8 +9,9 @@
 //     CMakeLists.txt:37; restated from Eigen 3.3.7: two-sided Jacobi, sweep
 //     order p=1..2,q<p, threshold max(FLT_MIN, 2*eps*maxDiag), unblocked
 //     lower Cholesky + two triangular solves).
-// PARITY UNPINNED for those two: the reference has no tests or vectors and
-// neither library is installed here, so oracle==library cannot be checked.
+// PARITY UNPINNED bit-for-bit for those two: the reference has no tests or vectors
+// and neither library is installed here.  Their VALUES are pinned against numpy
+// float64 / LAPACK (tests/test_numeric_pins.py: SVD 1e-5, fit 1e-4, LLT 1e-10).
 // Arithmetic contract (what the CUDA kernels must reproduce bit-for-bit):
 //   FP32 for the fit, FP64 for scoring, NO fused multiply-add anywhere,
 //   3-term sums associate as a + (b + c) (Eigen's unrolled redux tree),

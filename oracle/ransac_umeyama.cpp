@@ -4,7 +4,8 @@
 // executable in the reference (the others dereference a null camera or read an
 // uninitialised covariance), so only those are restated.  Eigen::umeyama
 // (Eigen unpinned; restated from Eigen 3.3.7 Geometry/Umeyama.h, no scaling)
-// -> PARITY UNPINNED.  Arithmetic contract: FP32, no FMA, sums over the n
+// -> PARITY UNPINNED bit-for-bit; values pinned against numpy Kabsch to 1e-4
+// (tests/test_numeric_pins.py).  Arithmetic contract: FP32, no FMA, sums over the n
 // correspondences and over 3-term products run left to right.
 #include "oracle.h"
 
