@@ -228,12 +228,33 @@ void orc_ransac_umeyama(const Point3f* p1, const Point3f* p2, const DMatch* m, i
 void orc_umeyama3(const float* src, const float* dst, int n, float* T) { umeyama3(src, dst, n, T); }
 }
 
+namespace orc {
+thread_local double g_stage_s[ST_COUNT];
+double StageTimer::now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+}
+
 // ---------------- timed CPU baseline: the whole tracked-frame path ----------------
 // Frame ctor hot part (Core/Frame.cpp:51,91-117, no lens distortion) + Tracking::visualOdometry
 // core (System/Tracking.cpp:125-130) over a sequence, single thread.  Returns frames tracked.
+// stage_s (may be NULL): ST_COUNT seconds per stage of THIS call; iters_out (may be NULL): executed RANSAC iterations per pair.
+extern "C" int orc_track_sequence2(int nframes, const uint8_t* const* gray, const float* const* depth, int w, int h, float fx, float fy, float cx,
+    float cy, int nfeatures, float ratio, int iters, unsigned min_inl, float max_mahal, unsigned sample, unsigned seed, int* inliers_out,
+    int* iters_out, double* stage_s, long long* se3_stats);
 extern "C" int orc_track_sequence(int nframes, const uint8_t* const* gray, const float* const* depth, int w, int h, float fx, float fy, float cx,
     float cy, int nfeatures, float ratio, int iters, unsigned min_inl, float max_mahal, unsigned sample, unsigned seed, int* inliers_out)
 {
+    return orc_track_sequence2(nframes, gray, depth, w, h, fx, fy, cx, cy, nfeatures, ratio, iters, min_inl, max_mahal, sample, seed, inliers_out,
+        nullptr, nullptr, nullptr);
+}
+extern "C" int orc_track_sequence2(int nframes, const uint8_t* const* gray, const float* const* depth, int w, int h, float fx, float fy, float cx,
+    float cy, int nfeatures, float ratio, int iters, unsigned min_inl, float max_mahal, unsigned sample, unsigned seed, int* inliers_out,
+    int* iters_out, double* stage_s, long long* se3_stats)
+{
+    // se3_stats (may be NULL): totals over the call of {E_s, E_f, A, V, rounds, pairs}: shortcut / full evaluations of
+    // errorFunction2, TFC adds, SVDs, refinement rounds (the operation counts of SURVEY 8d's RANSAC flop model)
+    long long tot[6] = { 0, 0, 0, 0, 0, 0 };
+    for (int i = 0; i < ST_COUNT; i++)
+        g_stage_s[i] = 0.0;
     OrbExtractor orb(nfeatures, 1.2f, 8, 20, 7);
     GlibcRand rng;
     rng.seed(seed);
@@ -261,16 +282,29 @@ extern "C" int orc_track_sequence(int nframes, const uint8_t* const* gray, const
             if (m.size() >= min_inl)
                 for (const DMatch& mm : m)
                     co[mm.trainIdx] = 1;
-            ransac_se3(pp.data(), cp.data(), m, prm, rng, latch, r, nullptr);
+            {
+                StageTimer t(ST_RANSAC);
+                Se3Stats st = {};
+                ransac_se3(pp.data(), cp.data(), m, prm, rng, latch, r, &st);
+                tot[0] += st.es, tot[1] += st.ef, tot[2] += st.adds, tot[3] += st.svds, tot[4] += st.rounds, tot[5]++;
+            }
             if (r.ok)
                 for (const DMatch& mm : r.inliers)
                     co[mm.trainIdx] = 0;
             if (inliers_out)
                 inliers_out[f - 1] = (int)r.inliers.size();
+            if (iters_out)
+                iters_out[f - 1] = r.iters_executed;
             tracked++;
         }
         pk.swap(ck), pd.swap(cd), pp.swap(cp), po.swap(co);
     }
+    if (stage_s)
+        for (int i = 0; i < ST_COUNT; i++)
+            stage_s[i] = g_stage_s[i];
+    if (se3_stats)
+        for (int i = 0; i < 6; i++)
+            se3_stats[i] = tot[i];
     return tracked;
 }
 

@@ -20,7 +20,11 @@ int matcher_match(const uint8_t* qdesc, int nq, const uint8_t* tdesc, int nt, co
     if (nq <= 0 || nt < 2)
         return 0;
     std::vector<int> idx((size_t)nq * 2), dist((size_t)nq * 2);
-    knn2_hamming(qdesc, nq, tdesc, nt, idx.data(), dist.data());
+    {
+        StageTimer t(ST_KNN);
+        knn2_hamming(qdesc, nq, tdesc, nt, idx.data(), dist.data());
+    }
+    StageTimer t(ST_FILTER);
     std::set<int> used;
     for (int i = 0; i < nq; i++) {
         float d1 = (float)dist[i * 2], d2 = (float)dist[i * 2 + 1];

@@ -26,6 +26,16 @@ struct Point3f {
 };
 
 // ---- cvprim.cpp ----
+// per-thread stage timers of the CPU baseline (bench.py): seconds spent per stage since the last reset
+enum { ST_PYRAMID = 0, ST_FAST, ST_QUADTREE, ST_ANGLE, ST_BLUR, ST_DESCRIBE, ST_KNN, ST_FILTER, ST_RANSAC, ST_COUNT };
+extern thread_local double g_stage_s[ST_COUNT];
+struct StageTimer {
+    int id;
+    double t0;
+    static double now();
+    explicit StageTimer(int i) : id(i), t0(now()) {}
+    ~StageTimer() { g_stage_s[id] += now() - t0; }
+};
 int cv_round(float v);
 int cv_round_d(double v);
 int cv_floor(float v);

@@ -292,6 +292,7 @@ void OrbExtractor::compute_keypoints()
         const int hCell = (int)ceilf(height / nRows);
 
         std::vector<int> buf(3 * 64 * 64);
+        StageTimer* t_fast = new StageTimer(ST_FAST);
         for (int i = 0; i < nRows; i++) {
             const float iniY = (float)(minBorderY + i * hCell);
             float maxY = iniY + hCell + 6;
@@ -328,6 +329,8 @@ void OrbExtractor::compute_keypoints()
             }
         }
 
+        delete t_fast;
+        StageTimer t_qt(ST_QUADTREE);
         L.keypoints = distribute_quadtree(cand, minBorderX, maxBorderX, minBorderY, maxBorderY, mnFeaturesPerLevel[level]);
         const int scaledPatchSize = (int)(PATCH_SIZE * mvScaleFactor[level]);
         for (KeyPoint& kp : L.keypoints) {
@@ -337,6 +340,7 @@ void OrbExtractor::compute_keypoints()
             kp.size = (float)scaledPatchSize;
         }
     }
+    StageTimer t_ang(ST_ANGLE);
     for (int level = 0; level < nlevels; ++level)
         for (KeyPoint& kp : levels[level].keypoints)
             kp.angle = ic_angle(levels[level], kp.x, kp.y);
@@ -367,7 +371,10 @@ void OrbExtractor::extract(const uint8_t* img, int w, int h, int stride, std::ve
     desc.clear();
     if (!img || w <= 0 || h <= 0)
         return;
-    compute_pyramid(img, w, h, stride);
+    {
+        StageTimer t(ST_PYRAMID);
+        compute_pyramid(img, w, h, stride);
+    }
     compute_keypoints();
 
     int total = 0;
@@ -383,7 +390,11 @@ void OrbExtractor::extract(const uint8_t* img, int w, int h, int stride, std::ve
             continue;
         // clone() of the un-padded ROI, then GaussianBlur with REFLECT_101
         L.blurred.resize((size_t)L.w * L.h);
-        gauss7_u8(L.image(), L.w, L.h, L.stride, L.blurred.data(), L.w);
+        {
+            StageTimer t(ST_BLUR);
+            gauss7_u8(L.image(), L.w, L.h, L.stride, L.blurred.data(), L.w);
+        }
+        StageTimer t(ST_DESCRIBE);
         for (int i = 0; i < n; i++)
             describe(L.blurred.data(), L.w, L.keypoints[i], desc.data() + (size_t)(offset + i) * 32);
         offset += n;
