@@ -360,6 +360,26 @@ def cvorb_leg(rgbdfe, torch, local_rank, gray_d, depth_d, cam, inv_factor, B, nf
     return out
 
 
+def shim_leg(frames, cam, nfeat, n_frames=300):
+    """The drop-in caller's path: ONE camera, blocking calls through the reference's class interfaces (Frame ctor ->
+    Extractor::detectAndCompute, Matcher::match, RansacSE3::compute on host vectors, Tracking.cpp:121-163) in the C++
+    caller tests/cpp/host_track.cpp, timed per class call with the host clock."""
+    exe = os.path.join(ROOT, "rgbd-slam_b200", "lib", "host_track")
+    with tempfile.TemporaryDirectory() as td:
+        inp, outp = os.path.join(td, "in.bin"), os.path.join(td, "out.json")
+        sub = frames[:24]
+        with open(inp, "wb") as f:
+            np.array([len(sub), W, H, nfeat], np.int32).tofile(f)
+            np.array([cam["fx"], cam["fy"], cam["cx"], cam["cy"]], np.float32).tofile(f)
+            for fr in sub:
+                np.ascontiguousarray(fr[0], np.uint8).tofile(f)
+                np.ascontiguousarray(fr[1], np.float32).tofile(f)
+        subprocess.check_call([exe, inp, outp, "42", "orb2", "bench", str(n_frames)], stdout=sys.stderr)
+        r = json.load(open(outp))
+    r["what"] = "tests/cpp/host_track.cpp bench mode: Frame(gray, depth, extractor) + Matcher(0.9).match + RansacSE3(200,10,3,4).compute per frame, blocking, host vectors in and out"
+    return r
+
+
 def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     """BASELINE configs[3] and [4] through the C ABI (rgbdfe_verify_sharded_enqueue / _collect, NCCL made by
     rgbdfe_nccl_comm_create): a FIXED job -- 1 query vs `--verify-kf` (4096) keyframes of 1000 features, the keyframes
@@ -552,7 +572,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
-    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify"],
+    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify", "shim"],
                     help="diagnostic: time only the extraction half or only the match/RANSAC chains (not a bench value)")
     ap.add_argument("--verify-kf", type=int, default=4096, help="keyframes of the fixed loop-closure verification job (BASELINE configs[3]), sharded over the GPUs")
     args = ap.parse_args()
@@ -598,6 +618,9 @@ def main():
 
     B, F = args.batch, args.frames
     cam, frames = make_sequence(F)
+    if args.mode == "shim":  # diagnostic: the class-shim leg alone
+        print(json.dumps({"class_shim_path": {"feats_2000": shim_leg(frames, cam, NFEAT), "feats_1000": shim_leg(frames, cam, 1000)}}))
+        return
     gray_h = torch.from_numpy(np.stack([f[0] for f in frames])).pin_memory()
     depth_h = torch.from_numpy(np.stack([f[2] for f in frames])).pin_memory()  # raw 16-bit depth, as read from the PNG
     inv_factor = float(np.float32(1.0) / np.float32(DEPTH_FACTOR))
@@ -896,6 +919,14 @@ def main():
     except Exception as ex:  # the headline metric does not depend on this leg
         verify = {"error": str(ex)[:300]}
 
+    # ---- the class-shim path (what a drop-in user of the reference's classes gets): one camera, blocking calls ----
+    shim = None
+    if rank == 0:
+        try:
+            shim = {"feats_2000": shim_leg(frames, cam, NFEAT), "feats_1000": shim_leg(frames, cam, 1000)}
+        except Exception as ex:
+            shim = {"error": str(ex)[:200]}
+
     cpu = parity = None
     if rank == 0 and not args.no_cpu:
         cores = len(os.sched_getaffinity(0))
@@ -966,6 +997,8 @@ def main():
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"])),
                        "parity_checked": (parity or {}).get("parity_checked"),
+                       "class_shim_frames_per_s_2000_feats": ((shim or {}).get("feats_2000") or {}).get("frames_per_s"),
+                       "class_shim_frames_per_s_1000_feats": ((shim or {}).get("feats_1000") or {}).get("frames_per_s"),
                        # the sharded leg (BASELINE configs[3] / [4]); details under the top-level key "verify"
                        "verify_pairs_per_s": (verify or {}).get("value"), "verify_keyframes_total": (verify or {}).get("keyframes_total"),
                        "verify_ms_per_query": (verify or {}).get("ms_per_query"), "verify_strong_efficiency": (verify or {}).get("strong_efficiency"),
@@ -977,7 +1010,7 @@ def main():
                     "d2h_bytes_per_step": S * B * 84,
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "class_shim_path": shim, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
         }))
     for q in reversed(seqs):  # contexts that share a stream close before its owner
         q.close()

@@ -291,6 +291,18 @@ int rgbdfe_frames_projection_match(rgbdfe_ctx* ctx, rgbdfe_frame* const* f1, rgb
 /* Diagnostic: rounds the ordered-claim fixpoint of the last projection call took per pair (1 + the longest chain of
  * keypoints that lost their first choice to an earlier one). */
 int rgbdfe_projection_rounds(rgbdfe_ctx* ctx, int* rounds, int npairs);
+/* Resident host-side frames for the class shims: Matcher::match(ref, cur) and RansacSE3::compute(F1, F2) are called on
+ * the same two Frames one after the other (Tracking.cpp:125-130) and `cur` becomes `ref` of the next call, so a caller
+ * that keeps a device copy per Frame uploads every descriptor / 3-D point set once instead of three times.
+ * frame_upload: descriptors (n x 32 B) + mvKeys3Dc (n x 12 B) into a frame made by rgbdfe_frame_create; asynchronous.
+ * frames_match = rgbdfe_match_knn2 and frames_ransac_se3 = rgbdfe_ransac_se3 on such frames (nq / nt / n1 / n2 are the
+ * counts uploaded); q_outlier (may be NULL) are F1's CURRENT mvbOutlier flags, uploaded on every call because the
+ * host changes them (Frame::setOutlier / setInlier). */
+int rgbdfe_frame_upload(rgbdfe_ctx* ctx, rgbdfe_frame* frame, const uint8_t* desc, const rgbdfe_point3f* xyz, int n);
+int rgbdfe_frames_match(rgbdfe_ctx* ctx, rgbdfe_frame* ref, rgbdfe_frame* cur, int nq, int nt, const uint8_t* q_outlier, float ratio,
+    int discard_outliers, rgbdfe_dmatch* out, int cap, int* n);
+int rgbdfe_frames_ransac_se3(rgbdfe_ctx* ctx, rgbdfe_frame* f1, rgbdfe_frame* f2, int n1, int n2, const rgbdfe_dmatch* matches, int nm, int iterations,
+    unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result, rgbdfe_dmatch* inliers, int cap);
 /* Copy a frame's data back (any pointer may be NULL). */
 int rgbdfe_frame_download(rgbdfe_ctx* ctx, rgbdfe_frame* frame, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
     uint8_t* outlier, int cap, int* n);
@@ -308,9 +320,20 @@ int rgbdfe_track(rgbdfe_ctx* ctx, rgbdfe_frame* ref, rgbdfe_frame* cur, float ra
  * sequential part.  count <= 65.  Asynchronous. */
 int rgbdfe_track_sequence(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, float ratio, int discard_outliers, int iterations,
     unsigned min_inlier_th, float max_mahal, unsigned sample_size, int update_f2, int first_result_slot);
-/* Synchronise and copy results [first, first+count) of the ring to the host.
- * inlier_trainidx (may be NULL) is count x cap ints. */
+/* Synchronise and copy results [first, first+count) of the ring to the host. */
 int rgbdfe_track_results(rgbdfe_ctx* ctx, int first, int count, rgbdfe_se3_result* results);
+/* The same plus RansacSE3::mvInliers (Solver/SolverSE3.h:55) of every pair: the slots must be those of the LAST
+ * rgbdfe_track / rgbdfe_track_sequence call of this context (the inlier sets live in its pair workspace).  The
+ * DMatch records of pair p are inliers[offsets[p] .. offsets[p + 1]) in the reference's order (offsets has count + 1
+ * entries); RGBDFE_E_CAPACITY when the total exceeds inlier_cap.  count <= 65. */
+int rgbdfe_track_results_inliers(rgbdfe_ctx* ctx, int first, int count, rgbdfe_se3_result* results, rgbdfe_dmatch* inliers, int inlier_cap,
+    int* offsets);
+/* What Frame keeps on the host after its constructor (mvKeys, mDescriptors, mvKeys3Dc) for count device-resident frames,
+ * enqueued on the context stream without synchronising: row i of every output is frame i, `cap` entries wide (whole
+ * rows travel, n[i] says how many are valid); pinned host buffers make the copies asynchronous.  Any of kps / desc /
+ * xyz may be NULL.  The buffers are complete after rgbdfe_sync(). */
+int rgbdfe_frames_download_async(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
+    int cap, int* n);
 
 /* ---- batched loop-pair verification (PoseGraph.cpp:135-154,260-284) ---- */
 /* A keyframe shard: n_kf keyframes x n_feat features each, resident on the

@@ -340,6 +340,7 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
         cudaEventDestroy(c->bulk_evt);
     if (c->bulk_stream)
         cudaStreamDestroy(c->bulk_stream);
+    cudaFree(c->d_packed), cudaFreeHost(c->h_packed);
     cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     if (c->owns_stream)
@@ -978,6 +979,89 @@ int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, 
     return cnt > cap ? RGBDFE_E_CAPACITY : RGBDFE_OK;
 }
 
+int rgbdfe_frames_download_async(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz, int cap,
+    int* n)
+{
+    if (!c || !frames || count < 0 || cap < 1 || !n)
+        return RGBDFE_E_ARG;
+    cudaSetDevice(c->device);
+    cudaStream_t s = c->stream;
+    for (int i = 0; i < count; i++) {
+        const rgbdfe_frame* f = frames[i];
+        if (!f)
+            return RGBDFE_E_ARG;
+        const size_t m = (size_t)std::min(cap, f->cap); // the count is on the device: whole-capacity rows travel
+        CUDA_TRY(c, cudaMemcpyAsync(n + i, f->n, sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (kps)
+            CUDA_TRY(c, cudaMemcpyAsync(kps + (size_t)i * cap, f->kps, m * sizeof(rgbdfe_keypoint), cudaMemcpyDeviceToHost, s));
+        if (desc)
+            CUDA_TRY(c, cudaMemcpyAsync(desc + (size_t)i * cap * 32, f->desc, m * 32, cudaMemcpyDeviceToHost, s));
+        if (xyz)
+            CUDA_TRY(c, cudaMemcpyAsync(xyz + (size_t)i * cap, f->xyz, m * sizeof(rgbdfe_point3f), cudaMemcpyDeviceToHost, s));
+    }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_frame_upload(rgbdfe_ctx* c, rgbdfe_frame* f, const uint8_t* desc, const rgbdfe_point3f* xyz, int n)
+{
+    if (!c || !f || n < 0 || (n > 0 && (!desc || !xyz)))
+        return RGBDFE_E_ARG;
+    if (n > f->cap) {
+        c->set_error("frame_upload: descriptor count exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    cudaSetDevice(c->device);
+    cudaStream_t s = c->stream;
+    if (n > 0) {
+        CUDA_TRY(c, cudaMemcpyAsync(f->desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(c, cudaMemcpyAsync(f->xyz, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, s));
+    }
+    k_set_int<<<1, 1, 0, s>>>(f->n, n);
+    c->launches++;
+    CUDA_TRY(c, cudaGetLastError());
+    return RGBDFE_OK;
+}
+
+int rgbdfe_frames_match(rgbdfe_ctx* c, rgbdfe_frame* Q, rgbdfe_frame* T, int nq, int nt, const uint8_t* q_outlier, float ratio, int discard_outliers,
+    rgbdfe_dmatch* out, int cap, int* n)
+{
+    if (!c || !Q || !T || !n || nq < 0 || nt < 0 || nq > Q->cap || nt > T->cap)
+        return RGBDFE_E_ARG;
+    *n = 0;
+    if (nq == 0 || nt == 0)
+        return RGBDFE_OK;
+    cudaSetDevice(c->device);
+    int rc = ensure_pairs(c, 1);
+    if (rc != RGBDFE_OK)
+        return rc;
+    cudaStream_t s = c->stream;
+    if (q_outlier)
+        CUDA_TRY(c, cudaMemcpyAsync(Q->outlier, q_outlier, (size_t)nq, cudaMemcpyHostToDevice, s));
+    MatchPair p = { Q->desc, T->desc, Q->n, T->n, q_outlier ? Q->outlier : nullptr, Q->xyz, T->xyz, nullptr };
+    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
+        return rc;
+    if ((rc = launch_match(c, c->d_pairs, 1, nq, nt, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
+        return rc;
+    // count and matches leave together through the pinned result staging: one synchronisation
+    int* h_cnt = reinterpret_cast<int*>(c->h_results);
+    rgbdfe_dmatch* h_m = reinterpret_cast<rgbdfe_dmatch*>(h_cnt + 4);
+    const int room = (int)std::min<size_t>((size_t)std::min(cap, nq), (sizeof(rgbdfe_se3_result) * c->result_cap - 16) / sizeof(rgbdfe_dmatch));
+    CUDA_TRY(c, cudaMemcpyAsync(h_cnt, c->d_nmatch, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (room > 0 && out)
+        CUDA_TRY(c, cudaMemcpyAsync(h_m, c->d_matches, (size_t)room * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(c, cudaStreamSynchronize(s));
+    const int cnt = *h_cnt;
+    *n = cnt;
+    const int m = std::min(cnt, cap);
+    if (m > 0 && out) {
+        if (m <= room)
+            memcpy(out, h_m, (size_t)m * sizeof(rgbdfe_dmatch));
+        else
+            CUDA_TRY(c, cudaMemcpy(out, c->d_matches, (size_t)m * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
+    }
+    return cnt > cap ? RGBDFE_E_CAPACITY : RGBDFE_OK;
+}
+
 int rgbdfe_match_knn2(rgbdfe_ctx* c, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt, const uint8_t* q_outlier,
     const rgbdfe_point3f* q_xyz, const rgbdfe_point3f* t_xyz, float ratio, int discard_outliers, rgbdfe_dmatch* out, int cap, int* n)
 {
@@ -992,34 +1076,12 @@ int rgbdfe_match_knn2(rgbdfe_ctx* c, const uint8_t* q_desc, int nq, const uint8_
         return RGBDFE_OK;
     if (!q_desc || !t_desc || !q_xyz || !t_xyz)
         return RGBDFE_E_ARG;
-    cudaSetDevice(c->device);
-    int rc = ensure_pairs(c, 1);
+    int rc = rgbdfe_frame_upload(c, c->scratch, q_desc, q_xyz, nq);
+    if (rc == RGBDFE_OK)
+        rc = rgbdfe_frame_upload(c, c->scratch2, t_desc, t_xyz, nt);
     if (rc != RGBDFE_OK)
         return rc;
-    rgbdfe_frame *Q = c->scratch, *T = c->scratch2;
-    cudaStream_t s = c->stream;
-    CUDA_TRY(c, cudaMemcpyAsync(Q->desc, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(T->desc, t_desc, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, q_xyz, (size_t)nq * 12, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(T->xyz, t_xyz, (size_t)nt * 12, cudaMemcpyHostToDevice, s));
-    if (q_outlier)
-        CUDA_TRY(c, cudaMemcpyAsync(Q->outlier, q_outlier, (size_t)nq, cudaMemcpyHostToDevice, s));
-    k_set_int<<<1, 1, 0, s>>>(Q->n, nq);
-    k_set_int<<<1, 1, 0, s>>>(T->n, nt);
-    c->launches += 2;
-    MatchPair p = { Q->desc, T->desc, Q->n, T->n, q_outlier ? Q->outlier : nullptr, Q->xyz, T->xyz, nullptr };
-    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
-        return rc;
-    if ((rc = launch_match(c, c->d_pairs, 1, nq, nt, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
-        return rc;
-    CUDA_TRY(c, cudaStreamSynchronize(s));
-    int cnt = 0;
-    CUDA_TRY(c, cudaMemcpy(&cnt, c->d_nmatch, sizeof(int), cudaMemcpyDeviceToHost));
-    *n = cnt;
-    const int m = std::min(cnt, cap);
-    if (m > 0 && out)
-        CUDA_TRY(c, cudaMemcpy(out, c->d_matches, (size_t)m * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
-    return cnt > cap ? RGBDFE_E_CAPACITY : RGBDFE_OK;
+    return rgbdfe_frames_match(c, c->scratch, c->scratch2, nq, nt, q_outlier, ratio, discard_outliers, out, cap, n);
 }
 
 int rgbdfe_rng_seed(rgbdfe_ctx* c, unsigned seed)
@@ -1121,10 +1183,10 @@ int rgbdfe_depth_cov_set(rgbdfe_ctx* c, int latched, double cov)
 
 extern "C" {
 
-int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches, int nm,
-    int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result, rgbdfe_dmatch* inliers, int cap)
+int rgbdfe_frames_ransac_se3(rgbdfe_ctx* c, rgbdfe_frame* F1, rgbdfe_frame* F2, int n1, int n2, const rgbdfe_dmatch* matches, int nm, int iterations,
+    unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result, rgbdfe_dmatch* inliers, int cap)
 {
-    if (!c || !result || nm < 0 || n1 < 0 || n2 < 0 || (nm > 0 && (!p1 || !p2 || !matches)))
+    if (!c || !F1 || !F2 || !result || nm < 0 || n1 < 0 || n2 < 0 || (nm > 0 && !matches))
         return RGBDFE_E_ARG;
     if (n1 > c->kp_cap || n2 > c->kp_cap || nm > c->kp_cap) {
         c->set_error("ransac_se3: input exceeds max_feats + 64");
@@ -1139,35 +1201,66 @@ int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgb
     int rc = ensure_pairs(c, 1);
     if (rc != RGBDFE_OK)
         return rc;
+    cudaStream_t s = c->stream;
+    if (nm > 0)
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_matches, matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyHostToDevice, s));
+    k_set_int<<<1, 1, 0, s>>>(c->d_nmatch, nm);
+    c->launches++;
+    MatchPair p = { nullptr, nullptr, F1->n, F2->n, nullptr, F1->xyz, F2->xyz, nullptr };
+    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
+        return rc;
+    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    if ((rc = launch_ransac_se3(c, c->d_pairs, 0, 1, prm, 0, 0, 0, 0, 0, c->d_results, nullptr)) != RGBDFE_OK)
+        return rc;
+    // result, sorted match list and inlier positions leave together through pinned staging: one synchronisation
+    const size_t stage_bytes = sizeof(rgbdfe_se3_result) * c->result_cap;
+    unsigned char* hb = reinterpret_cast<unsigned char*>(c->h_results);
+    const size_t off_sorted = 128, off_pos = off_sorted + (size_t)nm * sizeof(rgbdfe_dmatch);
+    const bool staged = inliers && nm > 0 && off_pos + (size_t)nm * sizeof(int) <= stage_bytes;
+    CUDA_TRY(c, cudaMemcpyAsync(hb, c->d_results, sizeof(*result), cudaMemcpyDeviceToHost, s));
+    if (staged) {
+        CUDA_TRY(c, cudaMemcpyAsync(hb + off_sorted, c->d_sorted, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(c, cudaMemcpyAsync(hb + off_pos, c->d_inl_pos, (size_t)nm * sizeof(int), cudaMemcpyDeviceToHost, s));
+    }
+    CUDA_TRY(c, cudaStreamSynchronize(s));
+    memcpy(result, hb, sizeof(*result));
+    if (inliers && result->n_inliers > 0) {
+        if (staged) {
+            const rgbdfe_dmatch* sorted = reinterpret_cast<const rgbdfe_dmatch*>(hb + off_sorted);
+            const int* pos = reinterpret_cast<const int*>(hb + off_pos);
+            for (int i = 0; i < result->n_inliers && i < cap; i++)
+                inliers[i] = sorted[pos[i]];
+        } else {
+            std::vector<rgbdfe_dmatch> sorted(nm);
+            std::vector<int> pos(result->n_inliers);
+            CUDA_TRY(c, cudaMemcpy(sorted.data(), c->d_sorted, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
+            CUDA_TRY(c, cudaMemcpy(pos.data(), c->d_inl_pos, (size_t)result->n_inliers * sizeof(int), cudaMemcpyDeviceToHost));
+            for (int i = 0; i < result->n_inliers && i < cap; i++)
+                inliers[i] = sorted[pos[i]];
+        }
+        if (result->n_inliers > cap)
+            return RGBDFE_E_CAPACITY;
+    }
+    return RGBDFE_OK;
+}
+
+int rgbdfe_ransac_se3(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches, int nm,
+    int iterations, unsigned min_inlier_th, float max_mahal, unsigned sample_size, rgbdfe_se3_result* result, rgbdfe_dmatch* inliers, int cap)
+{
+    if (!c || !result || nm < 0 || n1 < 0 || n2 < 0 || (nm > 0 && (!p1 || !p2 || !matches)))
+        return RGBDFE_E_ARG;
+    if (n1 > c->kp_cap || n2 > c->kp_cap || nm > c->kp_cap) {
+        c->set_error("ransac_se3: input exceeds max_feats + 64");
+        return RGBDFE_E_CAPACITY;
+    }
+    cudaSetDevice(c->device);
     rgbdfe_frame *Q = c->scratch, *T = c->scratch2;
     cudaStream_t s = c->stream;
     if (n1 > 0)
         CUDA_TRY(c, cudaMemcpyAsync(Q->xyz, p1, (size_t)n1 * 12, cudaMemcpyHostToDevice, s));
     if (n2 > 0)
         CUDA_TRY(c, cudaMemcpyAsync(T->xyz, p2, (size_t)n2 * 12, cudaMemcpyHostToDevice, s));
-    if (nm > 0)
-        CUDA_TRY(c, cudaMemcpyAsync(c->d_matches, matches, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyHostToDevice, s));
-    k_set_int<<<1, 1, 0, s>>>(c->d_nmatch, nm);
-    c->launches++;
-    MatchPair p = { nullptr, nullptr, Q->n, T->n, nullptr, Q->xyz, T->xyz, nullptr };
-    if ((rc = set_pair(c, 0, p)) != RGBDFE_OK)
-        return rc;
-    Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
-    if ((rc = launch_ransac_se3(c, c->d_pairs, 0, 1, prm, 0, 0, 0, 0, 0, c->d_results, nullptr)) != RGBDFE_OK)
-        return rc;
-    CUDA_TRY(c, cudaStreamSynchronize(s));
-    CUDA_TRY(c, cudaMemcpy(result, c->d_results, sizeof(*result), cudaMemcpyDeviceToHost));
-    if (inliers && result->n_inliers > 0) {
-        std::vector<rgbdfe_dmatch> sorted(nm);
-        std::vector<int> pos(result->n_inliers);
-        CUDA_TRY(c, cudaMemcpy(sorted.data(), c->d_sorted, (size_t)nm * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost));
-        CUDA_TRY(c, cudaMemcpy(pos.data(), c->d_inl_pos, (size_t)result->n_inliers * sizeof(int), cudaMemcpyDeviceToHost));
-        for (int i = 0; i < result->n_inliers && i < cap; i++)
-            inliers[i] = sorted[pos[i]];
-        if (result->n_inliers > cap)
-            return RGBDFE_E_CAPACITY;
-    }
-    return RGBDFE_OK;
+    return rgbdfe_frames_ransac_se3(c, Q, T, n1, n2, matches, nm, iterations, min_inlier_th, max_mahal, sample_size, result, inliers, cap);
 }
 
 int rgbdfe_ransac_umeyama(rgbdfe_ctx* c, const rgbdfe_point3f* p1, int n1, const rgbdfe_point3f* p2, int n2, const rgbdfe_dmatch* matches, int nm,
@@ -1285,6 +1378,7 @@ int rgbdfe_track(rgbdfe_ctx* c, rgbdfe_frame* ref, rgbdfe_frame* cur, float rati
     if ((rc = launch_match(c, c->d_pairs, 1, c->kp_cap, c->kp_cap, ratio, discard_outliers, nullptr)) != RGBDFE_OK)
         return rc;
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
+    c->last_track_slot = result_slot, c->last_track_pairs = 1;
     return launch_ransac_se3(c, c->d_pairs, 0, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + result_slot, nullptr);
 }
 
@@ -1334,6 +1428,7 @@ int rgbdfe_track_sequence(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count,
         return rc;
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
     rgbdfe::FusedFilter ff = { splits, ratio, discard_outliers };
+    c->last_track_slot = first_result_slot, c->last_track_pairs = np;
     for (int p = 0; p < np; p++)
         if ((rc = launch_ransac_se3(c, c->d_pairs, p, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + first_result_slot + p, &ff)) != RGBDFE_OK)
             return rc;
@@ -1355,6 +1450,71 @@ int rgbdfe_track_results(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result*
 }
 
 } // extern "C"
+
+namespace {
+// mvInliers of `count` pairs packed back to back: out[offsets[p] .. offsets[p + 1]) = sorted[pos[i]], offsets from the results
+__global__ void k_pack_inliers(const rgbdfe_se3_result* __restrict__ res, const rgbdfe_dmatch* __restrict__ sorted_all, const int* __restrict__ pos_all,
+    int match_cap, int pair0, rgbdfe_dmatch* __restrict__ out, int* __restrict__ offsets, int count)
+{
+    const int p = blockIdx.x;
+    int off = 0;
+    for (int i = 0; i < p; i++)
+        off += res[i].n_inliers;
+    const int n = res[p].n_inliers;
+    const rgbdfe_dmatch* sorted = sorted_all + (size_t)(pair0 + p) * match_cap;
+    const int* pos = pos_all + (size_t)(pair0 + p) * match_cap;
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+        out[off + i] = sorted[pos[i]];
+    if (threadIdx.x == 0) {
+        offsets[p] = off;
+        if (p == count - 1)
+            offsets[count] = off + n;
+    }
+}
+}
+
+extern "C" int rgbdfe_track_results_inliers(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result* results, rgbdfe_dmatch* inliers, int inlier_cap,
+    int* offsets)
+{
+    if (!c || first < 0 || count < 1 || count > CHAIN_MAX_FRAMES || first + count > c->result_cap || !results || !inliers || !offsets || inlier_cap < 0)
+        return RGBDFE_E_ARG;
+    const int pair0 = first - c->last_track_slot;
+    if (pair0 < 0 || pair0 + count > c->last_track_pairs) {
+        c->set_error("track_results_inliers: the slots must belong to the last rgbdfe_track / rgbdfe_track_sequence call of this context");
+        return RGBDFE_E_STATE;
+    }
+    cudaSetDevice(c->device);
+    const size_t total_cap = (size_t)count * c->kp_cap;
+    if (total_cap > c->packed_cap) {
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_packed), cudaFreeHost(c->h_packed);
+        c->d_packed = nullptr, c->h_packed = nullptr, c->packed_cap = 0;
+        CUDA_TRY(c, dmalloc(&c->d_packed, total_cap + 32)); // + room for the offsets behind the records
+        CUDA_TRY(c, cudaMallocHost((void**)&c->h_packed, (total_cap + 32) * sizeof(rgbdfe_dmatch)));
+        c->packed_cap = total_cap;
+    }
+    cudaStream_t s = c->stream;
+    int* d_off = reinterpret_cast<int*>(c->d_packed + c->packed_cap);
+    int* h_off = reinterpret_cast<int*>(c->h_packed + c->packed_cap);
+    k_pack_inliers<<<count, 256, 0, s>>>(c->d_results + first, c->d_sorted, c->d_inl_pos, c->kp_cap, pair0, c->d_packed, d_off, count);
+    c->launches++;
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_results + first, c->d_results + first, (size_t)count * sizeof(rgbdfe_se3_result), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(c, cudaMemcpyAsync(h_off, d_off, (size_t)(count + 1) * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(c, cudaStreamSynchronize(s));
+    memcpy(results, c->h_results + first, (size_t)count * sizeof(rgbdfe_se3_result));
+    memcpy(offsets, h_off, (size_t)(count + 1) * sizeof(int));
+    const int total = h_off[count];
+    if (total > inlier_cap) {
+        c->set_error("track_results_inliers: " + std::to_string(total) + " inliers exceed inlier_cap");
+        return RGBDFE_E_CAPACITY;
+    }
+    if (total > 0) { // the exact number of records, known only now
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_packed, c->d_packed, (size_t)total * sizeof(rgbdfe_dmatch), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(c, cudaStreamSynchronize(s));
+        memcpy(inliers, c->h_packed, (size_t)total * sizeof(rgbdfe_dmatch));
+    }
+    return RGBDFE_OK;
+}
 
 namespace rgbdfe { // helpers of this file used by verify.cu
 int api_ensure_pairs(rgbdfe_ctx* c, int npairs) { return ensure_pairs(c, npairs); }

@@ -256,6 +256,8 @@ struct rgbdfe_ctx {
     struct CvOrbWorkspace* cvorb = nullptr; // the cv::ORB branch of Extractor (row N3, orb_cv.cu), allocated by rgbdfe_cvorb_configure
     int extractor = 0;                      // RGBDFE_EXTRACTOR_ORB2 / RGBDFE_EXTRACTOR_ORB: which one the extraction entry points run
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
+    int last_track_slot = 0, last_track_pairs = 0; // result slots of the last rgbdfe_track / rgbdfe_track_sequence (pair p -> slot + p)
+    rgbdfe_dmatch* d_packed = nullptr; rgbdfe_dmatch* h_packed = nullptr; size_t packed_cap = 0; // rgbdfe_track_results_inliers staging
     struct VerifyState* verify = nullptr; // sharded verification: comm stream, result slots, query staging (verify.cu)
     bool latch_known = false;       // the host has seen the depth-covariance latch set (batched verification requires it)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)

@@ -42,10 +42,17 @@ int Matcher::match(Frame::Ptr ref, Frame::Ptr cur, vector<cv::DMatch>& vMatches1
     cv::Mat td = cur->mDescriptors.isContinuous() ? cur->mDescriptors : cur->mDescriptors.clone();
     vMatches12.resize(nq);
     int n = 0;
-    const int rc = rgbdfe_match_knn2(rgbdfe_host::ctx(), qd.data, nq, td.data, nt, outl.data(),
-        reinterpret_cast<const rgbdfe_point3f*>(ref->mvKeys3Dc.data()), reinterpret_cast<const rgbdfe_point3f*>(cur->mvKeys3Dc.data()), mfNNratio,
-        discardOutliers ? 1 : 0, reinterpret_cast<rgbdfe_dmatch*>(vMatches12.data()), (int)vMatches12.size(), &n);
-    if (rgbdfe_host::report("rgbdfe_match_knn2", rc) != RGBDFE_OK)
+    // both frames stay resident on the device keyed by content: `cur` of this call is `ref` of the next, and
+    // RansacSE3::compute names the same two frames right after (Tracking.cpp:127-130)
+    rgbdfe_frame* fq = rgbdfe_host::resident(qd.data, ref->mvKeys3Dc.data(), nq);
+    rgbdfe_frame* ft = rgbdfe_host::resident(td.data, cur->mvKeys3Dc.data(), nt);
+    if (!fq || !ft) {
+        vMatches12.clear();
+        return 0;
+    }
+    const int rc = rgbdfe_frames_match(rgbdfe_host::ctx(), fq, ft, nq, nt, outl.data(), mfNNratio, discardOutliers ? 1 : 0,
+        reinterpret_cast<rgbdfe_dmatch*>(vMatches12.data()), (int)vMatches12.size(), &n);
+    if (rgbdfe_host::report("rgbdfe_frames_match", rc) != RGBDFE_OK)
         n = 0; // errors map to "no matches", never to a CPU path
     vMatches12.resize(n);
     for (auto& m : vMatches12)

@@ -48,10 +48,22 @@ bool RansacSE3::compute(Frame::Ptr pF1, Frame::Ptr pF2, const vector<cv::DMatch>
 
     rgbdfe_se3_result res;
     vector<cv::DMatch> inl(m12.size());
-    const int rc = rgbdfe_ransac_se3(rgbdfe_host::ctx(), reinterpret_cast<const rgbdfe_point3f*>(pF1->mvKeys3Dc.data()), (int)pF1->mvKeys3Dc.size(),
-        reinterpret_cast<const rgbdfe_point3f*>(pF2->mvKeys3Dc.data()), (int)pF2->mvKeys3Dc.size(), reinterpret_cast<const rgbdfe_dmatch*>(m12.data()),
-        (int)m12.size(), mIterations, mMinInlierTh, mMaxMahalanobisDistance, mSampleSize, &res, reinterpret_cast<rgbdfe_dmatch*>(inl.data()),
-        (int)inl.size());
+    // the 3-D point sets are normally resident already (Matcher::match just ran on these frames); the key is the content
+    const int n1 = (int)pF1->mvKeys3Dc.size(), n2 = (int)pF2->mvKeys3Dc.size();
+    int rc;
+    rgbdfe_frame *f1 = nullptr, *f2 = nullptr;
+    if (n1 > 0 && n2 > 0 && (int)pF1->mDescriptors.rows == n1 && (int)pF2->mDescriptors.rows == n2 && pF1->mDescriptors.isContinuous()
+        && pF2->mDescriptors.isContinuous()) {
+        f1 = rgbdfe_host::resident(pF1->mDescriptors.data, pF1->mvKeys3Dc.data(), n1);
+        f2 = rgbdfe_host::resident(pF2->mDescriptors.data, pF2->mvKeys3Dc.data(), n2);
+    }
+    if (f1 && f2)
+        rc = rgbdfe_frames_ransac_se3(rgbdfe_host::ctx(), f1, f2, n1, n2, reinterpret_cast<const rgbdfe_dmatch*>(m12.data()), (int)m12.size(), mIterations,
+            mMinInlierTh, mMaxMahalanobisDistance, mSampleSize, &res, reinterpret_cast<rgbdfe_dmatch*>(inl.data()), (int)inl.size());
+    else
+        rc = rgbdfe_ransac_se3(rgbdfe_host::ctx(), reinterpret_cast<const rgbdfe_point3f*>(pF1->mvKeys3Dc.data()), n1,
+            reinterpret_cast<const rgbdfe_point3f*>(pF2->mvKeys3Dc.data()), n2, reinterpret_cast<const rgbdfe_dmatch*>(m12.data()), (int)m12.size(),
+            mIterations, mMinInlierTh, mMaxMahalanobisDistance, mSampleSize, &res, reinterpret_cast<rgbdfe_dmatch*>(inl.data()), (int)inl.size());
     if (rgbdfe_host::report("rgbdfe_ransac_se3", rc) != RGBDFE_OK)
         return false; // no CPU path: a failed call is a failed estimate
 

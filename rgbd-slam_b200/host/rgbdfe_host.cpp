@@ -2,6 +2,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <vector>
 
@@ -13,14 +14,40 @@ namespace {
     bool g_seeded = false;
     unsigned g_seed = 0;
 
+    struct Resident {
+        rgbdfe_frame* f = nullptr;
+        unsigned long long key = 0;
+        int n = -1;
+        unsigned long long stamp = 0;
+    };
     struct Holder {
         rgbdfe_ctx* c = nullptr;
+        Resident res[8];
+        unsigned long long clock = 0;
         ~Holder()
         {
-            if (c)
+            if (c) {
+                for (auto& r : res)
+                    if (r.f)
+                        rgbdfe_frame_destroy(c, r.f);
                 rgbdfe_destroy(c);
+            }
         }
     };
+    unsigned long long hash_words(const void* p, size_t bytes, unsigned long long h)
+    {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        size_t i = 0;
+        for (; i + 8 <= bytes; i += 8) {
+            unsigned long long w;
+            memcpy(&w, b + i, 8);
+            h = (h ^ w) * 0x9E3779B97F4A7C15ULL;
+            h ^= h >> 29;
+        }
+        for (; i < bytes; i++)
+            h = (h ^ b[i]) * 0x100000001B3ULL;
+        return h;
+    }
     thread_local Holder t_holder;
 }
 
@@ -52,6 +79,35 @@ rgbdfe_ctx* ctx()
         t_holder.c = c;
     }
     return t_holder.c;
+}
+
+rgbdfe_frame* resident(const void* desc, const void* xyz, int n)
+{
+    rgbdfe_ctx* c = ctx();
+    Holder& H = t_holder;
+    unsigned long long key = hash_words(desc, (size_t)n * 32, 0xcbf29ce484222325ULL ^ (unsigned long long)n);
+    key = hash_words(xyz, (size_t)n * 12, key);
+    Resident* slot = nullptr;
+    for (auto& r : H.res)
+        if (r.f && r.n == n && r.key == key) {
+            r.stamp = ++H.clock;
+            return r.f;
+        }
+    for (auto& r : H.res) // a free slot, else the least recently used
+        if (!slot || !r.f || (slot->f && r.stamp < slot->stamp)) {
+            slot = &r;
+            if (!r.f)
+                break;
+        }
+    if (!slot->f && report("rgbdfe_frame_create", rgbdfe_frame_create(c, &slot->f)) != RGBDFE_OK)
+        return nullptr;
+    if (report("rgbdfe_frame_upload", rgbdfe_frame_upload(c, slot->f, static_cast<const uint8_t*>(desc), static_cast<const rgbdfe_point3f*>(xyz), n))
+        != RGBDFE_OK) {
+        slot->n = -1;
+        return nullptr;
+    }
+    slot->key = key, slot->n = n, slot->stamp = ++H.clock;
+    return slot->f;
 }
 
 const void*& config_owner()

@@ -21,6 +21,13 @@ rgbdfe_ctx* ctx();
 // Which extractor object last configured the calling thread's context (ORB parameters are context state).
 const void*& config_owner();
 
+// Device-resident copy of a Frame's descriptors (n x 32 B) and mvKeys3Dc (n x 12 B) in the calling thread's context,
+// uploaded on first use.  Matcher::match(ref, cur) and RansacSE3::compute(ref, cur, ...) name the same two Frames and
+// `cur` is the next call's `ref`, so each set goes up once instead of three times.  The key is the CONTENT (a 64-bit
+// hash of both arrays and n), never an address: a Frame freed and reallocated at the same address cannot alias.
+// A small LRU (8 frames); returns nullptr on error (reported).
+rgbdfe_frame* resident(const void* desc, const void* xyz, int n);
+
 // Report `rc` (an RGBDFE_* code) of a failed call on stderr; returns rc.
 int report(const char* where, int rc);
 

@@ -433,6 +433,19 @@ class Context:
         self._chk(lib().rgbdfe_track_results(self.h, first, count, _p(res)))
         return res
 
+    def track_results_inliers(self, first, count):
+        """(results, [mvInliers of every pair]) of the last track / track_sequence call."""
+        res = np.zeros(count, SE3_DTYPE)
+        inl = np.zeros(count * self.kp_cap, DM_DTYPE)
+        off = np.zeros(count + 1, np.int32)
+        self._chk(lib().rgbdfe_track_results_inliers(self.h, first, count, _p(res), _p(inl), len(inl), _p(off)))
+        return res, [inl[off[i]:off[i + 1]].copy() for i in range(count)]
+
+    def frames_download_async(self, frames, kps, desc, xyz, n, cap):
+        """kps/desc/xyz/n: numpy arrays (ideally pinned) of [len(frames)][cap] rows; complete after sync()."""
+        fr = (C.c_void_p * len(frames))(*[f.h for f in frames])
+        self._chk(lib().rgbdfe_frames_download_async(self.h, fr, len(frames), _p(kps), _p(desc), _p(xyz), cap, _p(n)))
+
     # ---- batched verification ----
     def kfdb_create(self, desc, xyz):
         desc = np.ascontiguousarray(desc, np.uint8)

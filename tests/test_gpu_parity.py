@@ -346,12 +346,26 @@ def test_tracking_pipeline_device_resident(oracle, seq_vga, chain):
                 g_r = res[i - 1]
                 assert g_r["n_matches"] == len(m)
                 assert bool(g_r["ok"]) == r["ok"] and g_r["n_inliers"] == len(r["inliers"])
+                if chain is True:  # mvInliers of every pair of the chain (rgbdfe_track_results_inliers), order included
+                    if i == 1:
+                        res2, inl_lists = ctx.track_results_inliers(0, len(frames) - 1)
+                        assert res2.tobytes() == res.tobytes()
+                    assert inl_lists[i - 1].tobytes() == r["inliers"].tobytes()
                 assert g_r["iters_executed"] == r["iters_executed"]
                 assert np.abs(g_r["T21"].reshape(4, 4) - r["T"]).max() <= POSE_TOL
             gk, gd, gp, go = fr[i].download()
             assert (gk == k).all() and (gd == de).all() and (gp == p3).all()
             assert (go == outl).all(), f"outlier flags of frame {i}"
             prev = (k, de, p3, outl)
+        # the batch download (what Frame keeps on the host: mvKeys, mDescriptors, mvKeys3Dc) equals the per-frame one
+        cap, nf = ctx.kp_cap, len(fr)
+        kps, desc = np.zeros((nf, cap), rgbdfe.KP_DTYPE), np.zeros((nf, cap, 32), np.uint8)
+        xyz, n = np.zeros((nf, cap, 3), np.float32), np.zeros(nf, np.int32)
+        ctx.frames_download_async(fr, kps, desc, xyz, n, cap)
+        ctx.sync()
+        for i, f in enumerate(fr):
+            gk, gd, gp, _ = f.download()
+            assert n[i] == len(gk) and (kps[i, : n[i]] == gk).all() and (desc[i, : n[i]] == gd).all() and (xyz[i, : n[i]] == gp).all()
     finally:
         ctx.close()
 

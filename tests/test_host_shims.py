@@ -91,6 +91,11 @@ def test_visual_odometry_through_the_class_shims(oracle, seq_vga, tmp_path):
                 outl[m["trainIdx"]] = 1
             if r["ok"]:
                 outl[r["inliers"]["trainIdx"]] = 0
+            # Matcher::descriptorDistance (row a13): Hamming distance of 32-byte rows, recomputed from the oracle's descriptors
+            dd = rec["ddist"][ti]
+            ham = lambda a, b: float(np.unpackbits(a ^ b).sum())
+            assert int(dd[0]) == i
+            assert [float(x) for x in dd[1:4]] == [ham(prev[1][0], de[0]), ham(prev[1][1], de[-1]), 0.0]
             tr = rec["track"][ti]
             assert int(tr[2]) == len(m) and int(tr[4], 16) == fnv(m)
             assert int(tr[6]) == int(r["ok"]) and int(tr[8]) == len(r["inliers"]) and int(tr[10], 16) == fnv(r["inliers"])
@@ -178,3 +183,21 @@ def test_extractor_orb_orb_pair_through_the_class_shims(oracle, seq_vga, tmp_pat
                 rng.random_int(0, 999)
             ti += 1
         prev = (k, de, p3, outl)
+
+
+@pytest.mark.gpu
+def test_shim_path_timing_mode_runs(seq_vga, tmp_path):
+    """host_track's bench mode (the drop-in caller's blocking loop, timed per class call) produces sane numbers."""
+    import json
+
+    cam, frames = seq_vga
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.json"
+    with open(inp, "wb") as f:
+        np.array([len(frames), 640, 480, 1000], np.int32).tofile(f)
+        np.array([cam["fx"], cam["fy"], cam["cx"], cam["cy"]], np.float32).tofile(f)
+        for g, d in frames:
+            np.ascontiguousarray(g, np.uint8).tofile(f)
+            np.ascontiguousarray(d, np.float32).tofile(f)
+    subprocess.check_call([os.path.join(LIB, "host_track"), str(inp), str(outp), "42", "orb2", "bench", "40"])
+    r = json.load(open(outp))
+    assert r["frames"] == 40 and r["frames_per_s"] > 50 and r["ok_frac"] > 0.9 and r["mean_inliers"] > 100
