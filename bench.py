@@ -664,6 +664,17 @@ def main():
                 next(self.order)
             self.i, self.have_ref, self.n_res = 0, False, 0
             self.inliers, self.ok, self.n, self.iters = [], 0, 0, []
+            # e2e: what the class interface hands back per frame -- keypoints + descriptors (Extractor::detectAndCompute) and
+            # mvInliers (RansacSE3) -- lands in pinned host buffers, one set per frame set
+            cap = self.ctx_x.kp_cap
+            self.h_kps = [torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory().numpy() for _ in range(3)]
+            self.h_desc = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory().numpy() for _ in range(3)]
+            self.h_n = [torch.zeros(B, dtype=torch.int32).pin_memory().numpy() for _ in range(3)]
+            self.d2h_inlier_records = 0
+            self.pending_download = False
+            self.r_res = np.zeros(B + 1, rgbdfe.SE3_DTYPE)
+            self.r_inl = np.zeros((B + 1) * self.ctx_t.kp_cap, rgbdfe.DM_DTYPE)
+            self.r_off = np.zeros(B + 2, np.int32)
 
         def extract(self, batch, dev):
             idx = [next(self.order) for _ in range(B)]
@@ -683,6 +694,10 @@ def main():
             self.ctx_t.stream_wait(self.ctx_x)  # batch i was extracted by the previous step
             if args.mode != "chain":
                 self.extract(nxt, dev)          # batch i+1, concurrent with the chain below
+                if not dev:                     # e2e: the frames' host-side state comes back too (asynchronous, pinned)
+                    k = (i + 1) % 3
+                    self.ctx_x.frames_download_async(nxt, self.h_kps[k], self.h_desc[k], None, self.h_n[k], self.ctx_x.kp_cap)
+                    self.pending_download = True
             if args.mode == "serial":           # diagnostic: the chain waits for this extraction too (no overlap)
                 self.ctx_t.stream_wait(self.ctx_x)
             if args.mode == "extract":
@@ -696,7 +711,15 @@ def main():
             if self.n_res == 0:
                 self.i += 1
                 return
-            res = self.ctx_t.track_results(0, self.n_res)
+            if self.pending_download:  # e2e: results WITH the inlier sets, and the downloaded frames complete
+                res = self.r_res[: self.n_res]
+                self.ctx_t._chk(L.rgbdfe_track_results_inliers(self.ctx_t.h, 0, self.n_res, rgbdfe._p(res), rgbdfe._p(self.r_inl), len(self.r_inl),
+                                                               rgbdfe._p(self.r_off)))
+                self.d2h_inlier_records += int(self.r_off[self.n_res])
+                self.ctx_x.sync()
+                self.pending_download = False
+            else:
+                res = self.ctx_t.track_results(0, self.n_res)
             self.ok += int(res["ok"].sum())
             self.n += len(res)
             self.inliers.append(float(res["n_inliers"].mean()))
@@ -763,7 +786,10 @@ def main():
         run_steps(seqs, False, 1)
     proc, path = sample_clocks_start() if rank == 0 else (None, None)
     n_dev, ms_dev, launches = timed(seqs, True, args.steps)
+    for q in seqs:
+        q.d2h_inlier_records = 0
     n_e2e, ms_e2e, _ = timed(seqs, False, args.steps)
+    e2e_inlier_records = sum(q.d2h_inlier_records for q in seqs)
     # the same with the whole 16-bit depth map uploaded per frame (option host_zero_copy = 0)
     for q in seqs:
         q.ctx_x.set_option("host_zero_copy", 0)
@@ -1007,7 +1033,8 @@ def main():
                        "reloc_pairs_per_s": ((verify or {}).get("relocalisation") or {}).get("value"), "verify_error": (verify or {}).get("error")},
             "e2e": {"value": e2e, "unit": "frames/s",
                     "h2d_bytes_per_step": S * B * (W * H * (3 if args.full_upload else 1) + (0 if args.full_upload else NFEAT * 32)),
-                    "d2h_bytes_per_step": S * B * 84,
+                    "d2h_bytes_per_step": S * B * (seqs[0].ctx_x.kp_cap * 60 + 4 + 84 + 4) + e2e_inlier_records * 16 // max(args.steps, 1),
+                    "d2h_note": "per frame: keypoints (28 B) + descriptors (32 B) for the frame's whole capacity row, the count, the 84-byte RansacSE3 result and mvInliers (16 B per inlier DMatch) -- what Extractor::detectAndCompute and RansacSE3 hand back through the class interface",
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "class_shim_path": shim, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,

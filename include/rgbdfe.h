@@ -103,8 +103,8 @@ int rgbdfe_stream_wait(rgbdfe_ctx* waiter, rgbdfe_ctx* signaler);
 /* high != 0: the context's stream gets the device's highest priority (for the latency-bound match/RANSAC
  * chain next to a throughput-bound extraction context).  Synchronises the context. */
 int rgbdfe_set_stream_priority(rgbdfe_ctx* ctx, int high);
-/* `ctx` gives up its own stream and enqueues on `owner`'s from now on (same device; `owner` must outlive `ctx` or
- * `ctx` must get a stream of its own again through rgbdfe_set_stream_priority).  For many throughput-bound extraction
+/* `ctx` gives up its own stream and enqueues on `owner`'s from now on (same device).  The stream lives as long as any
+ * context enqueues on it: when its owner is destroyed or takes another stream first, ownership passes to a sharer.  For many throughput-bound extraction
  * contexts on one GPU: their big grids gain nothing from a stream each, while every extra stream aliases onto the 32
  * hardware work queues and can serialise an unrelated latency-bound chain behind them.  Synchronises `ctx`. */
 int rgbdfe_share_stream(rgbdfe_ctx* ctx, rgbdfe_ctx* owner);
@@ -330,7 +330,8 @@ int rgbdfe_track_results_inliers(rgbdfe_ctx* ctx, int first, int count, rgbdfe_s
     int* offsets);
 /* What Frame keeps on the host after its constructor (mvKeys, mDescriptors, mvKeys3Dc) for count device-resident frames,
  * enqueued on the context stream without synchronising: row i of every output is frame i, `cap` entries wide (whole
- * rows travel, n[i] says how many are valid); pinned host buffers make the copies asynchronous.  Any of kps / desc /
+ * rows travel, n[i] says how many are valid, the rest is unspecified); count <= 64; pinned host buffers make the copies
+ * asynchronous.  Any of kps / desc /
  * xyz may be NULL.  The buffers are complete after rgbdfe_sync(). */
 int rgbdfe_frames_download_async(rgbdfe_ctx* ctx, rgbdfe_frame* const* frames, int count, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz,
     int cap, int* n);
@@ -392,6 +393,24 @@ int rgbdfe_verify_sharded(rgbdfe_ctx* ctx, rgbdfe_kfdb* db, void* nccl_comm, int
     const rgbdfe_point3f* q_xyz, int nq, int n_queries, const rgbdfe_verify_params* params, rgbdfe_se3_result* results);
 /* Host arithmetic only: the gathered layout [rank][query][ceil(n_kf_total / n_ranks)] -> [query][n_kf_total]. */
 int rgbdfe_gathered_to_keyframe_order(const rgbdfe_se3_result* gathered, int n_ranks, int n_queries, int n_kf_total, rgbdfe_se3_result* out);
+
+/* ---- LoopDetector (PlaceRecognition/LoopDetector.cpp:22-84), scope row N4: candidate keyframes for detectLoop ---- */
+/* The bag-of-words vectors are INPUTS (DBoW3::BowVector = ascending (word id, double weight) pairs, made by
+ * Frame::computeBoW -> DBoW3::Vocabulary::transform, Core/Frame.cpp:243-249; DBoW3 and its vocabulary file are not part
+ * of the reference tree).  bowdb_add = LoopDetector::add (:22-26): keyframes keep their insertion order, which is the
+ * order of every inverted-file list; *index (may be NULL) receives the keyframe's index in the database. */
+typedef struct rgbdfe_bowdb rgbdfe_bowdb;
+int rgbdfe_bowdb_create(rgbdfe_ctx* ctx, rgbdfe_bowdb** db, int max_kf, int max_words_per_kf);
+void rgbdfe_bowdb_destroy(rgbdfe_ctx* ctx, rgbdfe_bowdb* db);
+int rgbdfe_bowdb_add(rgbdfe_ctx* ctx, rgbdfe_bowdb* db, int kf_id, const int* words, const double* weights, int n, int* index);
+/* LoopDetector::obtainCandidates(pKF) (:28-84) for the keyframe at query_index: `connected` = indices of
+ * pKF->getConnectedKFs() (empty: no candidates, :33-35), interval = mnInterval.  Vocabulary::score is DBoW3's L1 scoring
+ * (the ORB vocabulary's), accumulated in double over the common words in ascending order.  Returns at most five
+ * database indices in the reference's order (the encounter order of the inverted-file walk, or std::sort by
+ * Frame::CompareBoWscore when more than five qualify) with their scores.  The mnSharingWord marks persist in the
+ * database between calls, as the Frame member does (a second call for the same keyframe finds nothing, :56-57). */
+int rgbdfe_loop_candidates(rgbdfe_ctx* ctx, rgbdfe_bowdb* db, int query_index, const int* connected, int n_connected, int interval, int* candidates,
+    double* scores, int cap, int* n);
 
 #ifdef __cplusplus
 }

@@ -308,6 +308,23 @@ extern "C" int orc_track_sequence2(int nframes, const uint8_t* const* gray, cons
     return tracked;
 }
 
+// ---------------- LoopDetector (row N4) ----------------
+// `sort(possibleLoops.begin(), possibleLoops.end(), Frame::CompareBoWscore)` (PlaceRecognition/LoopDetector.cpp:79) with the
+// REAL std::sort of this image's libstdc++: scores descending, ties in whatever order introsort leaves them.
+extern "C" void orc_sort_bow_scores(double* score, int* idx, int n)
+{
+    struct E {
+        double s;
+        int k;
+    };
+    std::vector<E> v(n);
+    for (int i = 0; i < n; i++)
+        v[i] = E { score[i], idx[i] };
+    std::sort(v.begin(), v.end(), [](const E& a, const E& b) { return a.s > b.s; });
+    for (int i = 0; i < n; i++)
+        score[i] = v[i].s, idx[i] = v[i].k;
+}
+
 // ---------------- numeric pins (tests/test_numeric_pins.py): the third-party restatements, batch form ----------------
 extern "C" {
 // JacobiSVD<Matrix3f> restatement on n row-major 3x3 matrices.

@@ -7,6 +7,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <new>
 
 using namespace rgbdfe;
@@ -209,6 +211,35 @@ __global__ void k_build_chain_pairs(FrameChain fc, int np, MatchPair* dst)
     dst[p] = MatchPair { ref.desc, cur.desc, ref.n, cur.n, ref.outlier, ref.xyz, cur.xyz, cur.outlier };
 }
 __global__ void k_set_int(int* dst, int v) { *dst = v; }
+// rows [0, min(n, cap)) of every frame's keypoints / descriptors / points into [frame][cap] blocks, word by word
+__global__ void k_pack_frames(FrameBatch fb, unsigned* __restrict__ kps, unsigned* __restrict__ desc, unsigned* __restrict__ xyz, int* __restrict__ n_out,
+    int cap)
+{
+    const rgbdfe_frame& f = fb.f[blockIdx.y];
+    const int cnt = *f.n;
+    const int n = min(max(cnt, 0), min(cap, f.cap));
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        n_out[blockIdx.y] = cnt;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+    if (kps) {
+        const unsigned* src = reinterpret_cast<const unsigned*>(f.kps);
+        unsigned* dst = kps + (size_t)blockIdx.y * cap * 7;
+        for (int i = t; i < n * 7; i += nt)
+            dst[i] = src[i];
+    }
+    if (desc) {
+        const uint4* src = reinterpret_cast<const uint4*>(f.desc);
+        uint4* dst = reinterpret_cast<uint4*>(desc + (size_t)blockIdx.y * cap * 8);
+        for (int i = t; i < n * 2; i += nt)
+            dst[i] = src[i];
+    }
+    if (xyz) {
+        const unsigned* src = reinterpret_cast<const unsigned*>(f.xyz);
+        unsigned* dst = xyz + (size_t)blockIdx.y * cap * 3;
+        for (int i = t; i < n * 3; i += nt)
+            dst[i] = src[i];
+    }
+}
 
 void free_orb_workspaces(rgbdfe_ctx* c)
 {
@@ -340,11 +371,10 @@ void rgbdfe_destroy(rgbdfe_ctx* c)
         cudaEventDestroy(c->bulk_evt);
     if (c->bulk_stream)
         cudaStreamDestroy(c->bulk_stream);
-    cudaFree(c->d_packed), cudaFreeHost(c->h_packed);
+    cudaFree(c->d_packed), cudaFreeHost(c->h_packed), cudaFree(c->d_dl);
     cudaFree(c->d_dbg), cudaFree(c->d_cfg), cudaFree(c->d_rng), cudaFree(c->d_latch), cudaFree(c->d_const_n), cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
-    if (c->owns_stream)
-        cudaStreamDestroy(c->stream);
+    release_stream(c);
     delete c;
 }
 
@@ -375,8 +405,7 @@ int rgbdfe_set_stream_priority(rgbdfe_ctx* c, int high)
     CUDA_TRY(c, cudaDeviceGetStreamPriorityRange(&lo, &hi)); // numerically lower = higher priority
     cudaStream_t s = nullptr;
     CUDA_TRY(c, cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, high ? hi : lo));
-    if (c->owns_stream)
-        cudaStreamDestroy(c->stream);
+    release_stream(c);
     c->stream = s;
     c->owns_stream = true;
     return RGBDFE_OK;
@@ -388,10 +417,16 @@ int rgbdfe_share_stream(rgbdfe_ctx* c, rgbdfe_ctx* owner)
         return RGBDFE_E_ARG;
     cudaSetDevice(c->device);
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    if (c->owns_stream)
-        cudaStreamDestroy(c->stream);
-    c->stream = owner->stream;
+    rgbdfe_ctx* root = owner->stream_owner ? owner->stream_owner : owner; // sharing a sharer's stream = sharing its owner's
+    if (root == c) {
+        c->set_error("share_stream: the owner already enqueues on this context's stream");
+        return RGBDFE_E_ARG;
+    }
+    release_stream(c);
+    c->stream = root->stream;
     c->owns_stream = false;
+    c->stream_owner = root;
+    root->stream_sharers.push_back(c);
     return RGBDFE_OK;
 }
 
@@ -982,23 +1017,43 @@ int rgbdfe_frame_download(rgbdfe_ctx* c, rgbdfe_frame* f, rgbdfe_keypoint* kps, 
 int rgbdfe_frames_download_async(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, rgbdfe_keypoint* kps, uint8_t* desc, rgbdfe_point3f* xyz, int cap,
     int* n)
 {
-    if (!c || !frames || count < 0 || cap < 1 || !n)
+    if (!c || !frames || count < 0 || count > 64 || cap < 1 || !n)
         return RGBDFE_E_ARG;
+    if (count == 0)
+        return RGBDFE_OK;
     cudaSetDevice(c->device);
     cudaStream_t s = c->stream;
+    FrameBatch fb;
     for (int i = 0; i < count; i++) {
-        const rgbdfe_frame* f = frames[i];
-        if (!f)
+        if (!frames[i])
             return RGBDFE_E_ARG;
-        const size_t m = (size_t)std::min(cap, f->cap); // the count is on the device: whole-capacity rows travel
-        CUDA_TRY(c, cudaMemcpyAsync(n + i, f->n, sizeof(int), cudaMemcpyDeviceToHost, s));
-        if (kps)
-            CUDA_TRY(c, cudaMemcpyAsync(kps + (size_t)i * cap, f->kps, m * sizeof(rgbdfe_keypoint), cudaMemcpyDeviceToHost, s));
-        if (desc)
-            CUDA_TRY(c, cudaMemcpyAsync(desc + (size_t)i * cap * 32, f->desc, m * 32, cudaMemcpyDeviceToHost, s));
-        if (xyz)
-            CUDA_TRY(c, cudaMemcpyAsync(xyz + (size_t)i * cap, f->xyz, m * sizeof(rgbdfe_point3f), cudaMemcpyDeviceToHost, s));
+        fb.f[i] = *frames[i];
     }
+    // The frames are separate allocations: one kernel packs their valid rows into a staging block laid out like the
+    // outputs, and each output array then leaves in ONE copy (a batch of 64 frames would otherwise be 256 small ones).
+    const size_t row_words = 7 + 8 + 3; // KeyPoint 28 B, descriptor 32 B, Point3f 12 B
+    const size_t need = (size_t)count * cap * row_words * 4 + (size_t)count * 4;
+    if (need > c->dl_bytes) {
+        CUDA_TRY(c, cudaStreamSynchronize(s));
+        cudaFree(c->d_dl);
+        c->d_dl = nullptr, c->dl_bytes = 0;
+        CUDA_TRY(c, cudaMalloc((void**)&c->d_dl, need));
+        c->dl_bytes = need;
+    }
+    unsigned* d_kps = reinterpret_cast<unsigned*>(c->d_dl);
+    unsigned* d_desc = d_kps + (size_t)count * cap * 7;
+    unsigned* d_xyz = d_desc + (size_t)count * cap * 8;
+    int* d_n = reinterpret_cast<int*>(d_xyz + (size_t)count * cap * 3);
+    k_pack_frames<<<dim3(8, count), 256, 0, s>>>(fb, kps ? d_kps : nullptr, desc ? d_desc : nullptr, xyz ? d_xyz : nullptr, d_n, cap);
+    c->launches++;
+    CUDA_TRY(c, cudaGetLastError());
+    CUDA_TRY(c, cudaMemcpyAsync(n, d_n, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (kps)
+        CUDA_TRY(c, cudaMemcpyAsync(kps, d_kps, (size_t)count * cap * 28, cudaMemcpyDeviceToHost, s));
+    if (desc)
+        CUDA_TRY(c, cudaMemcpyAsync(desc, d_desc, (size_t)count * cap * 32, cudaMemcpyDeviceToHost, s));
+    if (xyz)
+        CUDA_TRY(c, cudaMemcpyAsync(xyz, d_xyz, (size_t)count * cap * 12, cudaMemcpyDeviceToHost, s));
     return RGBDFE_OK;
 }
 
@@ -1487,7 +1542,7 @@ extern "C" int rgbdfe_track_results_inliers(rgbdfe_ctx* c, int first, int count,
     const size_t total_cap = (size_t)count * c->kp_cap;
     if (total_cap > c->packed_cap) {
         CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_packed), cudaFreeHost(c->h_packed);
+        cudaFree(c->d_packed), cudaFreeHost(c->h_packed), cudaFree(c->d_dl);
         c->d_packed = nullptr, c->h_packed = nullptr, c->packed_cap = 0;
         CUDA_TRY(c, dmalloc(&c->d_packed, total_cap + 32)); // + room for the offsets behind the records
         CUDA_TRY(c, cudaMallocHost((void**)&c->h_packed, (total_cap + 32) * sizeof(rgbdfe_dmatch)));
@@ -1515,6 +1570,43 @@ extern "C" int rgbdfe_track_results_inliers(rgbdfe_ctx* c, int first, int count,
     }
     return RGBDFE_OK;
 }
+
+namespace rgbdfe {
+cudaError_t raise_dyn_smem(int device, const void* kernel, size_t bytes)
+{
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, size_t> have;
+    std::lock_guard<std::mutex> lk(mu);
+    size_t& cur = have[std::make_pair(device, kernel)];
+    if (bytes <= cur)
+        return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess)
+        cur = bytes;
+    return e;
+}
+
+void release_stream(rgbdfe_ctx* c)
+{
+    if (c->stream_owner) { // a sharer leaves
+        auto& v = c->stream_owner->stream_sharers;
+        v.erase(std::remove(v.begin(), v.end(), c), v.end());
+        c->stream_owner = nullptr;
+    } else if (c->owns_stream && !c->stream_sharers.empty()) { // an owner leaves while others still enqueue on the stream
+        rgbdfe_ctx* heir = c->stream_sharers.front();
+        heir->owns_stream = true;
+        heir->stream_owner = nullptr;
+        for (size_t i = 1; i < c->stream_sharers.size(); i++) {
+            c->stream_sharers[i]->stream_owner = heir;
+            heir->stream_sharers.push_back(c->stream_sharers[i]);
+        }
+        c->stream_sharers.clear();
+    } else if (c->owns_stream && c->stream)
+        cudaStreamDestroy(c->stream);
+    c->stream = nullptr;
+    c->owns_stream = false;
+}
+} // namespace rgbdfe
 
 namespace rgbdfe { // helpers of this file used by verify.cu
 int api_ensure_pairs(rgbdfe_ctx* c, int npairs) { return ensure_pairs(c, npairs); }

@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -221,6 +222,8 @@ struct rgbdfe_ctx {
     int knn_splits = 8;
     // option "overlap_blur": K3 (blur, needs only the pyramid) runs on a side stream beside K4 (quadtree, latency-bound)
     bool owns_stream = true; // false after rgbdfe_share_stream
+    rgbdfe_ctx* stream_owner = nullptr;   // whose stream this context enqueues on (rgbdfe_share_stream)
+    std::vector<rgbdfe_ctx*> stream_sharers; // contexts enqueuing on THIS context's stream
     int overlap_blur = 0;
     cudaStream_t side_stream = nullptr;
     cudaEvent_t side_fork = nullptr, side_join = nullptr;
@@ -258,6 +261,7 @@ struct rgbdfe_ctx {
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
     int last_track_slot = 0, last_track_pairs = 0; // result slots of the last rgbdfe_track / rgbdfe_track_sequence (pair p -> slot + p)
     rgbdfe_dmatch* d_packed = nullptr; rgbdfe_dmatch* h_packed = nullptr; size_t packed_cap = 0; // rgbdfe_track_results_inliers staging
+    unsigned char* d_dl = nullptr; size_t dl_bytes = 0; // rgbdfe_frames_download_async staging
     struct VerifyState* verify = nullptr; // sharded verification: comm stream, result slots, query staging (verify.cu)
     bool latch_known = false;       // the host has seen the depth-covariance latch set (batched verification requires it)
     long long* d_dbg = nullptr;     // %globaltimer stamps written by the chain kernels when debug timing is on (rgbdfe_debug_timeline)
@@ -271,6 +275,18 @@ struct rgbdfe_ctx {
 
     void set_error(const std::string& s) { err = s; }
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute and setting it REPLACES the value: the largest
+// size requested so far is kept per (device, kernel) for the whole process, under a lock (contexts of several devices
+// and host threads share the kernels), and the attribute only ever grows.  The caller has made c->device current.
+namespace rgbdfe {
+cudaError_t raise_dyn_smem(int device, const void* kernel, size_t bytes); // api.cu
+}
+template <class K>
+inline cudaError_t ensure_dyn_smem(rgbdfe_ctx* c, K kernel, size_t bytes)
+{
+    return rgbdfe::raise_dyn_smem(c->device, (const void*)kernel, bytes);
+}
 
 #define CUDA_TRY(ctx, expr)                                                       \
     do {                                                                          \
@@ -371,6 +387,10 @@ struct FusedFilter {
 int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, const Se3Params& prm, int update_f2, int per_pair_rng,
     unsigned seed, int first_pair_index, int min_matches, rgbdfe_se3_result* d_results, const FusedFilter* ff);
 // api.cu
+// The context stops using c->stream (it is about to get another one, or to be destroyed): a sharer leaves its owner; an
+// owner with sharers hands the stream to the first of them (it stays alive as long as anyone enqueues on it), an owner
+// without sharers destroys it.
+void release_stream(rgbdfe_ctx* c);
 int api_ensure_pairs(rgbdfe_ctx* c, int npairs);
 Se3Params api_make_params(rgbdfe_ctx* c, int iterations, unsigned min_inl, float max_mahal, unsigned sample);
 int api_pointer_kind(const void* p, const void** dev); // 0 pageable host, 1 device, 2 pinned host

@@ -1047,11 +1047,7 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
             kcap *= 2;
         kcap = std::min(kcap, 24576);
         const size_t smem = (size_t)kcap * 8 + (size_t)(h + 2) * sizeof(int);
-        static size_t configured[64] = { 0 };
-        if (smem > configured[c->device]) {
-            CUDA_TRY(c, cudaFuncSetAttribute(k_cv_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured[c->device] = smem;
-        }
+        CUDA_TRY(c, ensure_dyn_smem(c, k_cv_select, smem));
         k_cv_select<<<dim3(C.nlevels, count), CV_SEL_THREADS, smem, c->stream>>>(C, W->d_pyr, W->pyr_slot, W->d_score, W->blur_slot, W->d_cand,
             W->d_lr, W->d_hkey, W->d_hcount, W->d_out, W->d_out_count, kcap);
         k_cv_gather<<<count, 256, 0, c->stream>>>(C, W->d_out, W->d_out_count, W->d_final, W->d_final_count, W->d_gscratch);

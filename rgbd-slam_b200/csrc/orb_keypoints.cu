@@ -475,11 +475,7 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
     while (SC < NC)
         SC <<= 1;
     size_t smem = (size_t)SC * 8 + (size_t)NC * (2 * sizeof(QtNode) + 4 * 4 + 4 * 5) + QT_THREADS * 4;
-    static size_t configured = 0;
-    if (smem > configured) {
-        CUDA_TRY(c, cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    CUDA_TRY(c, ensure_dyn_smem(c, k_quadtree, smem));
     ProfScope prof(c, KID_QUADTREE);
     k_quadtree<<<dim3(c->cfg.nlevels, count), QT_THREADS, smem, c->stream>>>(c->d_cfg, c->d_cell_count, c->d_cell_list, c->cell_slot, c->d_cand,
         c->d_label, c->cand_slot, c->d_cand_count, c->d_sel, c->sel_slot, c->d_sel_count, NC, SC);

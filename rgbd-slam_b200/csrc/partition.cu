@@ -144,8 +144,7 @@ int rgbdfe_bind_partition(rgbdfe_ctx* c, int role)
         s_main = (cudaStream_t)a;
         s_bulk = (cudaStream_t)b;
     }
-    if (c->owns_stream)
-        cudaStreamDestroy(c->stream);
+    rgbdfe::release_stream(c);
     c->owns_stream = true;
     if (c->bulk_stream)
         cudaStreamDestroy(c->bulk_stream);

@@ -498,6 +498,45 @@ __device__ void warp_try_replay(const ReplayCtx& R, int pair, int chunk_end, int
     }
 }
 
+// Draw the samples of iterations [sampled_k, sampled_k + chunk) of a pair ahead of their consumption, so that iteration
+// `need` exists.  Called by one warp that would otherwise wait for the replay to draw them; takes the pair lock (held
+// only by resident, running warps) or backs off for a moment.  scratch: as for warp_try_replay.
+__device__ void warp_draw_ahead(const ReplayCtx& R, int pair, int need, int chunk, unsigned* scratch, int lane)
+{
+    ReplayState* rp = R.replay + pair;
+    int* lock = R.lock_all + pair;
+    int got = 0;
+    if (lane == 0)
+        got = atomicCAS(lock, 0, 1) == 0;
+    got = __shfl_sync(0xffffffffu, got, 0);
+    if (!got) {
+        __nanosleep(200);
+        return;
+    }
+    __threadfence();
+    ReplayState st = load_state(rp);
+    const int max_iters = min(R.prm.iterations, MAX_ITERS);
+    if (!st.done && st.run && st.sampled_k <= need && st.sampled_k < max_iters && st.nm >= (int)R.prm.sample_size) {
+        const int k1 = min(max(need + 1, st.sampled_k + chunk), max_iters);
+        int calls = st.sampled_calls;
+        warp_sample_chunk(scratch, reinterpret_cast<int*>(scratch + RNG_HIST + RNG_BLOCK), R.pair_rng + pair, st.nm, (int)R.prm.sample_size, st.sampled_k,
+            k1, R.samples_all + (size_t)pair * MAX_ITERS * SE3_MAX_SAMPLE, R.rng_used_all + (size_t)pair * MAX_ITERS, calls, lane);
+        st.sampled_calls = calls;
+        st.sampled_k = k1;
+        if (lane == 0) {
+            // only the two sampler fields changed; the replay fields are re-read under the lock by whoever holds it next
+            *reinterpret_cast<volatile int*>(&rp->sampled_calls) = st.sampled_calls;
+            __threadfence();
+            *reinterpret_cast<volatile int*>(&rp->sampled_k) = st.sampled_k;
+        }
+    }
+    if (lane == 0) {
+        __threadfence();
+        atomicExch(lock, 0);
+    }
+    __syncwarp();
+}
+
 // ---------------------------------------------------------------------------------------
 // One hypothesis = one CTA.  Shared memory (dynamic), capA = cap rounded up to 4:
 //   double g_d2[capA]                 d^2 of the current inliers, list order
@@ -886,6 +925,7 @@ template <int THREADS, int NPT>
 __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
 {
     __shared__ int s_done;
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
     const int pair = R.slot0 + blockIdx.y;
     for (int h = hyp_begin + blockIdx.x; h < hyp_end || h == hyp_begin + (int)blockIdx.x; h += gridDim.x) {
         cta_se3_hypothesis<THREADS, NPT>(R, w_all, pair, h, hyp_begin, hyp_end, next_end, blockIdx.x == 0 && h == hyp_begin);
@@ -893,14 +933,18 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
         if (hn >= hyp_end)
             break;
         __syncthreads(); // the replay of warp 0 used the shared scratch
-        if (threadIdx.x == 0) {
-            // the next iteration of this CTA may not be drawn yet: the replay draws more once everything drawn so far has
-            // been consumed without ending the loop (every drawn iteration is owned by a CTA that publishes it)
+        if (threadIdx.x < 32) {
+            // The next iteration of this CTA may not be drawn yet.  The replay draws more once everything drawn so far has
+            // been consumed, but that needs every CTA of the pair to have run, and CTAs of a grid need not be co-resident
+            // (small SM partitions, many contexts on one GPU): waiting for them could starve them of the slot this CTA
+            // holds.  Samples depend only on the match count and the pair's stream, so this warp draws the chunk itself,
+            // under the pair lock, whenever nobody has yet.
             const ReplayState* rp = R.replay + pair;
             int d;
             while (!(d = ld_volatile(&rp->done) | (ld_volatile(&rp->run) ^ 1)) && next_end < 0 && ld_volatile(&rp->sampled_k) <= hn)
-                __nanosleep(200);
-            s_done = d;
+                warp_draw_ahead(R, pair, hn, -next_end, reinterpret_cast<unsigned*>(smem_dyn), threadIdx.x);
+            if (threadIdx.x == 0)
+                s_done = d;
         }
         __syncthreads();
         if (s_done)
@@ -911,11 +955,7 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
 template <int THREADS, int NPT>
 static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end, int max_ctas)
 {
-    static size_t configured = 0;
-    if (smem > configured) {
-        CUDA_TRY(c, cudaFuncSetAttribute(k_se3_hypotheses<THREADS, NPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    CUDA_TRY(c, ensure_dyn_smem(c, k_se3_hypotheses<THREADS, NPT>, smem));
     int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
     if (nblk > max_ctas)
         nblk = max_ctas;
@@ -948,11 +988,7 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
     const size_t min_smem = ((size_t)RNG_SCRATCH_WORDS + c->mask_words) * 4;
     if (hyp_smem < min_smem)
         hyp_smem = min_smem;
-    static size_t conf_prep = 0;
-    if (prep_smem > conf_prep) {
-        CUDA_TRY(c, cudaFuncSetAttribute(k_se3_prepare, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prep_smem));
-        conf_prep = prep_smem;
-    }
+    CUDA_TRY(c, ensure_dyn_smem(c, k_se3_prepare, prep_smem));
     {
         ProfScope prof(c, KID_SE3_PREPARE);
         FusedFilter f = { 0, 0.0f, 0, 0, 0 };

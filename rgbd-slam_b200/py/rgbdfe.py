@@ -446,6 +446,28 @@ class Context:
         fr = (C.c_void_p * len(frames))(*[f.h for f in frames])
         self._chk(lib().rgbdfe_frames_download_async(self.h, fr, len(frames), _p(kps), _p(desc), _p(xyz), cap, _p(n)))
 
+    # ---- LoopDetector (row N4) ----
+    def bowdb_create(self, max_kf, max_words_per_kf):
+        h = C.c_void_p()
+        self._chk(lib().rgbdfe_bowdb_create(self.h, C.byref(h), max_kf, max_words_per_kf))
+        return h
+
+    def bowdb_destroy(self, db):
+        lib().rgbdfe_bowdb_destroy(self.h, db)
+
+    def bowdb_add(self, db, kf_id, words, weights):
+        words = np.ascontiguousarray(words, np.int32)
+        weights = np.ascontiguousarray(weights, np.float64)
+        idx = C.c_int()
+        self._chk(lib().rgbdfe_bowdb_add(self.h, db, int(kf_id), _p(words), _p(weights), len(words), C.byref(idx)))
+        return idx.value
+
+    def loop_candidates(self, db, query_index, connected, interval):
+        conn = np.ascontiguousarray(connected, np.int32)
+        cand, sc, n = np.zeros(8, np.int32), np.zeros(8, np.float64), C.c_int()
+        self._chk(lib().rgbdfe_loop_candidates(self.h, db, int(query_index), _p(conn), len(conn), int(interval), _p(cand), _p(sc), 8, C.byref(n)))
+        return [(int(cand[i]), float(sc[i])) for i in range(n.value)]
+
     # ---- batched verification ----
     def kfdb_create(self, desc, xyz):
         desc = np.ascontiguousarray(desc, np.uint8)

@@ -3,6 +3,8 @@
 Bar (north_star): keypoints, descriptors, match indices and RANSAC inlier sets bit-exact;
 poses within 1e-5 (rotation entries and translation, FP32).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -93,6 +95,56 @@ def test_contexts_sharing_one_stream(ctx, oracle, seq_vga):
             assert len(k2) == len(ko2) and (d2 == do2).all() and (k2["x"] == ko2["x"]).all()
     finally:
         other.close()
+
+
+def test_shared_stream_outlives_its_owner(oracle, seq_vga):
+    """The owner of a shared stream is destroyed first: the stream passes to a sharer and keeps working."""
+    import rgbdfe
+
+    cam, frames = seq_vga
+    owner = rgbdfe.Context(0, 640, 480, 1000, 1)
+    a, b = rgbdfe.Context(0, 640, 480, 1000, 1), rgbdfe.Context(0, 640, 480, 1000, 1)
+    try:
+        a.share_stream(owner)
+        b.share_stream(a)  # sharing a sharer's stream = sharing its owner's
+        s = owner.stream
+        assert a.stream == s and b.stream == s
+        owner.close()
+        ko, do = oracle.Orb(1000).extract(frames[0][0])
+        for c in (a, b):
+            k, d = c.orb_extract(frames[0][0])
+            assert len(k) == len(ko) and (d == do).all()
+        a.close()  # the heir goes too: b inherits
+        k, d = b.orb_extract(frames[1][0])
+        assert len(k) > 100
+    finally:
+        for c in (owner, a, b):
+            c.close()
+
+
+def test_contexts_on_two_devices_in_one_process(oracle, seq_vga):
+    """Kernel attributes (dynamic shared memory limits) are per device: a second context on another GPU of the same
+    process must run the large-smem kernels (quadtree, RANSAC prepare / hypotheses) as well."""
+    import torch
+
+    import rgbdfe
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cam, frames = seq_vga
+    p1, p2, m = _pair(oracle, cam, frames, 0, 1)
+    res = []
+    for dev in (0, 1):
+        c = rgbdfe.Context(dev, 640, 480, 2000, 1)
+        try:
+            c.orb_configure(2000, 1.2, 8, 20, 7)
+            k, d = c.orb_extract(frames[0][0])
+            c.rng_seed(42)
+            res.append((k, d, c.ransac_se3(p1, p2, m, 200, 10, 3.0, 4)))
+        finally:
+            c.close()
+    assert (res[0][0] == res[1][0]).all() and (res[0][1] == res[1][1]).all()
+    _check_se3(res[0][2], res[1][2])
 
 
 def test_orb_fast_threshold_fallback(ctx, oracle):
@@ -253,6 +305,73 @@ def test_ransac_se3_hard_cases(ctx, oracle, seq_vga):
     ctx.rng_seed(7)
     ctx.depth_cov_set(0, 0.0)
     _check_se3(oracle.ransac_se3(p1, p2, mm, rng, latch), ctx.ransac_se3(p1, p2, mm))
+
+
+@pytest.mark.timeout(240)
+def test_ransac_hard_pairs_do_not_need_co_resident_ctas(oracle, seq_vga):
+    """A hard pair (no early break) walks all iterations with `ransac_first_chunk` CTAs that take turns; the CTAs of a grid
+    need not be co-resident: 24 contexts on 24 host threads at first_chunk = 32 (768 CTAs of 512 threads on 296 slots), and
+    one context on a small latency partition.  Results must still equal the oracle's."""
+    import threading
+
+    import rgbdfe
+
+    cam, frames = seq_vga
+    p1, p2, m = _pair(oracle, cam, frames, 0, 3)
+    rs = np.random.default_rng(19)
+    mm = m.copy()
+    bad = rs.random(len(mm)) < 0.85
+    mm["trainIdx"][bad] = rs.integers(0, len(p2), bad.sum())
+    want = []
+    for seed in (1, 2):
+        rng, latch = oracle.Rng(seed), oracle.Latch()
+        want.append(oracle.ransac_se3(p1, p2, mm, rng, latch, 500, 30, 3.0, 4))
+    assert min(w["iters_executed"] for w in want) > 100  # really a long loop
+    n_ctx = 24
+    ctxs = [rgbdfe.Context(0, 640, 480, 1000, 1) for _ in range(n_ctx)]
+    errs = []
+
+    def work(c, k):
+        try:
+            c.set_option("ransac_first_chunk", 32)
+            for rep in range(3):
+                seed = 1 + (k + rep) % 2
+                c.rng_seed(seed)
+                c.depth_cov_set(0, 0.0)
+                _check_se3(want[seed - 1], c.ransac_se3(p1, p2, mm, 500, 30, 3.0, 4))
+        except Exception as ex:  # noqa: BLE001
+            errs.append(repr(ex))
+
+    try:
+        th = [threading.Thread(target=work, args=(c, k)) for k, c in enumerate(ctxs)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        assert not errs, errs[:3]
+    finally:
+        for c in ctxs:
+            c.close()
+    # the same pair on an 8-SM latency partition (16 CTA slots for 32 CTAs); the SM split is fixed per process, so a child does it
+    import pickle
+    import subprocess
+    import sys
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as td:
+        pickle.dump((p1, p2, mm), open(os.path.join(td, "in.pkl"), "wb"))
+        code = (
+            "import sys, pickle; sys.path[:0] = %r\n"
+            "import rgbdfe\n"
+            "p1, p2, mm = pickle.load(open(%r, 'rb'))\n"
+            "part = rgbdfe.device_partition(0, 8)\n"
+            "c = rgbdfe.Context(0, 640, 480, 1000, 1)\n"
+            "if part is not None: c.bind_partition(rgbdfe.PART_LATENCY)\n"
+            "c.set_option('ransac_first_chunk', 32); c.rng_seed(1); c.depth_cov_set(0, 0.0)\n"
+            "r = c.ransac_se3(p1, p2, mm, 500, 30, 3.0, 4)\n"
+            "pickle.dump((part, r), open(%r, 'wb'))\n"
+        ) % ([p for p in sys.path if p], os.path.join(td, "in.pkl"), os.path.join(td, "out.pkl"))
+        subprocess.run([sys.executable, "-c", code], check=True, timeout=120)
+        part, r = pickle.load(open(os.path.join(td, "out.pkl"), "rb"))
+        _check_se3(want[0], r)
 
 
 def test_ransac_umeyama_parity(ctx, oracle, seq_vga):
