@@ -148,12 +148,13 @@ def native_oracle():
     return C.CDLL(path), "-O3 -march=native"
 
 
-def cpu_track(frames, cam, idx, threads=1, lib=None, want=False):
+def cpu_track(frames, cam, idx, threads=1, lib=None, want=False, cfg=None):
     """Time the oracle port over len(idx) frames per thread (one tracking chain per thread).
     Returns (tracked frames/s, seconds, mean per-thread stage seconds dict, (inliers, iters) of thread 0 if want)."""
     import orclib
 
     L = lib or orclib.lib()
+    w_, h_, nfeat_, iters_, min_inl_ = cfg or (W, H, NFEAT, ITERS, MIN_INL)
     n = len(idx)
     g = (C.c_void_p * n)(*[frames[i][0].ctypes.data for i in idx])
     d = (C.c_void_p * n)(*[frames[i][1].ctypes.data for i in idx])
@@ -164,8 +165,8 @@ def cpu_track(frames, cam, idx, threads=1, lib=None, want=False):
 
     def work(t):
         done[t] = L.orc_track_sequence2(
-            n, g, d, W, H, C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"]), NFEAT, C.c_float(RATIO), ITERS,
-            C.c_uint(MIN_INL), C.c_float(3.0), C.c_uint(4), C.c_uint(42 + t), inl if (want and t == 0) else None, its if (want and t == 0) else None, stage[t], stats if (want and t == 0) else None,
+            n, g, d, w_, h_, C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"]), nfeat_, C.c_float(RATIO), iters_,
+            C.c_uint(min_inl_), C.c_float(3.0), C.c_uint(4), C.c_uint(42 + t), inl if (want and t == 0) else None, its if (want and t == 0) else None, stage[t], stats if (want and t == 0) else None,
         )
 
     t0 = time.perf_counter()
@@ -516,6 +517,167 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     return out
 
 
+def config_leg(rgbdfe, torch, local_rank, cam_name, nfeat, iters, min_inl, n_frames, B_, S_, steps, no_cpu, what):
+    """Another BASELINE config through the same pipeline as the headline (batched extraction of device-resident frames in
+    one context, the match / RANSAC chain in another, S_ independent sequences in flight): frames/s on the device (CUDA
+    events), mean executed RANSAC iterations, and the CPU port (reference flags, all cores) on the same frames beside it."""
+    import synth
+
+    cam, fr_ = synth.sequence(cam_name, n=n_frames, seed=4321, noise_sigma=0.0, invalid_frac=0.0)
+    w_, h_ = cam["w"], cam["h"]
+    grays = [np.ascontiguousarray(g) for g, _ in fr_]
+    d16 = [np.rint(np.clip(np.nan_to_num(d, nan=0.0) * DEPTH_FACTOR, 0, 65535)).astype(np.uint16) for _, d in fr_]
+    inv = float(np.float32(1.0) / np.float32(DEPTH_FACTOR))
+    gd, dd = torch.from_numpy(np.stack(grays)).cuda(), torch.from_numpy(np.stack(d16)).cuda()
+    L = rgbdfe.lib()
+
+    class Q:
+        def __init__(self, k):
+            self.cx, self.ct = rgbdfe.Context(local_rank, w_, h_, nfeat, B_), rgbdfe.Context(local_rank, w_, h_, nfeat, 1)
+            self.cx.orb_configure(nfeat, 1.2, 8, 20, 7)
+            self.ct.set_stream_priority(True)
+            self.ct.set_option("ransac_first_chunk", 4 if S_ > 1 else 32)
+            self.ct.rng_seed(42 + k)
+            self.sets = [[rgbdfe.Frame(self.cx) for _ in range(B_)] for _ in range(3)]
+            self.order, self.i, self.have_ref = pingpong(n_frames), 0, False
+            for _ in range((k * 5) % n_frames):
+                next(self.order)
+            self.ok = self.n = 0
+            self.iters, self.inl = [], []
+
+        def extract(self, batch):
+            idx = [next(self.order) for _ in range(B_)]
+            fa = (C.c_void_p * B_)(*[f.h for f in batch])
+            gp = (C.c_void_p * B_)(*[gd[i].data_ptr() for i in idx])
+            dp = (C.c_void_p * B_)(*[dd[i].data_ptr() for i in idx])
+            self.cx._chk(L.rgbdfe_frames_extract_raw(self.cx.h, fa, B_, gp, w_, h_, w_, dp, w_, C.c_float(inv), C.c_float(cam["fx"]), C.c_float(cam["fy"]),
+                                                     C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+
+        def step(self):
+            i = self.i
+            cur, nxt = self.sets[i % 3], self.sets[(i + 1) % 3]
+            self.ct.stream_wait(self.cx)
+            self.extract(nxt)
+            chain = ([self.sets[(i - 1) % 3][-1]] if self.have_ref else []) + cur
+            self.ct.track_sequence(chain, 0, RATIO, True, iters, min_inl, 3.0, 4, True)
+            self.n_res = len(chain) - 1
+
+        def collect(self):
+            res = self.ct.track_results(0, self.n_res)
+            self.ok += int(res["ok"].sum())
+            self.n += len(res)
+            self.iters.append(float(res["iters_executed"].mean()))
+            self.inl.append(float(res["n_inliers"].mean()))
+            self.i += 1
+            self.have_ref = True
+
+        def close(self):
+            for st in self.sets:
+                for f in st:
+                    f.close()
+            self.cx.close()
+            self.ct.close()
+
+    qs = [Q(k) for k in range(S_)]
+    try:
+        for q in qs:
+            q.extract(q.sets[0])
+
+        def run(n):
+            for _ in range(n):
+                for q in qs:
+                    q.step()
+                for q in qs:
+                    q.collect()
+
+        run(2)
+        torch.cuda.synchronize()
+        stream = torch.cuda.ExternalStream(qs[0].ct.stream, device=local_rank)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for q in qs:
+            q.iters, q.inl, q.ok, q.n = [], [], 0, 0
+        e0.record(stream)
+        run(steps)
+        for q in qs:
+            qs[0].ct.stream_wait(q.cx)
+            qs[0].ct.stream_wait(q.ct)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        out = {"what": what, "value": steps * S_ * B_ / (ms * 1e-3), "unit": "frames/s", "image": f"{w_}x{h_}", "features": nfeat, "ransac": f"RansacSE3({iters}, {min_inl}, 3.0, 4)",
+               "sequences_in_flight": S_, "batch": B_, "mean_ransac_iterations": float(np.mean([x for q in qs for x in q.iters])),
+               "mean_inliers": float(np.mean([x for q in qs for x in q.inl])), "tracked_ok_frac": sum(q.ok for q in qs) / max(sum(q.n for q in qs), 1),
+               "keypoints_per_frame": int(len(qs[0].sets[0][0].download()[0]))}
+    finally:
+        for q in qs:
+            q.close()
+    if not no_cpu:
+        cores = len(os.sched_getaffinity(0))
+        nlib, flags = native_oracle()
+        fl = [(grays[i], d16[i].astype(np.float32) * (np.float32(1.0) / np.float32(DEPTH_FACTOR))) for i in range(n_frames)]
+        nf = min(n_frames, 9)
+        fps, dt, st, _ = cpu_track(fl, cam, list(range(nf)), cores, nlib, cfg=(w_, h_, nfeat, iters, min_inl))
+        out["cpu_port_frames_per_s"] = fps
+        out["cpu_note"] = f"oracle port built {flags}, {nf}-frame chains on {cores} threads, {dt:.1f} s"
+    return out
+
+
+def hard_ransac_leg(rgbdfe, torch, local_rank, no_cpu):
+    """RansacSE3 where it has to work: 256 pairs of 2000-feature frames whose descriptor matches are right but 70 % of the
+    matched 3-D points are wrong (moved at random), RansacSE3(500, 10, 3.0, 4): the loop runs hundreds of iterations per pair
+    instead of breaking after the first.  Pairs/s through rgbdfe_verify_sharded (one GPU), executed iterations from the results,
+    and the oracle port on a few of the same pairs beside it."""
+    import loopverify
+    import synth
+
+    n_pairs, nf = 256, 2000
+    qd, qp, kd, kp, _ = synth.synth_pair_sets(n_pairs, nf, seed=99, corr_frac=0.5, overlap_frac=1.0)
+    rng = np.random.default_rng(5)
+    bad = rng.random((n_pairs, nf)) < 0.7
+    z = rng.uniform(0.5, 4.5, (n_pairs, nf))
+    junk = np.stack([rng.uniform(-1, 1, (n_pairs, nf)) * z, rng.uniform(-0.8, 0.8, (n_pairs, nf)) * z, z], 2).astype(np.float32)
+    kp = np.where(bad[:, :, None], junk, kp)
+    v = loopverify.CudaShardedVerifier(local_rank, 0, 1, n_pairs, kd, kp, None, max_feats=nf)
+    v.params = rgbdfe.VerifyParams(0.9, 10, 500, 10, 3.0, 4, 42)
+    try:
+        res = v.verify(qd, qp, seed=42)[0]
+        stream = torch.cuda.ExternalStream(v.ctx.stream, device=local_rank)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 6
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for i in range(reps):
+            v.enqueue(qd, qp, nf, 1, i % 4, seed=42)
+            if i >= 3:
+                v.collect((i - 3) % 4, 1, want=False)
+        for i in range(reps - 3, reps):
+            v.collect(i % 4, 1, want=False)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+    finally:
+        v.close()
+    out = {"what": "hard RANSAC: 256 pairs x 2000 features, ~1000 matches per pair of which ~70 % are geometric outliers, RansacSE3(500, 10, 3.0, 4)",
+           "value": n_pairs / (ms * 1e-3), "unit": "pairs/s", "ms_per_256_pairs": ms, "mean_ransac_iterations": float(res["iters_executed"].mean()),
+           "mean_matches": float(res["n_matches"].mean()), "mean_inliers": float(res["n_inliers"].mean()), "ok_frac": float((res["ok"] != 0).mean())}
+    if not no_cpu:
+        import orclib
+
+        t0 = time.perf_counter()
+        its = []
+        for k in range(4):
+            m = orclib.match(kd[k], qd, np.zeros(nf, np.uint8), kp[k], qp, 0.9, True)
+            r_, l_ = orclib.Rng(42 + k), orclib.Latch()
+            l_.latched.value, l_.cov.value = 1, (0.01 * 2.0 * 2.0) ** 2
+            r = orclib.ransac_se3(kp[k], qp, m, r_, l_, 500, 10, 3.0, 4)
+            its.append(r["iters_executed"])
+            out["parity_first_pairs"] = bool(out.get("parity_first_pairs", True) and r["iters_executed"] == int(res[k]["iters_executed"])
+                                             and len(r["inliers"]) == int(res[k]["n_inliers"]))
+        out["cpu_port_pairs_per_s_one_thread"] = 4 / (time.perf_counter() - t0)
+        out["cpu_note"] = "oracle parity build (-O2), match + RansacSE3 of the first 4 pairs, one thread"
+    return out
+
+
 def run_reference(args, rank, world):
     """The CPU arm: the reference's algorithm on all host cores.  The reference itself cannot be built here (OpenCV / Eigen
     / PCL headers are absent), so this is (a) the oracle port compiled with the reference's flags and (b) the same with the
@@ -572,7 +734,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
-    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify", "shim"],
+    ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify", "shim", "configs"],
                     help="diagnostic: time only the extraction half or only the match/RANSAC chains (not a bench value)")
     ap.add_argument("--verify-kf", type=int, default=4096, help="keyframes of the fixed loop-closure verification job (BASELINE configs[3]), sharded over the GPUs")
     args = ap.parse_args()
@@ -618,6 +780,12 @@ def main():
 
     B, F = args.batch, args.frames
     cam, frames = make_sequence(F)
+    if args.mode == "configs":  # diagnostic: the other-config legs alone
+        o = {"configs0": config_leg(rgbdfe, torch, local_rank, "tum_fr1", 1000, 200, 10, 32, 32, 32, 4, args.no_cpu, "configs[0]"),
+             "configs2": config_leg(rgbdfe, torch, local_rank, "kinect2", 4000, 500, 10, 8, 8, 8, 4, args.no_cpu, "configs[2]"),
+             "hard": hard_ransac_leg(rgbdfe, torch, local_rank, args.no_cpu)}
+        print(json.dumps(o))
+        return
     if args.mode == "shim":  # diagnostic: the class-shim leg alone
         print(json.dumps({"class_shim_path": {"feats_2000": shim_leg(frames, cam, NFEAT), "feats_1000": shim_leg(frames, cam, 1000)}}))
         return
@@ -869,9 +1037,15 @@ def main():
     kn = roofline["per_kernel"].get("k_knn2_umma")
     if kn:
         tops = 2.0 * NFEAT * NFEAT * 256 * B / (kn["ms"] * 1e-3) / 1e12  # a batch's chain = B pairs of NFEAT x NFEAT descriptors
-        peak_tops = 2.0 * float(peaks.get("bf16_tflops", 2250.0))
+        peak_tops, peak_how = 2.0 * float(peaks.get("bf16_tflops", 2250.0)), "2 x measured dense bf16 (MEASURED_PEAKS.json)"
+        try:  # the measured dispatch rate of tcgen05.mma.kind::i8 on this pool's B200 (tools/micro/umma_rate.cu)
+            um = json.load(open(os.path.join(ROOT, "profiles", "r2_pipe_peaks.json")))["umma_i8_m128n128k32"]
+            peak_tops = 2.0 * um["mac_per_clk_per_sm"] * 148 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12
+            peak_how = "measured tcgen05.mma.kind::i8 dispatch rate (8181 MAC/clk/SM, profiles/r2_pipe_peaks.json) x 148 SMs x max SM clock"
+        except Exception:
+            pass
         kn.update({"bound": "tensor", "achieved_TOPs": tops, "peak_TOPs": peak_tops, "frac": tops / peak_tops,
-                   "how": "2 * Nq * Nt * 256 * pairs per launch / launch time; peak = 2 x measured dense bf16"})
+                   "how": "2 * Nq * Nt * 256 * pairs per launch / launch time; peak = " + peak_how})
 
     # ---- row N1: Frame preprocessing (BGR -> gray, 16-bit depth, undistortion, grid cells) + extraction, end to end ----
     frame_prep = projection = None
@@ -944,6 +1118,20 @@ def main():
         verify = verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world)
     except Exception as ex:  # the headline metric does not depend on this leg
         verify = {"error": str(ex)[:300]}
+
+    # ---- the other BASELINE configs and a hard-RANSAC workload, same pipeline (rank 0 only; not part of the headline) ----
+    other = {}
+    if rank == 0 and args.mode == "full":
+        for key, a in (("configs0_tum_1000", ("tum_fr1", 1000, 200, 10, 32, 32, 32, 4, "BASELINE configs[0]: TUM fr1-shaped 640x480, 1000 ORB features, RansacSE3(200, 10) as Tracking.cpp:129")),
+                       ("configs2_1080p_4000", ("kinect2", 4000, 500, 10, 8, 8, 8, 4, "BASELINE configs[2]: Kinect-v2-shaped 1920x1080 frames with registered depth, 4000 ORB features"))):
+            try:
+                other[key] = config_leg(rgbdfe, torch, local_rank, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], args.no_cpu, a[8])
+            except Exception as ex:
+                other[key] = {"error": str(ex)[:200]}
+        try:
+            other["hard_ransac"] = hard_ransac_leg(rgbdfe, torch, local_rank, args.no_cpu)
+        except Exception as ex:
+            other["hard_ransac"] = {"error": str(ex)[:200]}
 
     # ---- the class-shim path (what a drop-in user of the reference's classes gets): one camera, blocking calls ----
     shim = None
@@ -1023,6 +1211,10 @@ def main():
                        "multi_gpu": "replicas only (tracking does not shard); sharded verification under 'verify'",
                        "tracked_ok_frac": state["ok"] / max(state["n"], 1), "mean_inliers": float(np.mean(state["inliers"])),
                        "parity_checked": (parity or {}).get("parity_checked"),
+                       "configs0_tum_1000_feats_frames_per_s": (other.get("configs0_tum_1000") or {}).get("value"),
+                       "configs2_1080p_4000_feats_frames_per_s": (other.get("configs2_1080p_4000") or {}).get("value"),
+                       "hard_ransac_pairs_per_s": (other.get("hard_ransac") or {}).get("value"),
+                       "hard_ransac_mean_iterations": (other.get("hard_ransac") or {}).get("mean_ransac_iterations"),
                        "class_shim_frames_per_s_2000_feats": ((shim or {}).get("feats_2000") or {}).get("frames_per_s"),
                        "class_shim_frames_per_s_1000_feats": ((shim or {}).get("feats_1000") or {}).get("frames_per_s"),
                        # the sharded leg (BASELINE configs[3] / [4]); details under the top-level key "verify"
@@ -1037,7 +1229,7 @@ def main():
                     "d2h_note": "per frame: keypoints (28 B) + descriptors (32 B) for the frame's whole capacity row, the count, the 84-byte RansacSE3 result and mvInliers (16 B per inlier DMatch) -- what Extractor::detectAndCompute and RansacSE3 hand back through the class interface",
                     "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "class_shim_path": shim, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "class_shim_path": shim, "other_configs": other, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
         }))
     for q in reversed(seqs):  # contexts that share a stream close before its owner
         q.close()

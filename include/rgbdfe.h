@@ -91,8 +91,10 @@ int rgbdfe_sync(rgbdfe_ctx* ctx);
  * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
  * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU.
  * "host_zero_copy" (default 1): see rgbdfe_frames_extract.
- * "knn_umma" (default 1): the Hamming kNN of Matcher::match on tcgen05 (k_knn2_umma); 0 selects the mma.sync kernel
- * (k_knn2_hamming), kept for A/B measurements — both are held to the same parity tests.
+ * "knn_umma" (default 1): the Hamming kNN of Matcher::match on tcgen05: 1 = k_knn2_umma (two CTAs per SM, every warp does
+ * every job), 2 = the warp-specialised persistent variant k_knn2_umma_ws (query tile in tensor memory; measured 10 % slower, see
+ * DESIGN.md), 0 = the mma.sync kernel (k_knn2_hamming); 0 and 2 are kept for A/B measurements — all three are held to the
+ * same parity tests.
  * "knn_waves" (default 6): the train range of a pair is split over CTAs so that a kNN launch has about this many
  * waves of CTAs (latency of single pairs against redundant work for whole chains). */
 int rgbdfe_set_option(rgbdfe_ctx* ctx, const char* name, int value);

@@ -448,8 +448,12 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         c->knn_waves = value;
         return RGBDFE_OK;
     }
+    if (!strcmp(name, "knn_dbg")) {
+        c->knn_dbg = value;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "knn_umma")) {
-        c->knn_umma = value != 0;
+        c->knn_umma = value < 0 ? 0 : (value > 2 ? 2 : value);
         return RGBDFE_OK;
     }
     if (!strcmp(name, "ransac_first_chunk")) {

@@ -229,7 +229,9 @@ struct rgbdfe_ctx {
     cudaEvent_t side_fork = nullptr, side_join = nullptr;
     int knn_waves = 6; // train-range splits are chosen to give about this many waves of kNN CTAs (option "knn_waves")
     bool knn_umma_ready = false; // k_knn2_umma's dynamic shared memory attribute set on this context's device
-    int knn_umma = 1; // K7 on tcgen05 (match_umma.cu); 0 = the mma.sync kernel (option "knn_umma")
+    int knn_umma = 1; // K7 on tcgen05 (match_umma.cu): 1 = k_knn2_umma (default, the faster one as measured), 2 = the warp-specialised persistent variant, 0 = mma.sync (option "knn_umma")
+    int knn_dbg = 0;  // developer aid (option "knn_dbg"): bit 0 skips the fold, 1 the train expansion, 2 the multiplications -- wrong results, stage timing only
+    int sm_count = 0; // SMs of the device (grid of the persistent kNN kernel)
     MatchPair* d_pairs = nullptr;   MatchPair* h_pairs = nullptr; // pinned staging
     int4* d_partial = nullptr;      // [pairs][splits][kp_cap]
     rgbdfe_dmatch* d_matches = nullptr; // [pairs][kp_cap]  Matcher::match output (query order)

@@ -183,7 +183,9 @@ int knn_splits_for(const rgbdfe_ctx* c, int npairs)
 {
     const int qpb = c->knn_umma ? 128 : KNN_QPB; // queries per CTA of the selected kernel
     const int qblocks = (c->kp_cap + qpb - 1) / qpb;
-    const int want = (c->knn_waves * 2 * 148 + qblocks * npairs - 1) / (qblocks * npairs);
+    // the persistent kernel (knn_umma == 2) walks work items with a grid stride: splitting only has to give every SM a couple of items
+    const int want = c->knn_umma == 2 ? (2 * 148 + qblocks * npairs - 1) / (qblocks * npairs)
+                                      : (c->knn_waves * 2 * 148 + qblocks * npairs - 1) / (qblocks * npairs);
     const int room = std::max(npairs, 64 * c->knn_splits) / npairs;
     return std::max(1, std::min(std::min(want, c->knn_splits), room));
 }

@@ -242,15 +242,19 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     mbar_wait(&s_bar, 0);
     // image column c lives at s_img[r][c + mis]; s_S uses the same shift
     const int dw = cw - 6, dh = ch - 6;
-    const int th_lo = min(G.iniTh, G.minTh);
     const unsigned lt = (1u << lane) - 1;
-    {
-        // pair test on 4 adjacent pixels per thread: one word-aligned group of shared-memory columns [4g, 4g + 4)
-        const int s_first = 3 + mis; // shared-memory column of the first tested pixel of a row
-        const int g_lo = s_first >> 2, gpr = ((cw - 4 + mis) >> 2) - g_lo + 1;
-        const unsigned inv_gpr = G.inv_small[gpr];
-        const int ngroups = gpr * dh;
-        const unsigned c1 = 0x7fff7fffu - ((unsigned)th_lo | (unsigned)th_lo << 16);
+    // pair test geometry: 4 adjacent pixels per thread = one word-aligned group of shared-memory columns [4g, 4g + 4)
+    const int s_first = 3 + mis; // shared-memory column of the first tested pixel of a row
+    const int g_lo = s_first >> 2, gpr = ((cw - 4 + mis) >> 2) - g_lo + 1;
+    const unsigned inv_gpr = G.inv_small[gpr];
+    const int ngroups = gpr * dh;
+    // cv::FAST(iniThFAST) first; only a cell that comes out EMPTY is redone at minThFAST (:655-661).  Everything -- the pair
+    // test, the strengths, the NMS -- runs at the attempt's own threshold: a neighbour counts in the NMS only if it is a
+    // corner at that threshold, i.e. a candidate of the same attempt, and the candidates at 20 are a small part of those at 7.
+    int th = G.iniTh;
+    int ncand = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        const unsigned c1 = 0x7fff7fffu - ((unsigned)th | (unsigned)th << 16);
         for (int i0 = (tid & ~31); i0 < ngroups; i0 += FAST_THREADS) { // warp-uniform trip count
             const int i = i0 + lane;
             unsigned rA = 0, rB = 0;
@@ -296,17 +300,14 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
                     s_cand[base + n0 + n1 + n2 + __popc(b3 & lt)] = (unsigned short)(key + 3);
             }
         }
-    }
-    __syncthreads();
-    const int ncand = s_ncand;
-    for (int i = tid; i < ncand; i += FAST_THREADS) {
-        const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
-        const int S = fast_strength(&s_img[r][c + mis], PITCH, th_lo);
-        s_S[r][c + mis] = (uint8_t)min(S, 255);
-    }
-    __syncthreads();
-    int th = G.iniTh;
-    for (int attempt = 0; attempt < 2; attempt++) {
+        __syncthreads();
+        ncand = s_ncand;
+        for (int i = tid; i < ncand; i += FAST_THREADS) {
+            const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
+            const int S = fast_strength(&s_img[r][c + mis], PITCH, th);
+            s_S[r][c + mis] = (uint8_t)min(S, 255);
+        }
+        __syncthreads();
         // 3x3 non-max suppression inside the cell's window (cv::FAST, nonmaxSuppression = true), candidates only
         for (int i0 = 0; i0 < ncand; i0 += FAST_THREADS) {
             const int i = i0 + tid;
@@ -344,7 +345,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         __syncthreads();
         if (s_n > 0 || th == G.minTh)
             break;
-        th = G.minTh; // cv::FAST returned nothing at iniThFAST: retry at minThFAST (:658-661)
+        th = G.minTh; // cv::FAST returned nothing at iniThFAST: the cell is redone at minThFAST (:658-661)
+        if (tid == 0)
+            s_ncand = 0; // the candidates at the lower threshold include every one above; their strengths are rewritten
         __syncthreads();
     }
     // row-major output order (cv::FAST emits keypoints row by row): rank each survivor by its (r, c) key

@@ -204,7 +204,7 @@ def test_match_ties_and_degenerate(ctx, oracle):
     assert len(ctx.match(q[:0], t, z[:0], xyz_q[:0], xyz_t, 0.9, True)) == 0
 
 
-@pytest.mark.parametrize("umma", [1, 0])
+@pytest.mark.parametrize("umma", [2, 1, 0])
 def test_match_tile_edges_both_knn_kernels(ctx, oracle, umma):
     """Set sizes around the 128-wide tiles of the tcgen05 kernel (and the 256 / 128 of the mma.sync one), clustered
     descriptors (small distances, many equal ones: the (distance, trainIdx) order decides), several ratios."""
