@@ -408,30 +408,37 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
             return float(t.item())
         return ms
 
-    def timed_queries(v, queries, n_queries_per_call, calls, depth=3):
-        """`calls` enqueues of n_queries_per_call queries each, `depth` in flight; returns ms (device, max over ranks)."""
-        stream = torch.cuda.ExternalStream(v.ctx.stream, device=local_rank)
+    def timed_queries(vs, queries, n_queries_per_call, calls, depth=3, local_only=False):
+        """`calls` enqueues of n_queries_per_call queries each, `depth` in flight, round-robin over the verifiers `vs` (contexts of this
+        GPU: the latency-bound RANSAC tail of one call overlaps the kNN of the next); returns ms (device, max over ranks)."""
+        vs = vs if isinstance(vs, (list, tuple)) else [vs]
+        nv = len(vs)
+        stream = torch.cuda.ExternalStream(vs[0].ctx.stream, device=local_rank)
 
         def run(n):
             for i in range(n + depth):
                 if i >= depth:
-                    v.collect((i - depth) % 4, n_queries_per_call, want=True)
+                    j = i - depth
+                    vs[j % nv].collect((j // nv) % 4, n_queries_per_call, want=True)
                 if i < n:
                     qd, qp = queries[i % len(queries)]
-                    v.enqueue(qd, qp, N_FEAT, n_queries_per_call, i % 4, seed=42)
+                    vs[i % nv].enqueue(qd, qp, N_FEAT, n_queries_per_call, (i // nv) % 4, seed=42)
 
-        run(2)
-        if world > 1:
+        run(2 * nv)
+        if world > 1 and not local_only:
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = v.ctx.launches
+        l0 = sum(v.ctx.launches for v in vs)
         e0.record(stream)
         run(calls)
-        e1.record(stream)  # every slot was collected: all kernels, the gathers and the copies to the host have finished
+        for v in vs[1:]:  # every slot was collected (all kernels, gathers and copies to the host have finished); order the event behind all streams
+            vs[0].ctx.stream_wait(v.ctx)
+        e1.record(stream)
         e1.synchronize()
         torch.cuda.synchronize()
-        return max_over_ranks(e0.elapsed_time(e1)), v.ctx.launches - l0
+        ms_ = e0.elapsed_time(e1)
+        return (ms_ if local_only else max_over_ranks(ms_)), sum(v.ctx.launches for v in vs) - l0
 
     out = {"unit": "pairs/s", "features": N_FEAT, "api": "rgbdfe_verify_sharded_enqueue/_collect (C ABI), NCCL all-gather of 84 B/pair on the context's communication stream"}
     ident = bcast_id() if world > 1 else None
@@ -442,8 +449,19 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     lo, hi = rgbdfe.shard_range(n_kf, rank, world)
     v = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf, kd[lo:hi], kp[lo:hi], ident, max_feats=N_FEAT, depth_cov=cov)
     queries = [(np.ascontiguousarray(np.roll(qd, 13 * i, axis=0)), np.ascontiguousarray(np.roll(qp, 13 * i, axis=0))) for i in range(8)]
+    # `value`: the query frames are resident in HBM (device pointers are read in place); the host-memory form is timed beside it
+    q_dev = [(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()) for a, b in queries]
+    q_ptr = [(a.data_ptr(), b.data_ptr()) for a, b in q_dev]
     calls = 48
-    ms, launches = timed_queries(v, queries, 1, calls)
+    ms_host, _ = timed_queries(v, queries, 1, calls)
+    ms_one, launches = timed_queries(v, q_ptr, 1, calls)
+    # two contexts of this GPU take alternate queries (each its own stream, workspace, resident keyframe block and communicator)
+    vb = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf, kd[lo:hi], kp[lo:hi], bcast_id() if world > 1 else None, max_feats=N_FEAT, depth_cov=cov)
+    ms, _ = timed_queries([v, vb], q_ptr, 1, calls, depth=4)
+    vb.close()
+    out["host_queries_pairs_per_s"] = calls * n_kf / (ms_host * 1e-3)
+    out["one_context_pairs_per_s"] = calls * n_kf / (ms_one * 1e-3)
+    out["contexts_per_gpu"] = 2
     out.update({"value": calls * n_kf / (ms * 1e-3), "keyframes_total": n_kf, "keyframes_per_gpu": hi - lo, "ms_per_query": ms / calls,
                 "scaling": "strong (fixed 1 query x %d keyframes job, keyframes block-sharded over %d GPU(s))" % (n_kf, world),
                 "launches_per_query": launches / calls})
@@ -469,26 +487,13 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     if world > 1:
         single = None
         if rank == 0:
-            v1 = loopverify.CudaShardedVerifier(local_rank, 0, 1, n_kf, kd, kp, None, max_feats=N_FEAT, depth_cov=cov)
-            ms1 = None
+            v1 = [loopverify.CudaShardedVerifier(local_rank, 0, 1, n_kf, kd, kp, None, max_feats=N_FEAT, depth_cov=cov) for _ in range(2)]
             try:
-                stream = torch.cuda.ExternalStream(v1.ctx.stream, device=local_rank)
-                for _ in range(2):
-                    v1.verify(queries[0][0], queries[0][1])
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(stream)
-                n1 = 16
-                for i in range(n1 + 3):
-                    if i >= 3:
-                        v1.collect((i - 3) % 4, 1)
-                    if i < n1:
-                        v1.enqueue(queries[i % 8][0], queries[i % 8][1], N_FEAT, 1, i % 4, seed=42)
-                e1.record(stream)
-                e1.synchronize()
-                ms1 = e0.elapsed_time(e1) / n1
+                ms1, _ = timed_queries(v1, q_ptr, 1, 16, depth=4, local_only=True)
+                ms1 /= 16
             finally:
-                v1.close()
+                for x_ in v1:
+                    x_.close()
             single = n_kf / (ms1 * 1e-3)
         dist.barrier()
         if rank == 0:
@@ -499,19 +504,21 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
 
     # ---- configs[4]: batched relocalisation, 256 queries x 1024 keyframes, one gather per call ----
     try:
-        Q, n_kf4, per_call = 256, 1024, 64
+        Q, n_kf4, per_call = 256, 1024, 32
         qd4, qp4, kd4, kp4, _ = synth.synth_pair_sets(n_kf4, N_FEAT, seed=777, overlap_frac=0.05)
         lo, hi = rgbdfe.shard_range(n_kf4, rank, world)
-        v4 = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf4, kd4[lo:hi], kp4[lo:hi], bcast_id() if world > 1 else None,
-                                            max_feats=N_FEAT, depth_cov=cov)
+        v4 = [loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf4, kd4[lo:hi], kp4[lo:hi], bcast_id() if world > 1 else None,
+                                             max_feats=N_FEAT, depth_cov=cov) for _ in range(2)]
         qs = np.stack([np.roll(qd4, 7 * i, axis=0) for i in range(per_call)])
         ps = np.stack([np.roll(qp4, 7 * i, axis=0) for i in range(per_call)])
-        ms4, _ = timed_queries(v4, [(qs, ps)], per_call, Q // per_call, depth=2)
-        out["relocalisation"] = {"value": Q * n_kf4 / (ms4 * 1e-3), "unit": "pairs/s", "queries": Q, "keyframes_total": n_kf4,
-                                 "keyframes_per_gpu": hi - lo, "ms_total": ms4,
+        reps4 = 3  # three 256-query batches back to back: start-up and tail of the two-context pipeline amortised
+        ms4, _ = timed_queries(v4, [(qs, ps)], per_call, reps4 * Q // per_call, depth=4)
+        out["relocalisation"] = {"value": reps4 * Q * n_kf4 / (ms4 * 1e-3), "unit": "pairs/s", "queries": Q, "keyframes_total": n_kf4,
+                                 "keyframes_per_gpu": hi - lo, "ms_per_256_query_batch": ms4 / reps4,
                                  "what": "BASELINE configs[4]: 256 query frames x 1024 keyframes, all pairs match + RansacSE3(200, 30), "
-                                         "%d queries per call, one all-gather per call" % per_call}
-        v4.close()
+                                         "%d queries per call, one all-gather per call, two contexts per GPU taking alternate calls" % per_call}
+        for x_ in v4:
+            x_.close()
     except Exception as ex:
         out["relocalisation"] = {"error": str(ex)[:200]}
     return out

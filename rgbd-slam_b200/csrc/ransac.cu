@@ -922,33 +922,49 @@ __device__ __forceinline__ void cta_se3_hypothesis(const ReplayCtx& R, const flo
 // walk the chunk's iterations in order and leave as soon as the pair is finished -- instead of one CTA per
 // iteration launched just to find that out.
 template <int THREADS, int NPT>
-__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end)
+__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end, int npairs)
 {
-    __shared__ int s_done;
+    __shared__ int s_done, s_skip;
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    const int pair = R.slot0 + blockIdx.y;
-    for (int h = hyp_begin + blockIdx.x; h < hyp_end || h == hyp_begin + (int)blockIdx.x; h += gridDim.x) {
-        cta_se3_hypothesis<THREADS, NPT>(R, w_all, pair, h, hyp_begin, hyp_end, next_end, blockIdx.x == 0 && h == hyp_begin);
-        const int hn = h + (int)gridDim.x;
-        if (hn >= hyp_end)
-            break;
-        __syncthreads(); // the replay of warp 0 used the shared scratch
-        if (threadIdx.x < 32) {
-            // The next iteration of this CTA may not be drawn yet.  The replay draws more once everything drawn so far has
-            // been consumed, but that needs every CTA of the pair to have run, and CTAs of a grid need not be co-resident
-            // (small SM partitions, many contexts on one GPU): waiting for them could starve them of the slot this CTA
-            // holds.  Samples depend only on the match count and the pair's stream, so this warp draws the chunk itself,
-            // under the pair lock, whenever nobody has yet.
-            const ReplayState* rp = R.replay + pair;
-            int d;
-            while (!(d = ld_volatile(&rp->done) | (ld_volatile(&rp->run) ^ 1)) && next_end < 0 && ld_volatile(&rp->sampled_k) <= hn)
-                warp_draw_ahead(R, pair, hn, -next_end, reinterpret_cast<unsigned*>(smem_dyn), threadIdx.x);
-            if (threadIdx.x == 0)
-                s_done = d;
+    // The first chunk has one grid row per pair.  Later chunks exist only for the pairs whose loop has not ended (a few per
+    // cent of a verification batch): a small grid walks the pairs, one uniform read each.
+    for (int py = blockIdx.y; py < npairs; py += gridDim.y) {
+        const int pair = R.slot0 + py;
+        if (hyp_begin > 0) {
+            if (threadIdx.x == 0) {
+                const ReplayState* rp = R.replay + pair;
+                s_skip = ld_volatile(&rp->done) == 2 ? 1 : 0; // finalised (also every pair that never ran)
+            }
+            __syncthreads();
+            const int skip = s_skip;
+            __syncthreads();
+            if (skip)
+                continue;
         }
-        __syncthreads();
-        if (s_done)
-            break;
+        for (int h = hyp_begin + blockIdx.x; h < hyp_end || h == hyp_begin + (int)blockIdx.x; h += gridDim.x) {
+            cta_se3_hypothesis<THREADS, NPT>(R, w_all, pair, h, hyp_begin, hyp_end, next_end, blockIdx.x == 0 && h == hyp_begin);
+            const int hn = h + (int)gridDim.x;
+            if (hn >= hyp_end)
+                break;
+            __syncthreads(); // the replay of warp 0 used the shared scratch
+            if (threadIdx.x < 32) {
+                // The next iteration of this CTA may not be drawn yet.  The replay draws more once everything drawn so far has
+                // been consumed, but that needs every CTA of the pair to have run, and CTAs of a grid need not be co-resident
+                // (small SM partitions, many contexts on one GPU): waiting for them could starve them of the slot this CTA
+                // holds.  Samples depend only on the match count and the pair's stream, so this warp draws the chunk itself,
+                // under the pair lock, whenever nobody has yet.
+                const ReplayState* rp = R.replay + pair;
+                int d;
+                while (!(d = ld_volatile(&rp->done) | (ld_volatile(&rp->run) ^ 1)) && next_end < 0 && ld_volatile(&rp->sampled_k) <= hn)
+                    warp_draw_ahead(R, pair, hn, -next_end, reinterpret_cast<unsigned*>(smem_dyn), threadIdx.x);
+                if (threadIdx.x == 0)
+                    s_done = d;
+            }
+            __syncthreads();
+            if (s_done)
+                break;
+        }
+        __syncthreads(); // the next pair reuses the shared state
     }
 }
 
@@ -959,7 +975,8 @@ static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem
     int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
     if (nblk > max_ctas)
         nblk = max_ctas;
-    k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, npairs), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end);
+    const int rows = b == 0 ? npairs : (npairs < 37 ? npairs : 37); // later chunks: 8 x 37 = 296 CTAs = one resident wave walks the pairs
+    k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, rows), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end, npairs);
     c->launches++;
     return RGBDFE_OK;
 }
