@@ -739,6 +739,7 @@ def main():
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--core-only", action="store_true", help="profiling runs: only the headline workload, none of the other legs")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
     ap.add_argument("--mode", default="full", choices=["full", "extract", "chain", "serial", "verify", "shim", "configs"],
@@ -1057,6 +1058,8 @@ def main():
     # ---- row N1: Frame preprocessing (BGR -> gray, 16-bit depth, undistortion, grid cells) + extraction, end to end ----
     frame_prep = projection = None
     try:
+        if args.core_only:
+            raise RuntimeError("skipped (--core-only)")
         tum = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989, dist=[0.262383, -0.953104, -0.005358, 0.002628, 1.163314],
                    factor=DEPTH_FACTOR)
         nseq = 8
@@ -1116,19 +1119,23 @@ def main():
 
     # ---- row N3: the cv::ORB branch of Extractor ----
     try:
+        if args.core_only:
+            raise RuntimeError("skipped (--core-only)")
         cvorb = cvorb_leg(rgbdfe, torch, local_rank, gray_d, depth_d, cam, inv_factor, B, NFEAT, args.no_cpu, frames)
     except Exception as ex:
         cvorb = {"error": str(ex)[:200]}
 
     # ---- sharded loop-pair verification (the part of the path that shards), N >= 1 ----
     try:
+        if args.core_only:
+            raise RuntimeError("skipped (--core-only)")
         verify = verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world)
     except Exception as ex:  # the headline metric does not depend on this leg
         verify = {"error": str(ex)[:300]}
 
     # ---- the other BASELINE configs and a hard-RANSAC workload, same pipeline (rank 0 only; not part of the headline) ----
     other = {}
-    if rank == 0 and args.mode == "full":
+    if rank == 0 and args.mode == "full" and not args.core_only:
         for key, a in (("configs0_tum_1000", ("tum_fr1", 1000, 200, 10, 32, 32, 32, 4, "BASELINE configs[0]: TUM fr1-shaped 640x480, 1000 ORB features, RansacSE3(200, 10) as Tracking.cpp:129")),
                        ("configs2_1080p_4000", ("kinect2", 4000, 500, 10, 8, 8, 8, 4, "BASELINE configs[2]: Kinect-v2-shaped 1920x1080 frames with registered depth, 4000 ORB features"))):
             try:
@@ -1142,7 +1149,7 @@ def main():
 
     # ---- the class-shim path (what a drop-in user of the reference's classes gets): one camera, blocking calls ----
     shim = None
-    if rank == 0:
+    if rank == 0 and not args.core_only:
         try:
             shim = {"feats_2000": shim_leg(frames, cam, NFEAT), "feats_1000": shim_leg(frames, cam, 1000)}
         except Exception as ex:
