@@ -53,17 +53,20 @@ ALG_BYTES = {
     "k_knn2_umma": (NFEAT + NFEAT) * 32 + NFEAT * 16,  # both descriptor sets once + one int4 per query
 }
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
-# captures summarised in profiles/r1_ncu_full_brief.txt, and the unit that actually limits each kernel there.
+# captures summarised in profiles/r2_ncu_full_brief.txt, and the unit that actually limits each kernel there.
 NCU_TRAFFIC_64 = {
-    "k_fast_cells": 65.02e6 + 3.64e6, "k_gauss7": 72.84e6 + 31.39e6, "k_orient_describe": 139.05e6 + 9.66e6,
+    "k_fast_cells": 65.02e6 + 3.82e6, "k_gauss7": 72.85e6 + 32.05e6, "k_orient_describe": 139.07e6 + 9.30e6,
     "k_knn2_umma": 4.21e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
+# warp instructions of one 64-frame launch (smsp__inst_executed.sum) -> thread instructions per pixel of the levels it covers
+NCU_WARP_INST_64 = {"k_fast_cells": 218.26e6, "k_gauss7": 86.54e6, "k_orient_describe": 115.37e6, "k_quadtree": 31.92e6, "k_knn2_umma": 50.57e6}
 NCU_LIMITER = {
-    "k_fast_cells": "issue slots 79 % busy, ALU pipe 62 % (16-bit-lane min/max work), tiles staged by TMA: instruction-bound; DRAM traffic = 1.1x algorithmic, 4 % of peak",
-    "k_gauss7": "issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 59 %; DRAM 17 % of peak",
-    "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 74 %; DRAM 16 % of peak",
-    "k_knn2_umma": "tcgen05.mma kind::i8 (UTCIMMA), tensor pipe 30 % busy; the 8 warps that expand the operands and drain TMEM into the top-2 issue 45 % of the time (2 CTAs x 8 warps per SM: TMEM-bound occupancy); DRAM < 1 % of peak",
+    "k_fast_cells": "instruction-bound: issue slots 76 % busy, integer ALU pipe 61 % (16-bit-lane min/max; every integer ALU instruction costs a warp two issue clocks), tiles staged by TMA; DRAM traffic = 1.1x algorithmic, 4 % of peak",
+    "k_gauss7": "instruction-bound: issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 60 %; DRAM 17 % of peak",
+    "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 73 %; DRAM 16 % of peak: the gather set of a 64-frame batch (141 MB) exceeds the 126 MB L2",
+    "k_knn2_umma": "tcgen05.mma kind::i8 (UTCIMMA), tensor pipe 32 % busy; the warps that expand the operands and drain TMEM into the top-2 keep the integer ALU pipe 45 % busy and wait on each other at CTA barriers (2 CTAs x 8 warps per SM: TMEM-bound occupancy); DRAM < 1 % of peak",
     "k_quadtree": "latency (shared-memory atomics and scans, one CTA per level and frame): issue 32 %",
+    "k_se3_hypotheses": "latency: one pair = 4-32 CTAs of dependent FP32 / FP64 chains; sm throughput 2 %, FP64 pipe 5 %, issue 14 % (ncu, profiles/r2_ncu_full_brief.txt)",
 }
 METRIC = "tracked frames/s (ORB+match+SE3 RANSAC, 640x480)"
 WORKLOAD = "ICL-NUIM-shaped 640x480, 2000 ORB feats, kNN k=2 ratio 0.9, RansacSE3 500 iters (BASELINE configs[1])"
@@ -1032,6 +1035,8 @@ def main():
         "traffic": (traffic * B / 64.0) if traffic else None,
         "algorithmic_bytes_per_launch": per_launch_bytes,
         "limiter": NCU_LIMITER.get(dom),
+        "thread_instructions_per_pixel": (NCU_WARP_INST_64[dom] * 32 / (64.0 * SUM_P)) if dom in NCU_WARP_INST_64 else None,
+        "bound_note": "the kernel is instruction-bound, not memory-bound: `frac` says how far it is from the HBM roof, `limiter` and the instructions per pixel say what to cut",
         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
         "per_kernel": {k: {"ms": v[0] / v[1], "algorithmic_GBps": ALG_BYTES[k] * B / (v[0] / v[1] * 1e-3) / 1e9} for k, v in kernels.items()
                        if k in ALG_BYTES and v[1] > 0},

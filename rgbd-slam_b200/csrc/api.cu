@@ -255,6 +255,10 @@ void free_orb_workspaces(rgbdfe_ctx* c)
 
 void free_pair_workspaces(rgbdfe_ctx* c)
 {
+    for (auto& g : c->chain_graph_cache) // the captured launches name these buffers
+        if (g.exec)
+            cudaGraphExecDestroy(g.exec);
+    c->chain_graph_cache.clear();
     cudaFree(c->d_pairs), cudaFree(c->d_partial), cudaFree(c->d_matches), cudaFree(c->d_sorted), cudaFree(c->d_P1), cudaFree(c->d_P2), cudaFree(c->d_w), cudaFree(c->d_nmatch), cudaFree(c->d_samples);
     cudaFree(c->d_rng_used), cudaFree(c->d_hyp), cudaFree(c->d_hyp_mask), cudaFree(c->d_replay), cudaFree(c->d_inl_pos), cudaFree(c->d_pair_rng), cudaFree(c->d_hyp_ready), cudaFree(c->d_pair_lock);
     c->d_sorted = nullptr, c->d_P1 = nullptr, c->d_P2 = nullptr, c->d_w = nullptr;
@@ -446,6 +450,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         if (value < 1 || value > 64)
             return RGBDFE_E_ARG;
         c->knn_waves = value;
+        return RGBDFE_OK;
+    }
+    if (!strcmp(name, "chain_graphs")) {
+        c->chain_graphs = value != 0;
         return RGBDFE_OK;
     }
     if (!strcmp(name, "knn_dbg")) {
@@ -1488,10 +1496,71 @@ int rgbdfe_track_sequence(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count,
     Se3Params prm = make_params(c, iterations, min_inlier_th, max_mahal, sample_size);
     rgbdfe::FusedFilter ff = { splits, ratio, discard_outliers };
     c->last_track_slot = first_result_slot, c->last_track_pairs = np;
-    for (int p = 0; p < np; p++)
-        if ((rc = launch_ransac_se3(c, c->d_pairs, p, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + first_result_slot + p, &ff)) != RGBDFE_OK)
+    // The sequential part is two small kernels per pair, 128 dependent launches for a 64-frame batch, every one with the same
+    // arguments batch after batch (the pair table is rebuilt above, workspaces and result slots are fixed).  Launches are a
+    // host-side resource -- the driver serialises them per device context, about 3.5 us each, which with 32 sequences in flight
+    // was a third of the whole step -- so the launch sequence of a chain is captured once per (length, parameters) and replayed
+    // as ONE graph launch.  The first call with a given key runs un-captured (it also raises the kernels' shared-memory limits).
+    const bool graphable = c->chain_graphs && np >= 4 && !c->profiling && !c->dbg_on;
+    ChainGraphKey key;
+    memset(&key, 0, sizeof(key)); // compared bytewise: padding must be defined
+    key = ChainGraphKey { np, first_result_slot, splits, discard_outliers, iterations, (int)min_inlier_th, (int)sample_size, update_f2, c->ransac_first_chunk,
+        ratio, max_mahal, (void*)c->d_pairs };
+    ChainGraph* cg = nullptr;
+    if (graphable) {
+        for (auto& g : c->chain_graph_cache)
+            if (!memcmp(&g.key, &key, sizeof(key))) {
+                cg = &g;
+                break;
+            }
+        if (!cg) {
+            if (c->chain_graph_cache.size() >= 8) { // a handful of chain shapes per context; drop the oldest
+                if (c->chain_graph_cache.front().exec)
+                    cudaGraphExecDestroy(c->chain_graph_cache.front().exec);
+                c->chain_graph_cache.erase(c->chain_graph_cache.begin());
+            }
+            ChainGraph fresh;
+            memset(&fresh.key, 0, sizeof(fresh.key));
+            fresh.key = key;
+            c->chain_graph_cache.push_back(fresh);
+            cg = &c->chain_graph_cache.back();
+        }
+    }
+    if (cg && cg->exec) {
+        CUDA_TRY(c, cudaGraphLaunch(cg->exec, c->stream));
+        c->launches += 2 * np; // the graph's kernel nodes
+        return RGBDFE_OK;
+    }
+    const bool capture = cg && cg->seen > 0; // second call with this key
+    if (capture)
+        CUDA_TRY(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    for (int p = 0; p < np && rc == RGBDFE_OK; p++)
+        rc = launch_ransac_se3(c, c->d_pairs, p, 1, prm, update_f2, 0, 0, 0, 0, c->d_results + first_result_slot + p, &ff);
+    if (capture) {
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        if (rc != RGBDFE_OK || e != cudaSuccess || !graph) {
+            if (graph)
+                cudaGraphDestroy(graph);
+            cudaGetLastError();
+            if (rc == RGBDFE_OK) {
+                c->set_error(std::string("track_sequence: stream capture failed: ") + cudaGetErrorString(e));
+                rc = RGBDFE_E_CUDA;
+            }
             return rc;
-    return RGBDFE_OK;
+        }
+        const cudaError_t ei = cudaGraphInstantiate(&cg->exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) {
+            cg->exec = nullptr;
+            c->set_error(std::string("track_sequence: cudaGraphInstantiate: ") + cudaGetErrorString(ei));
+            return RGBDFE_E_CUDA;
+        }
+        CUDA_TRY(c, cudaGraphLaunch(cg->exec, c->stream)); // nothing ran during the capture
+    }
+    if (cg)
+        cg->seen++;
+    return rc;
 }
 
 int rgbdfe_track_results(rgbdfe_ctx* c, int first, int count, rgbdfe_se3_result* results)

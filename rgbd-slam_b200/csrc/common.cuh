@@ -177,6 +177,18 @@ struct UmeState {
     int total_calls; // rand() calls made while drawing all initial iterations
 };
 
+// A captured chain (rgbdfe_track_sequence): the 2 x np kernel launches of the sequential part as one graph.
+struct ChainGraphKey {
+    int np, first_slot, splits, discard, iterations, min_inl, sample, update_f2, first_chunk;
+    float ratio, max_mahal;
+    void* pairs; // the workspace generation
+};
+struct ChainGraph {
+    ChainGraphKey key;
+    cudaGraphExec_t exec = nullptr;
+    int seen = 0;
+};
+
 struct rgbdfe_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -261,6 +273,8 @@ struct rgbdfe_ctx {
     struct CvOrbWorkspace* cvorb = nullptr; // the cv::ORB branch of Extractor (row N3, orb_cv.cu), allocated by rgbdfe_cvorb_configure
     int extractor = 0;                      // RGBDFE_EXTRACTOR_ORB2 / RGBDFE_EXTRACTOR_ORB: which one the extraction entry points run
     struct ProjWorkspace* proj = nullptr; // Matcher::projectionMatch buffers, allocated on first use (projection.cu)
+    bool chain_graphs = true; // option "chain_graphs": replay a chain's launch sequence as one CUDA graph
+    std::vector<ChainGraph> chain_graph_cache;
     int last_track_slot = 0, last_track_pairs = 0; // result slots of the last rgbdfe_track / rgbdfe_track_sequence (pair p -> slot + p)
     rgbdfe_dmatch* d_packed = nullptr; rgbdfe_dmatch* h_packed = nullptr; size_t packed_cap = 0; // rgbdfe_track_results_inliers staging
     unsigned char* d_dl = nullptr; size_t dl_bytes = 0; // rgbdfe_frames_download_async staging

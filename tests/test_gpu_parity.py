@@ -489,6 +489,42 @@ def test_tracking_pipeline_device_resident(oracle, seq_vga, chain):
         ctx.close()
 
 
+def test_chain_replayed_as_a_graph_is_identical(oracle):
+    """rgbdfe_track_sequence captures a chain's launch sequence on the second call with the same shape and replays it as one CUDA
+    graph afterwards: call 1 (plain launches), call 2 (capture + launch) and call 3 (replay) must give the same bytes -- results,
+    inlier lists, outlier flags, rand() position -- and the first pair must equal the oracle."""
+    import rgbdfe
+    import synth
+
+    cam, frames = synth.sequence("tum_fr1", n=6, seed=777)
+    ctx = rgbdfe.Context(0, 640, 480, 1000, 6)
+    try:
+        fr = [rgbdfe.Frame(ctx) for _ in frames]
+        runs = []
+        for rep in range(4):
+            if rep == 3:
+                ctx.set_option("chain_graphs", 0)  # and once more without graphs
+            ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)  # resets the outlier flags
+            ctx.rng_seed(42)
+            ctx.depth_cov_set(0, 0.0)
+            ctx.track_sequence(fr, 0)
+            res, inl = ctx.track_results_inliers(0, len(frames) - 1)
+            flags = b"".join(f.download()[3].tobytes() for f in fr)
+            runs.append((res.tobytes(), b"".join(x.tobytes() for x in inl), flags, ctx.rng_get_state().tobytes()))
+        assert runs[0] == runs[1] == runs[2] == runs[3]
+        res = np.frombuffer(runs[0][0], rgbdfe.SE3_DTYPE)
+        assert res["ok"].all() and res["n_inliers"].min() > 100
+        orb = oracle.Orb(1000)
+        k0, d0 = orb.extract(frames[0][0])
+        k1, d1 = orb.extract(frames[1][0])
+        p0, p1 = _unproject(cam, k0, frames[0][1]), _unproject(cam, k1, frames[1][1])
+        m = oracle.match(d0, d1, np.zeros(len(k0), np.uint8), p0, p1, 0.9, True)
+        r = oracle.ransac_se3(p0, p1, m, oracle.Rng(42), oracle.Latch(), 200, 10, 3.0, 4)
+        assert res[0]["n_matches"] == len(m) and res[0]["n_inliers"] == len(r["inliers"]) and res[0]["iters_executed"] == r["iters_executed"]
+    finally:
+        ctx.close()
+
+
 def test_verify_batch_matches_per_pair_oracle(oracle):
     """Config-4-shaped (small): one query vs keyframes, per-pair srand(seed + index)."""
     import rgbdfe
