@@ -83,89 +83,107 @@ __device__ void warp_partition_range(SKey* a, int f, int l, int* Lpos, int* Rpos
     *cut_out = cut;
 }
 
-// All PREP_THREADS threads call this.  a: smem keys; scratch: Lpos[n], Rpos[n], leaves[n],
-// lists: 2 x QCAP ranges (f, l, depth packed in int3).
+// Called by the first `nthr` threads of the CTA (a multiple of 32); a: smem keys; scratch: Lpos[n], Rpos[n], leaves[n], a queue of
+// SORT_QCAP ranges (f, l, depth) in qa and its publication flags in qb.  Synchronises on named barrier 1.
+//
+// Ranges are independent once created, so there is no level-by-level barrier: every warp takes a range from a shared queue and
+// follows it depth-first -- partition, hand the right part to the queue (another warp picks it up at once), go on with the left
+// part -- until what it holds is a leaf.  The critical path is the two or three big partitions at the top; the many small ranges
+// below them (17 .. 40 keys: match distances are heavily tied) run concurrently instead of costing a CTA barrier per level.
+// Every range > 16 that is ever queued is a distinct node of the recursion tree with >= 17 keys: at most 2 n / 17 < SORT_QCAP
+// pushes for n <= 4096, so queue slots are never reused.  counters: [0] head, [1] tail, [2] ranges in flight, [3] leaves.
 #define SORT_QCAP 512
-// Called by the first `nthr` threads of the CTA (a multiple of 32); synchronises on named barrier 1.
 #define SORT_BAR() asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory")
-__device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, int3* qa, int3* qb, int* counters /* [3] */, int nthr, long long* dbg = nullptr)
+__device__ void cta_std_sort(SKey* a, int n, int* Lpos, int* Rpos, int* leaves, int3* qa, int3* qb, int* counters /* [4] */, int nthr, long long* dbg = nullptr)
 {
-    int dbg_level = 0;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     if (n <= 1)
         return;
+    volatile int* vc = counters;
+    volatile int* ready = reinterpret_cast<volatile int*>(qb); // ready[slot] = slot + 1 once qa[slot] is written
+    for (int i = tid; i < SORT_QCAP; i += nthr)
+        ready[i] = 0;
     if (tid == 0) {
         int lg = 0;
         for (int t = n; t > 1; t >>= 1)
             lg++;
-        counters[0] = 0; // next-list size
-        counters[1] = 0; // leaf count
+        counters[0] = 0, counters[3] = 0;
         if (n > 16) {
             qa[0] = make_int3(0, n, 2 * lg);
-            counters[2] = 1; // current-list size
+            counters[1] = 1, counters[2] = 1;
         } else {
             leaves[0] = 0 | (n << 16);
-            counters[1] = 1;
-            counters[2] = 0;
+            counters[1] = 0, counters[2] = 0, counters[3] = 1;
         }
     }
     SORT_BAR();
-    int3* cur = qa;
-    int3* nxt = qb;
-    while (true) {
-        const int ncur = counters[2];
-        if (ncur == 0)
-            break;
-        if (dbg && tid == 0 && dbg_level < 40) {
-            dbg[2 * dbg_level] = dbg_now();
-            dbg[2 * dbg_level + 1] = ncur;
-            dbg_level++;
+    if (tid == 0 && n > 16)
+        ready[0] = 1;
+    if (dbg && tid == 0)
+        dbg[0] = dbg_now();
+    for (;;) {
+        // ---- take a range ----
+        int f = 0, l = 0, depth = -1;
+        if (lane == 0) {
+            for (;;) {
+                const int h = vc[0];
+                if (h < vc[1]) {
+                    if (atomicCAS(&counters[0], h, h + 1) == h) {
+                        while (ready[h] != h + 1) { }
+                        __threadfence_block();
+                        const int3 rg = qa[h];
+                        f = rg.x, l = rg.y, depth = rg.z;
+                        break;
+                    }
+                } else if (vc[2] == 0)
+                    break; // nothing queued and nothing in flight: the sort is done
+            }
         }
-        for (int r = warp; r < ncur; r += nwarps) {
-            const int3 rg = cur[r];
-            const int f = rg.x, l = rg.y, depth = rg.z;
+        f = __shfl_sync(0xffffffffu, f, 0), l = __shfl_sync(0xffffffffu, l, 0), depth = __shfl_sync(0xffffffffu, depth, 0);
+        if (depth < 0)
+            break;
+        // ---- follow it depth-first ----
+        for (;;) {
+            if (l - f <= 16) {
+                if (lane == 0 && l - f > 1)
+                    leaves[atomicAdd(&counters[3], 1)] = f | (l << 16);
+                break;
+            }
             if (depth == 0) { // heapsort fallback of __introsort_loop; the range is then fully sorted
                 if (lane == 0)
                     heap_sort_(a + f, a + l, KeyLess());
                 __syncwarp();
-                continue;
+                break;
             }
             int cut;
-            warp_partition_range(a, f, l, Lpos, Rpos, lane, &cut, (dbg && r == 0 && dbg_level < 12) ? dbg + 80 + 8 * dbg_level : nullptr);
-            if (dbg && r == 0 && lane == 0 && dbg_level < 12) dbg[80 + 8 * dbg_level + 6] = l - f;
+            warp_partition_range(a, f, l, Lpos, Rpos, lane, &cut);
+            depth--;
+            // right part [cut, l): to the queue when it needs another partition, a leaf otherwise; this warp keeps the left part
             if (lane == 0) {
-                // right part [cut, l) and left part [f, cut), both with depth - 1
-                const int parts[2][2] = { { cut, l }, { f, cut } };
-                for (int s = 0; s < 2; s++) {
-                    const int pf = parts[s][0], pl = parts[s][1];
-                    if (pl - pf > 16) {
-                        const int slot = atomicAdd(&counters[0], 1);
-                        if (slot < SORT_QCAP)
-                            nxt[slot] = make_int3(pf, pl, depth - 1);
-                    } else if (pl - pf > 1) {
-                        const int slot = atomicAdd(&counters[1], 1);
-                        leaves[slot] = pf | (pl << 16);
+                if (l - cut > 16) {
+                    atomicAdd(&counters[2], 1);
+                    const int slot = atomicAdd(&counters[1], 1);
+                    if (slot < SORT_QCAP) {
+                        qa[slot] = make_int3(cut, l, depth);
+                        __threadfence_block();
+                        ready[slot] = slot + 1;
                     }
-                }
+                } else if (l - cut > 1)
+                    leaves[atomicAdd(&counters[3], 1)] = cut | (l << 16);
             }
+            l = cut;
         }
-        if (dbg && tid == 0 && dbg_level < 12) dbg[80 + 8 * dbg_level + 5] = dbg_now();
-        SORT_BAR();
-        if (tid == 0) {
-            counters[2] = min(counters[0], SORT_QCAP);
-            counters[0] = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            atomicSub(&counters[2], 1);
         }
-        int3* t = cur;
-        cur = nxt;
-        nxt = t;
-        SORT_BAR();
+        __syncwarp();
     }
-    if (dbg && tid == 0 && dbg_level < 40) {
-        dbg[2 * dbg_level] = dbg_now();
-        dbg[2 * dbg_level + 1] = -counters[1];
-    }
+    SORT_BAR();
+    if (dbg && tid == 0)
+        dbg[2] = dbg_now(), dbg[3] = -counters[3];
     // final insertion sort, leaf by leaf (stable insertion == __final_insertion_sort restricted to the leaf)
-    const int nleaves = counters[1];
+    const int nleaves = counters[3];
     for (int r = tid; r < nleaves; r += nthr) {
         const int f = leaves[r] & 0xffff, l = leaves[r] >> 16;
         for (int i = f + 1; i < l; i++) {
