@@ -527,7 +527,7 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     return out
 
 
-def config_leg(rgbdfe, torch, local_rank, cam_name, nfeat, iters, min_inl, n_frames, B_, S_, steps, no_cpu, what):
+def config_leg(rgbdfe, torch, local_rank, cam_name, nfeat, iters, min_inl, n_frames, B_, S_, steps, no_cpu, what, first_chunk=4):
     """Another BASELINE config through the same pipeline as the headline (batched extraction of device-resident frames in
     one context, the match / RANSAC chain in another, S_ independent sequences in flight): frames/s on the device (CUDA
     events), mean executed RANSAC iterations, and the CPU port (reference flags, all cores) on the same frames beside it."""
@@ -546,7 +546,7 @@ def config_leg(rgbdfe, torch, local_rank, cam_name, nfeat, iters, min_inl, n_fra
             self.cx, self.ct = rgbdfe.Context(local_rank, w_, h_, nfeat, B_), rgbdfe.Context(local_rank, w_, h_, nfeat, 1)
             self.cx.orb_configure(nfeat, 1.2, 8, 20, 7)
             self.ct.set_stream_priority(True)
-            self.ct.set_option("ransac_first_chunk", 4 if S_ > 1 else 32)
+            self.ct.set_option("ransac_first_chunk", first_chunk if S_ > 1 else 32)
             self.ct.rng_seed(42 + k)
             self.sets = [[rgbdfe.Frame(self.cx) for _ in range(B_)] for _ in range(3)]
             self.order, self.i, self.have_ref = pingpong(n_frames), 0, False
@@ -615,7 +615,7 @@ def config_leg(rgbdfe, torch, local_rank, cam_name, nfeat, iters, min_inl, n_fra
         e1.synchronize()
         ms = e0.elapsed_time(e1)
         out = {"what": what, "value": steps * S_ * B_ / (ms * 1e-3), "unit": "frames/s", "image": f"{w_}x{h_}", "features": nfeat, "ransac": f"RansacSE3({iters}, {min_inl}, 3.0, 4)",
-               "sequences_in_flight": S_, "batch": B_, "mean_ransac_iterations": float(np.mean([x for q in qs for x in q.iters])),
+               "sequences_in_flight": S_, "batch": B_, "ransac_first_chunk": first_chunk, "mean_ransac_iterations": float(np.mean([x for q in qs for x in q.iters])),
                "mean_inliers": float(np.mean([x for q in qs for x in q.inl])), "tracked_ok_frac": sum(q.ok for q in qs) / max(sum(q.n for q in qs), 1),
                "keypoints_per_frame": int(len(qs[0].sets[0][0].download()[0]))}
     finally:
@@ -793,7 +793,7 @@ def main():
     cam, frames = make_sequence(F)
     if args.mode == "configs":  # diagnostic: the other-config legs alone
         o = {"configs0": config_leg(rgbdfe, torch, local_rank, "tum_fr1", 1000, 200, 10, 32, 32, 32, 4, args.no_cpu, "configs[0]"),
-             "configs2": config_leg(rgbdfe, torch, local_rank, "kinect2", 4000, 500, 10, 8, 8, 8, 4, args.no_cpu, "configs[2]"),
+             "configs2": config_leg(rgbdfe, torch, local_rank, "kinect2", 4000, 500, 10, 8, 8, 8, 4, args.no_cpu, "configs[2]", first_chunk=32),
              "hard": hard_ransac_leg(rgbdfe, torch, local_rank, args.no_cpu)}
         print(json.dumps(o))
         return
@@ -1144,7 +1144,8 @@ def main():
         for key, a in (("configs0_tum_1000", ("tum_fr1", 1000, 200, 10, 32, 32, 32, 4, "BASELINE configs[0]: TUM fr1-shaped 640x480, 1000 ORB features, RansacSE3(200, 10) as Tracking.cpp:129")),
                        ("configs2_1080p_4000", ("kinect2", 4000, 500, 10, 8, 8, 8, 4, "BASELINE configs[2]: Kinect-v2-shaped 1920x1080 frames with registered depth, 4000 ORB features"))):
             try:
-                other[key] = config_leg(rgbdfe, torch, local_rank, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], args.no_cpu, a[8])
+                other[key] = config_leg(rgbdfe, torch, local_rank, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], args.no_cpu, a[8],
+                                        first_chunk=32 if key.startswith("configs2") else 4)  # configs[2]'s pairs run hundreds of iterations: 32 hypotheses at a time
             except Exception as ex:
                 other[key] = {"error": str(ex)[:200]}
         try:

@@ -236,8 +236,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         s_ncand = 0;
         s_n = 0;
     }
-    for (int i = tid; i < (PITCH / 4) * ch; i += FAST_THREADS)
-        reinterpret_cast<unsigned*>(&s_S[0][0])[i] = 0u;
+    for (int i = tid; i < (PITCH / 16) * ch; i += FAST_THREADS) // 16-byte stores: six per row, one or two passes
+        reinterpret_cast<uint4*>(&s_S[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     mbar_wait(&s_bar, 0);
     // image column c lives at s_img[r][c + mis]; s_S uses the same shift

@@ -975,7 +975,7 @@ static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem
     int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
     if (nblk > max_ctas)
         nblk = max_ctas;
-    const int rows = b == 0 ? npairs : (npairs < 148 ? npairs : 148); // later chunks: at most 8 x 148 CTAs walk the pairs (an all-finished batch costs four idle waves, a hard one keeps every SM busy)
+    const int rows = b == 0 ? npairs : (npairs < 296 ? npairs : 296); // later chunks: at most 8 x 296 CTAs walk the pairs (an all-finished batch costs a few idle waves, a hard one keeps every SM busy)
     k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, rows), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end, npairs);
     c->launches++;
     return RGBDFE_OK;
