@@ -738,7 +738,8 @@ def main():
     ap.add_argument("--extract-streams", type=int, default=0, help="extraction contexts share this many streams (0 = one stream each)")
     ap.add_argument("--overlap-blur", type=int, default=0, help="diagnostic: run the blur beside the quadtree on a side stream")
     ap.add_argument("--knn-waves", type=int, default=0, help="diagnostic: waves of kNN CTAs the train-range split aims for (0 = library default)")
-    ap.add_argument("--first-chunk", type=int, default=4, help="speculative RANSAC iterations of the first launch when several sequences share the GPU")
+    ap.add_argument("--first-chunk", type=int, default=1, help="speculative RANSAC iterations of the first launch when several sequences share the GPU "
+                    "(1: no speculation; measured 72.9 k / 69.6 k / 64.8 k / 56.7 k frames/s at 1 / 2 / 4 / 8: idle speculative CTAs take SM space from the throughput kernels)")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
     ap.add_argument("--no-cpu", action="store_true")
