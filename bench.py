@@ -743,6 +743,7 @@ def main():
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--profile-host", action="store_true", help="diagnostic: the per-kernel timing pass runs with pinned HOST inputs (the e2e path)")
     ap.add_argument("--core-only", action="store_true", help="profiling runs: only the headline workload, none of the other legs")
     ap.add_argument("--latency-sms", type=int, default=0,
                     help="SMs given to the match/RANSAC chains (green-context partition); 0 = share all SMs through stream priorities")
@@ -1004,7 +1005,7 @@ def main():
         cx._chk(lib.rgbdfe_profile_enable(cx.h, 1))
     prof_steps = 2
     for _ in range(prof_steps):
-        step(True)
+        step(not args.profile_host)
     for cx in (ctx_x, ctx_t):
         a_ms = (C.c_double * 16)()
         a_cnt = (C.c_longlong * 16)()
