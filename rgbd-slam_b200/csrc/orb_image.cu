@@ -188,6 +188,8 @@ __global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cf
 // dependent global loads.
 struct FastGrid {
     int iniTh, minTh;
+    int rows;     // rows of the largest cell window (max hCell + 6): the shared-memory images are sized for the configuration, not for CELL_MAX_DIM
+    int cand_cap; // pixels of the largest cell window
     unsigned inv_small[32]; // 0xffffffff / d + 1 for d = 1..31: i / d == umulhi(i, inv_small[d]) (groups per cell row)
 };
 // Tensor maps of the pyramid levels, resident in global memory (one 128-byte descriptor per level): the padded level of
@@ -202,7 +204,7 @@ struct FastCell {
     short outX, outY, level, box_rows; // box_rows = hCell + 6: rows of the level's TMA box
 };
 
-#define FAST_THREADS 256
+#define FAST_THREADS 128 // 4 warps per cell: 225 pixel groups of the pair test in two passes, the later (sparser) phases idle fewer warps; measured 0.225 / 0.196 / 0.207 ms at 256 / 128 / 64
 __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FastGrid G, const FastMaps* __restrict__ maps, const FastCell* __restrict__ cells,
     int* __restrict__ cell_count, unsigned* __restrict__ cell_list, int cell_slot)
 {
@@ -218,10 +220,15 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         return;
     }
     constexpr int PITCH = CELL_MAX_DIM + 24; // window + up to 15 bytes of alignment shift, multiple of 16
-    __shared__ __align__(128) uint8_t s_img[CELL_MAX_DIM][PITCH];
-    __shared__ __align__(16) uint8_t s_S[CELL_MAX_DIM][PITCH];
-    __shared__ unsigned short s_cand[CELL_MAX_DIM * CELL_MAX_DIM]; // pixels that pass the pair test: r << 8 | c
-    __shared__ unsigned short s_keep[CELL_MAX_DIM * CELL_MAX_DIM]; // NMS survivors of this attempt: r << 8 | c, unordered
+    // dynamic shared memory sized for this configuration's largest cell (a 37 x 37 window at 640 x 480: 12.6 KB instead of the
+    // 34.5 KB of a CELL_MAX_DIM window, so that threads, not shared memory, limit the CTAs per SM)
+    extern __shared__ __align__(128) uint8_t fast_smem[];
+    uint8_t* const s_img = fast_smem;                                  // [rows][PITCH], TMA destination
+    uint8_t* const s_S = fast_smem + (size_t)G.rows * PITCH;           // [rows][PITCH] corner strengths (PITCH * rows is a multiple of 32)
+    unsigned short* const s_cand = reinterpret_cast<unsigned short*>(s_S + (size_t)G.rows * PITCH); // pixels that pass the pair test: r << 8 | c
+    unsigned short* const s_keep = s_cand + G.cand_cap;               // NMS survivors of this attempt: r << 8 | c, unordered
+#define S_IMG(r, x) s_img[(r) * PITCH + (x)]
+#define S_S(r, x) s_S[(r) * PITCH + (x)]
     __shared__ int s_ncand, s_n;
     __shared__ __align__(8) uint64_t s_bar;
     // The cell's window is staged by the TMA unit: one thread arms the barrier and issues the tensor copy (box 96 x
@@ -232,12 +239,12 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     if (tid == 0) {
         mbar_init(&s_bar, 1);
         mbar_expect_tx(&s_bar, (unsigned)PITCH * (unsigned)cd.box_rows);
-        tma_load_3d(&s_img[0][0], &maps->map[cd.level], wx - mis, EDGE_THRESHOLD + cd.iniY, slot, &s_bar);
+        tma_load_3d(s_img, &maps->map[cd.level], wx - mis, EDGE_THRESHOLD + cd.iniY, slot, &s_bar);
         s_ncand = 0;
         s_n = 0;
     }
     for (int i = tid; i < (PITCH / 16) * ch; i += FAST_THREADS) // 16-byte stores: six per row, one or two passes
-        reinterpret_cast<uint4*>(&s_S[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+        reinterpret_cast<uint4*>(s_S)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     mbar_wait(&s_bar, 0);
     // image column c lives at s_img[r][c + mis]; s_S uses the same shift
@@ -264,7 +271,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
                 const int g = g_lo + (i - rr * gpr);
                 r = 3 + rr;
                 s0 = 4 * g;
-                const unsigned* w = reinterpret_cast<const unsigned*>(&s_img[r][0]) + g; // PITCH is a multiple of 4
+                const unsigned* w = reinterpret_cast<const unsigned*>(&S_IMG(r, 0)) + g; // PITCH is a multiple of 4
                 constexpr int RW = PITCH / 4;
                 const unsigned cm = w[-1], cc = w[0], cp = w[1];
                 const unsigned up3 = w[-3 * RW], dn3 = w[3 * RW];
@@ -304,8 +311,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         ncand = s_ncand;
         for (int i = tid; i < ncand; i += FAST_THREADS) {
             const int r = s_cand[i] >> 8, c = s_cand[i] & 255;
-            const int S = fast_strength(&s_img[r][c + mis], PITCH, th);
-            s_S[r][c + mis] = (uint8_t)min(S, 255);
+            const int S = fast_strength(&S_IMG(r, c + mis), PITCH, th);
+            S_S(r, c + mis) = (uint8_t)min(S, 255);
         }
         __syncthreads();
         // 3x3 non-max suppression inside the cell's window (cv::FAST, nonmaxSuppression = true), candidates only
@@ -316,7 +323,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             if (i < ncand) {
                 rc = s_cand[i];
                 const int r = rc >> 8, c = (rc & 255) + mis;
-                const int S = s_S[r][c];
+                const int S = S_S(r, c);
                 if (S > th) {
                     const int sc = S - 1;
                     keep = true;
@@ -326,7 +333,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
                         for (int dx = -1; dx <= 1; dx++) {
                             if (dx == 0 && dy == 0)
                                 continue;
-                            const int Sn = s_S[r + dy][c + dx];
+                            const int Sn = S_S(r + dy, c + dx);
                             const int sn = Sn > th ? Sn - 1 : 0;
                             keep = keep && (sc > sn);
                         }
@@ -359,7 +366,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             rank += s_keep[j] < key;
         if (rank < CELL_CAP) {
             const int r = key >> 8, c = key & 255;
-            out_list[rank] = pack_cand(c + cd.outX, r + cd.outY, s_S[r][c + mis] - 1);
+            out_list[rank] = pack_cand(c + cd.outX, r + cd.outY, S_S(r, c + mis) - 1);
         }
     }
     if (tid == 0)
@@ -425,6 +432,8 @@ static int prepare_fast(rgbdfe_ctx* c)
     std::vector<FastCell> cells(cfg.total_cells);
     for (int l = 0; l < cfg.nlevels; l++) {
         const LevelDesc& L = cfg.lv[l];
+        G.rows = std::max(G.rows, (L.hCell + 6 + 3) & ~3); // multiple of 4: PITCH * rows stays a multiple of 128
+        G.cand_cap = std::max(G.cand_cap, ((L.wCell + 6) * (L.hCell + 6) + 7) & ~7);
         for (int ci = 0; ci < L.nRows; ci++)
             for (int cj = 0; cj < L.nCols; cj++) {
                 // ORBextractor.cpp:636-653 (coordinates relative to minBorder = EDGE_THRESHOLD - 3 = 16)
@@ -474,7 +483,9 @@ int launch_fast(rgbdfe_ctx* c, int count)
     ProfScope prof(c, KID_FAST);
     FastGrid& G = *static_cast<FastGrid*>(c->fast_grid);
     G.iniTh = c->cfg.iniTh, G.minTh = c->cfg.minTh;
-    k_fast_cells<<<dim3(c->cfg.total_cells, count), FAST_THREADS, 0, c->stream>>>(G, static_cast<const FastMaps*>(c->d_fast_maps), static_cast<const FastCell*>(c->d_fast_cells), c->d_cell_count,
+    const size_t smem = 2 * (size_t)G.rows * (CELL_MAX_DIM + 24) + 4 * (size_t)G.cand_cap;
+    CUDA_TRY(c, ensure_dyn_smem(c, k_fast_cells, smem));
+    k_fast_cells<<<dim3(c->cfg.total_cells, count), FAST_THREADS, smem, c->stream>>>(G, static_cast<const FastMaps*>(c->d_fast_maps), static_cast<const FastCell*>(c->d_fast_cells), c->d_cell_count,
         c->d_cell_list, c->cell_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
