@@ -418,11 +418,13 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
         nv = len(vs)
         stream = torch.cuda.ExternalStream(vs[0].ctx.stream, device=local_rank)
 
+        res_buf = np.zeros((n_queries_per_call, vs[0].n_kf), rgbdfe.SE3_DTYPE)  # every collect unpacks the full list into the same host array
+
         def run(n):
             for i in range(n + depth):
                 if i >= depth:
                     j = i - depth
-                    vs[j % nv].collect((j // nv) % 4, n_queries_per_call, want=True)
+                    vs[j % nv].collect((j // nv) % 4, n_queries_per_call, out=res_buf)
                 if i < n:
                     qd, qp = queries[i % len(queries)]
                     vs[i % nv].enqueue(qd, qp, N_FEAT, n_queries_per_call, (i // nv) % 4, seed=42)
@@ -515,7 +517,8 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
         qs = np.stack([np.roll(qd4, 7 * i, axis=0) for i in range(per_call)])
         ps = np.stack([np.roll(qp4, 7 * i, axis=0) for i in range(per_call)])
         reps4 = 3  # three 256-query batches back to back: start-up and tail of the two-context pipeline amortised
-        ms4, _ = timed_queries(v4, [(qs, ps)], per_call, reps4 * Q // per_call, depth=4)
+        qs_d, ps_d = torch.from_numpy(qs).cuda(), torch.from_numpy(ps).cuda()  # query frames resident in HBM, as for configs[3]
+        ms4, _ = timed_queries(v4, [(qs_d.data_ptr(), ps_d.data_ptr())], per_call, reps4 * Q // per_call, depth=4)
         out["relocalisation"] = {"value": reps4 * Q * n_kf4 / (ms4 * 1e-3), "unit": "pairs/s", "queries": Q, "keyframes_total": n_kf4,
                                  "keyframes_per_gpu": hi - lo, "ms_per_256_query_batch": ms4 / reps4,
                                  "what": "BASELINE configs[4]: 256 query frames x 1024 keyframes, all pairs match + RansacSE3(200, 30), "

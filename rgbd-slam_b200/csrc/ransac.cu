@@ -921,8 +921,11 @@ __device__ __forceinline__ void cta_se3_hypothesis(const ReplayCtx& R, const flo
 // only for the pairs whose loop has not ended (mean executed iterations on tracking data: 1.1), get a few CTAs that
 // walk the chunk's iterations in order and leave as soon as the pair is finished -- instead of one CTA per
 // iteration launched just to find that out.
-template <int THREADS, int NPT>
-__global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end, int npairs)
+// MINB > 1 caps the registers per thread (65536 / (THREADS * MINB)): un-capped, a hypothesis CTA of any of these shapes takes the
+// whole register file of its SM (512 x 128, 256 x 248), and a latency-bound CTA that mostly waits on dependent FP chains then keeps
+// every throughput kernel off that SM.
+template <int THREADS, int NPT, int MINB = 1>
+__global__ void __launch_bounds__(THREADS, MINB) k_se3_hypotheses(ReplayCtx R, const float* __restrict__ w_all, int hyp_begin, int hyp_end, int next_end, int npairs)
 {
     __shared__ int s_done, s_skip;
     extern __shared__ __align__(16) unsigned char smem_dyn[];
@@ -968,15 +971,15 @@ __global__ void __launch_bounds__(THREADS) k_se3_hypotheses(ReplayCtx R, const f
     }
 }
 
-template <int THREADS, int NPT>
+template <int THREADS, int NPT, int MINB = 1>
 static int launch_hyp(rgbdfe_ctx* c, const ReplayCtx& R, int npairs, size_t smem, int b, int e, int next_end, int max_ctas)
 {
-    CUDA_TRY(c, ensure_dyn_smem(c, k_se3_hypotheses<THREADS, NPT>, smem));
+    CUDA_TRY(c, (ensure_dyn_smem(c, k_se3_hypotheses<THREADS, NPT, MINB>, smem)));
     int nblk = e - b > 0 ? e - b : 1; // at least one CTA per pair: it drives the replay when there is nothing to evaluate
     if (nblk > max_ctas)
         nblk = max_ctas;
     const int rows = b == 0 ? npairs : (npairs < 296 ? npairs : 296); // later chunks: at most 8 x 296 CTAs walk the pairs (an all-finished batch costs a few idle waves, a hard one keeps every SM busy)
-    k_se3_hypotheses<THREADS, NPT><<<dim3(nblk, rows), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end, npairs);
+    k_se3_hypotheses<THREADS, NPT, MINB><<<dim3(nblk, rows), THREADS, smem, c->stream>>>(R, c->d_w, b, e, next_end, npairs);
     c->launches++;
     return RGBDFE_OK;
 }
@@ -1053,6 +1056,8 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
             break;
         ProfScope prof(c, KID_SE3_HYP);
         int rc;
+        // Tracking chains keep 512-thread CTAs without a register cap: capped 128- / 256-thread CTAs (128 registers,
+        // ~180 B of spills) measured 74-77 k frames/s against 78-79 k on the headline workload.
         if (few || cap > 2304) {
             if (cap <= 1536)
                 rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
@@ -1060,10 +1065,10 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
                 rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
             else
                 rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
-        } else if (cap <= 1152)
-            rc = launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
+        } else if (cap <= 1152) // verification batches: thousands of CTAs, occupancy matters more than the spills
+            rc = launch_hyp<128, 9, 4>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         else
-            rc = launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
+            rc = launch_hyp<256, 9, 2>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         if (rc != RGBDFE_OK)
             return rc;
         if (e >= iters)

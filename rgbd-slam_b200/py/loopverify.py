@@ -87,8 +87,8 @@ class CudaShardedVerifier:
         self.params.seed = seed
         self.ctx.verify_sharded_enqueue(self.db, self.comm, self.world, self.rank, self.n_kf, q_desc, q_xyz, nq, n_queries, self.params, slot)
 
-    def collect(self, slot, n_queries, want=True):
-        return self.ctx.verify_sharded_collect(slot, n_queries, self.n_kf, want)
+    def collect(self, slot, n_queries, want=True, out=None):
+        return self.ctx.verify_sharded_collect(slot, n_queries, self.n_kf, want, out)
 
     def verify(self, q_desc, q_xyz, seed=42):
         q_desc = np.ascontiguousarray(q_desc, np.uint8)

@@ -504,8 +504,9 @@ class Context:
         px = _p(q_xyz) if isinstance(q_xyz, np.ndarray) else C.c_void_p(int(q_xyz))
         self._chk(lib().rgbdfe_verify_sharded_enqueue(self.h, db, comm, n_ranks, rank, n_kf_total, pd, px, nq, n_queries, C.byref(params), slot))
 
-    def verify_sharded_collect(self, slot, n_queries, n_kf_total, want=True):
-        res = np.zeros((n_queries, n_kf_total), SE3_DTYPE) if want else None
+    def verify_sharded_collect(self, slot, n_queries, n_kf_total, want=True, out=None):
+        """out: a preallocated (n_queries, n_kf_total) SE3_DTYPE array to fill (callers in a loop avoid a fresh allocation per call)."""
+        res = out if out is not None else (np.zeros((n_queries, n_kf_total), SE3_DTYPE) if want else None)
         self._chk(lib().rgbdfe_verify_sharded_collect(self.h, slot, _p(res)))
         return res
 
