@@ -83,6 +83,8 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
     int cells = 0, cand = 0, sel = 0, tx = 0, ty = 0, tiles = 0;
     std::vector<int> xofs, yofs;
     std::vector<short> xa, yb;
+    std::vector<int2> xpad;
+    std::vector<int4> ypad;
     for (int l = 0; l < g.nlevels; l++) {
         LevelDesc& L = g.lv[l];
         const float s = c->inv_scale[l];
@@ -130,13 +132,26 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
         g.blur_tile_start[l] = tiles;
         tiles += ((L.w + 63) / 64) * ((L.h + 31) / 32);
         if (l > 0) {
-            xofs.resize(tx + L.w);
-            xa.resize(2 * (tx + L.w));
-            yofs.resize(ty + L.h);
-            yb.resize(2 * (ty + L.h));
-            resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xofs.data() + tx, xa.data() + 2 * tx, yofs.data() + ty, yb.data() + 2 * ty);
-            tx += L.w;
-            ty += L.h;
+            const LevelDesc& P = g.lv[l - 1];
+            xofs.resize(L.w), xa.resize(2 * L.w), yofs.resize(L.h), yb.resize(2 * L.h);
+            resize_tables(P.w, P.h, L.w, L.h, xofs.data(), xa.data(), yofs.data(), yb.data());
+            // padded forms: a ring pixel is the level's own pixel at the REFLECT_101 coordinate (what copyMakeBorder
+            // copies), columns past the padded width (row pitch) repeat the last one
+            const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
+            xpad.resize(tx + L.pstride);
+            ypad.resize(ty + ph);
+            for (int px = 0; px < L.pstride; px++) {
+                const int x = reflect101(std::min(px, pw - 1) - EDGE_THRESHOLD, L.w);
+                xpad[tx + px] = make_int2(EDGE_THRESHOLD + xofs[x], (int)((unsigned short)xa[2 * x] | (unsigned)(unsigned short)xa[2 * x + 1] << 16));
+            }
+            for (int py = 0; py < ph; py++) {
+                const int y = reflect101(py - EDGE_THRESHOLD, L.h);
+                const int r0 = std::min(std::max(yofs[y], 0), P.h - 1), r1 = std::min(std::max(yofs[y] + 1, 0), P.h - 1);
+                ypad[ty + py] = make_int4((EDGE_THRESHOLD + r0) * P.pstride, (EDGE_THRESHOLD + r1) * P.pstride,
+                    (int)((unsigned short)yb[2 * y] | (unsigned)(unsigned short)yb[2 * y + 1] << 16), 0);
+            }
+            tx += L.pstride;
+            ty += ph;
         }
     }
     g.blur_tile_start[g.nlevels] = tiles;
@@ -153,10 +168,8 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     CUDA_TRY(c, cudaMemcpy(c->d_cfg, &g, sizeof(g), cudaMemcpyHostToDevice));
     if (tx > 0) {
-        CUDA_TRY(c, cudaMemcpy(c->d_tab_xofs, xofs.data(), tx * sizeof(int), cudaMemcpyHostToDevice));
-        CUDA_TRY(c, cudaMemcpy(c->d_tab_xa, xa.data(), 2 * tx * sizeof(short), cudaMemcpyHostToDevice));
-        CUDA_TRY(c, cudaMemcpy(c->d_tab_yofs, yofs.data(), ty * sizeof(int), cudaMemcpyHostToDevice));
-        CUDA_TRY(c, cudaMemcpy(c->d_tab_yb, yb.data(), 2 * ty * sizeof(short), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_xpad, xpad.data(), tx * sizeof(int2), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_ypad, ypad.data(), ty * sizeof(int4), cudaMemcpyHostToDevice));
     }
     return RGBDFE_OK;
 }
@@ -246,11 +259,11 @@ void free_orb_workspaces(rgbdfe_ctx* c)
     cudaFree(c->d_img), cudaFree(c->d_depth), cudaFree(c->d_pyr), cudaFree(c->d_blur);
     cudaFree(c->d_cell_count), cudaFree(c->d_cell_list), cudaFree(c->d_cand), cudaFree(c->d_label);
     cudaFree(c->d_cand_count), cudaFree(c->d_sel), cudaFree(c->d_sel_count);
-    cudaFree(c->d_tab_xofs), cudaFree(c->d_tab_xa), cudaFree(c->d_tab_yofs), cudaFree(c->d_tab_yb);
+    cudaFree(c->d_tab_xpad), cudaFree(c->d_tab_ypad);
     c->d_img = nullptr, c->d_depth = nullptr, c->d_pyr = nullptr, c->d_blur = nullptr;
     c->d_cell_count = nullptr, c->d_cell_list = nullptr, c->d_cand = nullptr, c->d_label = nullptr;
     c->d_cand_count = nullptr, c->d_sel = nullptr, c->d_sel_count = nullptr;
-    c->d_tab_xofs = nullptr, c->d_tab_xa = nullptr, c->d_tab_yofs = nullptr, c->d_tab_yb = nullptr;
+    c->d_tab_xpad = nullptr, c->d_tab_ypad = nullptr;
 }
 
 void free_pair_workspaces(rgbdfe_ctx* c)
@@ -529,7 +542,7 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
         cells += nc * nr;
         cand += nc * nr * CELL_CAP;
         sel += c->quota[l] + 16;
-        tx += w, ty += h;
+        tx += align_up(w + 38, 64), ty += h + 38;
     }
     const size_t B = (size_t)c->max_batch;
     c->img_slot = (size_t)align_up(c->max_w, 64) * c->max_h;
@@ -547,10 +560,8 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
     CUDA_TRY(c, dmalloc(&c->d_cand_count, B * RGBDFE_MAX_LEVELS));
     CUDA_TRY(c, dmalloc(&c->d_sel, B * sel));
     CUDA_TRY(c, dmalloc(&c->d_sel_count, B * RGBDFE_MAX_LEVELS));
-    CUDA_TRY(c, dmalloc(&c->d_tab_xofs, (size_t)tx));
-    CUDA_TRY(c, dmalloc(&c->d_tab_xa, (size_t)2 * tx));
-    CUDA_TRY(c, dmalloc(&c->d_tab_yofs, (size_t)ty));
-    CUDA_TRY(c, dmalloc(&c->d_tab_yb, (size_t)2 * ty));
+    CUDA_TRY(c, dmalloc(&c->d_tab_xpad, (size_t)tx));
+    CUDA_TRY(c, dmalloc(&c->d_tab_ypad, (size_t)ty));
     CUDA_TRY(c, cudaMemset(c->d_sel_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
     CUDA_TRY(c, cudaMemset(c->d_cand_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
     memset(&c->cfg, 0, sizeof(c->cfg)); // geometry is rebuilt on the next extract

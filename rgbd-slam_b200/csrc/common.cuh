@@ -29,7 +29,7 @@ struct LevelDesc {
     int cand_cap;
     int quota;           // mnFeaturesPerLevel
     int sel_off, sel_cap;
-    int tab_x_off, tab_y_off; // resize coefficient tables (level > 0)
+    int tab_x_off, tab_y_off; // first entry of the level in the padded resize tables (level > 0)
     float scale;         // mvScaleFactor[level]
     int patch_size;      // int(31 * scale)
 };
@@ -221,7 +221,10 @@ struct rgbdfe_ctx {
     int* d_cand_count = nullptr; // [slot][level]
     SelKp* d_sel = nullptr; int sel_slot = 0;
     int* d_sel_count = nullptr;  // [slot][level]
-    int* d_tab_xofs = nullptr; short* d_tab_xa = nullptr; int* d_tab_yofs = nullptr; short* d_tab_yb = nullptr;
+    // resize tables of levels > 0 over PADDED coordinates (ring and pitch padding resolved on the host):
+    // x: (source column offset in the padded source row, alpha0 | alpha1 << 16) per padded column of the row pitch;
+    // y: (byte offset of source row 0, of source row 1, beta0 | beta1 << 16, 0) per padded row
+    int2* d_tab_xpad = nullptr; int4* d_tab_ypad = nullptr;
     int tab_x_cap = 0, tab_y_cap = 0;
     uint8_t* h_img = nullptr;   // pinned staging
     float* h_depth = nullptr;
