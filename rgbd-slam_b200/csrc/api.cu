@@ -84,7 +84,8 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
     std::vector<int> xofs, yofs;
     std::vector<short> xa, yb;
     std::vector<int2> xpad;
-    std::vector<int4> ypad;
+    std::vector<PyrGroup> groups;
+    int nsrc_max = 0;
     for (int l = 0; l < g.nlevels; l++) {
         LevelDesc& L = g.lv[l];
         const float s = c->inv_scale[l];
@@ -138,20 +139,45 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
             // padded forms: a ring pixel is the level's own pixel at the REFLECT_101 coordinate (what copyMakeBorder
             // copies), columns past the padded width (row pitch) repeat the last one
             const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
+            const int ng = (ph + PYR_ROWS - 1) / PYR_ROWS;
             xpad.resize(tx + L.pstride);
-            ypad.resize(ty + ph);
+            groups.resize(ty + ng);
             for (int px = 0; px < L.pstride; px++) {
                 const int x = reflect101(std::min(px, pw - 1) - EDGE_THRESHOLD, L.w);
                 xpad[tx + px] = make_int2(EDGE_THRESHOLD + xofs[x], (int)((unsigned short)xa[2 * x] | (unsigned)(unsigned short)xa[2 * x + 1] << 16));
             }
-            for (int py = 0; py < ph; py++) {
-                const int y = reflect101(py - EDGE_THRESHOLD, L.h);
-                const int r0 = std::min(std::max(yofs[y], 0), P.h - 1), r1 = std::min(std::max(yofs[y] + 1, 0), P.h - 1);
-                ypad[ty + py] = make_int4((EDGE_THRESHOLD + r0) * P.pstride, (EDGE_THRESHOLD + r1) * P.pstride,
-                    (int)((unsigned short)yb[2 * y] | (unsigned)(unsigned short)yb[2 * y + 1] << 16), 0);
+            for (int gi = 0; gi < ng; gi++) {
+                PyrGroup G;
+                memset(&G, 0, sizeof(G));
+                for (int j = 0; j < PYR_ROWS; j++) {
+                    const int py = std::min(gi * PYR_ROWS + j, ph - 1);
+                    const int y = reflect101(py - EDGE_THRESHOLD, L.h);
+                    const int r[2] = { std::min(std::max(yofs[y], 0), P.h - 1), std::min(std::max(yofs[y] + 1, 0), P.h - 1) };
+                    unsigned sel = 0;
+                    for (int k = 0; k < 2; k++) {
+                        const int off = (EDGE_THRESHOLD + r[k]) * P.pstride;
+                        int i = 0;
+                        while (i < G.nsrc && G.off[i] != off)
+                            i++;
+                        if (i == G.nsrc) {
+                            if (G.nsrc == PYR_SRC_MAX) {
+                                c->set_error("scale factor too large for the pyramid kernel (more than 8 source rows per 4 output rows)");
+                                return RGBDFE_E_ARG;
+                            }
+                            G.off[G.nsrc++] = off;
+                        }
+                        sel |= (unsigned)i << (4 * k);
+                    }
+                    G.sel |= sel << (8 * j);
+                    G.beta[j] = (unsigned)(unsigned short)yb[2 * y] | (unsigned)(unsigned short)yb[2 * y + 1] << 16;
+                }
+                nsrc_max = std::max(nsrc_max, G.nsrc);
+                for (int i = G.nsrc; i < PYR_SRC_MAX; i++)
+                    G.off[i] = G.off[G.nsrc - 1];
+                groups[ty + gi] = G;
             }
             tx += L.pstride;
-            ty += ph;
+            ty += ng;
         }
     }
     g.blur_tile_start[g.nlevels] = tiles;
@@ -169,7 +195,8 @@ int build_level_config(rgbdfe_ctx* c, int w, int h)
     CUDA_TRY(c, cudaMemcpy(c->d_cfg, &g, sizeof(g), cudaMemcpyHostToDevice));
     if (tx > 0) {
         CUDA_TRY(c, cudaMemcpy(c->d_tab_xpad, xpad.data(), tx * sizeof(int2), cudaMemcpyHostToDevice));
-        CUDA_TRY(c, cudaMemcpy(c->d_tab_ypad, ypad.data(), ty * sizeof(int4), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(c->d_tab_group, groups.data(), ty * sizeof(PyrGroup), cudaMemcpyHostToDevice));
+        c->pyr_nsrc = nsrc_max;
     }
     return RGBDFE_OK;
 }
@@ -259,11 +286,11 @@ void free_orb_workspaces(rgbdfe_ctx* c)
     cudaFree(c->d_img), cudaFree(c->d_depth), cudaFree(c->d_pyr), cudaFree(c->d_blur);
     cudaFree(c->d_cell_count), cudaFree(c->d_cell_list), cudaFree(c->d_cand), cudaFree(c->d_label);
     cudaFree(c->d_cand_count), cudaFree(c->d_sel), cudaFree(c->d_sel_count);
-    cudaFree(c->d_tab_xpad), cudaFree(c->d_tab_ypad);
+    cudaFree(c->d_tab_xpad), cudaFree(c->d_tab_group);
     c->d_img = nullptr, c->d_depth = nullptr, c->d_pyr = nullptr, c->d_blur = nullptr;
     c->d_cell_count = nullptr, c->d_cell_list = nullptr, c->d_cand = nullptr, c->d_label = nullptr;
     c->d_cand_count = nullptr, c->d_sel = nullptr, c->d_sel_count = nullptr;
-    c->d_tab_xpad = nullptr, c->d_tab_ypad = nullptr;
+    c->d_tab_xpad = nullptr, c->d_tab_group = nullptr;
 }
 
 void free_pair_workspaces(rgbdfe_ctx* c)
@@ -542,7 +569,7 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
         cells += nc * nr;
         cand += nc * nr * CELL_CAP;
         sel += c->quota[l] + 16;
-        tx += align_up(w + 38, 64), ty += h + 38;
+        tx += align_up(w + 38, 64), ty += (h + 38 + PYR_ROWS - 1) / PYR_ROWS;
     }
     const size_t B = (size_t)c->max_batch;
     c->img_slot = (size_t)align_up(c->max_w, 64) * c->max_h;
@@ -561,7 +588,7 @@ int rgbdfe_orb_configure(rgbdfe_ctx* c, int nfeatures, float scaleFactor, int nl
     CUDA_TRY(c, dmalloc(&c->d_sel, B * sel));
     CUDA_TRY(c, dmalloc(&c->d_sel_count, B * RGBDFE_MAX_LEVELS));
     CUDA_TRY(c, dmalloc(&c->d_tab_xpad, (size_t)tx));
-    CUDA_TRY(c, dmalloc(&c->d_tab_ypad, (size_t)ty));
+    CUDA_TRY(c, dmalloc(&c->d_tab_group, (size_t)ty));
     CUDA_TRY(c, cudaMemset(c->d_sel_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
     CUDA_TRY(c, cudaMemset(c->d_cand_count, 0, B * RGBDFE_MAX_LEVELS * sizeof(int)));
     memset(&c->cfg, 0, sizeof(c->cfg)); // geometry is rebuilt on the next extract

@@ -16,6 +16,17 @@
 #define QT_THREADS 256
 
 // One pyramid level.  Offsets are relative to a frame slot's base pointer.
+// Vertical resize program of PYR_ROWS consecutive padded rows of a level: the distinct source rows they read (byte
+// offsets into the padded source level; unused entries repeat the last one) and, per output row, which two of them it
+// blends (sel: 4 + 4 bits per row) with which coefficients (beta0 | beta1 << 16).
+#define PYR_ROWS 4
+#define PYR_SRC_MAX 8
+struct PyrGroup {
+    int off[PYR_SRC_MAX];
+    unsigned beta[PYR_ROWS];
+    unsigned sel;
+    int nsrc, pad0, pad1;
+};
 struct LevelDesc {
     int w, h;            // un-padded size
     int pstride;         // padded row stride in bytes (>= w + 38, multiple of 64)
@@ -29,7 +40,7 @@ struct LevelDesc {
     int cand_cap;
     int quota;           // mnFeaturesPerLevel
     int sel_off, sel_cap;
-    int tab_x_off, tab_y_off; // first entry of the level in the padded resize tables (level > 0)
+    int tab_x_off, tab_y_off; // first entry of the level in the padded column table / the row-group table (level > 0)
     float scale;         // mvScaleFactor[level]
     int patch_size;      // int(31 * scale)
 };
@@ -223,8 +234,9 @@ struct rgbdfe_ctx {
     int* d_sel_count = nullptr;  // [slot][level]
     // resize tables of levels > 0 over PADDED coordinates (ring and pitch padding resolved on the host):
     // x: (source column offset in the padded source row, alpha0 | alpha1 << 16) per padded column of the row pitch;
-    // y: (byte offset of source row 0, of source row 1, beta0 | beta1 << 16, 0) per padded row
-    int2* d_tab_xpad = nullptr; int4* d_tab_ypad = nullptr;
+    // y: one PyrGroup per PYR_ROWS padded rows
+    int2* d_tab_xpad = nullptr; PyrGroup* d_tab_group = nullptr;
+    int pyr_nsrc = 0; // most distinct source rows any row group of the current geometry reads
     int tab_x_cap = 0, tab_y_cap = 0;
     uint8_t* h_img = nullptr;   // pinned staging
     float* h_depth = nullptr;

@@ -67,69 +67,65 @@ __global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride,
 // pass as in OpenCV's resize.cpp) + ring in one pass over the PADDED level: ring pixels are resampled at their
 // reflected coordinates, which is what copyMakeBorder would copy.  The tables are indexed by padded coordinates
 // (ring reflection, edge clamps and the pitch padding resolved on the host), so the kernel has no border arithmetic.
-// One thread = 4 horizontally adjacent padded pixels x PYR_ROWS rows: the column entries are loaded once, and the
-// horizontal blends of a source row are kept in registers and reused by the next output row (consecutive output
-// rows share a source row: 1.2 blends per row instead of 2 at scale 1.2; the tags make it exact for any sequence
-// of rows, ring included, and every test on them is warp-uniform).  The source is read where it lies (level l-1
-// was written by the previous launch and sits in L2; neighbouring threads share its sectors through L1).
-#define PYR_ROWS 4
+// One thread = 4 horizontally adjacent padded pixels x PYR_ROWS rows.  The host lists, per group of PYR_ROWS rows,
+// the distinct source rows the group reads (6 at scale 1.2 instead of 2 per output row) and which two of them each
+// output row blends: the thread blends every listed source row horizontally first -- all its byte loads are
+// independent and in flight together -- parks the 16-bit results in its own shared-memory column (registers cannot
+// be indexed by the row number) and then blends vertically.  No barrier: a thread reads back only what it wrote.
+// The source is read where it lies (level l-1 was written by the previous launch and sits in L2; neighbouring
+// threads share its sectors through L1).
 struct PyrLevel {
     int ph, pstride;             // this level: padded rows, row pitch
     unsigned pyr_off;
     unsigned pyr_off_src;        // level l-1
-    int tab_x_off, tab_y_off;
+    int tab_x_off, tab_g_off;
 };
-__device__ __forceinline__ void pyr_hblend(const uint8_t* __restrict__ row, const int2 (&xe)[4], int (&t)[4])
-{
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint8_t* q = row + xe[k].x;
-        t[k] = (int)(q[0] * ((unsigned)xe[k].y & 0xffffu) + q[1] * ((unsigned)xe[k].y >> 16)) >> 4;
-    }
-}
+template <int NSRC>
 __global__ void __launch_bounds__(256) k_pyramid_resize_direct(const __grid_constant__ PyrLevel V, uint8_t* __restrict__ pyr, size_t pyr_slot,
-    const int2* __restrict__ xpad, const int4* __restrict__ ypad)
+    const int2* __restrict__ xpad, const PyrGroup* __restrict__ groups)
 {
+    __shared__ uint2 s_t[NSRC][256];
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
     const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    const int py0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYR_ROWS;
+    const int g = blockIdx.y * blockDim.y + threadIdx.y;
+    const int py0 = g * PYR_ROWS;
     if (px0 >= V.pstride || py0 >= V.ph)
         return;
     uint8_t* slot_base = pyr + blockIdx.z * pyr_slot;
     const uint8_t* src = slot_base + V.pyr_off_src;
-    int2 xe[4];
-    {
-        const int4* xp = reinterpret_cast<const int4*>(xpad + V.tab_x_off + px0);
-        const int4 e0 = xp[0], e1 = xp[1];
-        xe[0] = make_int2(e0.x, e0.y), xe[1] = make_int2(e0.z, e0.w), xe[2] = make_int2(e1.x, e1.y), xe[3] = make_int2(e1.z, e1.w);
-    }
-    const int4* yp = ypad + V.tab_y_off + py0;
-    uint8_t* dst = slot_base + V.pyr_off + (size_t)py0 * V.pstride + px0;
-    int t0[4], t1[4];
-    int tag0 = -1, tag1 = -1;
-    const int rows = min(PYR_ROWS, V.ph - py0);
-    for (int j = 0; j < rows; j++) {
-        const int4 ye = yp[j];
-        if (ye.x != tag0) {
-            if (ye.x == tag1) {
+    const int4* xp = reinterpret_cast<const int4*>(xpad + V.tab_x_off + px0);
+    const int4 e0 = xp[0], e1 = xp[1];
+    const int4* gp = reinterpret_cast<const int4*>(groups + V.tab_g_off + g);
+    const int4 o0 = gp[0], o1 = gp[1], bt = gp[2], m = gp[3];
+    const int off[8] = { o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w };
+    const int sx[4] = { e0.x, e0.z, e1.x, e1.z };
+    const unsigned al[4] = { (unsigned)e0.y, (unsigned)e0.w, (unsigned)e1.y, (unsigned)e1.w };
 #pragma unroll
-                for (int k = 0; k < 4; k++)
-                    t0[k] = t1[k];
-            } else
-                pyr_hblend(src + ye.x, xe, t0);
-            tag0 = ye.x;
-        }
-        if (ye.y != tag1) {
-            pyr_hblend(src + ye.y, xe, t1);
-            tag1 = ye.y;
-        }
-        const int b0 = (int)((unsigned)ye.z & 0xffffu), b1 = (int)((unsigned)ye.z >> 16);
-        unsigned out = 0;
+    for (int s = 0; s < NSRC; s++) {
+        const uint8_t* row = src + off[s];
+        unsigned t[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const int v = min((((b0 * t0[k]) >> 16) + ((b1 * t1[k]) >> 16) + 2) >> 2, 255);
-            out |= (unsigned)v << (8 * k);
+            const uint8_t* q = row + sx[k];
+            t[k] = (q[0] * (al[k] & 0xffffu) + q[1] * (al[k] >> 16)) >> 4; // <= 255 * 2049 >> 4: fits 16 bits
         }
-        *reinterpret_cast<unsigned*>(dst + (size_t)j * V.pstride) = out; // bytes past the padded width are pitch padding
+        s_t[s][tid] = make_uint2(t[1] * 65536u + t[0], t[3] * 65536u + t[2]);
+    }
+    const unsigned beta[4] = { (unsigned)bt.x, (unsigned)bt.y, (unsigned)bt.z, (unsigned)bt.w };
+    uint8_t* dst = slot_base + V.pyr_off + (size_t)py0 * V.pstride + px0;
+#pragma unroll
+    for (int j = 0; j < PYR_ROWS; j++) {
+        if (py0 + j < V.ph) {
+            const unsigned sel = (unsigned)m.x >> (8 * j);
+            const uint2 a = s_t[sel & 15u][tid], b = s_t[(sel >> 4) & 15u][tid];
+            const int b0 = (int)(beta[j] & 0xffffu), b1 = (int)(beta[j] >> 16);
+            // cv's saturate_cast never binds here: both coefficient pairs sum to <= 2049, so the value is <= 255
+            const unsigned v0 = (unsigned)((((b0 * (int)(a.x & 0xffffu)) >> 16) + ((b1 * (int)(b.x & 0xffffu)) >> 16) + 2) >> 2);
+            const unsigned v1 = (unsigned)((((b0 * (int)(a.x >> 16)) >> 16) + ((b1 * (int)(b.x >> 16)) >> 16) + 2) >> 2);
+            const unsigned v2 = (unsigned)((((b0 * (int)(a.y & 0xffffu)) >> 16) + ((b1 * (int)(b.y & 0xffffu)) >> 16) + 2) >> 2);
+            const unsigned v3 = (unsigned)((((b0 * (int)(a.y >> 16)) >> 16) + ((b1 * (int)(b.y >> 16)) >> 16) + 2) >> 2);
+            *reinterpret_cast<unsigned*>(dst + (size_t)j * V.pstride) = ((v3 * 256u + v2) * 256u + v1) * 256u + v0; // bytes past the padded width are pitch padding
+        }
     }
 }
 
@@ -415,9 +411,12 @@ int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_strid
             const LevelDesc& P = cfg.lv[l - 1];
             PyrLevel V;
             V.ph = ph, V.pstride = L.pstride, V.pyr_off = L.pyr_off, V.pyr_off_src = P.pyr_off;
-            V.tab_x_off = L.tab_x_off, V.tab_y_off = L.tab_y_off;
+            V.tab_x_off = L.tab_x_off, V.tab_g_off = L.tab_y_off;
             dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (ph + 4 * PYR_ROWS - 1) / (4 * PYR_ROWS), count);
-            k_pyramid_resize_direct<<<grd, blk, 0, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xpad, c->d_tab_ypad);
+            if (c->pyr_nsrc <= 6)
+                k_pyramid_resize_direct<6><<<grd, blk, 0, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xpad, c->d_tab_group);
+            else
+                k_pyramid_resize_direct<8><<<grd, blk, 0, c->stream>>>(V, c->d_pyr, c->pyr_slot, c->d_tab_xpad, c->d_tab_group);
         }
         c->launches++;
     }
