@@ -63,6 +63,42 @@ __global__ void __launch_bounds__(256) k_pyramid_base(int w, int h, int pstride,
     *reinterpret_cast<unsigned*>(pyr + slot * pyr_slot + pyr_off + (size_t)py * pstride + px0) = packed; // pstride is a multiple of 64
 }
 
+// Level 0 of a gray image, 16 padded pixels per thread (one 16-byte store): threads whose span is interior read five
+// aligned words and funnel-shift them into place (the source row starts at any byte offset); spans that touch the
+// ring go byte by byte through REFLECT_101.
+__global__ void __launch_bounds__(256) k_pyramid_base16(int w, int h, int pstride, unsigned pyr_off, const __grid_constant__ ImgPtrs img, int img_stride,
+    uint8_t* __restrict__ pyr, size_t pyr_slot)
+{
+    const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    const int py = blockIdx.y * blockDim.y + threadIdx.y;
+    if (px0 >= pstride || py >= h + 2 * EDGE_THRESHOLD)
+        return;
+    const int pw = w + 2 * EDGE_THRESHOLD;
+    const int slot = blockIdx.z;
+    const uint8_t* src = static_cast<const uint8_t*>(img.p[slot]) + (size_t)reflect101(py - EDGE_THRESHOLD, h) * img_stride;
+    uint4 out;
+    if (px0 >= EDGE_THRESHOLD && px0 + 15 < EDGE_THRESHOLD + w) {
+        const uint8_t* q = src + (px0 - EDGE_THRESHOLD);
+        const unsigned mis = (unsigned)(reinterpret_cast<size_t>(q) & 3);
+        const unsigned* qa = reinterpret_cast<const unsigned*>(q - mis);
+        const unsigned w0 = qa[0], w1 = qa[1], w2 = qa[2], w3 = qa[3], w4 = mis ? qa[4] : 0u; // qa[4] is touched only when it holds wanted bytes
+        const unsigned sh = 8 * mis;
+        out = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    } else {
+        unsigned o[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            unsigned packed = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                packed |= (unsigned)src[reflect101(min(px0 + 4 * i + k, pw - 1) - EDGE_THRESHOLD, w)] << (8 * k);
+            o[i] = packed;
+        }
+        out = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    *reinterpret_cast<uint4*>(pyr + slot * pyr_slot + pyr_off + (size_t)py * pstride + px0) = out; // pstride is a multiple of 64
+}
+
 // Level l >= 1: cv::resize(INTER_LINEAR) of level l-1 (8-bit fixed point, 11-bit coefficients, one rounding per
 // pass as in OpenCV's resize.cpp) + ring in one pass over the PADDED level: ring pixels are resampled at their
 // reflected coordinates, which is what copyMakeBorder would copy.  The tables are indexed by padded coordinates
@@ -405,8 +441,13 @@ int launch_pyramid(rgbdfe_ctx* c, int count, const ImgPtrs& gray, int gray_strid
         const LevelDesc& L = cfg.lv[l];
         const int pw = L.w + 2 * EDGE_THRESHOLD, ph = L.h + 2 * EDGE_THRESHOLD;
         if (l == 0) {
-            dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
-            k_pyramid_base<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, channels, c->d_pyr, c->pyr_slot);
+            if (channels == 1) {
+                dim3 blk(16, 16), grd((L.pstride / 16 + 15) / 16, (ph + 15) / 16, count);
+                k_pyramid_base16<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, c->d_pyr, c->pyr_slot);
+            } else {
+                dim3 blk(32, 8), grd((pw + 127) / 128, (ph + 7) / 8, count);
+                k_pyramid_base<<<grd, blk, 0, c->stream>>>(L.w, L.h, L.pstride, L.pyr_off, gray, gray_stride, channels, c->d_pyr, c->pyr_slot);
+            }
         } else {
             const LevelDesc& P = cfg.lv[l - 1];
             PyrLevel V;
