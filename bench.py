@@ -745,6 +745,8 @@ def main():
                     "(1: no speculation; measured 72.9 k / 69.6 k / 64.8 k / 56.7 k frames/s at 1 / 2 / 4 / 8: idle speculative CTAs take SM space from the throughput kernels)")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
+    ap.add_argument("--upload-mix", type=int, default=0, help="of every 8 sequences, this many upload the whole depth map (copy engine) while the others "
+                    "read the keypoint sectors in place (PCIe reads): balances PCIe bandwidth against the PCIe read rate")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--profile-host", action="store_true", help="diagnostic: the per-kernel timing pass runs with pinned HOST inputs (the e2e path)")
     ap.add_argument("--core-only", action="store_true", help="profiling runs: only the headline workload, none of the other legs")
@@ -825,7 +827,8 @@ def main():
             self.ctx_x = rgbdfe.Context(local_rank, W, H, NFEAT, B)
             self.ctx_t = rgbdfe.Context(local_rank, W, H, NFEAT, 1)
             self.ctx_x.orb_configure(NFEAT, 1.2, 8, 20, 7)
-            if args.full_upload:
+            self.full_upload = args.full_upload or (args.upload_mix > 0 and (k % 8) < args.upload_mix)
+            if self.full_upload:
                 self.ctx_x.set_option("host_zero_copy", 0)
             if args.overlap_blur:
                 self.ctx_x.set_option("overlap_blur", 1)
@@ -980,7 +983,7 @@ def main():
     run_steps(seqs, False, 1)
     n_up, ms_up, _ = timed(seqs, False, max(2, args.steps // 2))
     for q in seqs:
-        q.ctx_x.set_option("host_zero_copy", 0 if args.full_upload else 1)
+        q.ctx_x.set_option("host_zero_copy", 0 if q.full_upload else 1)
     clocks = sample_clocks_stop(proc, path, local_rank) if rank == 0 else None
     value = n_dev * world / (ms_dev * 1e-3)
     e2e = n_e2e * world / (ms_e2e * 1e-3)

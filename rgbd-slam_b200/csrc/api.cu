@@ -840,7 +840,10 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
         if ((rc = launch_quadtree(c, count)) != RGBDFE_OK)
             return rc;
     }
-    if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, make_frame_prep(w, h, fx, fy, cx, cy, dist, depth16 ? depth16_factor : 0.0f)))
+    const void* unused = nullptr;
+    const bool depth_on_host = depth_in_place && pointer_kind(dany[0], &unused) == 2; // pinned host memory read over PCIe
+    if ((rc = launch_describe(c, count, fb, dany != nullptr, dp, dstride, make_frame_prep(w, h, fx, fy, cx, cy, dist, depth16 ? depth16_factor : 0.0f),
+             depth_on_host))
         != RGBDFE_OK)
         return rc;
     return RGBDFE_OK;

@@ -389,7 +389,8 @@ int launch_fast(rgbdfe_ctx* c, int count);
 void free_fast_state(rgbdfe_ctx* c);
 // orb_keypoints.cu
 int launch_quadtree(rgbdfe_ctx* c, int count);
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep);
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep,
+    bool depth_on_host);
 // match.cu
 int launch_match(rgbdfe_ctx* c, const MatchPair* d_pairs, int npairs, int max_nq, int max_nt, float ratio, int discard, int* d_knn_out);
 int launch_knn(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int npairs, int max_nq, int splits);

@@ -465,6 +465,46 @@ __global__ void __launch_bounds__(256) k_orient_describe(const OrbConfig* __rest
     }
 }
 
+// Frame::uprojectCamera for a depth map that stays in pinned HOST memory (option "host_zero_copy"): one CTA per frame,
+// every thread issues its (up to) 8 PCIe sector reads before it uses the first -- ~2000 reads per frame in flight on a
+// handful of warps, instead of one read at the end of each K6 warp, which holds that warp's slot for the PCIe round trip.
+#define UNPROJ_THREADS 256
+#define UNPROJ_ILP 8
+__global__ void __launch_bounds__(UNPROJ_THREADS) k_unproject_host(const FrameBatch frames, const __grid_constant__ ImgPtrs depth, int depth_stride,
+    const __grid_constant__ FramePrep prep)
+{
+    const rgbdfe_frame F = frames.f[blockIdx.x];
+    const int n = *F.n;
+    const void* img = depth.p[blockIdx.x];
+    for (int base = 0; base < n; base += UNPROJ_THREADS * UNPROJ_ILP) {
+        float z[UNPROJ_ILP];
+#pragma unroll
+        for (int u = 0; u < UNPROJ_ILP; u++) {
+            const int gi = base + u * UNPROJ_THREADS + threadIdx.x;
+            z[u] = 0.f;
+            if (gi < n) {
+                const size_t di = (size_t)(int)F.kps[gi].y * depth_stride + (int)F.kps[gi].x; // the raw keypoint position
+                z[u] = prep.depth16_factor > 0.0f ? (float)static_cast<const unsigned short*>(img)[di] : static_cast<const float*>(img)[di];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNPROJ_ILP; u++) {
+            const int gi = base + u * UNPROJ_THREADS + threadIdx.x;
+            if (gi < n) {
+                const float zz = prep.depth16_factor > 0.0f ? __fmul_rn(z[u], prep.depth16_factor) : z[u];
+                const float2 un = F.pt_un[gi];
+                rgbdfe_point3f P = { 0.f, 0.f, 0.f };
+                if (zz > 0) {
+                    P.x = __fmul_rn(__fmul_rn(__fsub_rn(un.x, prep.cxf), zz), prep.invfx);
+                    P.y = __fmul_rn(__fmul_rn(__fsub_rn(un.y, prep.cyf), zz), prep.invfy);
+                    P.z = zz;
+                }
+                F.xyz[gi] = P;
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- launchers
 static bool g_pattern_uploaded[64] = { false };
 
@@ -484,7 +524,8 @@ int launch_quadtree(rgbdfe_ctx* c, int count)
     return RGBDFE_OK;
 }
 
-int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep)
+int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unproject, const ImgPtrs& depth, int depth_stride, const FramePrep& prep,
+    bool depth_on_host)
 {
     if (!g_pattern_uploaded[c->device]) {
         CUDA_TRY(c, cudaMemcpyToSymbolAsync(g_pattern, kBriefPattern, 1024, 0, cudaMemcpyHostToDevice, c->stream));
@@ -493,8 +534,12 @@ int launch_describe(rgbdfe_ctx* c, int count, const FrameBatch& frames, bool unp
     const int warps = c->kp_cap + 1; // one extra warp publishes the count
     ProfScope prof(c, KID_DESCRIBE);
     k_orient_describe<<<dim3((warps + 7) / 8, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot, c->d_sel,
-        c->sel_slot, c->d_sel_count, frames, depth, depth_stride, unproject ? 1 : 0, prep);
+        c->sel_slot, c->d_sel_count, frames, depth, depth_stride, (unproject && !depth_on_host) ? 1 : 0, prep);
     c->launches++;
+    if (unproject && depth_on_host) {
+        k_unproject_host<<<count, UNPROJ_THREADS, 0, c->stream>>>(frames, depth, depth_stride, prep);
+        c->launches++;
+    }
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;
 }
