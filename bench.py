@@ -849,7 +849,7 @@ def main():
             self.order = pingpong(F)
             for _ in range((k * 37) % F):  # sequences start at different frames
                 next(self.order)
-            self.i, self.have_ref, self.n_res = 0, False, 0
+            self.i, self.have_ref, self.n_res, self.pending = 0, False, 0, False
             self.inliers, self.ok, self.n, self.iters = [], 0, 0, []
             # e2e: what the class interface hands back per frame -- keypoints + descriptors (Extractor::detectAndCompute) and
             # mvInliers (RansacSE3) -- lands in pinned host buffers, one set per frame set
@@ -923,24 +923,28 @@ def main():
 
     pool = ThreadPoolExecutor(max_workers=args.host_threads) if args.host_threads > 1 else None
 
-    def run_group(group, dev):
-        for q in group:
-            q.enqueue(dev)
+    def run_group(group, dev, steps):
+        """A rolling pipeline: a sequence's results of step n are read just before its step n+1 is enqueued, so the other
+        sequences' work keeps the GPU busy while the host waits for one chain; everything is drained at the end."""
+        for _ in range(steps):
+            for q in group:
+                if q.pending:
+                    q.collect()
+                q.enqueue(dev)
+                q.pending = True
         for q in group:
             q.collect()
+            q.pending = False
 
     def run_steps(seqs, dev, steps):
-        """Every sequence enqueues one batch (extraction of the next + chain of the current) and then reads its results.
+        """Every sequence advances by `steps` batches (extraction of the next + chain of the current, then its results).
         The C-ABI calls release the GIL, so a few host threads can feed the 2 x len(seqs) streams concurrently."""
-        n = 0
         T = args.host_threads
-        for _ in range(steps):
-            if pool and len(seqs) > 1:
-                list(pool.map(lambda k: run_group(seqs[k::T], dev), range(T)))
-            else:
-                run_group(seqs, dev)
-            n += B * len(seqs)
-        return n
+        if pool and len(seqs) > 1:
+            list(pool.map(lambda k: run_group(seqs[k::T], dev, steps), range(T)))
+        else:
+            run_group(seqs, dev, steps)
+        return B * len(seqs) * steps
 
     def timed(seqs, dev, steps):
         if world > 1:
