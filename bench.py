@@ -745,8 +745,9 @@ def main():
                     "(1: no speculation; measured 72.9 k / 69.6 k / 64.8 k / 56.7 k frames/s at 1 / 2 / 4 / 8: idle speculative CTAs take SM space from the throughput kernels)")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads that enqueue the sequences' work")
     ap.add_argument("--full-upload", action="store_true", help="upload the whole depth map of every frame instead of reading the keypoint sectors in place")
-    ap.add_argument("--upload-mix", type=int, default=0, help="of every 8 sequences, this many upload the whole depth map (copy engine) while the others "
-                    "read the keypoint sectors in place (PCIe reads): balances PCIe bandwidth against the PCIe read rate")
+    ap.add_argument("--upload-mix", type=int, default=3, help="e2e: of every 8 batches of a sequence, this many upload the whole pinned depth map (copy engine); "
+                    "the others read the keypoint sectors in place (PCIe reads): the two transports have different limits")
+    ap.add_argument("--small-ctas", type=int, default=1, help="register-capped 128 / 256-thread hypothesis CTAs for the tracking chains (they leave room on their SM for the throughput kernels; 0 = 512-thread CTAs)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--profile-host", action="store_true", help="diagnostic: the per-kernel timing pass runs with pinned HOST inputs (the e2e path)")
     ap.add_argument("--core-only", action="store_true", help="profiling runs: only the headline workload, none of the other legs")
@@ -813,6 +814,10 @@ def main():
     gray_d, depth_d = gray_h.cuda(), depth_h.cuda()
     gp_h, dp_h = gray_h.numpy(), depth_h.numpy()
     L = rgbdfe.lib()
+    # addresses of the pool's frames, taken once: building them per call costs the enqueuing thread 0.1 ms per batch
+    gray_d_ptr, depth_d_ptr = [gray_d[i].data_ptr() for i in range(F)], [depth_d[i].data_ptr() for i in range(F)]
+    gray_h_ptr, depth_h_ptr = [gp_h[i].ctypes.data for i in range(F)], [dp_h[i].ctypes.data for i in range(F)]
+    c_cam = [C.c_float(inv_factor)] + [C.c_float(cam[k]) for k in ("fx", "fy", "cx", "cy")]
 
     part = rgbdfe.device_partition(local_rank, args.latency_sms) if args.latency_sms > 0 else None
 
@@ -827,9 +832,11 @@ def main():
             self.ctx_x = rgbdfe.Context(local_rank, W, H, NFEAT, B)
             self.ctx_t = rgbdfe.Context(local_rank, W, H, NFEAT, 1)
             self.ctx_x.orb_configure(NFEAT, 1.2, 8, 20, 7)
-            self.full_upload = args.full_upload or (args.upload_mix > 0 and (k % 8) < args.upload_mix)
+            self.full_upload = args.full_upload
             if self.full_upload:
                 self.ctx_x.set_option("host_zero_copy", 0)
+            self.ctx_x.set_option("depth_upload_of_8", args.upload_mix)
+            self.ctx_x.set_option("depth_upload_phase", k % 8)  # the sequences' upload turns are staggered
             if args.overlap_blur:
                 self.ctx_x.set_option("overlap_blur", 1)
             if args.extract_streams and k >= args.extract_streams:
@@ -842,10 +849,14 @@ def main():
             else:
                 self.ctx_t.set_stream_priority(True)
             self.ctx_t.set_option("ransac_first_chunk", first_chunk)
+            if args.small_ctas:
+                self.ctx_t.set_option("ransac_small_ctas", 1)
             if args.knn_waves:
                 self.ctx_t.set_option("knn_waves", args.knn_waves)
             self.ctx_t.rng_seed(42 + k)
             self.sets = [[rgbdfe.Frame(self.ctx_x) for _ in range(B)] for _ in range(3)]
+            self.fr_arr = [(C.c_void_p * B)(*[f.h for f in st]) for st in self.sets]
+            self.chain_ref = [(C.c_void_p * (B + 1))(*([self.sets[(k - 1) % 3][-1].h] + [f.h for f in self.sets[k]])) for k in range(3)]
             self.order = pingpong(F)
             for _ in range((k * 37) % F):  # sequences start at different frames
                 next(self.order)
@@ -863,36 +874,33 @@ def main():
             self.r_inl = np.zeros((B + 1) * self.ctx_t.kp_cap, rgbdfe.DM_DTYPE)
             self.r_off = np.zeros(B + 2, np.int32)
 
-        def extract(self, batch, dev):
+        def extract(self, k, dev):
+            """Extraction of the next 64 frames of the sequence into frame set k: device-resident inputs read in place, or
+            pinned host inputs (gray uploaded, depth read over PCIe) -- the same C-ABI call either way."""
             idx = [next(self.order) for _ in range(B)]
             cx = self.ctx_x
-            if dev:
-                fr = (C.c_void_p * B)(*[f.h for f in batch])
-                gp = (C.c_void_p * B)(*[gray_d[i].data_ptr() for i in idx])
-                dp = (C.c_void_p * B)(*[depth_d[i].data_ptr() for i in idx])
-                cx._chk(L.rgbdfe_frames_extract_raw(cx.h, fr, B, gp, W, H, W, dp, W, C.c_float(inv_factor), C.c_float(cam["fx"]),
-                                                    C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"])))
-            else:
-                cx.frames_extract_raw(batch, [gp_h[i] for i in idx], [dp_h[i] for i in idx], cam, inv_factor)
+            gp = (C.c_void_p * B)(*[(gray_d_ptr if (dev or os.environ.get("BENCH_E2E_GRAY_DEV")) else gray_h_ptr)[i] for i in idx])  # (diagnostic knob)
+            dp = (C.c_void_p * B)(*[(depth_d_ptr if (dev or os.environ.get("BENCH_E2E_DEPTH_DEV")) else depth_h_ptr)[i] for i in idx])  # (diagnostic knob)
+            cx._chk(L.rgbdfe_frames_extract_raw(cx.h, self.fr_arr[k], B, gp, W, H, W, dp, W, *c_cam))
 
         def enqueue(self, dev):
             i = self.i
-            cur, nxt = self.sets[i % 3], self.sets[(i + 1) % 3]
             self.ctx_t.stream_wait(self.ctx_x)  # batch i was extracted by the previous step
             if args.mode != "chain":
-                self.extract(nxt, dev)          # batch i+1, concurrent with the chain below
-                if not dev:                     # e2e: the frames' host-side state comes back too (asynchronous, pinned)
-                    k = (i + 1) % 3
-                    self.ctx_x.frames_download_async(nxt, self.h_kps[k], self.h_desc[k], None, self.h_n[k], self.ctx_x.kp_cap)
+                k = (i + 1) % 3
+                self.extract(k, dev)            # batch i+1, concurrent with the chain below
+                if not dev and not os.environ.get("BENCH_E2E_NO_DL"):  # e2e: the frames' host-side state comes back too (asynchronous, pinned)
+                    self.ctx_x._chk(L.rgbdfe_frames_download_async(self.ctx_x.h, self.fr_arr[k], B, rgbdfe._p(self.h_kps[k]), rgbdfe._p(self.h_desc[k]),
+                                                                   None, self.ctx_x.kp_cap, rgbdfe._p(self.h_n[k])))
                     self.pending_download = True
             if args.mode == "serial":           # diagnostic: the chain waits for this extraction too (no overlap)
                 self.ctx_t.stream_wait(self.ctx_x)
             if args.mode == "extract":
                 self.n_res = 0
                 return
-            chain = ([self.sets[(i - 1) % 3][-1]] if self.have_ref else []) + cur
-            self.ctx_t.track_sequence(chain, 0, RATIO, True, ITERS, MIN_INL, 3.0, 4, True)
-            self.n_res = len(chain) - 1
+            chain, n = (self.chain_ref[i % 3], B + 1) if self.have_ref else (self.fr_arr[i % 3], B)
+            self.ctx_t._chk(L.rgbdfe_track_sequence(self.ctx_t.h, chain, n, C.c_float(RATIO), 1, ITERS, C.c_uint(MIN_INL), C.c_float(3.0), C.c_uint(4), 1, 0))
+            self.n_res = n - 1
 
         def collect(self):
             if self.n_res == 0:
@@ -923,15 +931,24 @@ def main():
 
     pool = ThreadPoolExecutor(max_workers=args.host_threads) if args.host_threads > 1 else None
 
+    host_prof, host_prof_on = {}, [False]
+
     def run_group(group, dev, steps):
         """A rolling pipeline: a sequence's results of step n are read just before its step n+1 is enqueued, so the other
         sequences' work keeps the GPU busy while the host waits for one chain; everything is drained at the end."""
+        prof = host_prof.setdefault((dev, len(group)), [0.0, 0.0, 0]) if (os.environ.get("BENCH_HOSTPROF") and host_prof_on[0]) else None
         for _ in range(steps):
             for q in group:
+                t0 = time.perf_counter()
                 if q.pending:
                     q.collect()
+                t1 = time.perf_counter()
                 q.enqueue(dev)
                 q.pending = True
+                if prof is not None:
+                    prof[0] += t1 - t0
+                    prof[1] += time.perf_counter() - t1
+                    prof[2] += 1
         for q in group:
             q.collect()
             q.pending = False
@@ -954,7 +971,9 @@ def main():
         stream = torch.cuda.ExternalStream(seqs[0].ctx_t.stream, device=local_rank)
         l0 = sum(q.ctx_x.launches + q.ctx_t.launches for q in seqs)
         e0.record(stream)
+        host_prof_on[0] = True
         n = run_steps(seqs, dev, steps)
+        host_prof_on[0] = False
         for q in seqs:  # the last step's extraction (and every other sequence) belongs to the timed region
             seqs[0].ctx_t.stream_wait(q.ctx_x)
             seqs[0].ctx_t.stream_wait(q.ctx_t)
@@ -971,7 +990,7 @@ def main():
     S = max(1, args.sequences)
     seqs = [Seq(k, 32 if S == 1 else args.first_chunk) for k in range(S)]
     for q in seqs:
-        q.extract(q.sets[0], True)  # prime the pipelines
+        q.extract(0, True)  # prime the pipelines
     for _ in range(args.warmup):
         run_steps(seqs, True, 1)
         run_steps(seqs, False, 1)
@@ -989,7 +1008,10 @@ def main():
     for q in seqs:
         q.ctx_x.set_option("host_zero_copy", 0 if q.full_upload else 1)
     clocks = sample_clocks_stop(proc, path, local_rank) if rank == 0 else None
+    for dev_, (tc, te, n_) in host_prof.items():  # BENCH_HOSTPROF=1: host seconds per sequence-step in collect (incl. waiting) / enqueue
+        print(f"hostprof dev={dev_} collect {tc / n_ * 1e3:.3f} ms enqueue {te / n_ * 1e3:.3f} ms per sequence-step ({n_})", file=sys.stderr)
     value = n_dev * world / (ms_dev * 1e-3)
+    up_frac = 1.0 if args.full_upload else args.upload_mix / 8.0
     e2e = n_e2e * world / (ms_e2e * 1e-3)
     # one sequence alone (latency-bound reference point)
     single = None
@@ -1256,10 +1278,12 @@ def main():
                        "verify_parity": (verify or {}).get("parity"), "verify_parity_pairs_checked": (verify or {}).get("parity_pairs_checked"),
                        "reloc_pairs_per_s": ((verify or {}).get("relocalisation") or {}).get("value"), "verify_error": (verify or {}).get("error")},
             "e2e": {"value": e2e, "unit": "frames/s",
-                    "h2d_bytes_per_step": S * B * (W * H * (3 if args.full_upload else 1) + (0 if args.full_upload else NFEAT * 32)),
+                    "h2d_bytes_per_step": int(S * B * (W * H * (1 + 2 * up_frac) + (1 - up_frac) * NFEAT * 32)),
                     "d2h_bytes_per_step": S * B * (seqs[0].ctx_x.kp_cap * 60 + 4 + 84 + 4) + e2e_inlier_records * 16 // max(args.steps, 1),
                     "d2h_note": "per frame: keypoints (28 B) + descriptors (32 B) for the frame's whole capacity row, the count, the 84-byte RansacSE3 result and mvInliers (16 B per inlier DMatch) -- what Extractor::detectAndCompute and RansacSE3 hand back through the class interface",
-                    "h2d_note": "gray image uploaded per frame; of the pinned 16-bit depth map only the 32 B sectors under the <= 2000 keypoints cross PCIe (read in place by the back-projection)" if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
+                    "h2d_note": ("gray image uploaded per frame; the pinned 16-bit depth map is uploaded whole for %d of every 8 batches (copy engine) and read in place for the others (only the 32 B sectors under the <= 2000 keypoints cross PCIe: k_unproject_host) -- the two transports have different limits" % args.upload_mix) if not args.full_upload else "gray + whole 16-bit depth map uploaded per frame",
+                    "depth_transport": {"upload_batches_of_8": 8 if args.full_upload else args.upload_mix,
+                                        "why": "with the depth map resident the same run reaches the device-resident value; in-place reads alone sustain ~146 M sector reads/s, whole uploads alone are PCIe-bandwidth-bound (full_upload_value)"},
                     "full_upload_value": n_up / (ms_up * 1e-3) * world, "full_upload_h2d_bytes_per_step": S * B * W * H * 3},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "class_shim_path": shim, "other_configs": other, "verify": verify, "frame_prep": frame_prep, "projection_match": projection, "cvorb_extract": cvorb,
         }))

@@ -90,7 +90,13 @@ int rgbdfe_sync(rgbdfe_ctx* ctx);
 /* Tuning knobs that never change results.  "ransac_first_chunk" (default 32): how many RANSAC iterations the
  * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
  * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU.
- * "host_zero_copy" (default 1): see rgbdfe_frames_extract.
+ * "ransac_small_ctas" (default 0): the hypothesis CTAs of tracking chains are 128 / 256 threads with registers capped at 128
+ * (the verification path's shape) instead of 512 threads: slower for one chain, but an SM that hosts one still has room
+ * for the extraction kernels of other sequences (+4 % frames/s with 32 sequences on one GPU).
+ * "host_zero_copy" (default 1): see rgbdfe_frames_extract.  "depth_upload_of_8" (default 0): of every 8 extraction calls
+ * of the context, that many upload a pinned depth map whole although host_zero_copy is on (in-place reads are bound by the
+ * PCIe read rate, whole uploads by the PCIe bandwidth; a mix uses both); "depth_upload_phase": where in that cycle of 8
+ * the context starts, so that several contexts take turns.
  * "knn_umma" (default 1): the Hamming kNN of Matcher::match on tcgen05: 1 = k_knn2_umma (two CTAs per SM, every warp does
  * every job), 2 = the warp-specialised persistent variant k_knn2_umma_ws (query tile in tensor memory; measured 10 % slower, see
  * DESIGN.md), 0 = the mma.sync kernel (k_knn2_hamming); 0 and 2 are kept for A/B measurements — all three are held to the

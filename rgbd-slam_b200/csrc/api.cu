@@ -478,6 +478,16 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
 {
     if (!c || !name)
         return RGBDFE_E_ARG;
+    if (!strcmp(name, "depth_upload_of_8")) {
+        if (value < 0 || value > 8)
+            return RGBDFE_E_ARG;
+        c->depth_upload_of_8 = value;
+        return RGBDFE_OK;
+    }
+    if (!strcmp(name, "depth_upload_phase")) {
+        c->extract_calls = (unsigned)value;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "host_zero_copy")) {
         c->host_zero_copy = value != 0;
         return RGBDFE_OK;
@@ -502,6 +512,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
     }
     if (!strcmp(name, "knn_umma")) {
         c->knn_umma = value < 0 ? 0 : (value > 2 ? 2 : value);
+        return RGBDFE_OK;
+    }
+    if (!strcmp(name, "ransac_small_ctas")) {
+        c->ransac_small_ctas = value != 0;
         return RGBDFE_OK;
     }
     if (!strcmp(name, "ransac_first_chunk")) {
@@ -791,7 +805,10 @@ int run_extract(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count, const uin
     if ((rc = ensure_img_slots(c, channels)) != RGBDFE_OK)
         return rc;
     const bool gray_in_place = in_place_pointers((const void* const*)gray, count, false, gp.p);
-    const bool depth_in_place = dany && in_place_pointers(dany, count, c->host_zero_copy, dp.p);
+    // "depth_upload_of_8": of every 8 calls, that many upload a pinned depth map whole (copy engine) and the others read it
+    // in place (PCIe sector reads): the two transports have different limits and a mix uses both
+    const bool zero_copy_now = c->host_zero_copy && (int)(c->extract_calls++ & 7u) >= c->depth_upload_of_8;
+    const bool depth_in_place = dany && in_place_pointers(dany, count, zero_copy_now, dp.p);
     int gstride = stride, dstride = depth_stride;
     for (int i = 0; i < count; i++)
         fb.f[i] = *frames[i];
@@ -1545,7 +1562,7 @@ int rgbdfe_track_sequence(rgbdfe_ctx* c, rgbdfe_frame* const* frames, int count,
     const bool graphable = c->chain_graphs && np >= 4 && !c->profiling && !c->dbg_on;
     ChainGraphKey key;
     memset(&key, 0, sizeof(key)); // compared bytewise: padding must be defined
-    key = ChainGraphKey { np, first_result_slot, splits, discard_outliers, iterations, (int)min_inlier_th, (int)sample_size, update_f2, c->ransac_first_chunk,
+    key = ChainGraphKey { np, first_result_slot, splits, discard_outliers, iterations, (int)min_inlier_th, (int)sample_size, update_f2, c->ransac_first_chunk + 1000 * c->ransac_small_ctas,
         ratio, max_mahal, (void*)c->d_pairs };
     ChainGraph* cg = nullptr;
     if (graphable) {

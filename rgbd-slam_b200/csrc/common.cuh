@@ -207,6 +207,8 @@ struct rgbdfe_ctx {
     cudaEvent_t order_evt = nullptr; // rgbdfe_stream_wait
     cudaEvent_t bulk_evt = nullptr;  // stream <-> bulk_stream ordering
     int img_channels = 1;            // channels the image upload slots are sized for (3 after the first BGR batch)
+    int depth_upload_of_8 = 0;       // option: of every 8 extraction calls this many upload a pinned depth map although host_zero_copy is on
+    unsigned extract_calls = 0;
     bool host_zero_copy = true;      // a pinned host depth map is read in place by K6 (keypoint sectors only) instead of being uploaded
     std::string err;
     long long launches = 0;
@@ -281,6 +283,7 @@ struct rgbdfe_ctx {
     RngState* d_pair_rng = nullptr; // [pairs] per-pair streams (batched)
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
+    int ransac_small_ctas = 0;      // option: tracking chains use the register-capped 128 / 256-thread hypothesis CTAs of the verification path
     int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
     // K2 state (orb_image.cu): host copy of the kernel's parameter block (tensor maps of the pyramid levels) and the cell table
     void* fast_grid = nullptr; void* d_fast_cells = nullptr; void* d_fast_maps = nullptr; bool fast_ready = false;

@@ -1058,7 +1058,12 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
         int rc;
         // Tracking chains keep 512-thread CTAs without a register cap: capped 128- / 256-thread CTAs (128 registers,
         // ~180 B of spills) measured 74-77 k frames/s against 78-79 k on the headline workload.
-        if (few || cap > 2304) {
+        if (few && c->ransac_small_ctas && cap <= 2304) {
+            if (cap <= 1152)
+                rc = launch_hyp<128, 9, 4>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
+            else
+                rc = launch_hyp<256, 9, 2>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
+        } else if (few || cap > 2304) {
             if (cap <= 1536)
                 rc = launch_hyp<512, 3>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
             else if (cap <= 2560)

@@ -3,6 +3,7 @@
 Bar (north_star): keypoints, descriptors, match indices and RANSAC inlier sets bit-exact;
 poses within 1e-5 (rotation entries and translation, FP32).
 """
+import ctypes as C
 import os
 
 import numpy as np
@@ -287,11 +288,17 @@ def test_ransac_se3_hard_cases(ctx, oracle, seq_vga):
         mm["trainIdx"][bad] = rs.integers(0, len(p2), bad.sum())
         for iters, min_inl in ((200, 10), (500, 30)):
             rng, latch = oracle.Rng(seed), oracle.Latch()
-            ctx.rng_seed(seed)
-            ctx.depth_cov_set(0, 0.0)
             r_o = oracle.ransac_se3(p1, p2, mm, rng, latch, iters, min_inl, 3.0, 4)
-            r_g = ctx.ransac_se3(p1, p2, mm, iters, min_inl, 3.0, 4)
-            _check_se3(r_o, r_g)
+            # the tuning knobs never change results: speculative first chunk 32 / 4 / 1, 512-thread or register-capped small CTAs
+            for small, chunk in ((0, 32), (1, 32), (1, 1), (0, 4)):
+                ctx.set_option("ransac_small_ctas", small)
+                ctx.set_option("ransac_first_chunk", chunk)
+                ctx.rng_seed(seed)
+                ctx.depth_cov_set(0, 0.0)
+                r_g = ctx.ransac_se3(p1, p2, mm, iters, min_inl, 3.0, 4)
+                _check_se3(r_o, r_g)
+    ctx.set_option("ransac_small_ctas", 0)
+    ctx.set_option("ransac_first_chunk", 32)
     # fewer matches than the inlier threshold -> false, identity, stream untouched
     ctx.rng_seed(5)
     before = ctx.rng_get_state()
@@ -489,6 +496,54 @@ def test_tracking_pipeline_device_resident(oracle, seq_vga, chain):
         ctx.close()
 
 
+def test_pinned_host_depth_transports_are_identical(oracle):
+    """A raw 16-bit depth map in pinned host memory is either read in place over PCIe (k_unproject_host, option host_zero_copy,
+    the default), uploaded whole (host_zero_copy 0), or a mix of both by call (depth_upload_of_8); pageable memory is always
+    uploaded.  All must give the frames the device-resident input gives -- keypoints, descriptors and mvKeys3Dc bit for bit --
+    and mvKeys3Dc must equal the oracle's back-projection."""
+    import rgbdfe
+    import synth
+    import torch
+
+    cam, frames = synth.sequence("tum_fr1", n=4, seed=31)
+    inv = float(np.float32(1.0) / np.float32(5000.0))
+    gray = [np.ascontiguousarray(f[0]) for f in frames]
+    d16 = [np.clip(np.rint(f[1] * 5000.0), 0, 65535).astype(np.uint16) for f in frames]
+    pin_g = [torch.from_numpy(g).pin_memory() for g in gray]
+    pin_d = [torch.from_numpy(d.view(np.int16)).pin_memory() for d in d16]  # same bits as uint16
+    dev_g, dev_d = [t.cuda() for t in pin_g], [t.cuda() for t in pin_d]
+    ctx = rgbdfe.Context(0, 640, 480, 1000, 4)
+    try:
+        fr = [rgbdfe.Frame(ctx) for _ in frames]
+
+        def run(gp, dp):
+            n = len(fr)
+            fa = (C.c_void_p * n)(*[f.h for f in fr])
+            ctx._chk(rgbdfe.lib().rgbdfe_frames_extract_raw(ctx.h, fa, n, (C.c_void_p * n)(*gp), 640, 480, 640, (C.c_void_p * n)(*dp), 640,
+                                                            C.c_float(inv), C.c_float(cam["fx"]), C.c_float(cam["fy"]), C.c_float(cam["cx"]), C.c_float(cam["cy"])))
+            out = [f.download() for f in fr]
+            return b"".join(a.tobytes() for o in out for a in o[:3]), out
+
+        want, out = run([t.data_ptr() for t in dev_g], [t.data_ptr() for t in dev_d])
+        orb = oracle.Orb(1000)
+        for i, (g, _) in enumerate(frames):
+            k, de = orb.extract(g)
+            depth = d16[i].astype(np.float32) * np.float32(inv)
+            assert (out[i][0] == k).all() and (out[i][1] == de).all()
+            assert (out[i][2] == _unproject(cam, k, depth)).all()
+        host = ([t.data_ptr() for t in pin_g], [t.data_ptr() for t in pin_d])
+        for zero_copy, of8 in ((1, 0), (0, 0), (1, 4), (1, 4), (1, 8)):
+            ctx.set_option("host_zero_copy", zero_copy)
+            ctx.set_option("depth_upload_of_8", of8)
+            ctx.set_option("depth_upload_phase", 3)  # with of8 = 4: this call uploads, the next reads in place
+            for _ in range(2):
+                assert run(*host)[0] == want, (zero_copy, of8)
+        ctx.set_option("depth_upload_of_8", 0)
+        assert run([g.ctypes.data for g in gray], [d.ctypes.data for d in d16])[0] == want  # pageable host memory
+    finally:
+        ctx.close()
+
+
 def test_chain_replayed_as_a_graph_is_identical(oracle):
     """rgbdfe_track_sequence captures a chain's launch sequence on the second call with the same shape and replays it as one CUDA
     graph afterwards: call 1 (plain launches), call 2 (capture + launch) and call 3 (replay) must give the same bytes -- results,
@@ -501,9 +556,13 @@ def test_chain_replayed_as_a_graph_is_identical(oracle):
     try:
         fr = [rgbdfe.Frame(ctx) for _ in frames]
         runs = []
-        for rep in range(4):
+        for rep in range(7):
             if rep == 3:
                 ctx.set_option("chain_graphs", 0)  # and once more without graphs
+            if rep == 4:  # three more with the register-capped hypothesis CTAs and no speculation (the bench's setting): plain, capture, replay
+                ctx.set_option("chain_graphs", 1)
+                ctx.set_option("ransac_small_ctas", 1)
+                ctx.set_option("ransac_first_chunk", 1)
             ctx.frames_extract(fr, [f[0] for f in frames], [f[1] for f in frames], cam)  # resets the outlier flags
             ctx.rng_seed(42)
             ctx.depth_cov_set(0, 0.0)
@@ -511,7 +570,7 @@ def test_chain_replayed_as_a_graph_is_identical(oracle):
             res, inl = ctx.track_results_inliers(0, len(frames) - 1)
             flags = b"".join(f.download()[3].tobytes() for f in fr)
             runs.append((res.tobytes(), b"".join(x.tobytes() for x in inl), flags, ctx.rng_get_state().tobytes()))
-        assert runs[0] == runs[1] == runs[2] == runs[3]
+        assert all(r == runs[0] for r in runs[1:])
         res = np.frombuffer(runs[0][0], rgbdfe.SE3_DTYPE)
         assert res["ok"].all() and res["n_inliers"].min() > 100
         orb = oracle.Orb(1000)
