@@ -55,13 +55,13 @@ ALG_BYTES = {
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch over a 64-frame batch, from the ncu --set full
 # captures summarised in profiles/r2_ncu_full_brief.txt, and the unit that actually limits each kernel there.
 NCU_TRAFFIC_64 = {
-    "k_fast_cells": 65.02e6 + 3.82e6, "k_gauss7": 72.85e6 + 32.05e6, "k_orient_describe": 139.07e6 + 9.30e6,
+    "k_fast_cells": 65.00e6 + 3.70e6, "k_gauss7": 72.88e6 + 32.24e6, "k_orient_describe": 139.05e6 + 9.58e6,
     "k_knn2_umma": 4.21e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
 # warp instructions of one 64-frame launch (smsp__inst_executed.sum) -> thread instructions per pixel of the levels it covers
-NCU_WARP_INST_64 = {"k_fast_cells": 218.26e6, "k_gauss7": 86.54e6, "k_orient_describe": 115.37e6, "k_quadtree": 31.92e6, "k_knn2_umma": 50.57e6}
+NCU_WARP_INST_64 = {"k_fast_cells": 174.40e6, "k_gauss7": 86.54e6, "k_orient_describe": 115.37e6, "k_quadtree": 31.92e6, "k_knn2_umma": 50.57e6}
 NCU_LIMITER = {
-    "k_fast_cells": "instruction-bound: issue slots 76 % busy, integer ALU pipe 61 % (16-bit-lane min/max; every integer ALU instruction costs a warp two issue clocks), tiles staged by TMA; DRAM traffic = 1.1x algorithmic, 4 % of peak",
+    "k_fast_cells": "instruction-bound: issue slots 83 % busy, integer ALU pipe 74 % (16-bit-lane min/max; every integer ALU instruction costs a warp two issue clocks), tiles staged by TMA; DRAM traffic = 1.1x algorithmic, 5 % of peak",
     "k_gauss7": "instruction-bound: issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 60 %; DRAM 17 % of peak",
     "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 73 %; DRAM 16 % of peak: the gather set of a 64-frame batch (141 MB) exceeds the 126 MB L2",
     "k_knn2_umma": "tcgen05.mma kind::i8 (UTCIMMA), tensor pipe 32 % busy; the warps that expand the operands and drain TMEM into the top-2 keep the integer ALU pipe 45 % busy and wait on each other at CTA barriers (2 CTAs x 8 warps per SM: TMEM-bound occupancy); DRAM < 1 % of peak",
@@ -1017,10 +1017,12 @@ def main():
     single = None
     if S > 1:
         seqs[0].ctx_t.set_option("ransac_first_chunk", 32)
+        seqs[0].ctx_t.set_option("ransac_small_ctas", 0)  # one camera alone: 512-thread hypothesis CTAs, 32 speculative iterations
         run_steps(seqs[:1], True, 1)
         n1, ms1, _ = timed(seqs[:1], True, max(2, args.steps // 2))
         single = n1 / (ms1 * 1e-3)
         seqs[0].ctx_t.set_option("ransac_first_chunk", args.first_chunk)
+        seqs[0].ctx_t.set_option("ransac_small_ctas", args.small_ctas)
     ctx_x, ctx_t = seqs[0].ctx_x, seqs[0].ctx_t
     state = {"ok": sum(q.ok for q in seqs), "n": sum(q.n for q in seqs), "inliers": [x for q in seqs for x in q.inliers],
              "iters": [x for q in seqs for x in q.iters]}
