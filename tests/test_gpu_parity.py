@@ -56,6 +56,34 @@ def test_orb_stages_bit_exact(ctx, oracle, seq_vga, nfeat):
         assert (desc_o == desc_g).all(), "descriptors"
 
 
+@pytest.mark.parametrize("size", [(611, 397), (322, 251), (1000, 80)])
+def test_orb_odd_image_sizes(oracle, seq_vga, size):
+    """Widths and heights that are not multiples of 4 or 16 (row pitches with padding, level-0 spans that straddle the ring,
+    row groups that end inside a group of four): pyramid bytes with ring, keypoints and descriptors against the oracle."""
+    import rgbdfe
+
+    w, h = size
+    _, frames = seq_vga
+    big = np.concatenate([np.concatenate([frames[0][0], frames[1][0]], 1), np.concatenate([frames[2][0], frames[3][0]], 1)], 0)
+    gray = np.ascontiguousarray(big[37 : 37 + h, 91 : 91 + w])
+    ctx = rgbdfe.Context(0, w, h, 500, 1)
+    try:
+        nlev = 8 if h >= 200 else 2  # every level must stay above 40 px
+        ctx.orb_configure(500, 1.2, nlev, 20, 7)
+        orb = oracle.Orb(500, 1.2, nlev)
+        kps_o, desc_o = orb.extract(gray)
+        kps_g, desc_g = ctx.orb_extract(gray)
+        for l in range(nlev):
+            assert (ctx.pyramid_level(l) == orb.level_padded(l)).all(), f"pyramid level {l}"
+        assert len(kps_o) == len(kps_g) and len(kps_o) > 50
+        for f in ("x", "y", "response", "octave"):
+            assert (kps_o[f] == kps_g[f]).all(), f
+        assert (kps_o["angle"].view(np.uint32) == kps_g["angle"].view(np.uint32)).all()
+        assert (desc_o == desc_g).all()
+    finally:
+        ctx.close()
+
+
 def test_orb_blur_on_side_stream_same_result(ctx, oracle, seq_vga):
     """Option overlap_blur: K3 beside K4 on a side stream; several back-to-back extractions, same keypoints and descriptors."""
     cam, frames = seq_vga
