@@ -454,6 +454,9 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     lo, hi = rgbdfe.shard_range(n_kf, rank, world)
     v = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf, kd[lo:hi], kp[lo:hi], ident, max_feats=N_FEAT, depth_cov=cov)
     queries = [(np.ascontiguousarray(np.roll(qd, 13 * i, axis=0)), np.ascontiguousarray(np.roll(qp, 13 * i, axis=0))) for i in range(8)]
+    vcap = os.environ.get("BENCH_VERIFY_CAP")  # diagnostic: hypothesis CTA shape of the many-pairs path (option ransac_verify_cap)
+    if vcap is not None:
+        v.ctx.set_option("ransac_verify_cap", int(vcap))
     # `value`: the query frames are resident in HBM (device pointers are read in place); the host-memory form is timed beside it
     q_dev = [(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()) for a, b in queries]
     q_ptr = [(a.data_ptr(), b.data_ptr()) for a, b in q_dev]
@@ -462,6 +465,8 @@ def verify_leg(args, rgbdfe, torch, dist, rank, local_rank, world):
     ms_one, launches = timed_queries(v, q_ptr, 1, calls)
     # two contexts of this GPU take alternate queries (each its own stream, workspace, resident keyframe block and communicator)
     vb = loopverify.CudaShardedVerifier(local_rank, rank, world, n_kf, kd[lo:hi], kp[lo:hi], bcast_id() if world > 1 else None, max_feats=N_FEAT, depth_cov=cov)
+    if vcap is not None:
+        vb.ctx.set_option("ransac_verify_cap", int(vcap))
     ms, _ = timed_queries([v, vb], q_ptr, 1, calls, depth=4)
     vb.close()
     out["host_queries_pairs_per_s"] = calls * n_kf / (ms_host * 1e-3)

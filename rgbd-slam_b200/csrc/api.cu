@@ -514,6 +514,10 @@ int rgbdfe_set_option(rgbdfe_ctx* c, const char* name, int value)
         c->knn_umma = value < 0 ? 0 : (value > 2 ? 2 : value);
         return RGBDFE_OK;
     }
+    if (!strcmp(name, "ransac_verify_cap")) {
+        c->ransac_verify_cap = value;
+        return RGBDFE_OK;
+    }
     if (!strcmp(name, "ransac_small_ctas")) {
         c->ransac_small_ctas = value != 0;
         return RGBDFE_OK;

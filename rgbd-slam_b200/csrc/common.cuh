@@ -283,6 +283,7 @@ struct rgbdfe_ctx {
     RngState* d_pair_rng = nullptr; // [pairs] per-pair streams (batched)
     DepthLatch* d_latch = nullptr;
     double rcx = 0, rcy = 0;
+    int ransac_verify_cap = 1;      // many-pairs path: 1 = register-capped small hypothesis CTAs, 0 = 512-thread CTAs, -n = 512-thread CTAs below n pairs per launch
     int ransac_small_ctas = 0;      // option: tracking chains use the register-capped 128 / 256-thread hypothesis CTAs of the verification path
     int ransac_first_chunk = 32;    // hypotheses of the first launch of a latency-mode RANSAC (rgbdfe_set_option)
     // K2 state (orb_image.cu): host copy of the kernel's parameter block (tensor maps of the pyramid levels) and the cell table

@@ -1070,6 +1070,8 @@ int launch_ransac_se3(rgbdfe_ctx* c, const MatchPair* d_pairs, int slot0, int np
                 rc = launch_hyp<512, 5>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
             else
                 rc = launch_hyp<512, 8>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
+        } else if (c->ransac_verify_cap == 0 || (c->ransac_verify_cap < 0 && npairs < -c->ransac_verify_cap)) { // (A/B knob)
+            rc = cap <= 1152 ? launch_hyp<128, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas) : launch_hyp<256, 9>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         } else if (cap <= 1152) // verification batches: thousands of CTAs, occupancy matters more than the spills
             rc = launch_hyp<128, 9, 4>(c, R, npairs, hyp_smem, b, e, next_end, max_ctas);
         else
