@@ -14,6 +14,12 @@ additionally time the sharded loop-pair verification, reported under "verify".
 
 --impl reference: the CPU oracle port (oracle/, the reference's algorithm restated; the reference
 itself cannot be compiled here) on all host cores, same config / metric / unit.
+
+The host loop is a rolling pipeline over 32 independent sequences (see Seq / run_group): results of a sequence's
+previous batch are read just before its next batch is enqueued; the timed region ends with one drain.
+Diagnostics (never set by the driver): --mode, --profile-host, --upload-mix, --small-ctas, --first-chunk, and the
+environment knobs BENCH_HOSTPROF (host ms per sequence-step), BENCH_E2E_NO_DL / BENCH_E2E_DEPTH_DEV /
+BENCH_E2E_GRAY_DEV (take one transport out of the e2e run), BENCH_VERIFY_CAP (hypothesis CTA shape of the verify leg).
 """
 import argparse
 import ctypes as C
