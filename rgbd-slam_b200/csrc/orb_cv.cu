@@ -80,8 +80,11 @@ struct CvOrbWorkspace {
     int* d_final = nullptr;              // [slot][out_total] indices into d_out in output order
     int* d_final_count = nullptr;        // [slot]
     HKey* d_gscratch = nullptr;          // [slot][out_total] k_cv_gather's rare retainBest path
-    int* d_tab_ofs = nullptr;
-    unsigned short* d_tab_c1 = nullptr;
+    // resize tables over padded coordinates (see k_cv_pyr_level): columns (source offset, c0 | c1 << 16), row groups
+    int2* d_xpad = nullptr;
+    PyrGroup* d_group = nullptr;
+    int xpad_off[RGBDFE_MAX_LEVELS] = {}, group_off[RGBDFE_MAX_LEVELS] = {};
+    int pyr_nsrc = 0;
     int tab_cap = 0;
     int slots = 0;
     signed char* d_pattern = nullptr;
@@ -123,38 +126,62 @@ __global__ void __launch_bounds__(256) k_cv_pyr_base(const __grid_constant__ CvC
 
 // Level l >= 1: resize(prev, INTER_LINEAR_EXACT) + copyMakeBorder(REFLECT_101 | ISOLATED).  resize_bitExact: horizontal
 // blend in ufixedpoint16 (8 fractional bits), vertical blend of two such rows in ufixedpoint32, (v + 2^15) >> 16.
-// Tables hold, per destination index, the source offset and the second coefficient (first = 256 - second); indices
-// left of min / right of max are encoded as coefficient pairs (256, 0) / (0, 256) on a valid source pair.
-__global__ void __launch_bounds__(256) k_cv_pyr_level(const __grid_constant__ CvCfg C, int level, uint8_t* __restrict__ pyr, size_t pyr_slot,
-    const int* __restrict__ tab_ofs, const unsigned short* __restrict__ tab_c1)
+// Same organisation as k_pyramid_resize_direct (orb_image.cu): tables over PADDED coordinates built on the host (ring
+// reflection and pitch padding resolved there; indices left of min / right of max are coefficient pairs (256, 0) /
+// (0, 256) on a valid source pair), one thread = 4 padded pixels x PYR_ROWS rows, every distinct source row of the row
+// group blended horizontally once, the 16-bit results parked in the thread's own shared-memory column.
+struct CvPyr {
+    int ph, pstride;      // padded rows and row pitch of this level
+    unsigned dst_off;     // byte offset of padded (row 0, column 0) in a frame slot
+    unsigned src_off;     // byte offset of level pixel (0, 0) of level l - 1
+    int xpad_off, group_off;
+};
+template <int NSRC>
+__global__ void __launch_bounds__(256) k_cv_pyr_level(const __grid_constant__ CvPyr V, uint8_t* __restrict__ pyr, size_t pyr_slot,
+    const int2* __restrict__ xpad, const PyrGroup* __restrict__ groups)
 {
-    const CvLevel& L = C.lv[level];
-    const CvLevel& P = C.lv[level - 1];
-    const int slot = blockIdx.z;
-    const int wq = blockIdx.x * blockDim.x + threadIdx.x;
-    const int py = blockIdx.y * blockDim.y + threadIdx.y - CV_RING;
-    if (4 * wq >= L.pstride || py >= L.h + CV_RING)
+    __shared__ uint2 s_t[NSRC][256];
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    const int px0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int g = blockIdx.y * blockDim.y + threadIdx.y;
+    const int py0 = g * PYR_ROWS;
+    if (px0 >= V.pstride || py0 >= V.ph)
         return;
-    uint8_t* base = pyr + slot * pyr_slot;
-    const int ry = cv_reflect(py, L.h);
-    const int oy = tab_ofs[L.taby_off + ry];
-    const unsigned cy1 = tab_c1[L.taby_off + ry], cy0 = 256u - cy1;
-    const uint8_t* s0 = base + P.pyr_off + (size_t)oy * P.pstride;
-    const uint8_t* s1 = s0 + P.pstride;
-    unsigned v = 0;
+    uint8_t* slot_base = pyr + blockIdx.z * pyr_slot;
+    const uint8_t* src = slot_base + V.src_off;
+    const int4* xp = reinterpret_cast<const int4*>(xpad + V.xpad_off + px0);
+    const int4 e0 = xp[0], e1 = xp[1];
+    const int4* gp = reinterpret_cast<const int4*>(groups + V.group_off + g);
+    const int4 o0 = gp[0], o1 = gp[1], bt = gp[2], m = gp[3];
+    const int off[8] = { o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w };
+    const int sx[4] = { e0.x, e0.z, e1.x, e1.z };
+    const unsigned cx[4] = { (unsigned)e0.y, (unsigned)e0.w, (unsigned)e1.y, (unsigned)e1.w };
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        const int px = 4 * wq + j - CV_RING;
-        if (px < L.w + CV_RING) {
-            const int rx = cv_reflect(px, L.w);
-            const int ox = tab_ofs[L.tabx_off + rx];
-            const unsigned cx1 = tab_c1[L.tabx_off + rx], cx0 = 256u - cx1;
-            const unsigned h0 = cx0 * s0[ox] + cx1 * s0[ox + 1];
-            const unsigned h1 = cx0 * s1[ox] + cx1 * s1[ox + 1];
-            v |= ((h0 * cy0 + h1 * cy1 + 32768u) >> 16) << (8 * j);
+    for (int s = 0; s < NSRC; s++) {
+        const uint8_t* row = src + off[s];
+        unsigned t[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint8_t* q = row + sx[k];
+            t[k] = q[0] * (cx[k] & 0xffffu) + q[1] * (cx[k] >> 16); // <= 255 * 256
+        }
+        s_t[s][tid] = make_uint2(t[1] * 65536u + t[0], t[3] * 65536u + t[2]);
+    }
+    const unsigned beta[4] = { (unsigned)bt.x, (unsigned)bt.y, (unsigned)bt.z, (unsigned)bt.w };
+    uint8_t* dst = slot_base + V.dst_off + (size_t)py0 * V.pstride + px0;
+#pragma unroll
+    for (int j = 0; j < PYR_ROWS; j++) {
+        if (py0 + j < V.ph) {
+            const unsigned sel = (unsigned)m.x >> (8 * j);
+            const uint2 a = s_t[sel & 15u][tid], b = s_t[(sel >> 4) & 15u][tid];
+            const unsigned c0 = beta[j] & 0xffffu, c1 = beta[j] >> 16;
+            const unsigned v0 = ((a.x & 0xffffu) * c0 + (b.x & 0xffffu) * c1 + 32768u) >> 16;
+            const unsigned v1 = ((a.x >> 16) * c0 + (b.x >> 16) * c1 + 32768u) >> 16;
+            const unsigned v2 = ((a.y & 0xffffu) * c0 + (b.y & 0xffffu) * c1 + 32768u) >> 16;
+            const unsigned v3 = ((a.y >> 16) * c0 + (b.y >> 16) * c1 + 32768u) >> 16;
+            *reinterpret_cast<unsigned*>(dst + (size_t)j * V.pstride) = ((v3 * 256u + v2) * 256u + v1) * 256u + v0; // bytes past the padded width are pitch padding
         }
     }
-    *reinterpret_cast<unsigned*>(base + L.pyr_off + (ptrdiff_t)py * L.pstride - CV_RING + 4 * wq) = v;
 }
 
 __device__ __forceinline__ int cv_find_level(const CvCfg& C, int tile)
@@ -801,11 +828,11 @@ void free_buffers(CvOrbWorkspace* W)
 {
     cudaFree(W->d_pyr), cudaFree(W->d_blur), cudaFree(W->d_score), cudaFree(W->d_cand), cudaFree(W->d_lr), cudaFree(W->d_hkey);
     cudaFree(W->d_hcount), cudaFree(W->d_out), cudaFree(W->d_out_count), cudaFree(W->d_final), cudaFree(W->d_final_count);
-    cudaFree(W->d_tab_ofs), cudaFree(W->d_tab_c1), cudaFree(W->d_gscratch), cudaFree(W->d_maps);
+    cudaFree(W->d_xpad), cudaFree(W->d_group), cudaFree(W->d_gscratch), cudaFree(W->d_maps);
     W->d_gscratch = nullptr, W->d_maps = nullptr;
     W->d_pyr = W->d_blur = W->d_score = nullptr;
     W->d_cand = nullptr, W->d_lr = nullptr, W->d_hkey = nullptr, W->d_hcount = nullptr, W->d_out = nullptr, W->d_out_count = nullptr;
-    W->d_final = nullptr, W->d_final_count = nullptr, W->d_tab_ofs = nullptr, W->d_tab_c1 = nullptr;
+    W->d_final = nullptr, W->d_final_count = nullptr, W->d_xpad = nullptr, W->d_group = nullptr;
 }
 int cv_round_f(float v) { return (int)lrintf(v); }
 // interpolationLinear<uchar>::getCoeffs (resize.cpp), arithmetic in IEEE double (= softdouble)
@@ -966,16 +993,62 @@ static int cvorb_prepare(rgbdfe_ctx* c, int w, int h)
     CUDA_TRY(c, dmalloc(&W->d_final, (size_t)out * S * sizeof(int)));
     CUDA_TRY(c, dmalloc(&W->d_final_count, (size_t)S * sizeof(int)));
     CUDA_TRY(c, dmalloc(&W->d_gscratch, (size_t)out * S * sizeof(HKey)));
-    CUDA_TRY(c, dmalloc(&W->d_tab_ofs, (size_t)tab * sizeof(int)));
-    CUDA_TRY(c, dmalloc(&W->d_tab_c1, (size_t)tab * sizeof(unsigned short)));
     std::vector<int> ofs(tab, 0);
     std::vector<unsigned short> c1(tab, 0);
+    std::vector<int2> xpad;
+    std::vector<PyrGroup> groups;
+    W->pyr_nsrc = 0;
     for (int l = 1; l < C.nlevels; l++) {
-        exact_table(C.lv[l - 1].w, C.lv[l].w, &ofs[C.lv[l].tabx_off], &c1[C.lv[l].tabx_off]);
-        exact_table(C.lv[l - 1].h, C.lv[l].h, &ofs[C.lv[l].taby_off], &c1[C.lv[l].taby_off]);
+        const CvLevel &L = C.lv[l], &P = C.lv[l - 1];
+        exact_table(P.w, L.w, &ofs[L.tabx_off], &c1[L.tabx_off]);
+        exact_table(P.h, L.h, &ofs[L.taby_off], &c1[L.taby_off]);
+        // padded forms: a ring pixel is the level's own pixel at the REFLECT_101 coordinate, columns of the row pitch
+        // beyond the padded width repeat the last one
+        const int pw = L.w + 2 * CV_RING, ph = L.h + 2 * CV_RING, ng = (ph + PYR_ROWS - 1) / PYR_ROWS;
+        auto reflect = [](int p, int len) { p = p < 0 ? -p : p; return p >= len ? 2 * (len - 1) - p : p; };
+        W->xpad_off[l] = (int)xpad.size(), W->group_off[l] = (int)groups.size();
+        for (int px = 0; px < L.pstride; px++) {
+            const int x = reflect(std::min(px, pw - 1) - CV_RING, L.w);
+            const unsigned k1 = c1[L.tabx_off + x];
+            xpad.push_back(make_int2(ofs[L.tabx_off + x], (int)((256u - k1) | k1 << 16)));
+        }
+        for (int gi = 0; gi < ng; gi++) {
+            PyrGroup G;
+            memset(&G, 0, sizeof(G));
+            for (int j = 0; j < PYR_ROWS; j++) {
+                const int y = reflect(std::min(gi * PYR_ROWS + j, ph - 1) - CV_RING, L.h);
+                const int oy = ofs[L.taby_off + y];
+                unsigned sel = 0;
+                for (int k = 0; k < 2; k++) {
+                    const int off = (oy + k) * P.pstride;
+                    int i = 0;
+                    while (i < G.nsrc && G.off[i] != off)
+                        i++;
+                    if (i == G.nsrc) {
+                        if (G.nsrc == PYR_SRC_MAX) {
+                            c->set_error("cvorb: scale factor too large for the pyramid kernel (more than 8 source rows per 4 output rows)");
+                            return RGBDFE_E_ARG;
+                        }
+                        G.off[G.nsrc++] = off;
+                    }
+                    sel |= (unsigned)i << (4 * k);
+                }
+                G.sel |= sel << (8 * j);
+                const unsigned k1 = c1[L.taby_off + y];
+                G.beta[j] = (256u - k1) | k1 << 16;
+            }
+            W->pyr_nsrc = std::max(W->pyr_nsrc, G.nsrc);
+            for (int i = G.nsrc; i < PYR_SRC_MAX; i++)
+                G.off[i] = G.off[G.nsrc - 1];
+            groups.push_back(G);
+        }
     }
-    CUDA_TRY(c, cudaMemcpy(W->d_tab_ofs, ofs.data(), (size_t)tab * sizeof(int), cudaMemcpyHostToDevice));
-    CUDA_TRY(c, cudaMemcpy(W->d_tab_c1, c1.data(), (size_t)tab * sizeof(unsigned short), cudaMemcpyHostToDevice));
+    CUDA_TRY(c, dmalloc(&W->d_xpad, std::max<size_t>(xpad.size(), 1) * sizeof(int2)));
+    CUDA_TRY(c, dmalloc(&W->d_group, std::max<size_t>(groups.size(), 1) * sizeof(PyrGroup)));
+    if (!xpad.empty()) {
+        CUDA_TRY(c, cudaMemcpy(W->d_xpad, xpad.data(), xpad.size() * sizeof(int2), cudaMemcpyHostToDevice));
+        CUDA_TRY(c, cudaMemcpy(W->d_group, groups.data(), groups.size() * sizeof(PyrGroup), cudaMemcpyHostToDevice));
+    }
     {
         EncodeTiledFn enc = encode_tiled_fn();
         if (!enc) {
@@ -1022,11 +1095,21 @@ int launch_cvorb(rgbdfe_ctx* c, int count, int w, int h, const ImgPtrs& gray, in
         ProfScope prof(c, KID_PYRAMID);
         for (int l = 0; l < C.nlevels; l++) {
             const CvLevel& L = C.lv[l];
-            dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (L.h + 2 * CV_RING + 3) / 4, count);
-            if (l == 0)
+            const int ph = L.h + 2 * CV_RING;
+            if (l == 0) {
+                dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (ph + 3) / 4, count);
                 k_cv_pyr_base<<<grd, blk, 0, c->stream>>>(C, gray, gray_stride, W->d_pyr, W->pyr_slot);
-            else
-                k_cv_pyr_level<<<grd, blk, 0, c->stream>>>(C, l, W->d_pyr, W->pyr_slot, W->d_tab_ofs, W->d_tab_c1);
+            } else {
+                CvPyr V;
+                V.ph = ph, V.pstride = L.pstride;
+                V.dst_off = L.pyr_off - (unsigned)(CV_RING * L.pstride + CV_RING), V.src_off = C.lv[l - 1].pyr_off;
+                V.xpad_off = W->xpad_off[l], V.group_off = W->group_off[l];
+                dim3 blk(64, 4), grd((L.pstride / 4 + 63) / 64, (ph + 4 * PYR_ROWS - 1) / (4 * PYR_ROWS), count);
+                if (W->pyr_nsrc <= 6)
+                    k_cv_pyr_level<6><<<grd, blk, 0, c->stream>>>(V, W->d_pyr, W->pyr_slot, W->d_xpad, W->d_group);
+                else
+                    k_cv_pyr_level<8><<<grd, blk, 0, c->stream>>>(V, W->d_pyr, W->pyr_slot, W->d_xpad, W->d_group);
+            }
             c->launches++;
         }
     }
