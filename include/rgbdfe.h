@@ -91,8 +91,10 @@ int rgbdfe_sync(rgbdfe_ctx* ctx);
  * first hypothesis launch of a single pair evaluates speculatively; the rest follow in a second launch only
  * if the reference's loop has not ended by then.  Small values suit many concurrent sequences on one GPU.
  * "ransac_small_ctas" (default 0): the hypothesis CTAs of tracking chains are 128 / 256 threads with registers capped at 128
- * (the verification path's shape) instead of 512 threads: slower for one chain, but an SM that hosts one still has room
- * for the extraction kernels of other sequences (+4 % frames/s with 32 sequences on one GPU).
+ * (the verification path's shape) instead of 512 threads, which at 128 registers take an SM's whole register file: slower
+ * for one chain, but an SM that hosts one still has room for the extraction kernels of other sequences (+4 % frames/s
+ * with 32 sequences on one GPU).  "ransac_verify_cap" (default 1; 0 = the uncapped shapes, for A/B runs) is the same choice
+ * for the many-pairs path of rgbdfe_verify_*.
  * "host_zero_copy" (default 1): see rgbdfe_frames_extract.  "depth_upload_of_8" (default 0): of every 8 extraction calls
  * of the context, that many upload a pinned depth map whole although host_zero_copy is on (in-place reads are bound by the
  * PCIe read rate, whole uploads by the PCIe bandwidth; a mix uses both); "depth_upload_phase": where in that cycle of 8
