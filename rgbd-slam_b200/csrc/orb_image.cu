@@ -175,15 +175,25 @@ __global__ void __launch_bounds__(256) k_pyramid_resize_direct(const __grid_cons
 #define BLUR_TH 32
 #define BLUR_SROWS (BLUR_TH + 6)
 #define BLUR_SPITCH 80 // staged bytes per row: level columns tx0-3 .. tx0+76
-__global__ void __launch_bounds__(256) k_gauss7(const OrbConfig* __restrict__ cfg, const uint8_t* __restrict__ pyr, size_t pyr_slot,
+// Geometry of the blur's tile grid, passed by value (constant bank): the prologue has no dependent global loads.
+struct BlurLevel {
+    int w, h, pstride, bstride;
+    unsigned pyr_off, blur_off;
+};
+struct BlurGrid {
+    int nlevels;
+    int tile_start[RGBDFE_MAX_LEVELS + 1];
+    BlurLevel lv[RGBDFE_MAX_LEVELS];
+};
+__global__ void __launch_bounds__(256) k_gauss7(const __grid_constant__ BlurGrid G, const uint8_t* __restrict__ pyr, size_t pyr_slot,
     uint8_t* __restrict__ blur, size_t blur_slot)
 {
     // blockIdx.x enumerates tiles of all levels
     int level = 0;
-    while (level + 1 < cfg->nlevels && (int)blockIdx.x >= cfg->blur_tile_start[level + 1])
+    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.tile_start[level + 1])
         level++;
-    const LevelDesc L = cfg->lv[level];
-    const int t = blockIdx.x - cfg->blur_tile_start[level];
+    const BlurLevel L = G.lv[level];
+    const int t = blockIdx.x - G.tile_start[level];
     const int tiles_x = (L.w + BLUR_TW - 1) / BLUR_TW;
     const int ty = t / tiles_x;
     const int tx0 = (t - ty * tiles_x) * BLUR_TW, ty0 = ty * BLUR_TH;
@@ -347,10 +357,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             const int rel = s0 - s_first; // tested pixels of the row are rel + j in [0, dw)
             const bool k0 = (rA & 0x8000u) && (unsigned)rel < (unsigned)dw, k1 = (rA >> 31) && (unsigned)(rel + 1) < (unsigned)dw;
             const bool k2 = (rB & 0x8000u) && (unsigned)(rel + 2) < (unsigned)dw, k3 = (rB >> 31) && (unsigned)(rel + 3) < (unsigned)dw;
-            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
-            const unsigned b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
-            const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
-            if (b0 | b1 | b2 | b3) {
+            if (__any_sync(0xffffffffu, k0 | k1 | k2 | k3)) { // most groups of 128 pixels hold no candidate at all
+                const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+                const unsigned b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
+                const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
                 int base = 0;
                 if (lane == 0)
                     base = atomicAdd(&s_ncand, n0 + n1 + n2 + n3);
@@ -470,7 +480,16 @@ int launch_blur(rgbdfe_ctx* c, int count)
     const OrbConfig& cfg = c->cfg;
     const int total = cfg.blur_tile_start[cfg.nlevels];
     ProfScope prof(c, KID_BLUR);
-    k_gauss7<<<dim3(total, count), 256, 0, c->stream>>>(c->d_cfg, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot);
+    BlurGrid G;
+    memset(&G, 0, sizeof(G));
+    G.nlevels = cfg.nlevels;
+    for (int l = 0; l <= cfg.nlevels; l++)
+        G.tile_start[l] = cfg.blur_tile_start[l];
+    for (int l = 0; l < cfg.nlevels; l++) {
+        const LevelDesc& L = cfg.lv[l];
+        G.lv[l] = BlurLevel { L.w, L.h, L.pstride, L.bstride, L.pyr_off, L.blur_off };
+    }
+    k_gauss7<<<dim3(total, count), 256, 0, c->stream>>>(G, c->d_pyr, c->pyr_slot, c->d_blur, c->blur_slot);
     c->launches++;
     CUDA_TRY(c, cudaGetLastError());
     return RGBDFE_OK;
