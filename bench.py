@@ -65,10 +65,10 @@ NCU_TRAFFIC_64 = {
     "k_knn2_umma": 4.21e6, "k_quadtree": 8.17e6 + 0.01e6,
 }
 # warp instructions of one 64-frame launch (smsp__inst_executed.sum) -> thread instructions per pixel of the levels it covers
-NCU_WARP_INST_64 = {"k_fast_cells": 174.40e6, "k_gauss7": 86.54e6, "k_orient_describe": 115.37e6, "k_quadtree": 31.92e6, "k_knn2_umma": 50.57e6}
+NCU_WARP_INST_64 = {"k_fast_cells": 173.76e6, "k_gauss7": 84.20e6, "k_orient_describe": 115.37e6, "k_quadtree": 31.92e6, "k_knn2_umma": 50.57e6}
 NCU_LIMITER = {
     "k_fast_cells": "instruction-bound: issue slots 83 % busy, integer ALU pipe 74 % (16-bit-lane min/max; every integer ALU instruction costs a warp two issue clocks), tiles staged by TMA; DRAM traffic = 1.1x algorithmic, 5 % of peak",
-    "k_gauss7": "instruction-bound: issue slots 84 % busy (IDP4A/IDP2A filter taps), L1/shared 60 %; DRAM 17 % of peak",
+    "k_gauss7": "instruction-bound: issue slots 86 % busy (IDP4A/IDP2A filter taps), L1/shared 60 %; DRAM 18 % of peak",
     "k_orient_describe": "XU 50 % (atan2 / sin / cos), L1 74 %, issue 73 %; DRAM 16 % of peak: the gather set of a 64-frame batch (141 MB) exceeds the 126 MB L2",
     "k_knn2_umma": "tcgen05.mma kind::i8 (UTCIMMA), tensor pipe 32 % busy; the warps that expand the operands and drain TMEM into the top-2 keep the integer ALU pipe 45 % busy and wait on each other at CTA barriers (2 CTAs x 8 warps per SM: TMEM-bound occupancy); DRAM < 1 % of peak",
     "k_quadtree": "latency (shared-memory atomics and scans, one CTA per level and frame): issue 32 %",
